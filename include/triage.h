@@ -1,0 +1,183 @@
+/*
+ * triage.h — C ABI of the B200 batch triage engine (libtriage_b200.so).
+ *
+ * This is the drop-in boundary for llm-message-queue's one data-parallel path:
+ * internal/preprocessor content analysis -> priority label -> internal/priorityqueue
+ * dequeue order.  The reference has no FFI of its own (it is pure Go, CGO_ENABLED=0,
+ * deployments/Dockerfile:15-17); every entry point below cites the exported Go method
+ * it stands in for (paths relative to the reference repo).  A thin cgo shim keeps the
+ * Go signatures; plain pointers and sizes only, no torch types.
+ *
+ * All functions return 0 on success or a TRIAGE_E_* status; triage_last_error() gives a
+ * thread-local message for the last failure.  There is no CPU fallback: every compute
+ * entry point fails with TRIAGE_E_CUDA when no sm_100 device / kernel image is usable.
+ */
+#ifndef TRIAGE_B200_H
+#define TRIAGE_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* pkg/models/message.go:15-22 */
+#define TRIAGE_PRIO_UNSET    0
+#define TRIAGE_PRIO_REALTIME 1
+#define TRIAGE_PRIO_HIGH     2
+#define TRIAGE_PRIO_NORMAL   3
+#define TRIAGE_PRIO_LOW      4
+
+/* status codes; 1..3 map to the reference's error singletons (internal/priorityqueue/queue.go:213-217) */
+#define TRIAGE_OK            0
+#define TRIAGE_E_NOT_FOUND   1   /* ErrQueueNotFound */
+#define TRIAGE_E_FULL        2   /* ErrQueueFull     */
+#define TRIAGE_E_EMPTY       3   /* ErrQueueEmpty    */
+#define TRIAGE_E_PATTERN     4   /* AddKeywordPattern: not a (optionally "(?i)") literal, or unsupported */
+#define TRIAGE_E_ARG         5
+#define TRIAGE_E_CUDA        100 /* CUDA / NCCL failure, see triage_last_error() */
+
+/* Metadata["priority_reason"], internal/preprocessor/preprocessor.go:72,86,92 */
+#define TRIAGE_REASON_NONE             0
+#define TRIAGE_REASON_USER_OVERRIDE    1
+#define TRIAGE_REASON_USER_DEFAULT     2
+#define TRIAGE_REASON_CONTENT_KEYWORDS 3
+
+#define TRIAGE_UP_ABSENT        0   /* Metadata["user_priority"] absent or not a string  */
+#define TRIAGE_UP_UNRECOGNISED  5   /* a string that is none of realtime/high/normal/low */
+#define TRIAGE_META_VIP         1   /* Metadata has key "vip_user" (queue_factory.go:217) */
+
+#define TRIAGE_RF_ANALYZED      1   /* Metadata["analyzed"] = true (preprocessor.go:100)  */
+#define TRIAGE_RF_TIE           2   /* equal non-zero top scores: reference is random here */
+#define TRIAGE_RF_HAS_ANALYSIS  4   /* word_count/sentiment/contains_question were written */
+
+/* The fields of models.Message (pkg/models/message.go:58-74) the path reads, 16 bytes. */
+typedef struct {
+    uint8_t preset;        /* msg.Priority on entry */
+    uint8_t user_priority; /* Metadata["user_priority"].(string) lower-cased: 1..4, or TRIAGE_UP_* */
+    uint8_t user_default;  /* userPriorities[msg.UserID] resolved by the shim: 0 absent, 1..4  */
+    uint8_t meta_priority; /* Metadata["priority"].(string): 0 absent/unrecognised, 1..4       */
+    uint8_t flags;         /* TRIAGE_META_* */
+    uint8_t reserved[11];
+} triage_meta;
+
+/* What ProcessMessage + PushMessage write back, 16 bytes. */
+typedef struct {
+    uint8_t label;       /* msg.Priority after the path (post-rule when rules are on) */
+    uint8_t reason;      /* TRIAGE_REASON_* */
+    int8_t  sentiment;   /* -1 negative / 0 neutral / +1 positive */
+    uint8_t question;    /* contains_question */
+    uint8_t accepted;    /* 1 = admitted to its level queue */
+    uint8_t admit;       /* TRIAGE_OK / TRIAGE_E_NOT_FOUND / TRIAGE_E_FULL for this message */
+    uint8_t flags;       /* TRIAGE_RF_* */
+    uint8_t queue_level; /* level queue it was pushed to: fmt.Sprint(pre-rule Priority) (api/handlers.go:202) */
+    uint32_t words;      /* word_count */
+    uint16_t score_rt;   /* saturating realtime / high keyword scores (diagnostics) */
+    uint16_t score_hi;
+} triage_result;
+
+/* internal/priorityqueue/queue.go:60-68 (counters only) */
+typedef struct {
+    int64_t pending, processing, completed, failed;
+} triage_qstats;
+
+typedef struct {
+    int32_t  device;          /* CUDA ordinal */
+    int32_t  rules_enabled;   /* 1 = PriorityQueueType rules (queue_factory.go:202-204, 211-233) */
+    int64_t  max_queue_size;  /* per level queue; <= 0 unbounded (queue.go:101) */
+    uint64_t max_batch_bytes; /* capacity hints; buffers grow on demand when 0 */
+    uint32_t max_batch_msgs;
+    uint32_t flags;           /* reserved, 0 */
+} triage_opts;
+
+typedef struct triage_engine triage_engine;
+
+/* -- lifecycle.  Replaces preprocessor.NewPreprocessor (preprocessor.go:24) +
+ *    priorityqueue.NewMultiLevelQueue / AddQueue x4 (queue.go:70-90, cmd/queue-manager/main.go:58-63). */
+int32_t triage_create(const triage_opts *opts, triage_engine **out);
+void    triage_destroy(triage_engine *e);
+const char *triage_last_error(void);
+
+/* -- dictionary.  Replaces the pattern table built in NewPreprocessor (preprocessor.go:28-43),
+ *    AddKeywordPattern (:176-184), SetDefaultPriority (:187) and GetKeywordPatterns (:192). */
+int32_t triage_dict_reset(triage_engine *e, int32_t with_defaults);
+/* regexp source as AddKeywordPattern receives it: optional "(?i)" then a literal (metacharacters
+ * must be backslash-escaped).  Anything else -> TRIAGE_E_PATTERN (stated API deviation). */
+int32_t triage_dict_add_pattern(triage_engine *e, int32_t prio, const char *regex, uint32_t len);
+int32_t triage_dict_add_literal(triage_engine *e, int32_t prio, const uint8_t *lit, uint32_t len, int32_t ci);
+int32_t triage_dict_commit(triage_engine *e);            /* compile + upload the automaton */
+int32_t triage_dict_count(triage_engine *e, int32_t prio, uint32_t *n);
+int32_t triage_set_default_priority(triage_engine *e, int32_t prio);
+/* automaton facts for tests / DESIGN.md: states, warm-up bytes, table bytes */
+int32_t triage_dict_info(triage_engine *e, uint32_t *n_states, uint32_t *warm_bytes, uint32_t *table_bytes);
+
+/* -- pinned host arenas for the shim's ring buffers */
+int32_t triage_host_alloc(void **p, uint64_t bytes);
+int32_t triage_host_free(void *p);
+
+/* -- the hot path, host buffers.  One call = for every message i in arrival order:
+ *    ProcessMessage (preprocessor.go:56-114) then QueueManager.PushMessage(fmt.Sprint(Priority), msg)
+ *    (queue_manager.go:210-243 -> queue.go:92-119), i.e. BatchPushMessages semantics (:246-287):
+ *    a rejected message is skipped, not an error.  offsets has n+1 entries; message i is
+ *    bytes[offsets[i] .. offsets[i+1]).  enqueue_ns may be NULL: the engine then stamps strictly
+ *    increasing times (queue.go:108).  out (n entries) may be NULL.  handle_base receives the
+ *    handle of message 0; message i has handle_base + i.                                      */
+int32_t triage_submit(triage_engine *e, int32_t target_queue, const uint64_t *offsets, const uint8_t *bytes,
+                      const triage_meta *meta, const uint64_t *enqueue_ns, uint32_t n,
+                      triage_result *out, uint64_t *handle_base);
+/* target_queue = 0 routes every message to the level queue named after its label (the pipeline of
+ * api/handlers.go:178-202).  target_queue = a queue id pushes the whole batch into that one queue with
+ * item priority = int(msg.Priority): QueueManager.BatchPushMessages(queueName, msgs) (queue_manager.go:246-287). */
+
+/* ProcessMessage only (preprocessor.go:56-114) for a batch: labels + analysis, no queue is touched. */
+int32_t triage_process(triage_engine *e, const uint64_t *offsets, const uint8_t *bytes,
+                       const triage_meta *meta, uint32_t n, triage_result *out);
+
+/* -- same path with every input already resident in device memory (device pointers).  order_dev
+ *    (n x u32, device) receives this batch's dequeue permutation of admitted messages, results_dev
+ *    (n x triage_result, device) the labels; n_admitted is read back (4 bytes).  Does not touch the
+ *    host-side queues.  Used for the device-resident throughput figure and the multi-GPU driver. */
+int32_t triage_submit_device(triage_engine *e, const uint64_t *offsets_dev, const uint8_t *bytes_dev,
+                             uint64_t total_bytes, const triage_meta *meta_dev,
+                             const uint64_t *enqueue_ns_dev, uint32_t n, triage_result *results_dev,
+                             uint32_t *order_dev, uint32_t *n_admitted);
+
+/* -- dequeue.  triage_pop = MultiLevelQueue.Pop(name) (queue.go:121-139); triage_drain = the
+ *    realtime->high->normal->low loop of cmd/queue-manager/main.go:111-124 run max times, which is
+ *    also QueueManager.BatchPopMessages per level (queue_manager.go:326-367).                   */
+/* Queue ids: 1..4 are the built-in level queues realtime/high/normal/low.  QueueManager.CreateQueue(name, max)
+ * (queue_manager.go:170-188) makes further single-heap queues; ids are never reused. */
+int32_t triage_queue_create(triage_engine *e, int64_t max_size, int32_t *queue);
+int32_t triage_queue_delete(triage_engine *e, int32_t queue);                    /* DeleteQueue, :191-207 */
+int32_t triage_set_limits(triage_engine *e, int64_t max_queue_size, int32_t rules_enabled);
+int32_t triage_pop(triage_engine *e, int32_t level, uint64_t *handle);
+int32_t triage_peek(triage_engine *e, int32_t level, uint64_t *handle);
+int32_t triage_drain(triage_engine *e, uint32_t max, uint64_t *handles, uint8_t *levels, uint32_t *n_out);
+/* single push with an explicit item priority: MultiLevelQueue.Push(name, msg, priority) (queue.go:92) */
+int32_t triage_push(triage_engine *e, int32_t level, int32_t item_priority, uint64_t enqueue_ns, uint64_t *handle);
+int32_t triage_queue_size(triage_engine *e, int32_t level, uint64_t *size);       /* Size, queue.go:153 */
+int32_t triage_stats(triage_engine *e, int32_t level, triage_qstats *st);         /* GetStats, :165 */
+int32_t triage_complete(triage_engine *e, int32_t level);                         /* CompleteMessage, :197 */
+int32_t triage_fail(triage_engine *e, int32_t level);                             /* FailMessage, :205 */
+
+/* -- instrumentation: device times (CUDA events on the engine's stream) of the last submit */
+typedef struct {
+    float scan_ms, finalize_ms, order_ms, total_ms; /* kernels only */
+    float h2d_ms, d2h_ms;                           /* triage_submit only */
+    uint32_t launches;                              /* kernels launched by the last submit */
+    uint32_t order_passes;                          /* radix digit passes executed */
+    uint64_t scan_bytes;                            /* algorithmic bytes of the scan */
+} triage_timings;
+int32_t triage_last_timings(triage_engine *e, triage_timings *t);
+
+/* -- multi-GPU: one engine per rank/GPU; the caller broadcasts the 128-byte id (rank 0 makes it). */
+int32_t triage_comm_unique_id(uint8_t id[128]);
+int32_t triage_comm_init(triage_engine *e, int32_t nranks, int32_t rank, const uint8_t id[128]);
+/* all-gather every rank's sorted (key, global index) run of the last triage_submit_device and
+ * merge them: order_global_dev (sum of admitted, u32 global indices = rank_base + local index)
+ * receives the whole-job dequeue order on every rank.  rank_base[r] = first global index of rank r. */
+int32_t triage_merge_allgather(triage_engine *e, const uint64_t *rank_base, uint32_t *order_global_dev,
+                               uint64_t capacity, uint64_t *n_total);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,491 @@
+// dfa_build.cc — see dfa_build.h.  Host only; runs once per triage_dict_commit.
+#include "dfa_build.h"
+
+#include <algorithm>
+#include <cstring>
+#include <map>
+#include <unordered_map>
+
+namespace triage {
+
+bool EventVec::operator==(const EventVec &o) const { return std::memcmp(this, &o, sizeof(EventVec)) == 0; }
+bool EventVec::empty() const {
+    EventVec z;
+    std::memset(&z, 0, sizeof(z));
+    return *this == z;
+}
+
+namespace {
+
+// ---- UTF-8 (same validity rules as Go's unicode/utf8) -------------------------------------
+bool decode_rune(const std::string &s, size_t i, uint32_t *r, uint32_t *w) {
+    auto b = [&](size_t k) { return static_cast<uint8_t>(s[k]); };
+    uint8_t b0 = b(i);
+    size_t n = s.size() - i;
+    if (b0 < 0x80) { *r = b0; *w = 1; return true; }
+    if (b0 < 0xC2 || b0 > 0xF4) return false;
+    if (b0 < 0xE0) {
+        if (n < 2 || (b(i + 1) & 0xC0) != 0x80) return false;
+        *r = ((b0 & 0x1Fu) << 6) | (b(i + 1) & 0x3Fu); *w = 2; return true;
+    }
+    if (b0 < 0xF0) {
+        uint8_t lo = b0 == 0xE0 ? 0xA0 : 0x80, hi = b0 == 0xED ? 0x9F : 0xBF;
+        if (n < 3 || b(i + 1) < lo || b(i + 1) > hi || (b(i + 2) & 0xC0) != 0x80) return false;
+        *r = ((b0 & 0x0Fu) << 12) | ((b(i + 1) & 0x3Fu) << 6) | (b(i + 2) & 0x3Fu); *w = 3; return true;
+    }
+    uint8_t lo = b0 == 0xF0 ? 0x90 : 0x80, hi = b0 == 0xF4 ? 0x8F : 0xBF;
+    if (n < 4 || b(i + 1) < lo || b(i + 1) > hi || (b(i + 2) & 0xC0) != 0x80 || (b(i + 3) & 0xC0) != 0x80) return false;
+    *r = ((b0 & 0x07u) << 18) | ((b(i + 1) & 0x3Fu) << 12) | ((b(i + 2) & 0x3Fu) << 6) | (b(i + 3) & 0x3Fu);
+    *w = 4;
+    return true;
+}
+
+bool is_ascii_letter(uint32_t r) { return (r >= 'a' && r <= 'z') || (r >= 'A' && r <= 'Z'); }
+uint32_t ascii_lower(uint32_t r) { return (r >= 'A' && r <= 'Z') ? r + 32 : r; }
+
+// ---- NFA for the substring patterns (keywords + question words) ---------------------------
+struct NfaNode {
+    std::vector<std::pair<uint8_t, uint32_t>> edges;  // (byte, target)
+    int accept_event = -1;                            // index into pattern events when a pattern ends here
+};
+
+struct Nfa {
+    std::vector<NfaNode> nodes;  // node 0 = root (always active)
+    std::vector<EventVec> accept;  // per accepting node event
+    uint32_t max_bytes = 1;
+
+    Nfa() { nodes.emplace_back(); }
+    uint32_t add_node() { nodes.emplace_back(); return static_cast<uint32_t>(nodes.size() - 1); }
+
+    // one symbol = a set of alternative byte strings leading from `from` to a fresh node
+    uint32_t add_symbol(uint32_t from, const std::vector<std::string> &alts) {
+        uint32_t to = add_node();
+        for (const std::string &a : alts) {
+            uint32_t cur = from;
+            for (size_t k = 0; k < a.size(); k++) {
+                uint32_t nxt = (k + 1 == a.size()) ? to : add_node();
+                nodes[cur].edges.emplace_back(static_cast<uint8_t>(a[k]), nxt);
+                cur = nxt;
+            }
+        }
+        return to;
+    }
+};
+
+enum FoldKind { FOLD_NONE, FOLD_REGEXP, FOLD_TOLOWER };
+
+// alternatives a content rune may take to match pattern rune r
+std::vector<std::string> symbol_alts(uint32_t r, const std::string &raw, FoldKind fold) {
+    std::vector<std::string> alts;
+    if (fold != FOLD_NONE && is_ascii_letter(r)) {
+        uint32_t lo = ascii_lower(r);
+        alts.push_back(std::string(1, static_cast<char>(lo)));
+        alts.push_back(std::string(1, static_cast<char>(lo - 32)));
+        if (lo == 'k') alts.push_back("\xE2\x84\xAA");                       // U+212A, both folds
+        if (lo == 's' && fold == FOLD_REGEXP) alts.push_back("\xC5\xBF");    // U+017F, SimpleFold orbit only
+        if (lo == 'i' && fold == FOLD_TOLOWER) alts.push_back("\xC4\xB0");   // U+0130, unicode.ToLower only
+    } else {
+        alts.push_back(raw);
+    }
+    return alts;
+}
+
+uint32_t add_pattern(Nfa *nfa, const std::string &lit, FoldKind fold, const EventVec &ev) {
+    uint32_t cur = 0, bytes = 0;
+    for (size_t i = 0; i < lit.size();) {
+        uint32_t r = 0, w = 1;
+        decode_rune(lit, i, &r, &w);
+        std::vector<std::string> alts = symbol_alts(r, lit.substr(i, w), fold);
+        size_t longest = 0;
+        for (auto &a : alts) longest = std::max(longest, a.size());
+        bytes += static_cast<uint32_t>(longest);
+        cur = nfa->add_symbol(cur, alts);
+        i += w;
+    }
+    nfa->nodes[cur].accept_event = static_cast<int>(nfa->accept.size());
+    nfa->accept.push_back(ev);
+    nfa->max_bytes = std::max(nfa->max_bytes, bytes);
+    return cur;
+}
+
+// ---- sentiment trie (whole-field equality after strings.ToLower) --------------------------
+struct SentTrie {
+    struct Node { std::map<uint8_t, uint16_t> next; uint8_t pos = 0, neg = 0; };
+    std::vector<Node> nodes;  // 0 = root
+    uint32_t max_bytes = 0;
+    SentTrie() { nodes.emplace_back(); }
+    uint16_t child(uint16_t n, uint8_t b) {
+        auto it = nodes[n].next.find(b);
+        if (it != nodes[n].next.end()) return it->second;
+        uint16_t id = static_cast<uint16_t>(nodes.size());
+        nodes.emplace_back();
+        nodes[n].next[b] = id;
+        return id;
+    }
+    void add(const char *word, bool positive) {
+        // byte-level trie; a letter's alternatives rejoin at one node, so walk sets of nodes
+        std::vector<uint16_t> cur{0};
+        uint32_t bytes = 0;
+        for (const char *p = word; *p; p++) {
+            std::vector<std::string> alts = symbol_alts(static_cast<uint8_t>(*p), std::string(1, *p), FOLD_TOLOWER);
+            size_t longest = 0;
+            for (auto &a : alts) longest = std::max(longest, a.size());
+            bytes += static_cast<uint32_t>(longest);
+            // all alternatives of one symbol must land on the same logical node: use the lower-case
+            // single-byte child as the canonical target and alias the others to it.
+            std::vector<uint16_t> nxt;
+            for (uint16_t n : cur) {
+                uint16_t canon = child(n, static_cast<uint8_t>(alts[0][0]));
+                for (size_t a = 1; a < alts.size(); a++) {
+                    uint16_t c = n;
+                    for (size_t k = 0; k + 1 < alts[a].size(); k++) c = child(c, static_cast<uint8_t>(alts[a][k]));
+                    nodes[c].next[static_cast<uint8_t>(alts[a].back())] = canon;
+                }
+                nxt.push_back(canon);
+            }
+            std::sort(nxt.begin(), nxt.end());
+            nxt.erase(std::unique(nxt.begin(), nxt.end()), nxt.end());
+            cur = nxt;
+        }
+        for (uint16_t n : cur) { if (positive) nodes[n].pos++; else nodes[n].neg++; }
+        max_bytes = std::max(max_bytes, bytes);
+    }
+    static constexpr uint16_t DEAD = 0xFFFF;
+    uint16_t step(uint16_t n, uint8_t b) const {
+        if (n == DEAD) return DEAD;
+        auto it = nodes[n].next.find(b);
+        return it == nodes[n].next.end() ? DEAD : it->second;
+    }
+};
+
+// ---- multi-byte whitespace recogniser (unicode.IsSpace beyond ASCII) -----------------------
+enum WsProg : uint8_t { WS_NONE = 0, WS_C2, WS_E1, WS_E1_9A, WS_E2, WS_E2_80, WS_E2_81, WS_E3, WS_E3_80 };
+enum WsStep { WS_PENDING, WS_COMPLETE, WS_FAIL };
+
+bool is_ascii_space(uint8_t b) { return (b >= 0x09 && b <= 0x0D) || b == 0x20; }
+
+WsProg ws_lead(uint8_t b) {
+    switch (b) {
+        case 0xC2: return WS_C2;
+        case 0xE1: return WS_E1;
+        case 0xE2: return WS_E2;
+        case 0xE3: return WS_E3;
+        default: return WS_NONE;
+    }
+}
+
+WsStep ws_continue(WsProg p, uint8_t b, WsProg *next) {
+    switch (p) {
+        case WS_C2: return (b == 0x85 || b == 0xA0) ? WS_COMPLETE : WS_FAIL;            // U+0085, U+00A0
+        case WS_E1: if (b == 0x9A) { *next = WS_E1_9A; return WS_PENDING; } return WS_FAIL;
+        case WS_E1_9A: return b == 0x80 ? WS_COMPLETE : WS_FAIL;                         // U+1680
+        case WS_E2:
+            if (b == 0x80) { *next = WS_E2_80; return WS_PENDING; }
+            if (b == 0x81) { *next = WS_E2_81; return WS_PENDING; }
+            return WS_FAIL;
+        case WS_E2_80:                                                                   // U+2000-200A, 2028, 2029, 202F
+            return ((b >= 0x80 && b <= 0x8A) || b == 0xA8 || b == 0xA9 || b == 0xAF) ? WS_COMPLETE : WS_FAIL;
+        case WS_E2_81: return b == 0x9F ? WS_COMPLETE : WS_FAIL;                         // U+205F
+        case WS_E3: if (b == 0x80) { *next = WS_E3_80; return WS_PENDING; } return WS_FAIL;
+        case WS_E3_80: return b == 0x80 ? WS_COMPLETE : WS_FAIL;                         // U+3000
+        default: return WS_FAIL;
+    }
+}
+
+// ---- product configuration ------------------------------------------------------------------
+struct Config {
+    uint8_t in_field = 0;  // 0: last completed rune was whitespace / message start; 1: inside a field
+    uint8_t ws = WS_NONE;  // bytes of a possible multi-byte whitespace rune seen so far
+    uint16_t sent = 0;     // sentiment trie node (frozen while ws is pending), DEAD when the field cannot match
+    std::vector<uint32_t> kw;  // active NFA nodes, sorted
+    std::string key() const {
+        std::string k;
+        k.push_back(static_cast<char>(in_field));
+        k.push_back(static_cast<char>(ws));
+        k.append(reinterpret_cast<const char *>(&sent), 2);
+        k.append(reinterpret_cast<const char *>(kw.data()), kw.size() * 4);
+        return k;
+    }
+};
+
+struct Out {
+    bool word_start = false;
+    EventVec ev;
+};
+
+void add_event(EventVec *a, const EventVec &b) {
+    for (int i = 0; i < 4; i++) a->kw[i] = static_cast<uint16_t>(a->kw[i] + b.kw[i]);
+    a->pos = static_cast<uint8_t>(a->pos + b.pos);
+    a->neg = static_cast<uint8_t>(a->neg + b.neg);
+    a->question = (a->question || b.question) ? 1 : 0;
+}
+
+struct Machine {
+    Nfa nfa;
+    SentTrie sent;
+
+    void ws_complete(Config *c, Out *o) const {
+        if (c->in_field && c->sent != SentTrie::DEAD) {
+            const auto &n = sent.nodes[c->sent];
+            o->ev.pos = static_cast<uint8_t>(o->ev.pos + n.pos);
+            o->ev.neg = static_cast<uint8_t>(o->ev.neg + n.neg);
+        }
+        c->in_field = 0;
+        c->sent = 0;
+        c->ws = WS_NONE;
+    }
+
+    void fresh_byte(Config *c, uint8_t b, Out *o) const {
+        if (is_ascii_space(b)) { ws_complete(c, o); return; }
+        WsProg lead = ws_lead(b);
+        if (lead != WS_NONE) { c->ws = lead; return; }   // undecided: context and sentiment node stay frozen
+        if (!c->in_field) {
+            o->word_start = true;
+            c->in_field = 1;
+            c->sent = sent.step(0, b);
+        } else {
+            c->sent = sent.step(c->sent, b);
+        }
+    }
+
+    Config step(const Config &in, uint8_t b, Out *o) const {
+        Config c = in;
+        // keyword / question NFA: consumes every byte, root is always active
+        std::vector<uint32_t> nk;
+        auto follow = [&](uint32_t node) {
+            for (auto &e : nfa.nodes[node].edges) {
+                if (e.first != b) continue;
+                const NfaNode &t = nfa.nodes[e.second];
+                if (t.accept_event >= 0) add_event(&o->ev, nfa.accept[t.accept_event]);
+                if (!t.edges.empty()) nk.push_back(e.second);
+            }
+        };
+        follow(0);
+        for (uint32_t n : in.kw) follow(n);
+        std::sort(nk.begin(), nk.end());
+        // NOTE: duplicates are kept out — two NFA paths reaching the same node are the same thread
+        nk.erase(std::unique(nk.begin(), nk.end()), nk.end());
+        c.kw = nk;
+        // whitespace / field context
+        if (c.ws != WS_NONE) {
+            WsProg nxt = WS_NONE;
+            WsStep r = ws_continue(static_cast<WsProg>(c.ws), b, &nxt);
+            if (r == WS_PENDING) { c.ws = nxt; return c; }
+            if (r == WS_COMPLETE) { ws_complete(&c, o); return c; }
+            // the pending bytes were not whitespace: they are field content that matches no sentiment word
+            if (!c.in_field) { o->word_start = true; c.in_field = 1; }
+            c.sent = SentTrie::DEAD;
+            c.ws = WS_NONE;
+        }
+        fresh_byte(&c, b, o);
+        return c;
+    }
+
+    Out end_of_message(const Config &c) const {
+        Out o;
+        std::memset(&o.ev, 0, sizeof(o.ev));
+        if (c.ws != WS_NONE) {
+            if (!c.in_field) o.word_start = true;   // a truncated sequence is an invalid, non-space rune
+        } else if (c.in_field && c.sent != SentTrie::DEAD) {
+            o.ev.pos = sent.nodes[c.sent].pos;
+            o.ev.neg = sent.nodes[c.sent].neg;
+        }
+        return o;
+    }
+};
+
+std::vector<uint32_t> fold_runes(const std::string &s, bool ci) {
+    std::vector<uint32_t> out;
+    for (size_t i = 0; i < s.size();) {
+        uint32_t r = 0, w = 1;
+        decode_rune(s, i, &r, &w);
+        out.push_back(ci ? ascii_lower(r) : r);
+        i += w;
+    }
+    return out;
+}
+
+}  // namespace
+
+std::string validate_literal(const std::string &bytes, bool ci) {
+    if (bytes.empty()) return "empty pattern";
+    for (size_t i = 0; i < bytes.size();) {
+        uint32_t r = 0, w = 1;
+        if (!decode_rune(bytes, i, &r, &w)) return "pattern is not valid UTF-8";
+        if (r == 0xFFFD) return "U+FFFD in a pattern is not supported";
+        if (ci && r >= 0x80) return "non-ASCII rune in a (?i) pattern is not supported";
+        i += w;
+    }
+    return "";
+}
+
+bool literal_is_bordered(const std::string &bytes, bool ci) {
+    std::vector<uint32_t> r = fold_runes(bytes, ci);
+    // prefix function: a non-zero value at the end means a proper prefix equals a suffix
+    std::vector<size_t> pi(r.size(), 0);
+    for (size_t i = 1; i < r.size(); i++) {
+        size_t k = pi[i - 1];
+        while (k > 0 && r[i] != r[k]) k = pi[k - 1];
+        if (r[i] == r[k]) k++;
+        pi[i] = k;
+    }
+    return !r.empty() && pi.back() > 0;
+}
+
+bool parse_regex_literal(const char *s, uint32_t len, bool *ci, std::string *lit, std::string *err) {
+    uint32_t i = 0;
+    *ci = false;
+    lit->clear();
+    if (len >= 4 && std::memcmp(s, "(?i)", 4) == 0) { *ci = true; i = 4; }
+    static const char meta[] = "\\.+*?()|[]{}^$";
+    for (; i < len; i++) {
+        char c = s[i];
+        if (c == '\\') {
+            if (i + 1 >= len) { *err = "trailing backslash"; return false; }
+            char n = s[i + 1];
+            if (std::strchr(meta, n) == nullptr || n == '\0') { *err = "escape class is not a literal"; return false; }
+            lit->push_back(n);
+            i++;
+        } else if (c != '\0' && std::strchr(meta, c) != nullptr) {
+            *err = "regexp metacharacter: only (?i)-prefixed literals are supported";
+            return false;
+        } else {
+            lit->push_back(c);
+        }
+    }
+    if (lit->empty()) { *err = "empty pattern"; return false; }
+    return true;
+}
+
+std::string build_dfa(const std::vector<DictEntry> &dict, Dfa *out) {
+    Machine m;
+    for (const DictEntry &d : dict) {
+        std::string e = validate_literal(d.bytes, d.ci);
+        if (!e.empty()) return e;
+        if (d.prio < 1 || d.prio > 4) return "priority out of range";
+        EventVec ev;
+        std::memset(&ev, 0, sizeof(ev));
+        ev.kw[d.prio - 1] = 1;
+        add_pattern(&m.nfa, d.bytes, d.ci ? FOLD_REGEXP : FOLD_NONE, ev);
+    }
+    // preprocessor.go:51 — question words, matched as keyword + " " in strings.ToLower(content)
+    for (const char *q : {"what", "how", "why", "when", "where", "who"}) {
+        EventVec ev;
+        std::memset(&ev, 0, sizeof(ev));
+        ev.question = 1;
+        add_pattern(&m.nfa, std::string(q) + " ", FOLD_TOLOWER, ev);
+    }
+    // preprocessor.go:49-50
+    for (const char *w : {"good", "great", "excellent", "happy", "satisfied"}) m.sent.add(w, true);
+    for (const char *w : {"bad", "terrible", "awful", "angry", "frustrated"}) m.sent.add(w, false);
+
+    // ---- reachable configurations (BFS) ----
+    std::unordered_map<std::string, uint32_t> ids;
+    std::vector<Config> cfgs;
+    auto intern = [&](const Config &c) {
+        std::string k = c.key();
+        auto it = ids.find(k);
+        if (it != ids.end()) return it->second;
+        uint32_t id = static_cast<uint32_t>(cfgs.size());
+        ids.emplace(std::move(k), id);
+        cfgs.push_back(c);
+        return id;
+    };
+    Config start;   // field start, nothing pending
+    Config neutral; // mid-field, no partial matches
+    neutral.in_field = 1;
+    neutral.sent = SentTrie::DEAD;
+    uint32_t start_id = intern(start), neutral_id = intern(neutral);
+
+    std::vector<EventVec> events(1);
+    std::memset(&events[0], 0, sizeof(EventVec));
+    auto event_id = [&](const EventVec &e) -> uint32_t {
+        for (uint32_t i = 0; i < events.size(); i++) if (events[i] == e) return i;
+        events.push_back(e);
+        return static_cast<uint32_t>(events.size() - 1);
+    };
+
+    struct Trans { uint32_t next; uint32_t ev; bool ws; };
+    std::vector<Trans> trans;  // cfg-major, 256 per configuration
+    std::vector<uint32_t> eom_ev;
+    std::vector<uint8_t> eom_ws;
+    constexpr uint32_t kHardCap = 1u << 16;
+    for (uint32_t s = 0; s < cfgs.size(); s++) {
+        if (cfgs.size() > kHardCap) return "dictionary automaton exceeds 65536 configurations";
+        Config cur = cfgs[s];
+        for (uint32_t b = 0; b < 256; b++) {
+            Out o;
+            std::memset(&o.ev, 0, sizeof(o.ev));
+            Config nx = m.step(cur, static_cast<uint8_t>(b), &o);
+            trans.push_back({intern(nx), event_id(o.ev), o.word_start});
+        }
+        Out e = m.end_of_message(cur);
+        eom_ev.push_back(event_id(e.ev));
+        eom_ws.push_back(e.word_start ? 1 : 0);
+    }
+    uint32_t n = static_cast<uint32_t>(cfgs.size());
+    out->n_states_unminimised = n;
+
+    // ---- minimise (Moore partition refinement on outputs + successor classes) ----
+    std::vector<uint32_t> cls(n, 0);
+    {
+        std::map<std::string, uint32_t> sig;
+        for (uint32_t s = 0; s < n; s++) {
+            std::string k;
+            k.append(reinterpret_cast<const char *>(&eom_ev[s]), 4);
+            k.push_back(static_cast<char>(eom_ws[s]));
+            for (uint32_t b = 0; b < 256; b++) {
+                const Trans &t = trans[s * 256 + b];
+                k.append(reinterpret_cast<const char *>(&t.ev), 4);
+                k.push_back(t.ws ? 1 : 0);
+            }
+            auto it = sig.emplace(k, static_cast<uint32_t>(sig.size())).first;
+            cls[s] = it->second;
+        }
+    }
+    for (;;) {
+        std::map<std::string, uint32_t> sig;
+        std::vector<uint32_t> ncls(n);
+        for (uint32_t s = 0; s < n; s++) {
+            std::string k;
+            k.append(reinterpret_cast<const char *>(&cls[s]), 4);
+            for (uint32_t b = 0; b < 256; b++) k.append(reinterpret_cast<const char *>(&cls[trans[s * 256 + b].next]), 4);
+            auto it = sig.emplace(k, static_cast<uint32_t>(sig.size())).first;
+            ncls[s] = it->second;
+        }
+        uint32_t before = *std::max_element(cls.begin(), cls.end()) + 1;
+        uint32_t after = static_cast<uint32_t>(sig.size());
+        cls.swap(ncls);
+        if (after == before) break;
+    }
+    uint32_t nmin = *std::max_element(cls.begin(), cls.end()) + 1;
+    if (nmin > kMaxStatesD8) return "dictionary automaton has " + std::to_string(nmin) + " states; this build supports " + std::to_string(kMaxStatesD8);
+    if (events.size() - 1 > kMaxEventsD8) return "dictionary automaton has too many distinct event vectors";
+
+    out->n_states = nmin;
+    out->table.assign(static_cast<size_t>(nmin) * 256, 0);
+    out->eom.assign(nmin, 0);
+    std::vector<bool> done(nmin, false);
+    for (uint32_t s = 0; s < n; s++) {
+        uint32_t c = cls[s];
+        if (done[c]) continue;
+        done[c] = true;
+        for (uint32_t b = 0; b < 256; b++) {
+            const Trans &t = trans[s * 256 + b];
+            out->table[static_cast<size_t>(c) * 256 + b] =
+                static_cast<uint16_t>(cls[t.next] | (t.ev << 8) | (t.ws ? 0x8000u : 0u));
+        }
+        out->eom[c] = static_cast<uint8_t>(eom_ev[s] | (eom_ws[s] ? 0x80u : 0u));
+    }
+    out->events = events;
+    out->start_state = static_cast<uint8_t>(cls[start_id]);
+    out->neutral_state = static_cast<uint8_t>(cls[neutral_id]);
+    // longest byte distance an event can depend on: a keyword's own bytes, or for a sentiment word
+    // the tail of a multi-byte whitespace before it (2), the word, and the whitespace after it (3)
+    out->span = std::max<uint32_t>(m.nfa.max_bytes, m.sent.max_bytes + 5);
+    out->warm_bytes = ((out->span - 1 + 15) / 16) * 16;
+    if (out->warm_bytes == 0) out->warm_bytes = 16;
+    return "";
+}
+
+}  // namespace triage

@@ -1,0 +1,59 @@
+// dfa_build.h — host-side dictionary compiler: keyword literals + the reference's fixed
+// sentiment / question word lists + Go whitespace -> one byte-level Mealy DFA.
+//
+// What it encodes (reference: internal/preprocessor/preprocessor.go):
+//   * keyword patterns, substring semantics, "(?i)" folding with regexp's SimpleFold orbits
+//     (s ~ U+017F, k ~ U+212A)                                              :28-43, :144-149
+//   * strings.Fields word starts over unicode.IsSpace                       :204-205
+//   * whole-field equality with the 5+5 sentiment words after strings.ToLower (:211-223),
+//     where U+0130 lowers to 'i' and U+212A to 'k'
+//   * question words + " " as substrings of the lower-cased content         :235-243
+// Every equivalence is at the byte level; lead bytes are never consumed as continuation
+// bytes by Go's UTF-8 decoder, which is what makes that exact ("byte-level exactness").
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace triage {
+
+struct DictEntry {
+    uint8_t prio;       // 1..4
+    bool ci;            // "(?i)" literal
+    std::string bytes;  // valid UTF-8 literal
+};
+
+// counters one transition can bump (word starts are a separate bit)
+struct EventVec {
+    uint16_t kw[4];  // realtime, high, normal, low keyword matches ending on this byte
+    uint8_t pos, neg, question;
+    bool operator==(const EventVec &o) const;
+    bool empty() const;
+};
+
+// Dense table format "D8": entry(state, byte) is 16 bits:
+//   bits 0..7  next state      bits 8..14 event id (0 = none)      bit 15 word start
+constexpr uint32_t kMaxStatesD8 = 256;
+constexpr uint32_t kMaxEventsD8 = 127;
+
+struct Dfa {
+    uint32_t n_states = 0;
+    std::vector<uint16_t> table;      // n_states * 256
+    std::vector<uint8_t> eom;         // per state: bit 7 word start, bits 0..6 event id, applied at end of message
+    std::vector<EventVec> events;     // id -> counters (events[0] is all-zero)
+    uint8_t start_state = 0;          // at a message start (field start, nothing pending)
+    uint8_t neutral_state = 0;        // mid-field, no partial match: where a warm-up begins
+    uint32_t span = 1;                // longest byte distance an event can depend on
+    uint32_t warm_bytes = 16;         // span-1 rounded up to 16
+    uint32_t n_states_unminimised = 0;
+};
+
+// returns "" on success, else a message (too many states / events for D8, bordered pattern, ...)
+std::string validate_literal(const std::string &bytes, bool ci);
+bool literal_is_bordered(const std::string &bytes, bool ci);
+std::string build_dfa(const std::vector<DictEntry> &dict, Dfa *out);
+
+// "(?i)literal" / "literal" with backslash escapes -> DictEntry fields; false if not a literal
+bool parse_regex_literal(const char *s, uint32_t len, bool *ci, std::string *lit, std::string *err);
+
+}  // namespace triage

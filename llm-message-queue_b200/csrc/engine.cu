@@ -1,0 +1,767 @@
+// engine.cu — the C ABI of include/triage.h: engine object, device buffers, streams, the host-side
+// level queues (the part of MultiLevelQueue that is bookkeeping, not arithmetic) and the NCCL merge.
+//
+// No CPU fallback lives here: every compute entry point launches the sm_100a kernels of kernels.cu
+// and returns TRIAGE_E_CUDA if that is impossible.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/triage.h"
+#include "dfa_build.h"
+#include "kernels.cuh"
+
+using namespace triage;
+
+namespace {
+
+thread_local std::string g_err;
+int32_t fail(int32_t code, const std::string &msg) { g_err = msg; return code; }
+
+#define CU(call)                                                                                          \
+    do {                                                                                                  \
+        cudaError_t _e = (call);                                                                          \
+        if (_e != cudaSuccess)                                                                            \
+            return fail(TRIAGE_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(_e));               \
+    } while (0)
+
+// ---- lazily bound NCCL (so the library loads on hosts without it) ----------------------------
+struct NcclApi {
+    void *h = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+    bool load(std::string *err) {
+        if (h) return true;
+        h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) { *err = std::string("dlopen libnccl.so.2: ") + dlerror(); return false; }
+        GetUniqueId = reinterpret_cast<decltype(GetUniqueId)>(dlsym(h, "ncclGetUniqueId"));
+        CommInitRank = reinterpret_cast<decltype(CommInitRank)>(dlsym(h, "ncclCommInitRank"));
+        AllGather = reinterpret_cast<decltype(AllGather)>(dlsym(h, "ncclAllGather"));
+        CommDestroy = reinterpret_cast<decltype(CommDestroy)>(dlsym(h, "ncclCommDestroy"));
+        GetErrorString = reinterpret_cast<decltype(GetErrorString)>(dlsym(h, "ncclGetErrorString"));
+        if (!GetUniqueId || !CommInitRank || !AllGather || !CommDestroy || !GetErrorString) { *err = "libnccl: missing symbols"; return false; }
+        return true;
+    }
+};
+NcclApi g_nccl;
+
+template <class T>
+struct DevBuf {
+    T *p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t n, bool keep = false) {
+        if (n <= cap) return cudaSuccess;
+        size_t want = n + n / 8 + 64;
+        T *np = nullptr;
+        cudaError_t e = cudaMalloc(&np, want * sizeof(T));
+        if (e != cudaSuccess) return e;
+        if (p && keep) e = cudaMemcpy(np, p, cap * sizeof(T), cudaMemcpyDeviceToDevice);
+        if (p) cudaFree(p);
+        p = np; cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+struct QItem { int32_t prio; uint64_t ts; uint64_t handle; };
+inline bool qless(const QItem &a, const QItem &b) {   // queue.go:22-27 + handle (sequence) as the final tie-break
+    if (a.prio != b.prio) return a.prio < b.prio;
+    if (a.ts != b.ts) return a.ts < b.ts;
+    return a.handle < b.handle;
+}
+struct LevelQueue {
+    std::vector<QItem> items;   // sorted by qless from head
+    size_t head = 0;
+    int64_t max_size = 0;       // <= 0: unbounded (queue.go:101)
+    bool alive = true;
+    triage_qstats st{0, 0, 0, 0};
+    size_t size() const { return items.size() - head; }
+    void compact() { if (head > 4096 && head * 2 > items.size()) { items.erase(items.begin(), items.begin() + head); head = 0; } }
+};
+
+constexpr int kHeaderWords = 64;   // per-rank merge header (u64): n_adm, 16 counts, 16 first keys, 16 last keys
+
+}  // namespace
+
+struct triage_engine {
+    triage_opts opts{};
+    int sm_count = 0;
+    int max_smem_optin = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[6]{};
+    int32_t default_prio = TRIAGE_PRIO_NORMAL;
+    std::vector<DictEntry> dict;
+    bool dict_dirty = true;
+    Dfa dfa;
+    DevBuf<uint16_t> d_table;
+    DevBuf<EventPacked> d_events;
+    DevBuf<uint8_t> d_eom;
+    DeviceDfa ddfa{};
+    // batch buffers (triage_submit) and scratch
+    DevBuf<uint8_t> d_bytes;
+    DevBuf<uint64_t> d_offsets, d_ts, d_pending;
+    DevBuf<int64_t> d_maxsize;
+    DevBuf<triage_meta> d_meta;
+    DevBuf<triage_result> d_results;
+    DevBuf<uint32_t> d_counters, d_tile_first, d_order, d_perm_a, d_perm_b, d_blockhist, d_totals, d_small;
+    DevBuf<uint8_t> d_bucket, d_bucket2;
+    uint32_t *h_small = nullptr;   // pinned: [0] flags, [1] n_admitted, [2..17] bucket counts, [32..] digit hist
+    std::vector<uint32_t> h_order;
+    std::vector<triage_result> h_results_tmp;
+    // host queues
+    std::mutex mu;
+    std::vector<LevelQueue> q;   // q[0] unused; 1..4 = realtime/high/normal/low; further ids from triage_queue_create
+    uint64_t next_handle = 1;
+    uint64_t next_stamp = 0;
+    triage_timings tm{};
+    // last device run (for the multi-GPU merge)
+    const uint32_t *last_order = nullptr;
+    const uint8_t *last_bucket = nullptr;
+    const uint64_t *last_ts = nullptr;
+    uint32_t last_n = 0, last_n_adm = 0;
+    uint32_t last_counts[16]{};
+    // comm
+    ncclComm_t comm = nullptr;
+    int nranks = 1, rank = 0;
+    DevBuf<uint64_t> d_run_keys, d_all_keys, d_header, d_all_header;
+    DevBuf<uint32_t> d_run_gidx, d_all_gidx;
+    uint64_t *h_header = nullptr;   // pinned, nranks * kHeaderWords
+};
+
+namespace {
+
+int32_t commit_dict(triage_engine *e) {
+    if (!e->dict_dirty) return TRIAGE_OK;
+    Dfa dfa;
+    std::string err = build_dfa(e->dict, &dfa);
+    if (!err.empty()) return fail(TRIAGE_E_PATTERN, err);
+    if (dfa.warm_bytes > kMaxWarm) return fail(TRIAGE_E_PATTERN, "pattern too long for the scan's warm-up window");
+    std::vector<EventPacked> ev(dfa.events.size());
+    for (size_t i = 0; i < dfa.events.size(); i++) {
+        const EventVec &v = dfa.events[i];
+        ev[i] = {uint32_t(v.kw[0]) | uint32_t(v.kw[1]) << 16, uint32_t(v.kw[2]) | uint32_t(v.kw[3]) << 16,
+                 uint32_t(v.pos) | uint32_t(v.neg) << 8 | uint32_t(v.question) << 16, 0};
+    }
+    std::vector<uint8_t> eom(256, 0);
+    std::copy(dfa.eom.begin(), dfa.eom.end(), eom.begin());
+    DeviceDfa d{};
+    d.n_states = dfa.n_states; d.n_events = (uint32_t)ev.size(); d.warm = dfa.warm_bytes;
+    d.start_state = dfa.start_state; d.neutral_state = dfa.neutral_state;
+    if (scan_smem_bytes(d) > (size_t)e->max_smem_optin)
+        return fail(TRIAGE_E_PATTERN, "dictionary automaton (" + std::to_string(dfa.n_states) + " states) does not fit in shared memory");
+    CU(e->d_table.ensure(dfa.table.size()));
+    CU(e->d_events.ensure(ev.size()));
+    CU(e->d_eom.ensure(256));
+    // the previous automaton may still be in use by a kernel on the stream
+    CU(cudaStreamSynchronize(e->stream));
+    CU(cudaMemcpy(e->d_table.p, dfa.table.data(), dfa.table.size() * 2, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(e->d_events.p, ev.data(), ev.size() * sizeof(EventPacked), cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(e->d_eom.p, eom.data(), 256, cudaMemcpyHostToDevice));
+    d.table = e->d_table.p; d.events = e->d_events.p; d.eom = e->d_eom.p;
+    e->ddfa = d;
+    e->dfa = dfa;
+    e->dict_dirty = false;
+    return TRIAGE_OK;
+}
+
+// The whole device pipeline on e->stream.  All pointers are device pointers.
+enum RunMode { RUN_ROUTED = 0, RUN_SINGLE_QUEUE = 1, RUN_PROCESS_ONLY = 2 };
+
+int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, const uint8_t *bytes, uint64_t total,
+                   const triage_meta *meta, const uint64_t *ts, uint32_t n, triage_result *results, uint32_t *order,
+                   const uint64_t pending[4], const int64_t max_size[4], uint32_t *n_admitted) {
+    int32_t rc = commit_dict(e);
+    if (rc) return rc;
+    if ((reinterpret_cast<uintptr_t>(bytes) & 15) != 0) return fail(TRIAGE_E_ARG, "device arena must be 16-byte aligned");
+    cudaStream_t s = e->stream;
+    uint32_t launches = 0;
+    e->tm = triage_timings{};
+    *n_admitted = 0;
+    if (n == 0) return TRIAGE_OK;
+    const uint32_t ntiles = (uint32_t)((total + kScanTile - 1) / kScanTile);
+    const uint32_t nblocks = (n + kOrderBlock - 1) / kOrderBlock;
+    CU(e->d_counters.ensure((size_t)n * CNT_STRIDE));
+    CU(e->d_tile_first.ensure((size_t)ntiles + 2));
+    CU(e->d_bucket.ensure(n));
+    CU(e->d_bucket2.ensure(n));
+    CU(e->d_blockhist.ensure((size_t)nblocks * 256));
+    CU(e->d_totals.ensure(260));
+    CU(e->d_small.ensure(32 + 8 * 256));
+    CU(e->d_pending.ensure(4));
+    CU(e->d_maxsize.ensure(4));
+    OrderScratch sc{e->d_blockhist.p, e->d_totals.p, nblocks};
+
+    CU(cudaEventRecord(e->ev[0], s));
+    CU(cudaMemsetAsync(e->d_counters.p, 0, (size_t)n * CNT_STRIDE * sizeof(uint32_t), s));
+    CU(cudaMemsetAsync(e->d_small.p, 0, (32 + 8 * 256) * sizeof(uint32_t), s));
+    ScanArgs sa{bytes, offsets, total, n, e->d_counters.p, e->d_tile_first.p, ntiles};
+    if (ntiles) {
+        CU(launch_tile_index(sa, s)); launches++;
+        CU(cudaEventRecord(e->ev[1], s));
+        CU(launch_scan(sa, e->ddfa, e->sm_count, s)); launches++;
+    } else {
+        CU(cudaEventRecord(e->ev[1], s));
+    }
+    CU(cudaEventRecord(e->ev[2], s));
+    const int32_t single = mode == RUN_SINGLE_QUEUE ? 1 : 0;
+    FinalizeArgs fa{e->d_counters.p, meta, offsets, ts, n, e->default_prio, mode == RUN_PROCESS_ONLY ? 0 : e->opts.rules_enabled,
+                    single, results, e->d_bucket.p, e->d_small.p};
+    CU(launch_finalize(fa, s)); launches++;
+    CU(cudaEventRecord(e->ev[3], s));
+    if (mode == RUN_PROCESS_ONLY) {
+        CU(cudaEventRecord(e->ev[4], s));
+        CU(cudaStreamSynchronize(s));
+        float ms0 = 0;
+        cudaEventElapsedTime(&ms0, e->ev[1], e->ev[2]); e->tm.scan_ms = ms0;
+        cudaEventElapsedTime(&ms0, e->ev[2], e->ev[3]); e->tm.finalize_ms = ms0;
+        cudaEventElapsedTime(&ms0, e->ev[0], e->ev[4]); e->tm.total_ms = ms0;
+        e->tm.launches = launches;
+        e->tm.scan_bytes = total + 8ull * (n + 1) + 32ull * n;
+        return TRIAGE_OK;
+    }
+    const uint8_t *bucket = e->d_bucket.p;
+    bool bounded = false;
+    for (int i = 0; i < 4; i++) if (max_size[i] > 0) bounded = true;
+    if (bounded) {
+        CU(cudaMemcpyAsync(e->d_pending.p, pending, 4 * sizeof(uint64_t), cudaMemcpyHostToDevice, s));
+        CU(cudaMemcpyAsync(e->d_maxsize.p, max_size, 4 * sizeof(int64_t), cudaMemcpyHostToDevice, s));
+        CU(launch_admit(e->d_bucket.p, e->d_bucket2.p, results, n, e->d_pending.p, e->d_maxsize.p, single, sc, s)); launches += 3;
+        bucket = e->d_bucket2.p;
+    }
+    // fast path: arrival order is time order, so the dequeue order is one stable 16-way split
+    CU(launch_partition_u8(bucket, nullptr, n, 16, true, order, e->d_small.p + 2, sc, s)); launches += 4;
+    CU(cudaEventRecord(e->ev[4], s));
+    CU(cudaMemcpyAsync(e->h_small, e->d_small.p, 32 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(e->h_small + 1, e->d_totals.p + 256, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    uint32_t passes = 1;
+    if (e->h_small[0] & 1u) {
+        // enqueue times are not monotone in arrival order: LSD radix over the time key first (stable, so equal
+        // times keep arrival order = sequence), skipping digit positions on which every key agrees
+        CU(e->d_perm_a.ensure(n));
+        CU(e->d_perm_b.ensure(n));
+        CU(launch_key_digit_hist(ts, nullptr, n, e->d_small.p + 32, s)); launches++;
+        CU(cudaMemcpyAsync(e->h_small + 32, e->d_small.p + 32, 8 * 256 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+        CU(cudaStreamSynchronize(s));
+        const uint32_t *perm = nullptr;
+        uint32_t *bufs[2] = {e->d_perm_a.p, e->d_perm_b.p};
+        int which = 0;
+        for (uint32_t b = 0; b < 8; b++) {
+            bool trivial = false;
+            for (uint32_t d = 0; d < 256; d++) if (e->h_small[32 + b * 256 + d] == n) trivial = true;
+            if (trivial) continue;
+            CU(launch_partition_key(ts, 8 * b, perm, n, bufs[which], sc, s)); launches += 3;
+            perm = bufs[which];
+            which ^= 1;
+            passes++;
+        }
+        CU(launch_partition_u8(bucket, perm, n, 16, true, order, e->d_small.p + 2, sc, s)); launches += 4;
+        CU(cudaEventRecord(e->ev[4], s));
+        CU(cudaMemcpyAsync(e->h_small, e->d_small.p, 32 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+        CU(cudaMemcpyAsync(e->h_small + 1, e->d_totals.p + 256, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+        CU(cudaStreamSynchronize(s));
+    }
+    *n_admitted = e->h_small[1];
+    for (int b = 0; b < 16; b++) e->last_counts[b] = e->h_small[2 + b];
+    e->last_order = order; e->last_bucket = bucket; e->last_ts = ts; e->last_n = n; e->last_n_adm = *n_admitted;
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e->ev[1], e->ev[2]); e->tm.scan_ms = ms;
+    cudaEventElapsedTime(&ms, e->ev[2], e->ev[3]); e->tm.finalize_ms = ms;
+    cudaEventElapsedTime(&ms, e->ev[3], e->ev[4]); e->tm.order_ms = ms;
+    cudaEventElapsedTime(&ms, e->ev[0], e->ev[4]); e->tm.total_ms = ms;
+    e->tm.launches = launches;
+    e->tm.order_passes = passes;
+    e->tm.scan_bytes = total + 8ull * (n + 1) + 32ull * n;
+    return TRIAGE_OK;
+}
+
+uint64_t now_ns() {
+    return (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::system_clock::now().time_since_epoch()).count();
+}
+
+bool queue_ok(const triage_engine *e, int32_t q) { return q >= 1 && (size_t)q < e->q.size() && e->q[q].alive; }
+
+}  // namespace
+
+extern "C" {
+
+const char *triage_last_error(void) { return g_err.c_str(); }
+
+int32_t triage_create(const triage_opts *opts, triage_engine **out) {
+    if (!opts || !out) return fail(TRIAGE_E_ARG, "null argument");
+    int ndev = 0;
+    CU(cudaGetDeviceCount(&ndev));
+    if (opts->device < 0 || opts->device >= ndev) return fail(TRIAGE_E_CUDA, "no such CUDA device");
+    CU(cudaSetDevice(opts->device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, opts->device));
+    if (prop.major != 10) return fail(TRIAGE_E_CUDA, std::string("this library is built for sm_100a only, found ") + prop.name);
+    triage_engine *e = new triage_engine();
+    e->opts = *opts;
+    e->sm_count = prop.multiProcessorCount;
+    e->max_smem_optin = (int)prop.sharedMemPerBlockOptin;
+    cudaError_t ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
+    for (int i = 0; i < 6 && ce == cudaSuccess; i++) ce = cudaEventCreate(&e->ev[i]);
+    if (ce == cudaSuccess) ce = cudaHostAlloc(reinterpret_cast<void **>(&e->h_small), (32 + 8 * 256) * sizeof(uint32_t), cudaHostAllocDefault);
+    if (ce != cudaSuccess) { delete e; return fail(TRIAGE_E_CUDA, cudaGetErrorString(ce)); }
+    e->q.resize(5);
+    for (int l = 1; l <= 4; l++) e->q[l].max_size = opts->max_queue_size;
+    // preprocessor.go:28-43 default dictionary
+    triage_dict_reset(e, 1);
+    *out = e;
+    return TRIAGE_OK;
+}
+
+void triage_destroy(triage_engine *e) {
+    if (!e) return;
+    cudaSetDevice(e->opts.device);
+    cudaStreamSynchronize(e->stream);
+    if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
+    e->d_table.release(); e->d_events.release(); e->d_eom.release(); e->d_bytes.release(); e->d_offsets.release();
+    e->d_ts.release(); e->d_pending.release(); e->d_maxsize.release(); e->d_meta.release(); e->d_results.release(); e->d_counters.release();
+    e->d_tile_first.release(); e->d_order.release(); e->d_perm_a.release(); e->d_perm_b.release(); e->d_blockhist.release();
+    e->d_totals.release(); e->d_small.release(); e->d_bucket.release(); e->d_bucket2.release(); e->d_run_keys.release();
+    e->d_all_keys.release(); e->d_header.release(); e->d_all_header.release(); e->d_run_gidx.release(); e->d_all_gidx.release();
+    if (e->h_small) cudaFreeHost(e->h_small);
+    if (e->h_header) cudaFreeHost(e->h_header);
+    for (auto &ev : e->ev) if (ev) cudaEventDestroy(ev);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+int32_t triage_dict_reset(triage_engine *e, int32_t with_defaults) {
+    if (!e) return fail(TRIAGE_E_ARG, "null engine");
+    e->dict.clear();
+    if (with_defaults) {
+        for (const char *w : {"immediate", "emergency", "asap", "right now"}) e->dict.push_back({TRIAGE_PRIO_REALTIME, true, w});
+        for (const char *w : {"urgent", "important", "priority", "critical", "soon"}) e->dict.push_back({TRIAGE_PRIO_HIGH, true, w});
+    }
+    e->dict_dirty = true;
+    return TRIAGE_OK;
+}
+
+int32_t triage_dict_add_literal(triage_engine *e, int32_t prio, const uint8_t *lit, uint32_t len, int32_t ci) {
+    if (!e || !lit) return fail(TRIAGE_E_ARG, "null argument");
+    if (prio < 1 || prio > 4) return fail(TRIAGE_E_PATTERN, "priority must be 1..4");
+    std::string s(reinterpret_cast<const char *>(lit), len);
+    std::string err = validate_literal(s, ci != 0);
+    if (!err.empty()) return fail(TRIAGE_E_PATTERN, err);
+    if (literal_is_bordered(s, ci != 0))
+        return fail(TRIAGE_E_PATTERN, "self-overlapping literal (a proper prefix equals a suffix): non-overlapping match counting for it is not supported yet");
+    e->dict.push_back({(uint8_t)prio, ci != 0, s});
+    e->dict_dirty = true;
+    return TRIAGE_OK;
+}
+
+int32_t triage_dict_add_pattern(triage_engine *e, int32_t prio, const char *regex, uint32_t len) {
+    if (!e || !regex) return fail(TRIAGE_E_ARG, "null argument");
+    bool ci = false;
+    std::string lit, err;
+    if (!parse_regex_literal(regex, len, &ci, &lit, &err)) return fail(TRIAGE_E_PATTERN, err);
+    return triage_dict_add_literal(e, prio, reinterpret_cast<const uint8_t *>(lit.data()), (uint32_t)lit.size(), ci ? 1 : 0);
+}
+
+int32_t triage_dict_commit(triage_engine *e) {
+    if (!e) return fail(TRIAGE_E_ARG, "null engine");
+    CU(cudaSetDevice(e->opts.device));
+    return commit_dict(e);
+}
+
+int32_t triage_dict_count(triage_engine *e, int32_t prio, uint32_t *n) {
+    if (!e || !n) return fail(TRIAGE_E_ARG, "null argument");
+    uint32_t c = 0;
+    for (auto &d : e->dict) if (d.prio == prio) c++;
+    *n = c;
+    return TRIAGE_OK;
+}
+
+int32_t triage_set_default_priority(triage_engine *e, int32_t prio) {
+    if (!e) return fail(TRIAGE_E_ARG, "null engine");
+    e->default_prio = prio;   // preprocessor.go:187 accepts any value
+    return TRIAGE_OK;
+}
+
+int32_t triage_dict_info(triage_engine *e, uint32_t *n_states, uint32_t *warm_bytes, uint32_t *table_bytes) {
+    if (!e) return fail(TRIAGE_E_ARG, "null engine");
+    CU(cudaSetDevice(e->opts.device));
+    int32_t rc = commit_dict(e);
+    if (rc) return rc;
+    if (n_states) *n_states = e->dfa.n_states;
+    if (warm_bytes) *warm_bytes = e->dfa.warm_bytes;
+    if (table_bytes) *table_bytes = e->dfa.n_states * 512u;
+    return TRIAGE_OK;
+}
+
+int32_t triage_host_alloc(void **p, uint64_t bytes) {
+    if (!p) return fail(TRIAGE_E_ARG, "null argument");
+    CU(cudaHostAlloc(p, bytes ? bytes : 1, cudaHostAllocDefault));
+    return TRIAGE_OK;
+}
+int32_t triage_host_free(void *p) {
+    CU(cudaFreeHost(p));
+    return TRIAGE_OK;
+}
+
+int32_t triage_submit_device(triage_engine *e, const uint64_t *offsets_dev, const uint8_t *bytes_dev, uint64_t total_bytes,
+                             const triage_meta *meta_dev, const uint64_t *enqueue_ns_dev, uint32_t n,
+                             triage_result *results_dev, uint32_t *order_dev, uint32_t *n_admitted) {
+    if (!e || !n_admitted || (n && (!offsets_dev || !meta_dev || !results_dev || !order_dev))) return fail(TRIAGE_E_ARG, "null argument");
+    if (total_bytes && !bytes_dev) return fail(TRIAGE_E_ARG, "null arena");
+    CU(cudaSetDevice(e->opts.device));
+    const uint64_t pending[4] = {0, 0, 0, 0};
+    const int64_t ms[4] = {e->opts.max_queue_size, e->opts.max_queue_size, e->opts.max_queue_size, e->opts.max_queue_size};
+    return run_device(e, RUN_ROUTED, offsets_dev, bytes_dev, total_bytes, meta_dev, enqueue_ns_dev, n, results_dev, order_dev, pending, ms,
+                      n_admitted);
+}
+
+namespace {
+
+// H2D of one batch into the engine's own buffers.  offsets are rebased to start at 0.
+int32_t upload_batch(triage_engine *e, const uint64_t *offsets, const uint8_t *bytes, const triage_meta *meta,
+                     const uint64_t *enqueue_ns, uint32_t n, uint64_t *total_out) {
+    const uint64_t total = offsets[n] - offsets[0];
+    if (total && !bytes) return fail(TRIAGE_E_ARG, "null arena");
+    cudaStream_t s = e->stream;
+    CU(e->d_bytes.ensure(total + 32));
+    CU(e->d_offsets.ensure((size_t)n + 1));
+    CU(e->d_meta.ensure(n));
+    CU(e->d_results.ensure(n));
+    CU(e->d_order.ensure(n));
+    if (enqueue_ns) CU(e->d_ts.ensure(n));
+    std::vector<uint64_t> rebased;
+    const uint64_t *off_src = offsets;
+    if (offsets[0] != 0) {
+        rebased.resize((size_t)n + 1);
+        for (uint32_t i = 0; i <= n; i++) rebased[i] = offsets[i] - offsets[0];
+        off_src = rebased.data();
+    }
+    if (total) CU(cudaMemcpyAsync(e->d_bytes.p, bytes + offsets[0], total, cudaMemcpyHostToDevice, s));
+    CU(cudaMemsetAsync(e->d_bytes.p + total, 0, 32, s));   // the last tile's bulk copy rounds up to 16 bytes
+    CU(cudaMemcpyAsync(e->d_offsets.p, off_src, ((size_t)n + 1) * 8, cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(e->d_meta.p, meta, (size_t)n * sizeof(triage_meta), cudaMemcpyHostToDevice, s));
+    if (enqueue_ns) CU(cudaMemcpyAsync(e->d_ts.p, enqueue_ns, (size_t)n * 8, cudaMemcpyHostToDevice, s));
+    CU(cudaStreamSynchronize(s));   // `rebased` goes out of scope; also separates the H2D time
+    *total_out = total;
+    return TRIAGE_OK;
+}
+
+}  // namespace
+
+int32_t triage_process(triage_engine *e, const uint64_t *offsets, const uint8_t *bytes, const triage_meta *meta, uint32_t n,
+                       triage_result *out) {
+    if (!e || (n && (!offsets || !meta || !out))) return fail(TRIAGE_E_ARG, "null argument");
+    CU(cudaSetDevice(e->opts.device));
+    std::lock_guard<std::mutex> lock(e->mu);
+    if (n == 0) return TRIAGE_OK;
+    auto t0 = std::chrono::steady_clock::now();
+    uint64_t total = 0;
+    int32_t rc = upload_batch(e, offsets, bytes, meta, nullptr, n, &total);
+    if (rc) return rc;
+    auto t1 = std::chrono::steady_clock::now();
+    const uint64_t pending[4] = {0, 0, 0, 0};
+    const int64_t ms[4] = {0, 0, 0, 0};
+    uint32_t n_adm = 0;
+    rc = run_device(e, RUN_PROCESS_ONLY, e->d_offsets.p, e->d_bytes.p, total, e->d_meta.p, nullptr, n, e->d_results.p, e->d_order.p,
+                    pending, ms, &n_adm);
+    if (rc) return rc;
+    auto t2 = std::chrono::steady_clock::now();
+    CU(cudaMemcpyAsync(out, e->d_results.p, (size_t)n * sizeof(triage_result), cudaMemcpyDeviceToHost, e->stream));
+    CU(cudaStreamSynchronize(e->stream));
+    auto t3 = std::chrono::steady_clock::now();
+    e->tm.h2d_ms = std::chrono::duration<float, std::milli>(t1 - t0).count();
+    e->tm.d2h_ms = std::chrono::duration<float, std::milli>(t3 - t2).count();
+    return TRIAGE_OK;
+}
+
+int32_t triage_submit(triage_engine *e, int32_t target_queue, const uint64_t *offsets, const uint8_t *bytes, const triage_meta *meta,
+                      const uint64_t *enqueue_ns, uint32_t n, triage_result *out, uint64_t *handle_base) {
+    if (!e || (n && (!offsets || !meta))) return fail(TRIAGE_E_ARG, "null argument");
+    CU(cudaSetDevice(e->opts.device));
+    std::lock_guard<std::mutex> lock(e->mu);
+    if (target_queue != 0 && !queue_ok(e, target_queue)) return fail(TRIAGE_E_NOT_FOUND, "queue not found");
+    if (handle_base) *handle_base = e->next_handle;
+    if (n == 0) return TRIAGE_OK;
+    cudaStream_t s = e->stream;
+    auto t0 = std::chrono::steady_clock::now();
+    uint64_t total = 0;
+    int32_t rc = upload_batch(e, offsets, bytes, meta, enqueue_ns, n, &total);
+    if (rc) return rc;
+    auto t1 = std::chrono::steady_clock::now();
+    uint64_t pending[4] = {0, 0, 0, 0};
+    int64_t ms[4] = {0, 0, 0, 0};
+    if (target_queue == 0) {
+        for (int l = 1; l <= 4; l++) { pending[l - 1] = e->q[l].size(); ms[l - 1] = e->q[l].max_size; }
+    } else {
+        pending[0] = e->q[target_queue].size();
+        ms[0] = e->q[target_queue].max_size;
+    }
+    uint32_t n_adm = 0;
+    rc = run_device(e, target_queue ? RUN_SINGLE_QUEUE : RUN_ROUTED, e->d_offsets.p, e->d_bytes.p, total, e->d_meta.p,
+                    enqueue_ns ? e->d_ts.p : nullptr, n, e->d_results.p, e->d_order.p, pending, ms, &n_adm);
+    if (rc) return rc;
+    auto t2 = std::chrono::steady_clock::now();
+    triage_result *res = out;
+    if (!res) { e->h_results_tmp.resize(n); res = e->h_results_tmp.data(); }
+    e->h_order.resize(n_adm);
+    CU(cudaMemcpyAsync(res, e->d_results.p, (size_t)n * sizeof(triage_result), cudaMemcpyDeviceToHost, s));
+    if (n_adm) CU(cudaMemcpyAsync(e->h_order.data(), e->d_order.p, (size_t)n_adm * 4, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    auto t3 = std::chrono::steady_clock::now();
+    e->tm.h2d_ms = std::chrono::duration<float, std::milli>(t1 - t0).count();
+    e->tm.d2h_ms = std::chrono::duration<float, std::milli>(t3 - t2).count();
+    // queue.go:105-116: admitted messages enter their queue; the device order is already
+    // (queue, item priority, time, sequence), so each queue receives one sorted run
+    uint64_t stamp0 = 0;
+    if (!enqueue_ns) { stamp0 = std::max(now_ns(), e->next_stamp); e->next_stamp = stamp0 + n; }
+    const uint64_t base = e->next_handle;
+    const int qlo = target_queue ? target_queue : 1, qhi = target_queue ? target_queue : 4;
+    std::vector<size_t> run_begin(e->q.size(), 0);
+    for (int l = qlo; l <= qhi; l++) run_begin[l] = e->q[l].items.size();
+    for (uint32_t k = 0; k < n_adm; k++) {
+        uint32_t i = e->h_order[k];
+        const triage_result &r = res[i];
+        QItem it{r.label, enqueue_ns ? enqueue_ns[i] : stamp0 + i, base + i};
+        e->q[target_queue ? target_queue : r.queue_level].items.push_back(it);
+    }
+    for (int l = qlo; l <= qhi; l++) {
+        LevelQueue &lq = e->q[l];
+        size_t added = lq.items.size() - run_begin[l];
+        lq.st.pending += (int64_t)added;
+        if (added && run_begin[l] > lq.head && qless(lq.items[run_begin[l]], lq.items[run_begin[l] - 1]))
+            std::inplace_merge(lq.items.begin() + lq.head, lq.items.begin() + run_begin[l], lq.items.end(), qless);
+    }
+    e->next_handle = base + n;
+    return TRIAGE_OK;
+}
+
+int32_t triage_queue_create(triage_engine *e, int64_t max_size, int32_t *queue) {
+    if (!e || !queue) return fail(TRIAGE_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lock(e->mu);
+    e->q.emplace_back();
+    e->q.back().max_size = max_size;
+    *queue = (int32_t)e->q.size() - 1;
+    return TRIAGE_OK;
+}
+
+int32_t triage_queue_delete(triage_engine *e, int32_t queue) {
+    if (!e) return fail(TRIAGE_E_ARG, "null engine");
+    std::lock_guard<std::mutex> lock(e->mu);
+    if (!queue_ok(e, queue) || queue <= 4) return fail(TRIAGE_E_NOT_FOUND, "queue not found");
+    e->q[queue] = LevelQueue();
+    e->q[queue].alive = false;
+    return TRIAGE_OK;
+}
+
+int32_t triage_set_limits(triage_engine *e, int64_t max_queue_size, int32_t rules_enabled) {
+    if (!e) return fail(TRIAGE_E_ARG, "null engine");
+    std::lock_guard<std::mutex> lock(e->mu);
+    e->opts.max_queue_size = max_queue_size;
+    e->opts.rules_enabled = rules_enabled;
+    for (int l = 1; l <= 4; l++) e->q[l].max_size = max_queue_size;
+    return TRIAGE_OK;
+}
+
+int32_t triage_push(triage_engine *e, int32_t level, int32_t item_priority, uint64_t enqueue_ns, uint64_t *handle) {
+    if (!e) return fail(TRIAGE_E_ARG, "null engine");
+    std::lock_guard<std::mutex> lock(e->mu);
+    if (!queue_ok(e, level)) return fail(TRIAGE_E_NOT_FOUND, "queue not found");
+    LevelQueue &lq = e->q[level];
+    if (lq.max_size > 0 && (int64_t)lq.size() >= lq.max_size) return fail(TRIAGE_E_FULL, "queue is full");
+    if (enqueue_ns == 0) { enqueue_ns = std::max(now_ns(), e->next_stamp); e->next_stamp = enqueue_ns + 1; }
+    QItem it{item_priority, enqueue_ns, e->next_handle++};
+    auto pos = std::upper_bound(lq.items.begin() + lq.head, lq.items.end(), it, qless);
+    lq.items.insert(pos, it);
+    lq.st.pending++;
+    if (handle) *handle = it.handle;
+    return TRIAGE_OK;
+}
+
+int32_t triage_pop(triage_engine *e, int32_t level, uint64_t *handle) {
+    if (!e || !handle) return fail(TRIAGE_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lock(e->mu);
+    if (!queue_ok(e, level)) return fail(TRIAGE_E_EMPTY, "queue is empty");   // queue.go:126-128: missing queue -> ErrQueueEmpty
+    LevelQueue &lq = e->q[level];
+    if (lq.size() == 0) return fail(TRIAGE_E_EMPTY, "queue is empty");
+    *handle = lq.items[lq.head++].handle;
+    lq.st.pending--;
+    lq.st.processing++;
+    lq.compact();
+    return TRIAGE_OK;
+}
+
+int32_t triage_peek(triage_engine *e, int32_t level, uint64_t *handle) {
+    if (!e || !handle) return fail(TRIAGE_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lock(e->mu);
+    if (!queue_ok(e, level)) return fail(TRIAGE_E_EMPTY, "queue is empty");
+    LevelQueue &lq = e->q[level];
+    if (lq.size() == 0) return fail(TRIAGE_E_EMPTY, "queue is empty");
+    *handle = lq.items[lq.head].handle;
+    return TRIAGE_OK;
+}
+
+int32_t triage_drain(triage_engine *e, uint32_t max, uint64_t *handles, uint8_t *levels, uint32_t *n_out) {
+    if (!e || !n_out || (max && !handles)) return fail(TRIAGE_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lock(e->mu);
+    uint32_t k = 0;
+    for (int l = 1; l <= 4 && k < max; l++) {   // cmd/queue-manager/main.go:112
+        LevelQueue &lq = e->q[l];
+        while (k < max && lq.size()) {
+            handles[k] = lq.items[lq.head++].handle;
+            if (levels) levels[k] = (uint8_t)l;
+            lq.st.pending--;
+            lq.st.processing++;
+            k++;
+        }
+        lq.compact();
+    }
+    *n_out = k;
+    return TRIAGE_OK;
+}
+
+int32_t triage_queue_size(triage_engine *e, int32_t level, uint64_t *size) {
+    if (!e || !size) return fail(TRIAGE_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lock(e->mu);
+    if (!queue_ok(e, level)) return fail(TRIAGE_E_NOT_FOUND, "queue not found");
+    *size = e->q[level].size();
+    return TRIAGE_OK;
+}
+
+int32_t triage_stats(triage_engine *e, int32_t level, triage_qstats *st) {
+    if (!e || !st) return fail(TRIAGE_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lock(e->mu);
+    if (!queue_ok(e, level)) return fail(TRIAGE_E_NOT_FOUND, "queue not found");
+    *st = e->q[level].st;
+    return TRIAGE_OK;
+}
+
+int32_t triage_complete(triage_engine *e, int32_t level) {
+    if (!e) return fail(TRIAGE_E_ARG, "null engine");
+    std::lock_guard<std::mutex> lock(e->mu);
+    if (!queue_ok(e, level)) return TRIAGE_OK;   // updateStats ignores unknown queues (queue.go:192)
+    e->q[level].st.processing--;
+    e->q[level].st.completed++;
+    return TRIAGE_OK;
+}
+
+int32_t triage_fail(triage_engine *e, int32_t level) {
+    if (!e) return fail(TRIAGE_E_ARG, "null engine");
+    std::lock_guard<std::mutex> lock(e->mu);
+    if (!queue_ok(e, level)) return TRIAGE_OK;
+    e->q[level].st.processing--;
+    e->q[level].st.failed++;
+    return TRIAGE_OK;
+}
+
+int32_t triage_last_timings(triage_engine *e, triage_timings *t) {
+    if (!e || !t) return fail(TRIAGE_E_ARG, "null argument");
+    *t = e->tm;
+    return TRIAGE_OK;
+}
+
+// ------------------------------------------------------------------------------ multi-GPU ---
+int32_t triage_comm_unique_id(uint8_t id[128]) {
+    std::string err;
+    if (!g_nccl.load(&err)) return fail(TRIAGE_E_CUDA, err);
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+    ncclUniqueId u;
+    ncclResult_t r = g_nccl.GetUniqueId(&u);
+    if (r != ncclSuccess) return fail(TRIAGE_E_CUDA, std::string("ncclGetUniqueId: ") + g_nccl.GetErrorString(r));
+    std::memcpy(id, &u, 128);
+    return TRIAGE_OK;
+}
+
+int32_t triage_comm_init(triage_engine *e, int32_t nranks, int32_t rank, const uint8_t id[128]) {
+    if (!e || !id || nranks < 1 || rank < 0 || rank >= nranks) return fail(TRIAGE_E_ARG, "bad argument");
+    std::string err;
+    if (!g_nccl.load(&err)) return fail(TRIAGE_E_CUDA, err);
+    CU(cudaSetDevice(e->opts.device));
+    ncclUniqueId u;
+    std::memcpy(&u, id, 128);
+    ncclResult_t r = g_nccl.CommInitRank(&e->comm, nranks, u, rank);
+    if (r != ncclSuccess) return fail(TRIAGE_E_CUDA, std::string("ncclCommInitRank: ") + g_nccl.GetErrorString(r));
+    e->nranks = nranks;
+    e->rank = rank;
+    CU(cudaHostAlloc(reinterpret_cast<void **>(&e->h_header), (size_t)nranks * kHeaderWords * 8, cudaHostAllocDefault));
+    return TRIAGE_OK;
+}
+
+}  // extern "C"
+
+extern "C" int32_t triage_merge_allgather(triage_engine *e, const uint64_t *rank_base, uint32_t *order_global_dev, uint64_t capacity,
+                                          uint64_t *n_total) {
+    if (!e || !rank_base || !order_global_dev || !n_total) return fail(TRIAGE_E_ARG, "null argument");
+    if (!e->comm) return fail(TRIAGE_E_ARG, "triage_comm_init has not been called");
+    if (e->nranks > 8) return fail(TRIAGE_E_ARG, "at most 8 ranks");
+    CU(cudaSetDevice(e->opts.device));
+    cudaStream_t s = e->stream;
+    const uint32_t R = (uint32_t)e->nranks;
+    const uint32_t n_adm = e->last_n_adm;
+    // 1. my sorted run and its header
+    CU(e->d_run_keys.ensure(std::max<size_t>(n_adm, 1)));
+    CU(e->d_run_gidx.ensure(std::max<size_t>(n_adm, 1)));
+    CU(e->d_header.ensure(kHeaderWords));
+    CU(e->d_all_header.ensure((size_t)R * kHeaderWords));
+    uint64_t stamp_base = 0;   // ts == NULL: arrival index is the time; rank_base keeps ranks in sequence order
+    CU(launch_build_run(e->last_order, n_adm, e->last_bucket, e->last_ts, stamp_base + rank_base[e->rank], rank_base[e->rank],
+                        e->d_run_keys.p, e->d_run_gidx.p, s));
+    CU(launch_header(e->d_run_keys.p, n_adm, e->last_counts, e->d_header.p, s));
+    ncclResult_t r = g_nccl.AllGather(e->d_header.p, e->d_all_header.p, kHeaderWords, ncclUint64, e->comm, s);
+    if (r != ncclSuccess) return fail(TRIAGE_E_CUDA, std::string("ncclAllGather(header): ") + g_nccl.GetErrorString(r));
+    CU(cudaMemcpyAsync(e->h_header, e->d_all_header.p, (size_t)R * kHeaderWords * 8, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    // 2. geometry
+    ConcatTables t{};
+    t.n_ranks = R;
+    uint64_t total = 0;
+    uint32_t cap = 1;
+    for (uint32_t q = 0; q < R; q++) { t.cnt[q] = (uint32_t)e->h_header[q * kHeaderWords]; total += t.cnt[q]; cap = std::max(cap, t.cnt[q]); }
+    t.cap = cap;
+    *n_total = total;
+    if (total > capacity) return fail(TRIAGE_E_ARG, "order_global_dev is too small");
+    bool disjoint = true;   // per bucket, rank q's keys all <= rank q+1's keys?
+    uint32_t dst = 0;
+    for (uint32_t b = 0; b < 16; b++) {
+        uint64_t prev_last = 0; bool have_prev = false;
+        for (uint32_t q = 0; q < R; q++) {
+            const uint64_t *h = e->h_header + (size_t)q * kHeaderWords;
+            uint32_t c = (uint32_t)h[1 + b];
+            t.dst[q][b] = dst;
+            dst += c;
+            if (c) {
+                if (have_prev && h[17 + b] < prev_last) disjoint = false;
+                prev_last = h[33 + b]; have_prev = true;
+            }
+        }
+    }
+    for (uint32_t q = 0; q < R; q++) {
+        uint32_t acc = 0;
+        for (uint32_t b = 0; b < 16; b++) { t.lstart[q][b] = acc; acc += (uint32_t)e->h_header[(size_t)q * kHeaderWords + 1 + b]; }
+    }
+    // 3. all-gather the runs (equal counts per rank: padded to the largest run)
+    CU(e->d_run_keys.ensure(cap, true));
+    CU(e->d_run_gidx.ensure(cap, true));
+    CU(e->d_all_keys.ensure((size_t)R * cap));
+    CU(e->d_all_gidx.ensure((size_t)R * cap));
+    r = g_nccl.AllGather(e->d_run_keys.p, e->d_all_keys.p, cap, ncclUint64, e->comm, s);
+    if (r != ncclSuccess) return fail(TRIAGE_E_CUDA, std::string("ncclAllGather(keys): ") + g_nccl.GetErrorString(r));
+    r = g_nccl.AllGather(e->d_run_gidx.p, e->d_all_gidx.p, cap, ncclUint32, e->comm, s);
+    if (r != ncclSuccess) return fail(TRIAGE_E_CUDA, std::string("ncclAllGather(gidx): ") + g_nccl.GetErrorString(r));
+    // 4. merge: when the per-bucket key ranges of the ranks do not interleave (contiguous sequence shards, the
+    //    normal case) the merged order is pure offset arithmetic; otherwise rank every key by binary search
+    if (disjoint) CU(launch_concat(e->d_all_keys.p, e->d_all_gidx.p, t, order_global_dev, s));
+    else CU(launch_merge_strided(e->d_all_keys.p, e->d_all_gidx.p, t, order_global_dev, s));
+    CU(cudaStreamSynchronize(s));
+    return TRIAGE_OK;
+}

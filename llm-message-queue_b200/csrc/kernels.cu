@@ -1,0 +1,594 @@
+// kernels.cu — hand-written sm_100a kernels of the triage path.
+//
+//   tile_index_kernel   offsets -> first message of every arena tile (scratch)
+//   scan_kernel         the hot kernel: DFA byte scan of the packed arena, HBM-bound by design.
+//                       Persistent CTAs, one per SM; arena tiles are brought into shared memory by
+//                       1-D TMA bulk copies (cp.async.bulk + mbarrier, double buffered); the automaton
+//                       table lives in shared memory; every lane walks its own contiguous chunk with
+//                       conflict-free 128-bit shared loads; per-message word counts are combined across
+//                       neighbouring lanes with shuffles before one atomic per (warp, message).
+//   finalize_kernel     fused score -> label -> reason -> queue bucket (ProcessMessage decision tree)
+//   admit/partition     stable multi-split = LSD radix passes that emit the dequeue order
+//
+// Reference semantics: internal/preprocessor/preprocessor.go:56-249, internal/priorityqueue/queue.go:22-27,
+// 92-119, queue_manager.go:451-466, queue_factory.go:211-233, cmd/queue-manager/main.go:111-124.
+#include "kernels.cuh"
+
+namespace triage {
+
+// ------------------------------------------------------------------------------ PTX helpers --
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// 1-D TMA bulk copy global -> shared, completion signalled on an mbarrier (SASS: UBLKCP)
+__device__ __forceinline__ void tma_load_1d(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+// ------------------------------------------------------------------------------ tile index --
+__global__ void tile_index_kernel(const uint64_t *__restrict__ offsets, uint32_t n, uint32_t ntiles, uint32_t *__restrict__ tile_first) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t > ntiles) return;
+    if (t == ntiles) { tile_first[t] = n - 1; return; }
+    uint64_t pos = (uint64_t)t * kScanTile;
+    uint32_t lo = 0, hi = n + 1;   // first index with offsets[idx] > pos
+    while (lo < hi) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (offsets[mid] > pos) hi = mid; else lo = mid + 1;
+    }
+    tile_first[t] = lo - 1;
+}
+
+cudaError_t launch_tile_index(const ScanArgs &a, cudaStream_t s) {
+    uint32_t cnt = a.ntiles + 1;
+    tile_index_kernel<<<(cnt + 255) / 256, 256, 0, s>>>(a.offsets, a.n, a.ntiles, a.tile_first);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------ scan --
+// shared memory layout (bytes): [0,16) two mbarriers | table | events | eom(256) | stage0 | stage1 | list0 | list1
+struct ScanSmem {
+    uint32_t table, events, eom, stage0, stage1, list0, list1, total, stage_bytes;
+};
+__host__ __device__ inline ScanSmem scan_layout(uint32_t n_states, uint32_t n_events, uint32_t warm) {
+    ScanSmem L;
+    uint32_t o = 128;
+    L.table = o; o += n_states * 512u;
+    L.events = o; o += ((n_events * 16u + 127u) / 128u) * 128u;
+    L.eom = o; o += 256u;
+    L.stage_bytes = ((warm + kScanTile + 16u + 127u) / 128u) * 128u;
+    L.stage0 = o; o += L.stage_bytes;
+    L.stage1 = o; o += L.stage_bytes;
+    L.list0 = o; o += kListCap * 4u;
+    L.list1 = o; o += kListCap * 4u;
+    L.total = o;
+    return L;
+}
+size_t scan_smem_bytes(const DeviceDfa &d) { return scan_layout(d.n_states, d.n_events, d.warm).total; }
+
+__device__ __forceinline__ int32_t rel_clamp(uint64_t off, uint64_t tile_start) {
+    int64_t r = (int64_t)off - (int64_t)tile_start;
+    const int64_t lim = 1 << 30;
+    return (int32_t)(r < -lim ? -lim : (r > lim ? lim : r));
+}
+
+template <int NT, int C>
+__global__ void __launch_bounds__(NT, 1) scan_kernel(ScanArgs a, DeviceDfa d) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    constexpr uint32_t TILE = NT * C;
+    constexpr int LPT = (kListCap + NT - 1) / NT;
+    const ScanSmem L = scan_layout(d.n_states, d.n_events, d.warm);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem);
+    uint16_t *tbl = reinterpret_cast<uint16_t *>(smem + L.table);
+    EventPacked *events = reinterpret_cast<EventPacked *>(smem + L.events);
+    uint8_t *eom = smem + L.eom;
+    // buffers are addressed arithmetically (not through a pointer array) so the compiler keeps them in the
+    // shared state space (LDS, not generic LD)
+    auto stage_of = [&](uint32_t b) -> uint8_t * { return smem + L.stage0 + b * L.stage_bytes; };
+    auto list_of = [&](uint32_t b) -> int32_t * { return reinterpret_cast<int32_t *>(smem + L.list0 + b * (kListCap * 4u)); };
+    const uint32_t tid = threadIdx.x, lane = tid & 31;
+    const uint32_t G = gridDim.x;
+    const uint32_t warm = d.warm;
+
+    if (blockIdx.x >= a.ntiles) return;
+    const uint32_t nmine = (a.ntiles - blockIdx.x + G - 1) / G;
+
+    if (tid == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    // automaton -> shared memory
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(d.table);
+        uint4 *dst = reinterpret_cast<uint4 *>(tbl);
+        for (uint32_t i = tid; i < d.n_states * 32u; i += NT) dst[i] = src[i];
+        const uint4 *es = reinterpret_cast<const uint4 *>(d.events);
+        uint4 *ed = reinterpret_cast<uint4 *>(events);
+        for (uint32_t i = tid; i < d.n_events; i += NT) ed[i] = es[i];
+        for (uint32_t i = tid; i < 256; i += NT) eom[i] = d.eom[i];
+    }
+    __syncthreads();
+
+    auto issue_tile = [&](uint32_t tile, uint32_t buf) {   // one thread
+        uint64_t ts = (uint64_t)tile * TILE;
+        uint64_t te = ts + TILE < a.total ? ts + TILE : a.total;
+        uint64_t cs = ts >= warm ? ts - warm : 0;
+        uint32_t dst_off = (uint32_t)(cs + warm - ts);
+        uint32_t bytes = (uint32_t)(((te - cs) + 15u) & ~(uint64_t)15u);
+        mbar_expect_tx(&bars[buf], bytes);
+        tma_load_1d(stage_of(buf) + dst_off, a.bytes + cs, bytes, &bars[buf]);
+    };
+
+    // prologue: tile 0 of this CTA
+    uint32_t tile = blockIdx.x;
+    uint32_t first_cur = a.tile_first[tile], last_cur = a.tile_first[tile + 1];
+    if (tid == 0) issue_tile(tile, 0);
+    {
+        uint32_t cnt = last_cur - first_cur + 2;
+        if (cnt <= kListCap)
+            for (uint32_t i = tid; i < cnt; i += NT) list_of(0)[i] = rel_clamp(a.offsets[first_cur + i], (uint64_t)tile * TILE);
+    }
+    uint32_t first_nxt = 0, last_nxt = 0;
+    if (nmine > 1) { first_nxt = a.tile_first[tile + G]; last_nxt = a.tile_first[tile + G + 1]; }
+    __syncthreads();
+
+    for (uint32_t k = 0; k < nmine; k++, tile += G) {
+        const uint32_t buf = k & 1;
+        const bool has_next = k + 1 < nmine;
+        if (has_next && tid == 0) issue_tile(tile + G, buf ^ 1);
+        // start the loads that build the NEXT tile's message list; they are consumed after the scan
+        uint64_t nxt_off[LPT];
+        uint32_t cnt_nxt = 0;
+        uint32_t first_nn = 0, last_nn = 0;
+        if (has_next) {
+            cnt_nxt = last_nxt - first_nxt + 2;
+            if (cnt_nxt <= kListCap) {
+#pragma unroll
+                for (int j = 0; j < LPT; j++) {
+                    uint32_t i = tid + j * NT;
+                    nxt_off[j] = i < cnt_nxt ? a.offsets[first_nxt + i] : 0;
+                }
+            }
+            if (k + 2 < nmine) { first_nn = a.tile_first[tile + 2 * G]; last_nn = a.tile_first[tile + 2 * G + 1]; }
+        }
+
+        const uint64_t ts = (uint64_t)tile * TILE;
+        const int32_t tile_len = (int32_t)((ts + TILE < a.total ? ts + TILE : a.total) - ts);
+        const uint32_t cnt_cur = last_cur - first_cur + 2;
+
+        LaneCtx c;
+        c.tbl = tbl; c.events = events; c.eom = eom; c.stage = stage_of(buf);
+        c.list = cnt_cur <= kListCap ? list_of(buf) : nullptr;
+        c.list_abs = a.offsets; c.tile_start = (int64_t)ts;
+        c.list_n = cnt_cur; c.msg_lo = first_cur; c.counters = a.counters; c.warm = (int32_t)warm;
+        c.start_state = d.start_state; c.neutral_state = d.neutral_state;
+
+        mbar_wait(&bars[buf], (k >> 1) & 1);
+
+        uint32_t hm = 0xFFFFFFFFu, hw = 0;
+        const int32_t chunk = (int32_t)(tid * C);
+        if (chunk < tile_len) {
+            int32_t ce = chunk + C < tile_len ? chunk + C : tile_len;
+            lane_scan(c, chunk, ce, &hm, &hw);
+        }
+        // combine the head partials of neighbouring lanes that sit in the same message
+        {
+            const unsigned full = 0xFFFFFFFFu;
+            uint32_t prev = __shfl_up_sync(full, hm, 1);
+            bool head = lane == 0 || hm != prev;
+            uint32_t heads = __ballot_sync(full, head);
+            uint32_t v = hw;
+#pragma unroll
+            for (int dlt = 1; dlt < 32; dlt <<= 1) {
+                uint32_t t = __shfl_up_sync(full, v, dlt);
+                if ((int)lane >= dlt) v += t;
+            }
+            uint32_t above = heads & ~((2u << lane) - 1u);             // heads strictly above this lane
+            uint32_t end = above ? (uint32_t)__ffs(above) - 2u : 31u;   // last lane of this lane's group
+            uint32_t upto = __shfl_sync(full, v, end);
+            uint32_t before = __shfl_up_sync(full, v, 1);
+            if (lane == 0) before = 0;
+            if (head && hm != 0xFFFFFFFFu) {
+                uint32_t sum = upto - before;
+                if (sum) atomicAdd(a.counters + (uint64_t)hm * CNT_STRIDE + CNT_WORDS, sum);
+            }
+        }
+        // publish the next tile's list
+        if (has_next && cnt_nxt <= kListCap) {
+#pragma unroll
+            for (int j = 0; j < LPT; j++) {
+                uint32_t i = tid + j * NT;
+                if (i < cnt_nxt) list_of(buf ^ 1)[i] = rel_clamp(nxt_off[j], ts + (uint64_t)G * TILE);
+            }
+        }
+        first_cur = first_nxt; last_cur = last_nxt;
+        first_nxt = first_nn; last_nxt = last_nn;
+        __syncthreads();
+    }
+}
+
+cudaError_t launch_scan(const ScanArgs &a, const DeviceDfa &d, int sm_count, cudaStream_t s) {
+    if (a.ntiles == 0) return cudaSuccess;
+    size_t smem = scan_smem_bytes(d);
+    auto kern = scan_kernel<kScanThreads, kScanChunk>;
+    static size_t configured = 0;
+    if (smem > configured) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        configured = smem;
+    }
+    uint32_t grid = a.ntiles < (uint32_t)sm_count ? a.ntiles : (uint32_t)sm_count;
+    kern<<<grid, kScanThreads, smem, s>>>(a, d);
+    return cudaGetLastError();
+}
+
+// -------------------------------------------------------------------------------- finalize --
+__global__ void __launch_bounds__(256) finalize_kernel(FinalizeArgs a) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.n) return;
+    const uint4 c0 = reinterpret_cast<const uint4 *>(a.counters)[2 * (uint64_t)i];
+    const uint4 c1 = reinterpret_cast<const uint4 *>(a.counters)[2 * (uint64_t)i + 1];
+    const uint4 mraw = reinterpret_cast<const uint4 *>(a.meta)[i];
+    const uint64_t len = a.offsets[i + 1] - a.offsets[i];
+    const uint32_t preset = mraw.x & 0xFFu, up = (mraw.x >> 8) & 0xFFu, ud = (mraw.x >> 16) & 0xFFu, mp = mraw.x >> 24;
+    const uint32_t mflags = mraw.y & 0xFFu;
+    const uint32_t sc[5] = {0, c0.y, c0.z, c0.w, c1.x};
+
+    uint32_t label = preset, reason = TRIAGE_REASON_NONE, rflags = 0, words = 0, question = 0, srt = 0, shi = 0;
+    int32_t sentiment = 0;
+    if (preset == TRIAGE_PRIO_NORMAL || preset == 0) {           // preprocessor.go:63-65
+        uint32_t tie = 0;
+        if (up != TRIAGE_UP_ABSENT) {                            // :68-82
+            if (up >= 1 && up <= 4) { label = up; reason = TRIAGE_REASON_USER_OVERRIDE; }
+        } else if (ud != 0) {                                    // :83-86
+            label = ud; reason = TRIAGE_REASON_USER_DEFAULT;
+        } else {
+            if (len == 0) {                                      // :120-138
+                label = (mp >= 1 && mp <= 4) ? mp : (uint32_t)a.default_prio;
+            } else {                                             // :141-165, ties: most urgent wins + TIE flag
+                uint32_t best = 0, bp = (uint32_t)a.default_prio;
+#pragma unroll
+                for (uint32_t p = 1; p <= 4; p++) if (sc[p] > best) { best = sc[p]; bp = p; }
+                if (best > 0) for (uint32_t p = bp + 1; p <= 4; p++) if (sc[p] == best) tie = 1;
+                label = bp;
+                srt = sc[1] > 0xFFFFu ? 0xFFFFu : sc[1];
+                shi = sc[2] > 0xFFFFu ? 0xFFFFu : sc[2];
+            }
+            if (label != preset) reason = TRIAGE_REASON_CONTENT_KEYWORDS;
+        }
+        rflags = TRIAGE_RF_ANALYZED | (tie ? TRIAGE_RF_TIE : 0);
+        if (len > 0) {                                           // :199-249
+            words = c0.x;
+            sentiment = c1.y > c1.z ? 1 : (c1.z > c1.y ? -1 : 0);
+            question = c1.w ? 1 : 0;
+            rflags |= TRIAGE_RF_HAS_ANALYSIS;
+        }
+    }
+    // queue level = pre-rule label (api/handlers.go:202); rules mutate msg.Priority before the push
+    uint32_t level = label, bucket = 0xFF, admit = TRIAGE_E_NOT_FOUND, accepted = 0;
+    if (a.single_queue) {                                        // BatchPushMessages(queueName, ...): one heap, any int priority
+        if (a.rules_on) {
+            if (mflags & TRIAGE_META_VIP) label = TRIAGE_PRIO_HIGH;
+            else if (len > 10000) label = TRIAGE_PRIO_LOW;
+        }
+        bucket = label < 15 ? label : 15;
+        admit = TRIAGE_OK;
+        accepted = 1;
+    } else if (level >= 1 && level <= 4) {
+        if (a.rules_on) {                                        // queue_manager.go:451-466 / queue_factory.go:211-233
+            if (mflags & TRIAGE_META_VIP) label = TRIAGE_PRIO_HIGH;
+            else if (len > 10000) label = TRIAGE_PRIO_LOW;
+        }
+        bucket = (level - 1) * 4 + (label - 1);
+        admit = TRIAGE_OK;     // provisional: launch_admit applies the capacity rule
+        accepted = 1;
+    }
+    uint4 r;
+    r.x = label | (reason << 8) | ((uint32_t)(uint8_t)(int8_t)sentiment << 16) | (question << 24);
+    r.y = accepted | (admit << 8) | (rflags << 16) | (level << 24);
+    r.z = words;
+    r.w = srt | (shi << 16);
+    reinterpret_cast<uint4 *>(a.results)[i] = r;
+    a.bucket[i] = (uint8_t)bucket;
+    if (a.ts && i > 0 && a.ts[i] < a.ts[i - 1]) atomicOr(a.flags, 1u);
+}
+
+cudaError_t launch_finalize(const FinalizeArgs &a, cudaStream_t s) {
+    if (a.n == 0) return cudaSuccess;
+    finalize_kernel<<<(a.n + 255) / 256, 256, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------- order ---
+// Stable multi-split with up to 256 buckets.  Position k (in perm_in order, identity when null)
+// holds item perm_in[k]; digit(item) in [0,256) or 256 = leave out.
+struct DigU8 {
+    const uint8_t *d; bool drop_ff;
+    __device__ uint32_t operator()(uint32_t item) const { uint32_t v = d[item]; return (drop_ff && v == 0xFFu) ? 256u : v; }
+};
+struct DigLevel {
+    const uint8_t *b; uint32_t shift;   // shift 2: routed buckets (level-1)*4+(prio-1); shift 8: single queue
+    __device__ uint32_t operator()(uint32_t item) const { uint32_t v = b[item]; return v == 0xFFu ? 256u : (v >> shift); }
+};
+struct DigKey {
+    const uint64_t *k; uint32_t shift;
+    __device__ uint32_t operator()(uint32_t item) const { return (uint32_t)(k[item] >> shift) & 0xFFu; }
+};
+
+template <class Dig>
+__global__ void __launch_bounds__(kOrderBlock) split_hist_kernel(Dig dig, const uint32_t *__restrict__ perm_in, uint32_t n,
+                                                                uint32_t *__restrict__ blockhist) {
+    __shared__ uint32_t h[256];
+    for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) h[i] = 0;
+    __syncthreads();
+    uint32_t k = blockIdx.x * kOrderBlock + threadIdx.x;
+    if (k < n) {
+        uint32_t item = perm_in ? perm_in[k] : k;
+        uint32_t dg = dig(item);
+        if (dg < 256) atomicAdd(&h[dg], 1u);
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < 256; i += blockDim.x) blockhist[(uint64_t)blockIdx.x * 256 + i] = h[i];
+}
+
+// exclusive scan in digit-major order over (digit, block); blockhist[b][d] <- global exclusive offset,
+// totals[d] <- offset of (d, block 0), totals[256] <- total kept
+__global__ void __launch_bounds__(1024) split_scan_kernel(uint32_t *__restrict__ blockhist, uint32_t nblocks, uint32_t nb,
+                                                          uint32_t *__restrict__ totals) {
+    __shared__ uint32_t part[1024];
+    const uint64_t total = (uint64_t)nblocks * nb;   // digits >= nb never occur
+    const uint64_t per = (total + 1023) / 1024;
+    const uint64_t lo = per * threadIdx.x, hi = lo + per < total ? lo + per : total;
+    uint32_t s = 0;
+    for (uint64_t j = lo; j < hi; j++) { uint32_t dgt = (uint32_t)(j / nblocks), b = (uint32_t)(j % nblocks); s += blockhist[(uint64_t)b * 256 + dgt]; }
+    part[threadIdx.x] = s;
+    __syncthreads();
+    // inclusive scan of part (Hillis-Steele)
+    for (uint32_t off = 1; off < 1024; off <<= 1) {
+        uint32_t v = threadIdx.x >= off ? part[threadIdx.x - off] : 0;
+        __syncthreads();
+        part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    uint32_t run = threadIdx.x ? part[threadIdx.x - 1] : 0;
+    for (uint64_t j = lo; j < hi; j++) {
+        uint32_t dgt = (uint32_t)(j / nblocks), b = (uint32_t)(j % nblocks);
+        uint64_t idx = (uint64_t)b * 256 + dgt;
+        uint32_t c = blockhist[idx];
+        blockhist[idx] = run;
+        if (b == 0) totals[dgt] = run;
+        run += c;
+    }
+    __syncthreads();
+    for (uint32_t dgt = nb + threadIdx.x; dgt <= 256; dgt += 1024) totals[dgt] = part[1023];
+}
+
+struct ActPerm {
+    uint32_t *out;
+    __device__ void operator()(uint32_t item, uint32_t dg, uint32_t global_pos, uint32_t rank_in_bucket) const { out[global_pos] = item; }
+    __device__ void dropped(uint32_t item) const {}
+};
+struct ActAdmit {   // capacity rule of MultiLevelQueue.Push (queue.go:101-103), evaluated in arrival order
+    const uint64_t *pending; const int64_t *max_size; const uint8_t *bucket_in; uint8_t *bucket_out; triage_result *results;
+    __device__ void operator()(uint32_t item, uint32_t dg, uint32_t global_pos, uint32_t rank_in_bucket) const {
+        int64_t cap = max_size[dg];
+        bool ok = cap <= 0 || (int64_t)(pending[dg] + rank_in_bucket) < cap;
+        if (!ok) {
+            uint8_t *r = reinterpret_cast<uint8_t *>(results + item);
+            r[4] = 0;                 // accepted
+            r[5] = TRIAGE_E_FULL;     // admit
+            bucket_out[item] = 0xFF;
+        } else bucket_out[item] = bucket_in[item];
+    }
+    __device__ void dropped(uint32_t item) const { bucket_out[item] = bucket_in[item]; }
+};
+
+template <class Dig, class Act>
+__global__ void __launch_bounds__(kOrderBlock) split_scatter_kernel(Dig dig, Act act, const uint32_t *__restrict__ perm_in, uint32_t n,
+                                                                   const uint32_t *__restrict__ blockhist, const uint32_t *__restrict__ totals) {
+    __shared__ uint32_t wh[kOrderBlock / 32][256];   // per-warp digit counts -> exclusive prefix over warps
+    const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    for (uint32_t i = tid; i < (kOrderBlock / 32) * 256; i += kOrderBlock) (&wh[0][0])[i] = 0;
+    __syncthreads();
+    uint32_t k = blockIdx.x * kOrderBlock + tid;
+    uint32_t item = 0, dg = 256;
+    if (k < n) { item = perm_in ? perm_in[k] : k; dg = dig(item); }
+    uint32_t peers = __match_any_sync(0xFFFFFFFFu, dg);
+    uint32_t rank = __popc(peers & ((1u << lane) - 1u));
+    if (dg < 256 && rank == 0) wh[warp][dg] = __popc(peers);
+    __syncthreads();
+    if (tid < 256) {
+        uint32_t run = 0;
+#pragma unroll 4
+        for (uint32_t w = 0; w < kOrderBlock / 32; w++) { uint32_t c = wh[w][tid]; wh[w][tid] = run; run += c; }
+    }
+    __syncthreads();
+    if (dg < 256) {
+        uint32_t base = blockhist[(uint64_t)blockIdx.x * 256 + dg];
+        uint32_t local = wh[warp][dg] + rank;
+        act(item, dg, base + local, base - totals[dg] + local);
+    } else if (k < n) {
+        act.dropped(item);
+    }
+}
+
+template <class Dig, class Act>
+static cudaError_t run_split(Dig dig, Act act, const uint32_t *perm_in, uint32_t n, uint32_t nb, OrderScratch sc, cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    uint32_t nblocks = (n + kOrderBlock - 1) / kOrderBlock;
+    if (nblocks > sc.nblocks_cap) return cudaErrorInvalidValue;
+    split_hist_kernel<Dig><<<nblocks, kOrderBlock, 0, s>>>(dig, perm_in, n, sc.blockhist);
+    split_scan_kernel<<<1, 1024, 0, s>>>(sc.blockhist, nblocks, nb, sc.totals);
+    split_scatter_kernel<Dig, Act><<<nblocks, kOrderBlock, 0, s>>>(dig, act, perm_in, n, sc.blockhist, sc.totals);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_admit(const uint8_t *bucket_in, uint8_t *bucket_out, triage_result *results, uint32_t n,
+                         const uint64_t *pending_dev, const int64_t *max_size_dev, int32_t single_queue, OrderScratch sc,
+                         cudaStream_t s) {
+    // pending / max_size are indexed by level-1 (digit of DigLevel); a single target queue uses index 0
+    return run_split(DigLevel{bucket_in, single_queue ? 8u : 2u}, ActAdmit{pending_dev, max_size_dev, bucket_in, bucket_out, results},
+                     nullptr, n, 4, sc, s);
+}
+
+__global__ void copy_totals_kernel(const uint32_t *totals, uint32_t *out) {
+    uint32_t i = threadIdx.x;   // 256 threads; totals[d] are exclusive offsets, totals[256] the grand total
+    uint32_t nxt = totals[i + 1];
+    out[i] = nxt - totals[i];
+}
+
+cudaError_t launch_partition_u8(const uint8_t *digits, const uint32_t *perm_in, uint32_t n, uint32_t n_buckets, bool drop_ff,
+                                uint32_t *perm_out, uint32_t *bucket_counts_dev, OrderScratch sc, cudaStream_t s) {
+    if (n == 0) {
+        if (bucket_counts_dev) return cudaMemsetAsync(bucket_counts_dev, 0, 256 * sizeof(uint32_t), s);
+        return cudaSuccess;
+    }
+    cudaError_t e = run_split(DigU8{digits, drop_ff}, ActPerm{perm_out}, perm_in, n, n_buckets, sc, s);
+    if (e != cudaSuccess) return e;
+    if (bucket_counts_dev) copy_totals_kernel<<<1, 256, 0, s>>>(sc.totals, bucket_counts_dev);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_partition_key(const uint64_t *keys, uint32_t shift, const uint32_t *perm_in, uint32_t n, uint32_t *perm_out,
+                                 OrderScratch sc, cudaStream_t s) {
+    return run_split(DigKey{keys, shift}, ActPerm{perm_out}, perm_in, n, 256, sc, s);
+}
+
+__global__ void __launch_bounds__(256) key_digit_hist_kernel(const uint64_t *__restrict__ keys, const uint32_t *__restrict__ perm, uint32_t n,
+                                                             uint32_t *__restrict__ hist) {
+    __shared__ uint32_t h[8 * 256];
+    for (uint32_t i = threadIdx.x; i < 8 * 256; i += blockDim.x) h[i] = 0;
+    __syncthreads();
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        uint64_t key = keys[perm ? perm[k] : k];
+#pragma unroll
+        for (int b = 0; b < 8; b++) atomicAdd(&h[b * 256 + ((key >> (8 * b)) & 0xFF)], 1u);
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < 8 * 256; i += blockDim.x) if (h[i]) atomicAdd(&hist[i], h[i]);
+}
+
+cudaError_t launch_key_digit_hist(const uint64_t *keys, const uint32_t *perm, uint32_t n, uint32_t *hist, cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    uint32_t blocks = (n + 255) / 256;
+    if (blocks > 1184) blocks = 1184;
+    key_digit_hist_kernel<<<blocks, 256, 0, s>>>(keys, perm, n, hist);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------ multi-GPU merge ---
+__global__ void build_run_kernel(const uint32_t *__restrict__ order, uint32_t n_adm, const uint8_t *__restrict__ bucket,
+                                 const uint64_t *__restrict__ ts, uint64_t ts_base, uint64_t gidx_base,
+                                 uint64_t *__restrict__ run_keys, uint32_t *__restrict__ run_gidx) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_adm) return;
+    uint32_t item = order[k];
+    (void)bucket;
+    run_keys[k] = ts ? ts[item] : ts_base + item;
+    run_gidx[k] = (uint32_t)(gidx_base + item);
+}
+
+cudaError_t launch_build_run(const uint32_t *order, uint32_t n_adm, const uint8_t *bucket, const uint64_t *ts, uint64_t ts_base,
+                             uint64_t gidx_base, uint64_t *run_keys, uint32_t *run_gidx, cudaStream_t s) {
+    if (n_adm == 0) return cudaSuccess;
+    build_run_kernel<<<(n_adm + 255) / 256, 256, 0, s>>>(order, n_adm, bucket, ts, ts_base, gidx_base, run_keys, run_gidx);
+    return cudaGetLastError();
+}
+
+// per-rank header for the merge: [0] admitted, [1..16] bucket counts, [17..32] first key, [33..48] last key per bucket
+struct Counts16 { uint32_t c[16]; };
+__global__ void header_kernel(const uint64_t *__restrict__ run_keys, uint32_t n_adm, Counts16 cnt, uint64_t *__restrict__ header) {
+    uint32_t b = threadIdx.x;
+    if (b == 0) header[0] = n_adm;
+    if (b < 16) {
+        uint32_t start = 0;
+        for (uint32_t i = 0; i < b; i++) start += cnt.c[i];
+        header[1 + b] = cnt.c[b];
+        header[17 + b] = cnt.c[b] ? run_keys[start] : 0;
+        header[33 + b] = cnt.c[b] ? run_keys[start + cnt.c[b] - 1] : 0;
+    }
+}
+
+cudaError_t launch_header(const uint64_t *run_keys, uint32_t n_adm, const uint32_t *counts16_host, uint64_t *header_dev, cudaStream_t s) {
+    Counts16 c;
+    for (int i = 0; i < 16; i++) c.c[i] = counts16_host[i];
+    header_kernel<<<1, 32, 0, s>>>(run_keys, n_adm, c, header_dev);
+    return cudaGetLastError();
+}
+
+// fast merge: the ranks' key ranges do not interleave inside any bucket, so element j of (rank, bucket) goes to
+// dst[rank][bucket] + (j - lstart[rank][bucket])
+__global__ void __launch_bounds__(256) concat_kernel(const uint64_t *__restrict__ all_keys, const uint32_t *__restrict__ all_gidx,
+                                                     ConcatTables t, uint32_t *__restrict__ order_out) {
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t q = blockIdx.y;
+    if (j >= t.cnt[q]) return;
+    uint64_t idx = (uint64_t)q * t.cap + j;
+    uint32_t b = 0;
+#pragma unroll
+    for (uint32_t i = 1; i < 16; i++) if (j >= t.lstart[q][i]) b = i;   // lstart is non-decreasing; the last i wins
+    order_out[t.dst[q][b] + (j - t.lstart[q][b])] = all_gidx[idx];
+}
+
+cudaError_t launch_concat(const uint64_t *all_keys, const uint32_t *all_gidx, const ConcatTables &t, uint32_t *order_out, cudaStream_t s) {
+    dim3 grid((t.cap + 255) / 256, t.n_ranks);
+    concat_kernel<<<grid, 256, 0, s>>>(all_keys, all_gidx, t, order_out);
+    return cudaGetLastError();
+}
+
+// general merge: element j of run q goes to  j + sum over other runs of (#keys < mine, or <= mine for
+// lower-numbered runs), which keeps equal keys in rank order (lower rank = earlier sequence numbers)
+__global__ void __launch_bounds__(256) merge_strided_kernel(const uint64_t *__restrict__ all_keys, const uint32_t *__restrict__ all_gidx,
+                                                            ConcatTables t, uint32_t *__restrict__ order_out) {
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t q = blockIdx.y;
+    if (j >= t.cnt[q]) return;
+    const uint64_t key = all_keys[(uint64_t)q * t.cap + j];
+    uint32_t b = 0;
+#pragma unroll
+    for (uint32_t i = 1; i < 16; i++) if (j >= t.lstart[q][i]) b = i;
+    // destination = start of bucket b in the merged order + my rank inside the bucket across all runs
+    uint64_t pos = t.dst[0][b] + (j - t.lstart[q][b]);
+    for (uint32_t o = 0; o < t.n_ranks; o++) {
+        if (o == q) continue;
+        const uint64_t *k = all_keys + (uint64_t)o * t.cap;
+        const uint32_t ob = t.lstart[o][b];
+        const uint32_t oe = b < 15 ? t.lstart[o][b + 1] : t.cnt[o];
+        uint32_t lo = ob, hi = oe;
+        const bool le = o < q;
+        while (lo < hi) {
+            uint32_t mid = (lo + hi) >> 1;
+            uint64_t km = k[mid];
+            if (le ? km <= key : km < key) lo = mid + 1; else hi = mid;
+        }
+        pos += lo - ob;
+    }
+    order_out[pos] = all_gidx[(uint64_t)q * t.cap + j];
+}
+
+cudaError_t launch_merge_strided(const uint64_t *all_keys, const uint32_t *all_gidx, const ConcatTables &t, uint32_t *order_out, cudaStream_t s) {
+    dim3 grid((t.cap + 255) / 256, t.n_ranks);
+    merge_strided_kernel<<<grid, 256, 0, s>>>(all_keys, all_gidx, t, order_out);
+    return cudaGetLastError();
+}
+
+}  // namespace triage

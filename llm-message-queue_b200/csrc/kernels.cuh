@@ -1,0 +1,96 @@
+// kernels.cuh — launch wrappers of the sm_100a kernels (kernels.cu).  Internal to the library.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/triage.h"
+#include "scan_core.cuh"
+
+namespace triage {
+
+// compile-time geometry of the scan: NT lanes per tile, each owning C contiguous bytes.
+// C is an odd multiple of 16 so that the lanes' 128-bit shared loads are bank-conflict free.
+constexpr int kScanThreads = 1024;
+constexpr int kScanChunk = 48;
+constexpr uint32_t kScanTile = kScanThreads * kScanChunk;
+constexpr uint32_t kListCap = 2048;   // message starts per tile kept in shared memory (else global offsets)
+constexpr uint32_t kMaxWarm = 256;
+
+struct DeviceDfa {
+    const uint16_t *table;       // n_states * 256
+    const EventPacked *events;   // n_events
+    const uint8_t *eom;          // 256 (padded)
+    uint32_t n_states, n_events, warm, start_state, neutral_state;
+};
+
+struct ScanArgs {
+    const uint8_t *bytes;        // 16-byte aligned, readable up to round_up(total, 16)
+    const uint64_t *offsets;     // n + 1
+    uint64_t total;
+    uint32_t n;
+    uint32_t *counters;          // n * CNT_STRIDE, zeroed
+    uint32_t *tile_first;        // ntiles + 1 (scratch)
+    uint32_t ntiles;
+};
+
+struct FinalizeArgs {
+    const uint32_t *counters;
+    const triage_meta *meta;
+    const uint64_t *offsets;
+    const uint64_t *ts;          // nullable: arrival order is the time order
+    uint32_t n;
+    int32_t default_prio;
+    int32_t rules_on;
+    int32_t single_queue;        // 1: whole batch goes to one queue, bucket = min(int(Priority), 15)
+    triage_result *results;
+    uint8_t *bucket;             // per message: (level-1)*4 + (final-1), or 0xFF when the level queue does not exist
+    uint32_t *flags;             // [0] |= 1 when ts is not non-decreasing in arrival order
+};
+
+size_t scan_smem_bytes(const DeviceDfa &d);
+cudaError_t launch_tile_index(const ScanArgs &a, cudaStream_t s);
+cudaError_t launch_scan(const ScanArgs &a, const DeviceDfa &d, int sm_count, cudaStream_t s);
+cudaError_t launch_finalize(const FinalizeArgs &a, cudaStream_t s);
+
+// ---- ordering --------------------------------------------------------------------------------
+// Stable partition of items by an 8-bit digit.  perm_in == nullptr means the identity (arrival
+// order).  Items whose digit is 0xFF when `drop_ff` are left out.
+struct OrderScratch {
+    uint32_t *blockhist;   // nblocks * 256
+    uint32_t *totals;      // 256 + 1
+    uint32_t nblocks_cap;
+};
+constexpr int kOrderBlock = 1024;
+
+// level ranks -> admission (capacity), writes accepted/admit into results and turns the bucket of a
+// rejected message into 0xFF.  pending[4] = current queue lengths, max_size <= 0: unbounded.
+cudaError_t launch_admit(const uint8_t *bucket_in, uint8_t *bucket_out, triage_result *results, uint32_t n,
+                         const uint64_t *pending_dev, const int64_t *max_size_dev, int32_t single_queue, OrderScratch sc,
+                         cudaStream_t s);
+// digits: u8 per ITEM INDEX (not per position); out_perm[k] = item index at rank k.
+cudaError_t launch_partition_u8(const uint8_t *digits, const uint32_t *perm_in, uint32_t n, uint32_t n_buckets,
+                                bool drop_ff, uint32_t *perm_out, uint32_t *bucket_counts_dev /* 256 */,
+                                OrderScratch sc, cudaStream_t s);
+// one LSD pass over 64-bit keys: digit = (key[item] >> shift) & 0xFF
+cudaError_t launch_partition_key(const uint64_t *keys, uint32_t shift, const uint32_t *perm_in, uint32_t n,
+                                 uint32_t *perm_out, OrderScratch sc, cudaStream_t s);
+// per-digit-position histograms of keys[perm] over all 8 byte positions (decides which passes to run)
+cudaError_t launch_key_digit_hist(const uint64_t *keys, const uint32_t *perm, uint32_t n, uint32_t *hist /* 8*256, zeroed */,
+                                  cudaStream_t s);
+// run (time key, gidx) for the multi-GPU merge, in dequeue order (bucket-major)
+cudaError_t launch_build_run(const uint32_t *order, uint32_t n_adm, const uint8_t *bucket, const uint64_t *ts,
+                             uint64_t ts_base_if_null, uint64_t gidx_base, uint64_t *run_keys, uint32_t *run_gidx,
+                             cudaStream_t s);
+// ---- multi-GPU merge of the all-gathered runs (rank q's run at [q*cap, q*cap + cnt[q])) ----
+struct ConcatTables {
+    uint32_t cap;                 // stride between ranks in the gathered buffers
+    uint32_t n_ranks;
+    uint32_t cnt[8];              // admitted per rank
+    uint32_t dst[8][16];          // destination of the first element of (rank, bucket)
+    uint32_t lstart[8][16];       // start of bucket inside the rank's run
+};
+cudaError_t launch_header(const uint64_t *run_keys, uint32_t n_adm, const uint32_t *counts16_host, uint64_t *header_dev, cudaStream_t s);
+cudaError_t launch_concat(const uint64_t *all_keys, const uint32_t *all_gidx, const ConcatTables &t, uint32_t *order_out, cudaStream_t s);
+cudaError_t launch_merge_strided(const uint64_t *all_keys, const uint32_t *all_gidx, const ConcatTables &t, uint32_t *order_out, cudaStream_t s);
+
+}  // namespace triage

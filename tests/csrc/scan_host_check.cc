@@ -1,0 +1,96 @@
+// scan_host_check.cc — TEST HARNESS ONLY (never linked into libtriage_b200.so).
+// Compiles the product's dictionary compiler (csrc/dfa_build.cc) and the per-lane scan body
+// (csrc/scan_core.cuh) with g++ and walks every lane of every tile sequentially, so the
+// automaton and the tile/chunk/boundary logic can be checked against the oracle on a CPU box.
+#include <cstdint>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../llm-message-queue_b200/csrc/dfa_build.h"
+#include "../../llm-message-queue_b200/csrc/scan_core.cuh"
+
+using namespace triage;
+
+extern "C" {
+
+// dict: n_pat entries, literals concatenated in lits with lens[]; returns 0 ok, 4 on build error
+int hostcheck_scan(const uint8_t *prios, const uint8_t *cis, const uint32_t *lens, const uint8_t *lits, uint32_t n_pat,
+                   const uint64_t *offsets, const uint8_t *bytes, uint32_t n_msgs,
+                   uint32_t nt, uint32_t chunk, int use_abs_list,
+                   uint32_t *counters /* n_msgs * 8 */, uint32_t *info /* states, unmin, warm, events */, char *err, uint32_t errcap)
+{
+    std::vector<DictEntry> dict;
+    size_t o = 0;
+    for (uint32_t i = 0; i < n_pat; i++) {
+        dict.push_back({prios[i], cis[i] != 0, std::string(reinterpret_cast<const char *>(lits + o), lens[i])});
+        o += lens[i];
+    }
+    Dfa dfa;
+    std::string e = build_dfa(dict, &dfa);
+    if (!e.empty()) { std::strncpy(err, e.c_str(), errcap - 1); err[errcap - 1] = 0; return 4; }
+    info[0] = dfa.n_states; info[1] = dfa.n_states_unminimised; info[2] = dfa.warm_bytes; info[3] = (uint32_t)dfa.events.size();
+    if (n_msgs == 0) return 0;
+    std::vector<EventPacked> ev(dfa.events.size());
+    for (size_t i = 0; i < dfa.events.size(); i++) {
+        const EventVec &v = dfa.events[i];
+        ev[i] = {uint32_t(v.kw[0]) | uint32_t(v.kw[1]) << 16, uint32_t(v.kw[2]) | uint32_t(v.kw[3]) << 16,
+                 uint32_t(v.pos) | uint32_t(v.neg) << 8 | uint32_t(v.question) << 16, 0};
+    }
+    std::memset(counters, 0, sizeof(uint32_t) * 8 * n_msgs);
+    uint64_t total = offsets[n_msgs];
+    uint64_t tile = uint64_t(nt) * chunk;
+    int32_t warm = (int32_t)dfa.warm_bytes;
+    std::vector<uint8_t> stage_raw(tile + warm + 64);
+    uint8_t *stage = stage_raw.data();
+    while (reinterpret_cast<uintptr_t>(stage) & 15) stage++;
+    uint64_t ntiles = (total + tile - 1) / tile;
+    for (uint64_t t = 0; t < ntiles; t++) {
+        uint64_t ts = t * tile, te = std::min(total, ts + tile);
+        // stage [ts - warm, te)
+        std::memset(stage, 0xEE, tile + warm);
+        uint64_t cs = ts >= (uint64_t)warm ? ts - warm : 0;
+        std::memcpy(stage + (cs - (ts - warm)), bytes + cs, te - cs);
+        // messages intersecting the tile: upper_bound(offsets, ts) - 1 .. first boundary >= te
+        uint32_t lo = 0, hi = n_msgs + 1;
+        while (lo < hi) { uint32_t mid = (lo + hi) / 2; if (offsets[mid] > ts) hi = mid; else lo = mid + 1; }
+        uint32_t mlo = lo - 1, mhi = mlo;
+        while (offsets[mhi + 1] < te) mhi++;
+        std::vector<int32_t> list;
+        for (uint32_t m = mlo; m <= mhi + 1; m++) {
+            int64_t r = (int64_t)offsets[m] - (int64_t)ts;
+            const int64_t lim = 1 << 30;
+            list.push_back((int32_t)(r < -lim ? -lim : (r > lim ? lim : r)));
+        }
+        LaneCtx c;
+        c.tbl = dfa.table.data(); c.events = ev.data(); c.eom = dfa.eom.data(); c.stage = stage;
+        c.list = use_abs_list ? nullptr : list.data(); c.list_abs = offsets; c.tile_start = (int64_t)ts;
+        c.list_n = (uint32_t)list.size(); c.msg_lo = mlo; c.counters = counters; c.warm = warm;
+        c.start_state = dfa.start_state; c.neutral_state = dfa.neutral_state;
+        int32_t tile_len = (int32_t)(te - ts);
+        for (uint32_t l = 0; l < nt; l++) {
+            int32_t ch = (int32_t)(l * chunk);
+            if (ch >= tile_len) break;
+            int32_t ce = std::min<int32_t>(ch + (int32_t)chunk, tile_len);
+            uint32_t hm = 0, hw = 0;
+            lane_scan(c, ch, ce, &hm, &hw);
+            if (hw) counters[(uint64_t)hm * 8 + CNT_WORDS] += hw;
+        }
+    }
+    return 0;
+}
+
+int hostcheck_parse(const char *s, uint32_t len, int *ci, char *lit, uint32_t cap, uint32_t *lit_len)
+{
+    bool c; std::string l, e;
+    if (!parse_regex_literal(s, len, &c, &l, &e)) return 4;
+    if (l.size() > cap) return 5;
+    *ci = c; std::memcpy(lit, l.data(), l.size()); *lit_len = (uint32_t)l.size();
+    return 0;
+}
+
+int hostcheck_bordered(const uint8_t *lit, uint32_t len, int ci)
+{
+    return literal_is_bordered(std::string(reinterpret_cast<const char *>(lit), len), ci != 0) ? 1 : 0;
+}
+}

@@ -1,0 +1,49 @@
+"""Test helper: builds and binds tests/csrc/libscan_host_check.so (g++ build of the product's
+dictionary compiler + per-lane scan body).  TEST HARNESS — not a product code path."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+SRC = [os.path.join(HERE, "csrc", "scan_host_check.cc"),
+       os.path.join(ROOT, "llm-message-queue_b200", "csrc", "dfa_build.cc")]
+DEPS = SRC + [os.path.join(ROOT, "llm-message-queue_b200", "csrc", f) for f in ("dfa_build.h", "scan_core.cuh")]
+LIB = os.path.join(HERE, "csrc", "libscan_host_check.so")
+
+DEFAULT_DICT = [(1, True, b"immediate"), (1, True, b"emergency"), (1, True, b"asap"), (1, True, b"right now"),
+                (2, True, b"urgent"), (2, True, b"important"), (2, True, b"priority"), (2, True, b"critical"),
+                (2, True, b"soon")]
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB) or any(os.path.getmtime(s) > os.path.getmtime(LIB) for s in DEPS):
+            subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", LIB] + SRC)
+        _lib = C.CDLL(LIB)
+        _lib.hostcheck_scan.restype = C.c_int
+    return _lib
+
+
+def scan(dict_entries, offsets, data, nt=64, chunk=48, use_abs_list=False):
+    """returns (counters[n,8], info dict) or raises ValueError(build error)"""
+    n = len(offsets) - 1
+    prios = np.array([d[0] for d in dict_entries], np.uint8)
+    cis = np.array([1 if d[1] else 0 for d in dict_entries], np.uint8)
+    lens = np.array([len(d[2]) for d in dict_entries], np.uint32)
+    lits = np.frombuffer(b"".join(d[2] for d in dict_entries) or b"\0", np.uint8)
+    counters = np.zeros((max(n, 1), 8), np.uint32)
+    info = np.zeros(4, np.uint32)
+    err = C.create_string_buffer(256)
+    buf = data if len(data) else np.zeros(1, np.uint8)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    rc = lib().hostcheck_scan(p(prios), p(cis), p(lens), p(lits), len(dict_entries), p(offsets), p(buf), n,
+                              nt, chunk, 1 if use_abs_list else 0, p(counters), p(info), err, 256)
+    if rc != 0:
+        raise ValueError(err.value.decode())
+    return counters[:n], dict(states=int(info[0]), unminimised=int(info[1]), warm=int(info[2]), events=int(info[3]))

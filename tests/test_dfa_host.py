@@ -1,0 +1,81 @@
+"""CPU checks of the product's dictionary compiler and per-lane scan body (the same source the CUDA kernel
+compiles, built with g++ by tests/hostcheck.py) against the oracle: every counter of every message, for several
+tile geometries including the shipped one, both message-list modes, and custom dictionaries."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle import c_oracle as co
+from tests import hostcheck as hc
+
+
+def _expected(d, contents):
+    exp = np.zeros((len(contents), 8), np.uint32)
+    for i, c in enumerate(contents):
+        if not c:
+            continue
+        sc = co.scores(d, c)
+        w, p, n, q = co.analyze(c)
+        exp[i] = [w, sc[1], sc[2], sc[3], sc[4], p, n, int(q)]
+    return exp
+
+
+@pytest.mark.parametrize("nt,chunk", [(4, 16), (1, 48), (7, 80), (1024, 48)])
+def test_edge_cases_all_geometries(golden_dir, nt, chunk):
+    cases = json.load(open(os.path.join(golden_dir, "edge_cases.json")))
+    contents = [bytes.fromhex(e["content_hex"]) for e in cases]
+    off, data = co.pack(contents)
+    exp = _expected(co.Dict(), contents)
+    for abs_list in (False, True):
+        cnt, info = hc.scan(hc.DEFAULT_DICT, off, data, nt=nt, chunk=chunk, use_abs_list=abs_list)
+        assert info["states"] <= 256 and info["warm"] == 16
+        bad = np.nonzero((cnt != exp).any(axis=1))[0]
+        assert len(bad) == 0, (bad[:5], [contents[i][:40] for i in bad[:5]], cnt[bad[:5]], exp[bad[:5]])
+
+
+@pytest.mark.parametrize("seed,n,lo,hi,edge", [(99, 3000, 1, 600, 2000), (5, 400, 2000, 9000, 500), (6, 20000, 0, 40, 3000)])
+def test_generated_messages(seed, n, lo, hi, edge):
+    off, data, meta, ts = co.generate(seed, n, lo, hi, edge=edge)
+    contents = [bytes(data[int(off[i]):int(off[i + 1])]) for i in range(n)]
+    exp = _expected(co.Dict(), contents)
+    for nt, chunk in ((32, 48), (1024, 48)):
+        cnt, _ = hc.scan(hc.DEFAULT_DICT, off, data, nt=nt, chunk=chunk)
+        bad = np.nonzero((cnt != exp).any(axis=1))[0]
+        assert len(bad) == 0, (nt, chunk, bad[:5], cnt[bad[:5]], exp[bad[:5]])
+
+
+def test_custom_dictionary_mixed_case_sensitivity_and_utf8():
+    entries = hc.DEFAULT_DICT + [(4, False, b"Bulk"), (4, False, "批量".encode()), (3, True, b"ticket"), (1, False, b"P0"),
+                                 (2, True, b"risk now"), (4, True, b"now"), (2, False, b"right now")]
+    d = co.Dict()
+    for p, ci, lit in entries[len(hc.DEFAULT_DICT):]:
+        assert d.add(p, lit, ci) == 0
+    contents = [b"Bulk bulk BULK", "批量 批量x".encode(), b"TICKET ticket Ticket", b"P0 p0", b"RISK NOW ris\xe2\x84\xaa now right now Right now",
+                b"nownow right nowhere", b"x" * 100 + b"right now" + b"y" * 100, b"\xe6\x89\xb9\xe9\x87", b"ris\xe2\x84\xaanow"]
+    off, data = co.pack(contents)
+    exp = _expected(d, contents)
+    cnt, info = hc.scan(entries, off, data, nt=8, chunk=16)
+    assert (cnt == exp).all(), (cnt, exp)
+
+
+def test_long_pattern_widens_the_warm_up():
+    lit = b"this is a rather long literal pattern x"
+    entries = hc.DEFAULT_DICT + [(1, True, lit)]
+    d = co.Dict()
+    d.add(1, lit, True)
+    contents = [b"z" * k + lit.upper() + b" tail" for k in range(0, 70, 3)]
+    off, data = co.pack(contents)
+    cnt, info = hc.scan(entries, off, data, nt=4, chunk=16)
+    assert info["warm"] >= len(lit) - 1 and info["warm"] % 16 == 0
+    assert (cnt == _expected(d, contents)).all()
+
+
+def test_unsupported_dictionaries_are_refused():
+    with pytest.raises(ValueError):
+        hc.scan(hc.DEFAULT_DICT + [(2, False, b"\xff")], *co.pack([b"x"]))
+    # enough distinct long patterns to overflow the 256-state dense table
+    many = hc.DEFAULT_DICT + [(4, False, (f"w{i:03d}" * 3).encode()) for i in range(40)]
+    with pytest.raises(ValueError):
+        hc.scan(many, *co.pack([b"x"]))
