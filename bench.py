@@ -1,0 +1,308 @@
+#!/usr/bin/env python
+"""bench.py — msgs/sec of the preprocess + priority-order hot path on N B200s (one process per GPU).
+
+  python bench.py --gpus 1 --steps K --warmup W            # N=1
+  torchrun ... bench.py --gpus N --steps K --warmup W      # N>1: one rank per GPU, NCCL merge of sorted runs
+  python bench.py --impl reference ...                     # the reference arm: CPU restatement on the host cores
+
+A "step" is one pass of the hot path over one batch of synthetic messages: DFA scan of the arena, fused
+score->label->bucket, stable multi-split into the dequeue order, and for N>1 the all-gather + merge of the
+ranks' sorted runs.  Workload at every N: BASELINE.json configs[1] per GPU (1 Mi messages, 256 B-4 KB, 4 levels)
+=> weak scaling.  `value` is measured with the batch resident in HBM; `e2e` goes through the host-buffer C-ABI call
+(triage_submit) with pinned host buffers, H2D and D2H inside the timed region.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "msgs_per_sec_preprocess_plus_priority_order"
+N_PER_GPU = 1 << 20
+LEN_LO, LEN_HI = 256, 4096
+SEED = 0xC0FFEE02
+
+
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self._stop = threading.Event()
+        self._t = None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def start(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join(timeout=6)
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            for k, nm in enumerate(names):
+                if len(r) > 3 + k and r[3 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(self.rows)}
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def scan_traffic_from_profile():
+    """dram bytes per scan launch from the committed ncu capture, if any (profiles/scan_traffic.json)."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "scan_traffic.json")))
+    except Exception:
+        return None
+
+
+def cpu_reference_step(co, d, sample, threads):
+    off, data, meta, ts = sample
+    t0 = time.perf_counter()
+    co.pipeline(d, off, data, meta, ts, nthreads=threads)
+    return time.perf_counter() - t0
+
+
+def make_cpu_sample(co, n):
+    return co.generate(SEED + 77, n, LEN_LO, LEN_HI, edge=50)
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the CPU restatement of the Go path (oracle, kind "port": the Go reference cannot be built in
+    this image) timed on the host cores with all the threads it can use; bounded sample per step."""
+    if rank != 0:
+        return
+    from oracle import c_oracle as co
+    threads = os.cpu_count() or 1
+    d = co.Dict()
+    probe = make_cpu_sample(co, 2000)
+    t = cpu_reference_step(co, d, probe, threads)
+    rate = 2000 / max(t, 1e-6)
+    total_steps = args.steps + args.warmup
+    n = int(min(200000, max(2000, rate * min(20.0, 120.0 / max(total_steps, 1)))))
+    sample = make_cpu_sample(co, n)
+    for _ in range(args.warmup):
+        cpu_reference_step(co, d, sample, threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_reference_step(co, d, sample, threads)
+    dt = time.perf_counter() - t0
+    value = n * args.steps / dt
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "msgs/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1000 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": workload_config(args.gpus),
+            "cpu_baseline": {"value": value, "unit": "msgs/s", "cores": threads, "kind": "port",
+                             "sample": f"{n} messages of the same generator (len U[{LEN_LO},{LEN_HI}]) per step; preprocess on {threads} threads, "
+                                       "container/heap push+drain on 1 thread as the reference's mutex serialises it"},
+            "e2e": {"value": value, "unit": "msgs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(n_gpus):
+    return {"workload": "BASELINE configs[1] per GPU: 1Mi messages, content U[256,4096] bytes, 4 priority levels, default 9-keyword dictionary",
+            "messages_per_gpu": N_PER_GPU, "global_messages": N_PER_GPU * n_gpus,
+            "parallelism": f"shard{n_gpus}" if n_gpus > 1 else "single",
+            "l2_policy": "inputs (~2.3 GB per GPU) larger than the 126 MB L2; no flush needed",
+            "timestamps": "engine-stamped, strictly increasing in arrival order"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--messages", type=int, default=N_PER_GPU, help="messages per GPU (default: the BASELINE config)")
+    ap.add_argument("--skip-cpu", action="store_true")
+    ap.add_argument("--skip-e2e", action="store_true")
+    args = ap.parse_args()
+    rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    args.warmup = max(args.warmup, 3)
+
+    import torch
+    import torch.distributed as dist
+    import llm_message_queue_b200 as mq
+    from oracle import c_oracle as co   # generator + (rank 0, N=1) the timed CPU baseline
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    n = args.messages
+    # ---- synthetic batch of this rank (own seed => different content per rank) ----
+    off, data, meta, _ = co.generate(SEED + rank, n, LEN_LO, LEN_HI, edge=50)
+    total = int(off[-1])
+    eng = mq.Engine(device=local)
+    info = eng.dict_info()
+
+    pad = np.zeros(((total + 31) // 16) * 16, np.uint8)
+    pad[:total] = data
+    d_bytes = torch.from_numpy(pad).to(dev)
+    d_off = torch.from_numpy(off.view(np.int64)).to(dev)
+    d_meta = torch.from_numpy(meta.view(np.uint8).reshape(n, 16)).to(dev)
+    d_res = torch.zeros((n, 16), dtype=torch.uint8, device=dev)
+    d_ord = torch.zeros(n, dtype=torch.int32, device=dev)
+    d_gord = torch.zeros(n * world, dtype=torch.int32, device=dev) if world > 1 else None
+    rank_base = (np.arange(world, dtype=np.uint64) * np.uint64(n))
+    if world > 1:
+        uid = [mq.Engine.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        eng.comm_init(world, rank, uid[0])
+    torch.cuda.synchronize()
+
+    def step():
+        adm = eng.submit_device(d_off.data_ptr(), d_bytes.data_ptr(), total, d_meta.data_ptr(), None, n, d_res.data_ptr(), d_ord.data_ptr())
+        t = eng.timings()
+        if world > 1:
+            eng.merge_allgather(rank_base, d_gord.data_ptr(), n * world)
+        return adm, t
+
+    for _ in range(args.warmup):
+        step()
+    sampler = ClockSampler(local)
+    barrier(); torch.cuda.synchronize()
+    if rank == 0:
+        sampler.start()
+    eng.event_record(0)
+    t_wall = time.perf_counter()
+    scan_ms, fin_ms, ord_ms, launches, passes = [], [], [], 0, 0
+    for _ in range(args.steps):
+        adm, t = step()
+        scan_ms.append(t["scan_ms"]); fin_ms.append(t["finalize_ms"]); ord_ms.append(t["order_ms"])
+        launches += t["launches"] + (5 if world > 1 else 0)
+        passes = t["order_passes"]
+    eng.event_record(1)
+    dev_ms = eng.event_elapsed_ms(0, 1)
+    torch.cuda.synchronize(); barrier()
+    wall_ms = 1000 * (time.perf_counter() - t_wall)
+    clocks = sampler.stop() if rank == 0 else None
+    tt = torch.tensor([dev_ms, wall_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    dev_ms_max, wall_ms_max = float(tt[0]), float(tt[1])
+    ms_per_step = dev_ms_max / args.steps
+    value = n * world / (ms_per_step / 1000)
+
+    # ---- end to end through the host-buffer C ABI call (pinned host arenas, H2D + D2H timed) ----
+    e2e = None
+    if not args.skip_e2e:
+        h_bytes = eng.host_array(len(pad)); h_bytes[:] = pad
+        h_off = eng.host_array(off.nbytes, np.uint64); h_off[:] = off
+        h_meta = eng.host_array(meta.nbytes, np.uint8).view(mq.META_DTYPE); h_meta[:] = meta
+        h_res = eng.host_array(n * 16, np.uint8).view(mq.RESULT_DTYPE)
+        import ctypes as C
+        lib = mq._capi.lib()
+        base = C.c_uint64()
+
+        def e2e_step():
+            rc = lib.triage_submit(eng._h, 0, h_off.ctypes.data, h_bytes.ctypes.data, h_meta.ctypes.data, None, n, h_res.ctypes.data, C.byref(base))
+            if rc != 0:
+                raise RuntimeError(lib.triage_last_error())
+        e2e_steps = max(2, min(args.steps, 5))
+        e2e_step(); eng.drain(n)
+        barrier(); torch.cuda.synchronize()
+        dts = []
+        for _ in range(e2e_steps):
+            t0 = time.perf_counter()
+            e2e_step()
+            dts.append(time.perf_counter() - t0)
+            eng.drain(n)          # empty the level queues (host bookkeeping, outside the timed call)
+        tt = torch.tensor([sum(dts) / len(dts)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e_s = float(tt[0])
+        adm_now = int(h_res["accepted"].sum())
+        e2e = {"value": n * world / e2e_s, "unit": "msgs/s", "h2d_bytes_per_step": int(total + 8 * (n + 1) + 16 * n),
+               "d2h_bytes_per_step": int(16 * n + 4 * adm_now), "ms_per_step": 1000 * e2e_s, "steps": e2e_steps,
+               "api": "triage_submit (C ABI, pinned host buffers from triage_host_alloc; H2D, kernels, D2H of results + order inside)"}
+
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        t_scan = sum(scan_ms) / len(scan_ms)
+        alg = total + 8 * (n + 1) + 32 * n     # sum(len) + offsets + 16 B meta in + 16 B result out
+        achieved = alg / (t_scan / 1000) / 1e9
+        traffic = scan_traffic_from_profile()
+        roofline = {"bound": "hbm", "kernel": "scan_kernel<1024,48>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                    "frac": achieved / peak, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg,
+                    "kernel_ms": t_scan, "traffic": traffic["dram_bytes_per_launch"] if traffic else None,
+                    "step_share": {"scan_ms": t_scan, "finalize_ms": sum(fin_ms) / len(fin_ms), "order_ms": sum(ord_ms) / len(ord_ms),
+                                   "step_ms": ms_per_step}}
+        cpu_baseline = None
+        if world == 1 and not args.skip_cpu:
+            threads = os.cpu_count() or 1
+            d = co.Dict()
+            probe = make_cpu_sample(co, 2000)
+            rate = 2000 / max(cpu_reference_step(co, d, probe, threads), 1e-6)
+            ns = int(min(200000, max(2000, rate * 12.0)))
+            sample = make_cpu_sample(co, ns)
+            dt = cpu_reference_step(co, d, sample, threads)
+            cpu_baseline = {"value": ns / dt, "unit": "msgs/s", "cores": threads, "kind": "port",
+                            "sample": f"{ns} messages of the same generator, one pass ({dt:.1f} s): C restatement of the Go path, "
+                                      f"preprocess on {threads} threads, container/heap push+drain on 1 thread"}
+        line = {"metric": METRIC, "value": value, "unit": "msgs/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+                "data": "synthetic", "config": workload_config(world) | {"messages_per_gpu": n, "global_messages": n * world,
+                                                                          "arena_bytes_per_gpu": total, "automaton_states": info["states"],
+                                                                          "order_passes": passes},
+                "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+                "timing": {"device_ms_total": dev_ms_max, "wall_ms_total": wall_ms_max, "admitted": adm}}
+        print(json.dumps(line), flush=True)
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -167,6 +167,9 @@ typedef struct {
     uint64_t scan_bytes;                            /* algorithmic bytes of the scan */
 } triage_timings;
 int32_t triage_last_timings(triage_engine *e, triage_timings *t);
+/* CUDA events on the engine's own stream (torch.cuda.Event cannot see it): slots 0..3 */
+int32_t triage_event_record(triage_engine *e, int32_t slot);
+int32_t triage_event_elapsed_ms(triage_engine *e, int32_t from_slot, int32_t to_slot, float *ms);
 
 /* -- multi-GPU: one engine per rank/GPU; the caller broadcasts the 128-byte id (rank 0 makes it). */
 int32_t triage_comm_unique_id(uint8_t id[128]);

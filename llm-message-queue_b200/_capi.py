@@ -89,6 +89,8 @@ _SIGS = {
     "triage_complete": (C.c_int32, [C.c_void_p, C.c_int32]),
     "triage_fail": (C.c_int32, [C.c_void_p, C.c_int32]),
     "triage_last_timings": (C.c_int32, [C.c_void_p, C.POINTER(Timings)]),
+    "triage_event_record": (C.c_int32, [C.c_void_p, C.c_int32]),
+    "triage_event_elapsed_ms": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_float)]),
     "triage_comm_unique_id": (C.c_int32, [C.c_void_p]),
     "triage_comm_init": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     "triage_merge_allgather": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
@@ -204,6 +206,21 @@ class Engine:
         t = Timings()
         _check(lib().triage_last_timings(self._h, C.byref(t)))
         return {k: getattr(t, k) for k, _ in Timings._fields_}
+
+    def event_record(self, slot: int):
+        _check(lib().triage_event_record(self._h, slot))
+
+    def event_elapsed_ms(self, a: int, b: int) -> float:
+        ms = C.c_float()
+        _check(lib().triage_event_elapsed_ms(self._h, a, b, C.byref(ms)))
+        return ms.value
+
+    def host_array(self, nbytes: int, dtype=np.uint8):
+        """numpy array over pinned host memory (triage_host_alloc); freed with the engine's process."""
+        p = C.c_void_p()
+        _check(lib().triage_host_alloc(C.byref(p), int(nbytes)))
+        buf = (C.c_uint8 * int(nbytes)).from_address(p.value)
+        return np.frombuffer(buf, dtype=np.uint8).view(dtype)
 
     # -- queues -------------------------------------------------------------
     def queue_create(self, max_size=0) -> int:

@@ -101,6 +101,7 @@ struct triage_engine {
     int max_smem_optin = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[6]{};
+    cudaEvent_t user_ev[4]{};
     int32_t default_prio = TRIAGE_PRIO_NORMAL;
     std::vector<DictEntry> dict;
     bool dict_dirty = true;
@@ -314,6 +315,7 @@ int32_t triage_create(const triage_opts *opts, triage_engine **out) {
     e->max_smem_optin = (int)prop.sharedMemPerBlockOptin;
     cudaError_t ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
     for (int i = 0; i < 6 && ce == cudaSuccess; i++) ce = cudaEventCreate(&e->ev[i]);
+    for (int i = 0; i < 4 && ce == cudaSuccess; i++) ce = cudaEventCreate(&e->user_ev[i]);
     if (ce == cudaSuccess) ce = cudaHostAlloc(reinterpret_cast<void **>(&e->h_small), (32 + 8 * 256) * sizeof(uint32_t), cudaHostAllocDefault);
     if (ce != cudaSuccess) { delete e; return fail(TRIAGE_E_CUDA, cudaGetErrorString(ce)); }
     e->q.resize(5);
@@ -337,6 +339,7 @@ void triage_destroy(triage_engine *e) {
     if (e->h_small) cudaFreeHost(e->h_small);
     if (e->h_header) cudaFreeHost(e->h_header);
     for (auto &ev : e->ev) if (ev) cudaEventDestroy(ev);
+    for (auto &ev : e->user_ev) if (ev) cudaEventDestroy(ev);
     if (e->stream) cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -667,6 +670,21 @@ int32_t triage_fail(triage_engine *e, int32_t level) {
 int32_t triage_last_timings(triage_engine *e, triage_timings *t) {
     if (!e || !t) return fail(TRIAGE_E_ARG, "null argument");
     *t = e->tm;
+    return TRIAGE_OK;
+}
+
+int32_t triage_event_record(triage_engine *e, int32_t slot) {
+    if (!e || slot < 0 || slot > 3) return fail(TRIAGE_E_ARG, "bad argument");
+    CU(cudaSetDevice(e->opts.device));
+    CU(cudaEventRecord(e->user_ev[slot], e->stream));
+    return TRIAGE_OK;
+}
+
+int32_t triage_event_elapsed_ms(triage_engine *e, int32_t from_slot, int32_t to_slot, float *ms) {
+    if (!e || !ms || from_slot < 0 || from_slot > 3 || to_slot < 0 || to_slot > 3) return fail(TRIAGE_E_ARG, "bad argument");
+    CU(cudaSetDevice(e->opts.device));
+    CU(cudaEventSynchronize(e->user_ev[to_slot]));
+    CU(cudaEventElapsedTime(ms, e->user_ev[from_slot], e->user_ev[to_slot]));
     return TRIAGE_OK;
 }
 

@@ -109,7 +109,7 @@ def test_multi_level_queue_push_pop_peek_stats():
     for _ in range(2):
         q.fail_message("high")
     s = q.get_stats("high")
-    assert (s.completed_count, s.failed_count, s.processing_count, s.pending_count) == (3, 2, 0, 0)
+    assert (s.completed_count, s.failed_count, s.processing_count, s.pending_count) == (3, 2, 1, 0)   # 1: the pop at :63-86
     assert set(q.get_all_stats()) == {"realtime", "high", "normal", "low"}
 
 
