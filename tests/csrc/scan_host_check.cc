@@ -94,3 +94,21 @@ int hostcheck_bordered(const uint8_t *lit, uint32_t len, int ci)
     return literal_is_bordered(std::string(reinterpret_cast<const char *>(lit), len), ci != 0) ? 1 : 0;
 }
 }
+
+// exports the compiled D8 table (for offline layout / bank-conflict studies)
+extern "C" int hostcheck_table(const uint8_t *prios, const uint8_t *cis, const uint32_t *lens, const uint8_t *lits, uint32_t n_pat,
+                               uint16_t *table /* 256*256 */, uint32_t *info /* states, start, neutral, warm */)
+{
+    std::vector<DictEntry> dict;
+    size_t o = 0;
+    for (uint32_t i = 0; i < n_pat; i++) {
+        dict.push_back({prios[i], cis[i] != 0, std::string(reinterpret_cast<const char *>(lits + o), lens[i])});
+        o += lens[i];
+    }
+    Dfa dfa;
+    std::string e = build_dfa(dict, &dfa);
+    if (!e.empty()) return 4;
+    std::memcpy(table, dfa.table.data(), dfa.table.size() * 2);
+    info[0] = dfa.n_states; info[1] = dfa.start_state; info[2] = dfa.neutral_state; info[3] = dfa.warm_bytes;
+    return 0;
+}
