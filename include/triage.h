@@ -140,6 +140,19 @@ int32_t triage_submit_device(triage_engine *e, const uint64_t *offsets_dev, cons
                              const uint64_t *enqueue_ns_dev, uint32_t n, triage_result *results_dev,
                              uint32_t *order_dev, uint32_t *n_admitted);
 
+/* -- triage_submit_device for callers that may not allocate device memory (no counterpart in the reference: the Go
+ *    code has no device and no allocator to avoid).  Same arguments and results as triage_submit_device, but every byte of
+ *    kernel scratch comes from one fixed 3 MiB __device__ array inside the library instead of buffers grown with cudaMalloc,
+ *    so the call performs no cudaMalloc / cudaFree at all.  For serving loops and embedding applications that own all of
+ *    HBM or cannot afford the allocator's implicit synchronisation.  Limits: at most 65536 messages and 256 MiB of arena
+ *    per call (larger -> TRIAGE_E_ARG), the dictionary must already be committed with triage_dict_commit, and calls that
+ *    overlap on one GPU race on the shared array (serialise them).  The first call on a device looks the array up with
+ *    cudaGetSymbolAddress; make it before any stream capture.                                                        */
+int32_t triage_submit_device_static(triage_engine *e, const uint64_t *offsets_dev, const uint8_t *bytes_dev,
+                                    uint64_t total_bytes, const triage_meta *meta_dev,
+                                    const uint64_t *enqueue_ns_dev, uint32_t n, triage_result *results_dev,
+                                    uint32_t *order_dev, uint32_t *n_admitted);
+
 /* -- dequeue.  triage_pop = MultiLevelQueue.Pop(name) (queue.go:121-139); triage_drain = the
  *    realtime->high->normal->low loop of cmd/queue-manager/main.go:111-124 run max times, which is
  *    also QueueManager.BatchPopMessages per level (queue_manager.go:326-367).                   */

@@ -77,6 +77,8 @@ _SIGS = {
     "triage_process": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
     "triage_submit_device": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
                                          C.c_uint32, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32)]),
+    "triage_submit_device_static": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
+                                                C.c_uint32, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32)]),
     "triage_queue_create": (C.c_int32, [C.c_void_p, C.c_int64, C.POINTER(C.c_int32)]),
     "triage_queue_delete": (C.c_int32, [C.c_void_p, C.c_int32]),
     "triage_set_limits": (C.c_int32, [C.c_void_p, C.c_int64, C.c_int32]),
@@ -200,6 +202,14 @@ class Engine:
         adm = C.c_uint32()
         _check(lib().triage_submit_device(self._h, offsets_ptr, bytes_ptr, int(total), meta_ptr, ts_ptr, int(n), results_ptr,
                                           order_ptr, C.byref(adm)))
+        return adm.value
+
+    def submit_device_static(self, offsets_ptr, bytes_ptr, total, meta_ptr, ts_ptr, n, results_ptr, order_ptr) -> int:
+        """triage_submit_device without any device allocation: scratch lives in a fixed 3 MiB array inside the library
+        (<= 65536 messages, <= 256 MiB arena, dictionary committed beforehand)."""
+        adm = C.c_uint32()
+        _check(lib().triage_submit_device_static(self._h, offsets_ptr, bytes_ptr, int(total), meta_ptr, ts_ptr, int(n), results_ptr,
+                                                 order_ptr, C.byref(adm)))
         return adm.value
 
     def timings(self) -> dict:

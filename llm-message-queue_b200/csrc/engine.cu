@@ -783,3 +783,178 @@ extern "C" int32_t triage_merge_allgather(triage_engine *e, const uint64_t *rank
     CU(cudaStreamSynchronize(s));
     return TRIAGE_OK;
 }
+
+// =================================================================================================
+// triage_submit_device_static — the device-resident submit for callers that must not allocate.
+//
+// Who needs it: code that runs where cudaMalloc / cudaFree are off limits — a host thread inside a
+// latency-critical serving loop that may not take the allocator's implicit device synchronisation, a
+// plugin whose embedding application owns all device memory and forbids growth after start-up, or a
+// process that has already handed every byte of HBM to its own pools.  The regular entry points grow
+// their scratch buffers on demand (cudaMalloc inside DevBuf::ensure); this one never does: all the
+// scratch the kernels need (per-message counters, tile index, buckets, split histograms, permutation
+// ping-pong buffers) is carved out of ONE file-scope __device__ array below.
+//
+// Cost and limits: every GPU that loads this library keeps kStaticScratchBytes (3 MiB) of device memory
+// for the life of the process, and a batch may hold at most kStaticMaxMsgs messages / kStaticMaxBytes
+// arena bytes; larger batches are refused with TRIAGE_E_ARG.  The dictionary must already be committed
+// (triage_dict_commit allocates its table, so it is not done here).
+//
+// Set-up: the array's name is only a host-side handle.  The first call on each device resolves the real
+// device address with cudaGetSymbolAddress (with that device current) and caches it; make that first
+// call before starting any stream capture.
+//
+// Sharing: all calls, from every engine on that device, use the same array and it keeps whatever the last
+// call left behind.  Each call clears the parts that must start at zero (counters, flags), so back-to-back
+// calls are fine; calls that overlap in time on one GPU race on the scratch and must be serialised by the
+// caller.
+// =================================================================================================
+namespace {
+
+constexpr uint32_t kStaticMaxMsgs = 65536;
+constexpr uint64_t kStaticMaxBytes = 256ull << 20;
+constexpr size_t kStaticScratchBytes = 3u << 20;
+constexpr size_t kStaticAlign = 256;
+
+constexpr size_t up256(size_t x) { return (x + kStaticAlign - 1) / kStaticAlign * kStaticAlign; }
+constexpr size_t kStMaxTiles = kStaticMaxBytes / 16384 + 2;   // holds for any scan tile of >= 16 KiB
+constexpr size_t kStMaxBlocks = (kStaticMaxMsgs + kOrderBlock - 1) / kOrderBlock;
+constexpr size_t kStOffCounters = 0;
+constexpr size_t kStOffTileFirst = kStOffCounters + up256((size_t)kStaticMaxMsgs * CNT_STRIDE * 4);
+constexpr size_t kStOffBucket = kStOffTileFirst + up256(kStMaxTiles * 4);
+constexpr size_t kStOffBucket2 = kStOffBucket + up256(kStaticMaxMsgs);
+constexpr size_t kStOffBlockhist = kStOffBucket2 + up256(kStaticMaxMsgs);
+constexpr size_t kStOffTotals = kStOffBlockhist + up256(kStMaxBlocks * 256 * 4);
+constexpr size_t kStOffSmall = kStOffTotals + up256(260 * 4);
+constexpr size_t kStOffPending = kStOffSmall + up256((32 + 8 * 256) * 4);
+constexpr size_t kStOffMaxsize = kStOffPending + up256(4 * 8);
+constexpr size_t kStOffPermA = kStOffMaxsize + up256(4 * 8);
+constexpr size_t kStOffPermB = kStOffPermA + up256((size_t)kStaticMaxMsgs * 4);
+constexpr size_t kStEnd = kStOffPermB + up256((size_t)kStaticMaxMsgs * 4);
+static_assert(kStEnd <= kStaticScratchBytes, "static scratch layout does not fit");
+static_assert(kScanTile >= 16384, "tile index bound assumes tiles of at least 16 KiB");
+
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+std::mutex g_static_mu;
+unsigned char *g_static_ptr[64] = {};   // per device ordinal: device address of g_static_scratch
+
+// once per device, with that device current
+int32_t static_scratch_base(int device, unsigned char **out) {
+    if (device < 0 || device >= 64) return fail(TRIAGE_E_ARG, "device ordinal out of range for the static scratch table");
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_ptr[device]) {
+        void *p = nullptr;
+        CU(cudaGetSymbolAddress(&p, g_static_scratch));
+        g_static_ptr[device] = static_cast<unsigned char *>(p);
+    }
+    *out = g_static_ptr[device];
+    return TRIAGE_OK;
+}
+
+}  // namespace
+
+extern "C" int32_t triage_submit_device_static(triage_engine *e, const uint64_t *offsets_dev, const uint8_t *bytes_dev,
+                                               uint64_t total_bytes, const triage_meta *meta_dev, const uint64_t *enqueue_ns_dev,
+                                               uint32_t n, triage_result *results_dev, uint32_t *order_dev, uint32_t *n_admitted) {
+    if (!e || !n_admitted || (n && (!offsets_dev || !meta_dev || !results_dev || !order_dev))) return fail(TRIAGE_E_ARG, "null argument");
+    if (total_bytes && !bytes_dev) return fail(TRIAGE_E_ARG, "null arena");
+    if (n > kStaticMaxMsgs)
+        return fail(TRIAGE_E_ARG, "triage_submit_device_static: batch of " + std::to_string(n) + " messages exceeds the static scratch limit of " +
+                                      std::to_string(kStaticMaxMsgs));
+    if (total_bytes > kStaticMaxBytes)
+        return fail(TRIAGE_E_ARG, "triage_submit_device_static: arena of " + std::to_string(total_bytes) + " bytes exceeds the static scratch limit of " +
+                                      std::to_string(kStaticMaxBytes));
+    if (e->dict_dirty) return fail(TRIAGE_E_ARG, "triage_submit_device_static: call triage_dict_commit first (committing allocates, this entry point must not)");
+    if ((reinterpret_cast<uintptr_t>(bytes_dev) & 15) != 0) return fail(TRIAGE_E_ARG, "device arena must be 16-byte aligned");
+    CU(cudaSetDevice(e->opts.device));
+    unsigned char *base = nullptr;
+    int32_t rc = static_scratch_base(e->opts.device, &base);
+    if (rc) return rc;
+    *n_admitted = 0;
+    e->tm = triage_timings{};
+    if (n == 0) return TRIAGE_OK;
+
+    uint32_t *counters = reinterpret_cast<uint32_t *>(base + kStOffCounters);
+    uint32_t *tile_first = reinterpret_cast<uint32_t *>(base + kStOffTileFirst);
+    uint8_t *bucket = base + kStOffBucket;
+    uint8_t *bucket2 = base + kStOffBucket2;
+    uint32_t *blockhist = reinterpret_cast<uint32_t *>(base + kStOffBlockhist);
+    uint32_t *totals = reinterpret_cast<uint32_t *>(base + kStOffTotals);
+    uint32_t *small = reinterpret_cast<uint32_t *>(base + kStOffSmall);
+    uint64_t *pending_dev = reinterpret_cast<uint64_t *>(base + kStOffPending);
+    int64_t *maxsize_dev = reinterpret_cast<int64_t *>(base + kStOffMaxsize);
+    uint32_t *perm_a = reinterpret_cast<uint32_t *>(base + kStOffPermA);
+    uint32_t *perm_b = reinterpret_cast<uint32_t *>(base + kStOffPermB);
+
+    cudaStream_t s = e->stream;
+    uint32_t launches = 0;
+    const uint32_t ntiles = (uint32_t)((total_bytes + kScanTile - 1) / kScanTile);
+    const uint32_t nblocks = (n + kOrderBlock - 1) / kOrderBlock;
+    OrderScratch sc{blockhist, totals, (uint32_t)kStMaxBlocks};
+    (void)nblocks;
+
+    CU(cudaEventRecord(e->ev[0], s));
+    // the array keeps the previous call's contents: counters and flags must start at zero
+    CU(cudaMemsetAsync(counters, 0, (size_t)n * CNT_STRIDE * sizeof(uint32_t), s));
+    CU(cudaMemsetAsync(small, 0, (32 + 8 * 256) * sizeof(uint32_t), s));
+    ScanArgs sa{bytes_dev, offsets_dev, total_bytes, n, counters, tile_first, ntiles};
+    if (ntiles) {
+        CU(launch_tile_index(sa, s)); launches++;
+        CU(cudaEventRecord(e->ev[1], s));
+        CU(launch_scan(sa, e->ddfa, e->sm_count, s)); launches++;
+    } else {
+        CU(cudaEventRecord(e->ev[1], s));
+    }
+    CU(cudaEventRecord(e->ev[2], s));
+    FinalizeArgs fa{counters, meta_dev, offsets_dev, enqueue_ns_dev, n, e->default_prio, e->opts.rules_enabled, 0, results_dev, bucket, small};
+    CU(launch_finalize(fa, s)); launches++;
+    CU(cudaEventRecord(e->ev[3], s));
+    const uint8_t *bk = bucket;
+    if (e->opts.max_queue_size > 0) {
+        const uint64_t pending[4] = {0, 0, 0, 0};
+        const int64_t ms[4] = {e->opts.max_queue_size, e->opts.max_queue_size, e->opts.max_queue_size, e->opts.max_queue_size};
+        CU(cudaMemcpyAsync(pending_dev, pending, sizeof(pending), cudaMemcpyHostToDevice, s));
+        CU(cudaMemcpyAsync(maxsize_dev, ms, sizeof(ms), cudaMemcpyHostToDevice, s));
+        CU(cudaStreamSynchronize(s));   // the two host arrays above live on this stack frame
+        CU(launch_admit(bucket, bucket2, results_dev, n, pending_dev, maxsize_dev, 0, sc, s)); launches += 3;
+        bk = bucket2;
+    }
+    CU(launch_partition_u8(bk, nullptr, n, 16, true, order_dev, small + 2, sc, s)); launches += 4;
+    CU(cudaEventRecord(e->ev[4], s));
+    CU(cudaMemcpyAsync(e->h_small, small, 32 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(e->h_small + 1, totals + 256, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    uint32_t passes = 1;
+    if (e->h_small[0] & 1u) {   // enqueue times not monotone in arrival order: LSD radix over the time key first
+        CU(launch_key_digit_hist(enqueue_ns_dev, nullptr, n, small + 32, s)); launches++;
+        CU(cudaMemcpyAsync(e->h_small + 32, small + 32, 8 * 256 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+        CU(cudaStreamSynchronize(s));
+        const uint32_t *perm = nullptr;
+        uint32_t *bufs[2] = {perm_a, perm_b};
+        int which = 0;
+        for (uint32_t b = 0; b < 8; b++) {
+            bool trivial = false;
+            for (uint32_t d = 0; d < 256; d++) if (e->h_small[32 + b * 256 + d] == n) trivial = true;
+            if (trivial) continue;
+            CU(launch_partition_key(enqueue_ns_dev, 8 * b, perm, n, bufs[which], sc, s)); launches += 3;
+            perm = bufs[which];
+            which ^= 1;
+            passes++;
+        }
+        CU(launch_partition_u8(bk, perm, n, 16, true, order_dev, small + 2, sc, s)); launches += 4;
+        CU(cudaEventRecord(e->ev[4], s));
+        CU(cudaMemcpyAsync(e->h_small + 1, totals + 256, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+        CU(cudaStreamSynchronize(s));
+    }
+    *n_admitted = e->h_small[1];
+    float ms_ = 0;
+    cudaEventElapsedTime(&ms_, e->ev[1], e->ev[2]); e->tm.scan_ms = ms_;
+    cudaEventElapsedTime(&ms_, e->ev[2], e->ev[3]); e->tm.finalize_ms = ms_;
+    cudaEventElapsedTime(&ms_, e->ev[3], e->ev[4]); e->tm.order_ms = ms_;
+    cudaEventElapsedTime(&ms_, e->ev[0], e->ev[4]); e->tm.total_ms = ms_;
+    e->tm.launches = launches;
+    e->tm.order_passes = passes;
+    e->tm.scan_bytes = total_bytes + 8ull * (n + 1) + 32ull * n;
+    return TRIAGE_OK;
+}
