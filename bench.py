@@ -156,6 +156,7 @@ def main():
     ap.add_argument("--messages", type=int, default=N_PER_GPU, help="messages per GPU (default: the BASELINE config)")
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--check", action="store_true", help="verify the (merged) dequeue order against a numpy reference after warm-up")
     args = ap.parse_args()
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     if args.impl == "reference":
@@ -211,6 +212,25 @@ def main():
 
     for _ in range(args.warmup):
         step()
+    if args.check:
+        # whole-job dequeue order = stable sort of admitted messages by bucket, in global arrival order
+        from llm_message_queue_b200 import multigpu
+        res = d_res.cpu().numpy().view(mq.RESULT_DTYPE).reshape(n)
+        bucket = multigpu.bucket_of(res)
+        if world > 1:
+            allb = [None] * world
+            dist.all_gather_object(allb, bucket)
+            bucket_all = np.concatenate(allb)
+            got = d_gord.cpu().numpy().astype(np.int64)
+        else:
+            bucket_all = bucket
+            got = d_ord.cpu().numpy().astype(np.int64)
+        idx = np.nonzero(bucket_all != 255)[0]
+        want = idx[np.argsort(bucket_all[idx], kind="stable")]
+        ok = len(want) <= len(got) and np.array_equal(got[:len(want)], want)
+        print(f"[check rank {rank}] merged order {'OK' if ok else 'MISMATCH'} ({len(want)} admitted of {n * world})", file=sys.stderr, flush=True)
+        if not ok:
+            raise SystemExit(3)
     sampler = ClockSampler(local)
     barrier(); torch.cuda.synchronize()
     if rank == 0:
