@@ -46,6 +46,9 @@ struct Dfa {
     uint32_t span = 1;                // longest byte distance an event can depend on
     uint32_t warm_bytes = 16;         // span-1 rounded up to 16
     uint32_t n_states_unminimised = 0;
+    // pad bytes for the scan's in-register boundary masking (-1: none exists for this dictionary)
+    int head_pad = -1;   // START --head_pad--> START with no output
+    int tail_pad = -1;   // from every state: reading it emits exactly that state's end-of-message output, then nothing
 };
 
 // returns "" on success, else a message (too many states / events for D8, bordered pattern, ...)

@@ -106,7 +106,8 @@ struct triage_engine {
     std::vector<DictEntry> dict;
     bool dict_dirty = true;
     Dfa dfa;
-    DevBuf<uint16_t> d_table;
+    DevBuf<uint8_t> d_table;
+    ScanGeometry geom{0, 0, 0};
     DevBuf<EventPacked> d_events;
     DevBuf<uint8_t> d_eom;
     DeviceDfa ddfa{};
@@ -160,18 +161,25 @@ int32_t commit_dict(triage_engine *e) {
     DeviceDfa d{};
     d.n_states = dfa.n_states; d.n_events = (uint32_t)ev.size(); d.warm = dfa.warm_bytes;
     d.start_state = dfa.start_state; d.neutral_state = dfa.neutral_state;
-    if (scan_smem_bytes(d) > (size_t)e->max_smem_optin)
+    d.head_pad = dfa.head_pad; d.tail_pad = dfa.tail_pad;
+    ScanGeometry geom = pick_scan_geometry(d, (size_t)e->max_smem_optin);
+    if (geom.nt == 0)
         return fail(TRIAGE_E_PATTERN, "dictionary automaton (" + std::to_string(dfa.n_states) + " states) does not fit in shared memory");
-    CU(e->d_table.ensure(dfa.table.size()));
+    // rows padded to kRowBytes so that row r starts at shared-memory bank r (mod 32)
+    std::vector<uint8_t> padded((size_t)dfa.n_states * kRowBytes, 0);
+    for (uint32_t st = 0; st < dfa.n_states; st++)
+        std::memcpy(padded.data() + (size_t)st * kRowBytes, dfa.table.data() + (size_t)st * 256, 512);
+    CU(e->d_table.ensure(padded.size()));
     CU(e->d_events.ensure(ev.size()));
     CU(e->d_eom.ensure(256));
     // the previous automaton may still be in use by a kernel on the stream
     CU(cudaStreamSynchronize(e->stream));
-    CU(cudaMemcpy(e->d_table.p, dfa.table.data(), dfa.table.size() * 2, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(e->d_table.p, padded.data(), padded.size(), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(e->d_events.p, ev.data(), ev.size() * sizeof(EventPacked), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(e->d_eom.p, eom.data(), 256, cudaMemcpyHostToDevice));
     d.table = e->d_table.p; d.events = e->d_events.p; d.eom = e->d_eom.p;
     e->ddfa = d;
+    e->geom = geom;
     e->dfa = dfa;
     e->dict_dirty = false;
     return TRIAGE_OK;
@@ -191,7 +199,7 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     e->tm = triage_timings{};
     *n_admitted = 0;
     if (n == 0) return TRIAGE_OK;
-    const uint32_t ntiles = (uint32_t)((total + kScanTile - 1) / kScanTile);
+    const uint32_t ntiles = (uint32_t)((total + e->geom.tile - 1) / e->geom.tile);
     const uint32_t nblocks = (n + kOrderBlock - 1) / kOrderBlock;
     CU(e->d_counters.ensure((size_t)n * CNT_STRIDE));
     CU(e->d_tile_first.ensure((size_t)ntiles + 2));
@@ -207,11 +215,11 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     CU(cudaEventRecord(e->ev[0], s));
     CU(cudaMemsetAsync(e->d_counters.p, 0, (size_t)n * CNT_STRIDE * sizeof(uint32_t), s));
     CU(cudaMemsetAsync(e->d_small.p, 0, (32 + 8 * 256) * sizeof(uint32_t), s));
-    ScanArgs sa{bytes, offsets, total, n, e->d_counters.p, e->d_tile_first.p, ntiles};
+    ScanArgs sa{bytes, offsets, total, n, e->d_counters.p, e->d_tile_first.p, ntiles, e->geom.tile};
     if (ntiles) {
         CU(launch_tile_index(sa, s)); launches++;
         CU(cudaEventRecord(e->ev[1], s));
-        CU(launch_scan(sa, e->ddfa, e->sm_count, s)); launches++;
+        CU(launch_scan(sa, e->ddfa, e->geom, e->sm_count, s)); launches++;
     } else {
         CU(cudaEventRecord(e->ev[1], s));
     }
@@ -403,7 +411,7 @@ int32_t triage_dict_info(triage_engine *e, uint32_t *n_states, uint32_t *warm_by
     if (rc) return rc;
     if (n_states) *n_states = e->dfa.n_states;
     if (warm_bytes) *warm_bytes = e->dfa.warm_bytes;
-    if (table_bytes) *table_bytes = e->dfa.n_states * 512u;
+    if (table_bytes) *table_bytes = e->dfa.n_states * kRowBytes;
     return TRIAGE_OK;
 }
 
@@ -832,7 +840,7 @@ constexpr size_t kStOffPermA = kStOffMaxsize + up256(4 * 8);
 constexpr size_t kStOffPermB = kStOffPermA + up256((size_t)kStaticMaxMsgs * 4);
 constexpr size_t kStEnd = kStOffPermB + up256((size_t)kStaticMaxMsgs * 4);
 static_assert(kStEnd <= kStaticScratchBytes, "static scratch layout does not fit");
-static_assert(kScanTile >= 16384, "tile index bound assumes tiles of at least 16 KiB");
+static_assert(kMinScanTile >= 16384, "tile index bound assumes tiles of at least 16 KiB");
 
 static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
 
@@ -889,7 +897,7 @@ extern "C" int32_t triage_submit_device_static(triage_engine *e, const uint64_t 
 
     cudaStream_t s = e->stream;
     uint32_t launches = 0;
-    const uint32_t ntiles = (uint32_t)((total_bytes + kScanTile - 1) / kScanTile);
+    const uint32_t ntiles = (uint32_t)((total_bytes + e->geom.tile - 1) / e->geom.tile);
     const uint32_t nblocks = (n + kOrderBlock - 1) / kOrderBlock;
     OrderScratch sc{blockhist, totals, (uint32_t)kStMaxBlocks};
     (void)nblocks;
@@ -898,11 +906,11 @@ extern "C" int32_t triage_submit_device_static(triage_engine *e, const uint64_t 
     // the array keeps the previous call's contents: counters and flags must start at zero
     CU(cudaMemsetAsync(counters, 0, (size_t)n * CNT_STRIDE * sizeof(uint32_t), s));
     CU(cudaMemsetAsync(small, 0, (32 + 8 * 256) * sizeof(uint32_t), s));
-    ScanArgs sa{bytes_dev, offsets_dev, total_bytes, n, counters, tile_first, ntiles};
+    ScanArgs sa{bytes_dev, offsets_dev, total_bytes, n, counters, tile_first, ntiles, e->geom.tile};
     if (ntiles) {
         CU(launch_tile_index(sa, s)); launches++;
         CU(cudaEventRecord(e->ev[1], s));
-        CU(launch_scan(sa, e->ddfa, e->sm_count, s)); launches++;
+        CU(launch_scan(sa, e->ddfa, e->geom, e->sm_count, s)); launches++;
     } else {
         CU(cudaEventRecord(e->ev[1], s));
     }

@@ -44,11 +44,12 @@ __device__ __forceinline__ void tma_load_1d(void *dst, const void *src, uint32_t
 }
 
 // ------------------------------------------------------------------------------ tile index --
-__global__ void tile_index_kernel(const uint64_t *__restrict__ offsets, uint32_t n, uint32_t ntiles, uint32_t *__restrict__ tile_first) {
+__global__ void tile_index_kernel(const uint64_t *__restrict__ offsets, uint32_t n, uint32_t ntiles, uint32_t tile_bytes,
+                                  uint32_t *__restrict__ tile_first) {
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t > ntiles) return;
     if (t == ntiles) { tile_first[t] = n - 1; return; }
-    uint64_t pos = (uint64_t)t * kScanTile;
+    uint64_t pos = (uint64_t)t * tile_bytes;
     uint32_t lo = 0, hi = n + 1;   // first index with offsets[idx] > pos
     while (lo < hi) {
         uint32_t mid = (lo + hi) >> 1;
@@ -59,30 +60,28 @@ __global__ void tile_index_kernel(const uint64_t *__restrict__ offsets, uint32_t
 
 cudaError_t launch_tile_index(const ScanArgs &a, cudaStream_t s) {
     uint32_t cnt = a.ntiles + 1;
-    tile_index_kernel<<<(cnt + 255) / 256, 256, 0, s>>>(a.offsets, a.n, a.ntiles, a.tile_first);
+    tile_index_kernel<<<(cnt + 255) / 256, 256, 0, s>>>(a.offsets, a.n, a.ntiles, a.tile_bytes, a.tile_first);
     return cudaGetLastError();
 }
 
 // ------------------------------------------------------------------------------------ scan --
 // shared memory layout (bytes): [0,16) two mbarriers | table | events | eom(256) | stage0 | stage1 | list0 | list1
 struct ScanSmem {
-    uint32_t table, events, eom, stage0, stage1, list0, list1, total, stage_bytes;
+    uint32_t table, events, eom, stage0, list0, total, stage_bytes;
 };
-__host__ __device__ inline ScanSmem scan_layout(uint32_t n_states, uint32_t n_events, uint32_t warm) {
+__host__ __device__ inline ScanSmem scan_layout(uint32_t n_states, uint32_t n_events, uint32_t warm, uint32_t tile) {
     ScanSmem L;
     uint32_t o = 128;
-    L.table = o; o += n_states * 512u;
+    L.table = o; o += ((n_states * kRowBytes + 127u) / 128u) * 128u;
     L.events = o; o += ((n_events * 16u + 127u) / 128u) * 128u;
     L.eom = o; o += 256u;
-    L.stage_bytes = ((warm + kScanTile + 16u + 127u) / 128u) * 128u;
-    L.stage0 = o; o += L.stage_bytes;
-    L.stage1 = o; o += L.stage_bytes;
-    L.list0 = o; o += kListCap * 4u;
-    L.list1 = o; o += kListCap * 4u;
+    L.stage_bytes = ((warm + tile + 16u + 127u) / 128u) * 128u;
+    L.stage0 = o; o += 2 * L.stage_bytes;
+    L.list0 = o; o += 2 * kListCap * 4u;
     L.total = o;
     return L;
 }
-size_t scan_smem_bytes(const DeviceDfa &d) { return scan_layout(d.n_states, d.n_events, d.warm).total; }
+size_t scan_smem_bytes(const DeviceDfa &d, const ScanGeometry &g) { return scan_layout(d.n_states, d.n_events, d.warm, g.tile).total; }
 
 __device__ __forceinline__ int32_t rel_clamp(uint64_t off, uint64_t tile_start) {
     int64_t r = (int64_t)off - (int64_t)tile_start;
@@ -90,14 +89,14 @@ __device__ __forceinline__ int32_t rel_clamp(uint64_t off, uint64_t tile_start) 
     return (int32_t)(r < -lim ? -lim : (r > lim ? lim : r));
 }
 
-template <int NT, int C>
+template <int NT, int C, bool FAST>
 __global__ void __launch_bounds__(NT, 1) scan_kernel(ScanArgs a, DeviceDfa d) {
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr uint32_t TILE = NT * C;
     constexpr int LPT = (kListCap + NT - 1) / NT;
-    const ScanSmem L = scan_layout(d.n_states, d.n_events, d.warm);
+    const ScanSmem L = scan_layout(d.n_states, d.n_events, d.warm, TILE);
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem);
-    uint16_t *tbl = reinterpret_cast<uint16_t *>(smem + L.table);
+    uint8_t *tbl = smem + L.table;
     EventPacked *events = reinterpret_cast<EventPacked *>(smem + L.events);
     uint8_t *eom = smem + L.eom;
     // buffers are addressed arithmetically (not through a pointer array) so the compiler keeps them in the
@@ -116,11 +115,11 @@ __global__ void __launch_bounds__(NT, 1) scan_kernel(ScanArgs a, DeviceDfa d) {
         mbar_init(&bars[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    // automaton -> shared memory
+    // automaton -> shared memory (rows are 516 bytes: copy as 32-bit words)
     {
-        const uint4 *src = reinterpret_cast<const uint4 *>(d.table);
-        uint4 *dst = reinterpret_cast<uint4 *>(tbl);
-        for (uint32_t i = tid; i < d.n_states * 32u; i += NT) dst[i] = src[i];
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(d.table);
+        uint32_t *dst = reinterpret_cast<uint32_t *>(tbl);
+        for (uint32_t i = tid; i < d.n_states * (kRowBytes / 4); i += NT) dst[i] = src[i];
         const uint4 *es = reinterpret_cast<const uint4 *>(d.events);
         uint4 *ed = reinterpret_cast<uint4 *>(events);
         for (uint32_t i = tid; i < d.n_events; i += NT) ed[i] = es[i];
@@ -181,14 +180,25 @@ __global__ void __launch_bounds__(NT, 1) scan_kernel(ScanArgs a, DeviceDfa d) {
         c.list_abs = a.offsets; c.tile_start = (int64_t)ts;
         c.list_n = cnt_cur; c.msg_lo = first_cur; c.counters = a.counters; c.warm = (int32_t)warm;
         c.start_state = d.start_state; c.neutral_state = d.neutral_state;
+        c.head_pad4 = 0x01010101u * (uint32_t)(d.head_pad & 0xFF); c.tail_pad4 = 0x01010101u * (uint32_t)(d.tail_pad & 0xFF);
+        c.tbl_s = smem_u32(tbl);
 
         mbar_wait(&bars[buf], (k >> 1) & 1);
 
         uint32_t hm = 0xFFFFFFFFu, hw = 0;
         const int32_t chunk = (int32_t)(tid * C);
+        // the warp's first lane finds its message by binary search, the others walk forward from there
+        const int32_t warp_chunk = (int32_t)((tid & ~31u) * C);
+        uint32_t khint = 0;
+        if (warp_chunk < tile_len) {
+            if (lane == 0) khint = find_msg(c, warp_chunk);
+            khint = __shfl_sync(0xFFFFFFFFu, khint, 0);
+        }
         if (chunk < tile_len) {
             int32_t ce = chunk + C < tile_len ? chunk + C : tile_len;
-            lane_scan(c, chunk, ce, &hm, &hw);
+            uint32_t kk = find_msg_from(c, chunk, khint);
+            if (FAST) lane_scan_fast(c, chunk, ce, kk, &hm, &hw);
+            else lane_scan_slow(c, chunk, ce, kk, &hm, &hw);
         }
         // combine the head partials of neighbouring lanes that sit in the same message
         {
@@ -226,19 +236,42 @@ __global__ void __launch_bounds__(NT, 1) scan_kernel(ScanArgs a, DeviceDfa d) {
     }
 }
 
-cudaError_t launch_scan(const ScanArgs &a, const DeviceDfa &d, int sm_count, cudaStream_t s) {
-    if (a.ntiles == 0) return cudaSuccess;
-    size_t smem = scan_smem_bytes(d);
-    auto kern = scan_kernel<kScanThreads, kScanChunk>;
+// geometries in order of preference (more bytes per lane first: less warm-up overhead)
+static const ScanGeometry kGeometries[] = {{768, 80, 768 * 80}, {1024, 48, 1024 * 48}, {512, 48, 512 * 48}};
+
+ScanGeometry pick_scan_geometry(const DeviceDfa &d, size_t max_smem) {
+    for (const ScanGeometry &g : kGeometries)
+        if (scan_smem_bytes(d, g) <= max_smem) return g;
+    return ScanGeometry{0, 0, 0};
+}
+
+template <int NT, int C, bool FAST>
+static cudaError_t launch_scan_variant(const ScanArgs &a, const DeviceDfa &d, size_t smem, uint32_t grid, cudaStream_t s) {
+    auto kern = scan_kernel<NT, C, FAST>;
     static size_t configured = 0;
     if (smem > configured) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         configured = smem;
     }
-    uint32_t grid = a.ntiles < (uint32_t)sm_count ? a.ntiles : (uint32_t)sm_count;
-    kern<<<grid, kScanThreads, smem, s>>>(a, d);
+    kern<<<grid, NT, smem, s>>>(a, d);
     return cudaGetLastError();
+}
+
+cudaError_t launch_scan(const ScanArgs &a, const DeviceDfa &d, const ScanGeometry &g, int sm_count, cudaStream_t s) {
+    static_assert(768 * 80 >= kMinScanTile && 1024 * 48 >= kMinScanTile && 512 * 48 >= kMinScanTile, "tile too small");
+    if (a.ntiles == 0) return cudaSuccess;
+    size_t smem = scan_smem_bytes(d, g);
+    uint32_t grid = a.ntiles < (uint32_t)sm_count ? a.ntiles : (uint32_t)sm_count;
+    const bool fast = d.head_pad >= 0 && d.tail_pad >= 0;
+#define TRIAGE_SCAN_CASE(NT_, C_)                                                                        \
+    if (g.nt == NT_ && g.chunk == C_)                                                                    \
+        return fast ? launch_scan_variant<NT_, C_, true>(a, d, smem, grid, s) : launch_scan_variant<NT_, C_, false>(a, d, smem, grid, s);
+    TRIAGE_SCAN_CASE(768, 80)
+    TRIAGE_SCAN_CASE(1024, 48)
+    TRIAGE_SCAN_CASE(512, 48)
+#undef TRIAGE_SCAN_CASE
+    return cudaErrorInvalidValue;
 }
 
 // -------------------------------------------------------------------------------- finalize --

@@ -8,19 +8,19 @@
 
 namespace triage {
 
-// compile-time geometry of the scan: NT lanes per tile, each owning C contiguous bytes.
-// C is an odd multiple of 16 so that the lanes' 128-bit shared loads are bank-conflict free.
-constexpr int kScanThreads = 1024;
-constexpr int kScanChunk = 48;
-constexpr uint32_t kScanTile = kScanThreads * kScanChunk;
-constexpr uint32_t kListCap = 2048;   // message starts per tile kept in shared memory (else global offsets)
+// Geometry of the scan: NT lanes per tile, each owning C contiguous bytes.  C is an odd multiple of 16 so that the
+// lanes' 128-bit shared loads are bank-conflict free.  The variant is picked per dictionary by what fits in shared memory.
+struct ScanGeometry { uint32_t nt, chunk, tile; };
+constexpr uint32_t kMinScanTile = 16384;
+constexpr uint32_t kListCap = 1024;   // message starts per tile kept in shared memory (else global offsets)
 constexpr uint32_t kMaxWarm = 256;
 
 struct DeviceDfa {
-    const uint16_t *table;       // n_states * 256
+    const uint8_t *table;        // n_states * kRowBytes (padded rows)
     const EventPacked *events;   // n_events
     const uint8_t *eom;          // 256 (padded)
     uint32_t n_states, n_events, warm, start_state, neutral_state;
+    int32_t head_pad, tail_pad;  // -1: no inert pad byte exists, use the byte-at-a-time boundary path
 };
 
 struct ScanArgs {
@@ -31,6 +31,7 @@ struct ScanArgs {
     uint32_t *counters;          // n * CNT_STRIDE, zeroed
     uint32_t *tile_first;        // ntiles + 1 (scratch)
     uint32_t ntiles;
+    uint32_t tile_bytes;         // = geometry.tile
 };
 
 struct FinalizeArgs {
@@ -47,9 +48,11 @@ struct FinalizeArgs {
     uint32_t *flags;             // [0] |= 1 when ts is not non-decreasing in arrival order
 };
 
-size_t scan_smem_bytes(const DeviceDfa &d);
+// largest-throughput geometry whose shared memory fits; nt == 0 if none does
+ScanGeometry pick_scan_geometry(const DeviceDfa &d, size_t max_smem);
+size_t scan_smem_bytes(const DeviceDfa &d, const ScanGeometry &g);
 cudaError_t launch_tile_index(const ScanArgs &a, cudaStream_t s);
-cudaError_t launch_scan(const ScanArgs &a, const DeviceDfa &d, int sm_count, cudaStream_t s);
+cudaError_t launch_scan(const ScanArgs &a, const DeviceDfa &d, const ScanGeometry &g, int sm_count, cudaStream_t s);
 cudaError_t launch_finalize(const FinalizeArgs &a, cudaStream_t s);
 
 // ---- ordering --------------------------------------------------------------------------------

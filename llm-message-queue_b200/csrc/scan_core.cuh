@@ -1,22 +1,25 @@
 // scan_core.cuh — the per-lane body of the arena scan, written once for device and host.
 //
-// The CUDA kernel (scan_kernel.cu) calls lane_scan() from every thread; tests/csrc/ compiles the
-// very same function with g++ and walks all lanes of all tiles sequentially to check the
-// automaton + chunking logic against the oracle on machines without a GPU.  That host build is
-// a test harness only — the shipped library has no CPU path.
+// The CUDA kernel (kernels.cu) calls lane_scan*() from every thread; tests/csrc/ compiles the very same functions
+// with g++ and walks all lanes of all tiles sequentially to check the automaton + chunking logic against the oracle
+// on machines without a GPU.  That host build is a test harness only — the shipped library has no CPU path.
 //
-// Model: the arena is cut into tiles of NT*C bytes; lane l of a tile owns the C bytes starting at
-// tile_start + l*C.  A lane first walks `warm` bytes before its chunk (or from the message start,
-// whichever is later) with events discarded so that its automaton state is exact at the chunk
-// start (the automaton has finite memory `span` <= warm+1), then walks its chunk, splitting at
-// message boundaries.  Per-message counters live in global memory and are bumped with atomics.
+// Model: the arena is cut into tiles of NT*C bytes; lane l of a tile owns the C bytes starting at tile_start + l*C.
+// A lane first walks `warm` bytes before its chunk (or from the message start, whichever is later) with outputs
+// discarded so that its automaton state is exact at the chunk start (the automaton has finite memory `span` <= warm+1),
+// then walks its chunk in aligned 16-byte groups.  Message boundaries inside a group are handled WITHOUT leaving the
+// unrolled group code: the bytes that belong to a neighbouring message are overwritten in registers with pad bytes the
+// dictionary compiler proved inert (head pad: START --pad--> START, no output; tail pad: reading it from any state emits
+// exactly that state's end-of-message output, then nothing).  Per-message counters live in global memory (atomics).
 #pragma once
 #include <stdint.h>
 
 #if defined(__CUDACC__)
 #define TR_HD __host__ __device__ __forceinline__
+#define TR_COLD static __host__ __device__ __noinline__
 #else
 #define TR_HD inline
+#define TR_COLD static inline
 #endif
 
 namespace triage {
@@ -24,8 +27,14 @@ namespace triage {
 // per-message counters written by the scan, read by the finalize kernel (8 x u32 = 32 bytes)
 enum { CNT_WORDS = 0, CNT_KW = 1 /* ..4 */, CNT_POS = 5, CNT_NEG = 6, CNT_Q = 7, CNT_STRIDE = 8 };
 
+// Table rows are 256 16-bit entries + 4 bytes of padding: row r starts at bank r (mod 32), so lanes that read the
+// same byte pair in different states hit different banks.  The byte offset 516*state + 2*byte is one dp4a.
+constexpr uint32_t kRowBytes = 516;
+constexpr uint32_t kDpMul = 0xACACAC02u;   // dot((byte, st, st, st), (2, 172, 172, 172)) = 2*byte + 516*st
+
 // events[id]: x = kw_rt | kw_hi << 16, y = kw_norm | kw_low << 16, z = pos | neg << 8 | question << 16
 struct EventPacked { uint32_t x, y, z, w; };
+struct alignas(16) Quad { uint32_t a, b, c, d; };
 
 TR_HD void tr_add(uint32_t *p, uint32_t v) {
 #if defined(__CUDA_ARCH__)
@@ -41,16 +50,22 @@ TR_HD void tr_or(uint32_t *p, uint32_t v) {
     *p |= v;
 #endif
 }
-TR_HD uint32_t tr_idx(uint32_t word, uint32_t entry, uint32_t k) {
+// byte offset of entry (state of `entry`, byte k of `word`)
+TR_HD uint32_t tr_off(uint32_t word, uint32_t entry, uint32_t k) {
 #if defined(__CUDA_ARCH__)
-    return __byte_perm(word, entry, 0x7640u | k);   // (entry & 0xFF) << 8 | byte k of word; entry < 65536
+    return __dp4a(__byte_perm(word, entry, 0x4440u | k), kDpMul, 0u);
 #else
-    return ((entry & 0xFFu) << 8) | ((word >> (8 * k)) & 0xFFu);
+    return (entry & 0xFFu) * kRowBytes + 2u * ((word >> (8 * k)) & 0xFFu);
 #endif
 }
+TR_HD uint32_t tr_entry(const uint8_t *tbl, uint32_t off) { return *reinterpret_cast<const uint16_t *>(tbl + off); }
+
+struct LaneCtx;
+// one transition: returns the table entry for (state of `entry`, byte k of `word`)
+TR_HD uint32_t tr_next(const LaneCtx &c, uint32_t word, uint32_t entry, uint32_t k);
 
 struct LaneCtx {
-    const uint16_t *tbl;        // D8 table (shared memory on device)
+    const uint8_t *tbl;         // padded D8 table (shared memory on device), kRowBytes per state
     const EventPacked *events;  // event id -> counters
     const uint8_t *eom;         // per state end-of-message output
     const uint8_t *stage;       // staged bytes; stage[i] is the byte at tile-relative position i - warm
@@ -62,11 +77,26 @@ struct LaneCtx {
     uint32_t *counters;         // global, CNT_STRIDE per message
     int32_t warm;
     uint32_t start_state, neutral_state;
+    uint32_t head_pad4, tail_pad4;   // pad byte replicated x4 (fast path only)
+    uint32_t tbl_s;                  // device: address of tbl in the shared window (the dp4a accumulates onto it)
 };
 
-TR_HD void apply_event(const LaneCtx &c, uint32_t id, uint32_t msg) {
-    EventPacked e = c.events[id];
-    uint32_t *cnt = c.counters + (uint64_t)msg * CNT_STRIDE;
+TR_HD uint32_t tr_next(const LaneCtx &c, uint32_t word, uint32_t entry, uint32_t k) {
+#if defined(__CUDA_ARCH__)
+    // PRMT (byte, st, st, st) -> IDP.4A: table base + 2*byte + 516*st -> LDS.U16
+    uint32_t addr = __dp4a(__byte_perm(word, entry, 0x4440u | k), kDpMul, c.tbl_s);
+    uint16_t v;
+    asm("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
+    return v;
+#else
+    return tr_entry(c.tbl, tr_off(word, entry, k));
+#endif
+}
+
+// rare: kept out of line so the 16x unrolled replay stays small
+TR_COLD void apply_event_raw(const EventPacked *events, uint32_t *counters, uint32_t id, uint32_t msg) {
+    EventPacked e = events[id];
+    uint32_t *cnt = counters + (uint64_t)msg * CNT_STRIDE;
     if (e.x & 0xFFFFu) tr_add(cnt + CNT_KW + 0, e.x & 0xFFFFu);
     if (e.x >> 16) tr_add(cnt + CNT_KW + 1, e.x >> 16);
     if (e.y & 0xFFFFu) tr_add(cnt + CNT_KW + 2, e.y & 0xFFFFu);
@@ -75,51 +105,7 @@ TR_HD void apply_event(const LaneCtx &c, uint32_t id, uint32_t msg) {
     if ((e.z >> 8) & 0xFFu) tr_add(cnt + CNT_NEG, (e.z >> 8) & 0xFFu);
     if (e.z >> 16) tr_or(cnt + CNT_Q, 1u);
 }
-
-// one byte, full event handling
-TR_HD void step_slow(const LaneCtx &c, uint32_t byte, uint32_t &e, uint32_t &words, uint32_t msg, bool count) {
-    e = c.tbl[((e & 0xFFu) << 8) | byte];
-    if (count) {
-        words += e >> 15;
-        uint32_t id = (e >> 8) & 0x7Fu;
-        if (id) apply_event(c, id, msg);
-    }
-}
-
-// bytes [a, b) (tile-relative), byte at a time
-TR_HD void run_slow(const LaneCtx &c, int32_t a, int32_t b, uint32_t &e, uint32_t &words, uint32_t msg, bool count) {
-    for (int32_t p = a; p < b; p++) step_slow(c, c.stage[p + c.warm], e, words, msg, count);
-}
-
-#define TR_STEP4(wd)                                                          \
-    idx = tr_idx(wd, e, 0); e = c.tbl[idx]; words += e >> 15; ev |= e;        \
-    idx = tr_idx(wd, e, 1); e = c.tbl[idx]; words += e >> 15; ev |= e;        \
-    idx = tr_idx(wd, e, 2); e = c.tbl[idx]; words += e >> 15; ev |= e;        \
-    idx = tr_idx(wd, e, 3); e = c.tbl[idx]; words += e >> 15; ev |= e;
-
-// one aligned 16-byte group fully inside a segment; rare events are replayed byte by byte
-TR_HD void run_group16(const LaneCtx &c, int32_t p, uint32_t &e, uint32_t &words, uint32_t msg, bool count) {
-    struct alignas(16) Quad { uint32_t a, b, c, d; };
-    const Quad q = *reinterpret_cast<const Quad *>(c.stage + p + c.warm);   // one 128-bit shared load
-    uint32_t w0 = q.a, w1 = q.b, w2 = q.c, w3 = q.d;
-    uint32_t e0 = e, words0 = words, ev = 0, idx;
-    TR_STEP4(w0) TR_STEP4(w1) TR_STEP4(w2) TR_STEP4(w3)
-    if (!count) { words = words0; return; }
-    if (ev & 0x7F00u) {   // some transition carried a keyword / sentiment / question event
-        e = e0;
-        words = words0;
-        run_slow(c, p, p + 16, e, words, msg, true);
-    }
-}
-
-TR_HD void run_range(const LaneCtx &c, int32_t a, int32_t b, uint32_t &e, uint32_t &words, uint32_t msg, bool count) {
-    int32_t p = a;
-    int32_t head = (16 - ((p + c.warm) & 15)) & 15;        // stage is 16-byte aligned at index 0
-    if (head > b - p) head = b - p;
-    if (head) { run_slow(c, p, p + head, e, words, msg, count); p += head; }
-    for (; p + 16 <= b; p += 16) run_group16(c, p, e, words, msg, count);
-    if (p < b) run_slow(c, p, b, e, words, msg, count);
-}
+TR_HD void apply_event(const LaneCtx &c, uint32_t id, uint32_t msg) { apply_event_raw(c.events, c.counters, id, msg); }
 
 TR_HD int32_t list_at(const LaneCtx &c, uint32_t k) {
     if (c.list) return c.list[k];
@@ -128,8 +114,8 @@ TR_HD int32_t list_at(const LaneCtx &c, uint32_t k) {
     return (int32_t)(r < -lim ? -lim : (r > lim ? lim : r));
 }
 
-// index k into list with list[k] <= pos < list[k+1]  (upper_bound - 1; empty messages repeat a value,
-// so this lands on the one non-empty message that contains pos)
+// index k into list with list[k] <= pos < list[k+1]  (upper_bound - 1; empty messages repeat a value, so this lands on
+// the one non-empty message that contains pos)
 TR_HD uint32_t find_msg(const LaneCtx &c, int32_t pos) {
     uint32_t lo = 0, hi = c.list_n;   // first index with list[idx] > pos
     while (lo < hi) {
@@ -138,15 +124,155 @@ TR_HD uint32_t find_msg(const LaneCtx &c, int32_t pos) {
     }
     return lo - 1;
 }
+// same, walking forward from a hint known to be <= the answer (the warp's first lane)
+TR_HD uint32_t find_msg_from(const LaneCtx &c, int32_t pos, uint32_t k) {
+    while (list_at(c, k + 1) <= pos) k++;
+    return k;
+}
 
-// Walks the lane's chunk [chunk, chunk_end) (tile-relative).  Every segment is flushed with
-// atomics except the partial count of the message at the chunk start, which is returned in
-// (*head_msg, *head_words) so the caller can combine neighbouring lanes first.
-TR_HD void lane_scan(const LaneCtx &c, int32_t chunk, int32_t chunk_end, uint32_t *head_msg, uint32_t *head_words) {
-    uint32_t k = find_msg(c, chunk);
+// ------------------------------------------------------------------------------------------- group code ---
+#define TR_STEP(wd, k)                                                                      \
+    e = tr_next(c, wd, e, k); words += e >> 15; ev |= e;
+#define TR_STEP4(wd) TR_STEP(wd, 0) TR_STEP(wd, 1) TR_STEP(wd, 2) TR_STEP(wd, 3)
+
+// 16 transitions, no branches: e = state entry, words += word starts, ev |= every entry seen
+TR_HD void group16(const LaneCtx &c, const Quad &q, uint32_t &e, uint32_t &words, uint32_t &ev) {
+    TR_STEP4(q.a) TR_STEP4(q.b) TR_STEP4(q.c) TR_STEP4(q.d)
+}
+
+#define TR_STEPF(wd, k)                                                                     \
+    e = tr_next(c, wd, e, k); words += e >> 15;                                             \
+    if (e & 0x7F00u) apply_event(c, (e >> 8) & 0x7Fu, msg);
+#define TR_STEPF4(wd) TR_STEPF(wd, 0) TR_STEPF(wd, 1) TR_STEPF(wd, 2) TR_STEPF(wd, 3)
+
+// same 16 transitions with the (rare) events applied to message `msg`
+TR_HD void group16_events(const LaneCtx &c, const Quad &q, uint32_t &e, uint32_t &words, uint32_t msg) {
+    TR_STEPF4(q.a) TR_STEPF4(q.b) TR_STEPF4(q.c) TR_STEPF4(q.d)
+}
+
+// counted group: fast pass, replayed with event handling only when some transition carried an event
+TR_HD void group16_counted(const LaneCtx &c, const Quad &q, uint32_t &e, uint32_t &words, uint32_t msg) {
+    uint32_t e0 = e, w0 = words, ev = 0;
+    group16(c, q, e, words, ev);
+    if (ev & 0x7F00u) {
+        e = e0;
+        words = w0;
+        group16_events(c, q, e, words, msg);
+    }
+}
+
+TR_HD uint32_t low_mask(int32_t nbytes) { return nbytes <= 0 ? 0u : (nbytes >= 4 ? 0xFFFFFFFFu : ((1u << (8 * nbytes)) - 1u)); }
+// bytes [0, h) of the group <- pad
+TR_HD Quad mask_head(Quad q, int32_t h, uint32_t pad4) {
+    uint32_t m0 = low_mask(h), m1 = low_mask(h - 4), m2 = low_mask(h - 8), m3 = low_mask(h - 12);
+    q.a = (q.a & ~m0) | (pad4 & m0); q.b = (q.b & ~m1) | (pad4 & m1);
+    q.c = (q.c & ~m2) | (pad4 & m2); q.d = (q.d & ~m3) | (pad4 & m3);
+    return q;
+}
+// bytes [t, 16) of the group <- pad
+TR_HD Quad mask_tail(Quad q, int32_t t, uint32_t pad4) {
+    uint32_t m0 = ~low_mask(t), m1 = ~low_mask(t - 4), m2 = ~low_mask(t - 8), m3 = ~low_mask(t - 12);
+    q.a = (q.a & ~m0) | (pad4 & m0); q.b = (q.b & ~m1) | (pad4 & m1);
+    q.c = (q.c & ~m2) | (pad4 & m2); q.d = (q.d & ~m3) | (pad4 & m3);
+    return q;
+}
+TR_HD Quad load_quad(const LaneCtx &c, int32_t p) { return *reinterpret_cast<const Quad *>(c.stage + p + c.warm); }
+
+// ------------------------------------------------------------------------------------------- fast lane ---
+// Walks the lane's chunk [chunk, chunk_end) (tile-relative, chunk 16-aligned).  Every finished segment is flushed with
+// atomics except the partial word count of the message at the chunk start, which is returned in (*head_msg,
+// *head_words) so the caller can combine neighbouring lanes first.  k = list index of the message containing `chunk`.
+TR_HD void lane_scan_fast(const LaneCtx &c, int32_t chunk, int32_t chunk_end, uint32_t k, uint32_t *head_msg, uint32_t *head_words) {
     int32_t mstart = list_at(c, k), mend = list_at(c, k + 1);
     uint32_t msg = c.msg_lo + k;
-    // warm-up
+    // warm-up: state becomes exact at `chunk`
+    const int32_t ws = chunk - c.warm;
+    uint32_t e = mstart >= ws ? c.start_state : c.neutral_state;
+    {
+        uint32_t wdummy = 0, evdummy = 0;
+        for (int32_t g = ws; g < chunk; g += 16) {
+            if (mstart >= g + 16) continue;   // the whole group precedes the message
+            Quad q = load_quad(c, g);
+            if (mstart > g) q = mask_head(q, mstart - g, c.head_pad4);
+            group16(c, q, e, wdummy, evdummy);
+        }
+    }
+    uint32_t words = 0;
+    bool first = true;
+    *head_msg = msg;
+    *head_words = 0;
+    bool open = true;   // a message is in progress (its words not flushed yet)
+    for (int32_t g = chunk; g < chunk_end; g += 16) {
+        const int32_t gend = g + 16;
+        Quad q0 = load_quad(c, g);
+        if (mend > gend) {   // common case: the message runs through this whole group
+            group16_counted(c, q0, e, words, msg);
+            continue;
+        }
+        // one or more messages end inside (g, gend]
+        int32_t cur = g;
+        for (;;) {
+            const bool ends = mend <= gend;
+            const int32_t t = ends ? mend : gend;
+            Quad q = q0;
+            if (cur > g) q = mask_head(q, cur - g, c.head_pad4);
+            if (t < gend) q = mask_tail(q, t - g, c.tail_pad4);   // the first pad byte emits the end-of-message output
+            group16_counted(c, q, e, words, msg);
+            if (!ends) break;   // the (new) message continues into the next group
+            if (t == gend) {    // ended exactly on the group boundary: no pad byte was read, take the output from the table
+                uint32_t eo = c.eom[e & 0xFFu];
+                words += eo >> 7;
+                if (eo & 0x7Fu) apply_event(c, eo & 0x7Fu, msg);
+            }
+            if (c.stage[t - 1 + c.warm] == '?') tr_or(c.counters + (uint64_t)msg * CNT_STRIDE + CNT_Q, 1u);   // HasSuffix "?"
+            if (first) { *head_words = words; first = false; }
+            else if (words) tr_add(c.counters + (uint64_t)msg * CNT_STRIDE + CNT_WORDS, words);
+            words = 0;
+            open = false;
+            if (t >= chunk_end) break;
+            do { k++; } while (list_at(c, k + 1) == list_at(c, k));   // next non-empty message
+            msg = c.msg_lo + k;
+            mend = list_at(c, k + 1);
+            e = c.start_state;
+            open = true;
+            cur = t;
+            if (t == gend) break;   // it starts exactly at the next group
+        }
+    }
+    if (open) {   // the chunk ended inside a message: flush the partial count
+        if (first) *head_words = words;
+        else if (words) tr_add(c.counters + (uint64_t)msg * CNT_STRIDE + CNT_WORDS, words);
+    }
+}
+
+// ------------------------------------------------------------------------------------------- slow lane ---
+// Fallback for dictionaries without usable pad bytes: same walk, byte at a time around boundaries.
+TR_HD void step_slow(const LaneCtx &c, uint32_t byte, uint32_t &e, uint32_t &words, uint32_t msg, bool count) {
+    e = tr_entry(c.tbl, (e & 0xFFu) * kRowBytes + 2u * byte);
+    if (count) {
+        words += e >> 15;
+        uint32_t id = (e >> 8) & 0x7Fu;
+        if (id) apply_event(c, id, msg);
+    }
+}
+TR_HD void run_slow(const LaneCtx &c, int32_t a, int32_t b, uint32_t &e, uint32_t &words, uint32_t msg, bool count) {
+    for (int32_t p = a; p < b; p++) step_slow(c, c.stage[p + c.warm], e, words, msg, count);
+}
+TR_HD void run_range(const LaneCtx &c, int32_t a, int32_t b, uint32_t &e, uint32_t &words, uint32_t msg, bool count) {
+    int32_t p = a;
+    int32_t head = (16 - ((p + c.warm) & 15)) & 15;   // stage is 16-byte aligned at index 0
+    if (head > b - p) head = b - p;
+    if (head) { run_slow(c, p, p + head, e, words, msg, count); p += head; }
+    for (; p + 16 <= b; p += 16) {
+        Quad q = load_quad(c, p);
+        if (count) group16_counted(c, q, e, words, msg);
+        else { uint32_t w = 0, ev = 0; group16(c, q, e, w, ev); }
+    }
+    if (p < b) run_slow(c, p, b, e, words, msg, count);
+}
+TR_HD void lane_scan_slow(const LaneCtx &c, int32_t chunk, int32_t chunk_end, uint32_t k, uint32_t *head_msg, uint32_t *head_words) {
+    int32_t mstart = list_at(c, k), mend = list_at(c, k + 1);
+    uint32_t msg = c.msg_lo + k;
     int32_t ws = chunk - c.warm;
     uint32_t e;
     if (ws <= mstart) { ws = mstart; e = c.start_state; } else e = c.neutral_state;
@@ -165,12 +291,12 @@ TR_HD void lane_scan(const LaneCtx &c, int32_t chunk, int32_t chunk_end, uint32_
             uint32_t eo = c.eom[e & 0xFFu];
             words += eo >> 7;
             if (eo & 0x7Fu) apply_event(c, eo & 0x7Fu, msg);
-            if (c.stage[pos - 1 + c.warm] == '?') tr_or(c.counters + (uint64_t)msg * CNT_STRIDE + CNT_Q, 1u);  // HasSuffix "?"
+            if (c.stage[pos - 1 + c.warm] == '?') tr_or(c.counters + (uint64_t)msg * CNT_STRIDE + CNT_Q, 1u);
         }
         if (first) { *head_words = words; first = false; }
         else if (words) tr_add(c.counters + (uint64_t)msg * CNT_STRIDE + CNT_WORDS, words);
         words = 0;
-        if (pos == mend && pos < chunk_end) {   // next non-empty message
+        if (pos == mend && pos < chunk_end) {
             do { k++; } while (list_at(c, k + 1) == list_at(c, k));
             msg = c.msg_lo + k;
             mend = list_at(c, k + 1);

@@ -18,8 +18,10 @@ extern "C" {
 int hostcheck_scan(const uint8_t *prios, const uint8_t *cis, const uint32_t *lens, const uint8_t *lits, uint32_t n_pat,
                    const uint64_t *offsets, const uint8_t *bytes, uint32_t n_msgs,
                    uint32_t nt, uint32_t chunk, int use_abs_list,
-                   uint32_t *counters /* n_msgs * 8 */, uint32_t *info /* states, unmin, warm, events */, char *err, uint32_t errcap)
+                   uint32_t *counters /* n_msgs * 8 */, uint32_t *info /* states, unmin, warm, events, head_pad, tail_pad */,
+                   char *err, uint32_t errcap)
 {
+    // use_abs_list bit 0: global-offset message list; bit 1: force the byte-at-a-time fallback lane
     std::vector<DictEntry> dict;
     size_t o = 0;
     for (uint32_t i = 0; i < n_pat; i++) {
@@ -30,6 +32,7 @@ int hostcheck_scan(const uint8_t *prios, const uint8_t *cis, const uint32_t *len
     std::string e = build_dfa(dict, &dfa);
     if (!e.empty()) { std::strncpy(err, e.c_str(), errcap - 1); err[errcap - 1] = 0; return 4; }
     info[0] = dfa.n_states; info[1] = dfa.n_states_unminimised; info[2] = dfa.warm_bytes; info[3] = (uint32_t)dfa.events.size();
+    info[4] = (uint32_t)dfa.head_pad; info[5] = (uint32_t)dfa.tail_pad;
     if (n_msgs == 0) return 0;
     std::vector<EventPacked> ev(dfa.events.size());
     for (size_t i = 0; i < dfa.events.size(); i++) {
@@ -37,6 +40,11 @@ int hostcheck_scan(const uint8_t *prios, const uint8_t *cis, const uint32_t *len
         ev[i] = {uint32_t(v.kw[0]) | uint32_t(v.kw[1]) << 16, uint32_t(v.kw[2]) | uint32_t(v.kw[3]) << 16,
                  uint32_t(v.pos) | uint32_t(v.neg) << 8 | uint32_t(v.question) << 16, 0};
     }
+    // padded rows, exactly as the engine uploads them
+    std::vector<uint8_t> tbl((size_t)dfa.n_states * kRowBytes, 0);
+    for (uint32_t st = 0; st < dfa.n_states; st++)
+        std::memcpy(tbl.data() + (size_t)st * kRowBytes, dfa.table.data() + (size_t)st * 256, 512);
+    const bool fast = !(use_abs_list & 2) && dfa.head_pad >= 0 && dfa.tail_pad >= 0;
     std::memset(counters, 0, sizeof(uint32_t) * 8 * n_msgs);
     uint64_t total = offsets[n_msgs];
     uint64_t tile = uint64_t(nt) * chunk;
@@ -47,11 +55,9 @@ int hostcheck_scan(const uint8_t *prios, const uint8_t *cis, const uint32_t *len
     uint64_t ntiles = (total + tile - 1) / tile;
     for (uint64_t t = 0; t < ntiles; t++) {
         uint64_t ts = t * tile, te = std::min(total, ts + tile);
-        // stage [ts - warm, te)
-        std::memset(stage, 0xEE, tile + warm);
+        std::memset(stage, 0xEE, tile + warm + 16);
         uint64_t cs = ts >= (uint64_t)warm ? ts - warm : 0;
         std::memcpy(stage + (cs - (ts - warm)), bytes + cs, te - cs);
-        // messages intersecting the tile: upper_bound(offsets, ts) - 1 .. first boundary >= te
         uint32_t lo = 0, hi = n_msgs + 1;
         while (lo < hi) { uint32_t mid = (lo + hi) / 2; if (offsets[mid] > ts) hi = mid; else lo = mid + 1; }
         uint32_t mlo = lo - 1, mhi = mlo;
@@ -63,17 +69,23 @@ int hostcheck_scan(const uint8_t *prios, const uint8_t *cis, const uint32_t *len
             list.push_back((int32_t)(r < -lim ? -lim : (r > lim ? lim : r)));
         }
         LaneCtx c;
-        c.tbl = dfa.table.data(); c.events = ev.data(); c.eom = dfa.eom.data(); c.stage = stage;
-        c.list = use_abs_list ? nullptr : list.data(); c.list_abs = offsets; c.tile_start = (int64_t)ts;
+        c.tbl = tbl.data(); c.events = ev.data(); c.eom = dfa.eom.data(); c.stage = stage;
+        c.list = (use_abs_list & 1) ? nullptr : list.data(); c.list_abs = offsets; c.tile_start = (int64_t)ts;
         c.list_n = (uint32_t)list.size(); c.msg_lo = mlo; c.counters = counters; c.warm = warm;
         c.start_state = dfa.start_state; c.neutral_state = dfa.neutral_state;
+        c.tbl_s = 0;
+        c.head_pad4 = 0x01010101u * (uint32_t)(dfa.head_pad & 0xFF); c.tail_pad4 = 0x01010101u * (uint32_t)(dfa.tail_pad & 0xFF);
         int32_t tile_len = (int32_t)(te - ts);
+        uint32_t khint = 0;
         for (uint32_t l = 0; l < nt; l++) {
             int32_t ch = (int32_t)(l * chunk);
             if (ch >= tile_len) break;
             int32_t ce = std::min<int32_t>(ch + (int32_t)chunk, tile_len);
             uint32_t hm = 0, hw = 0;
-            lane_scan(c, ch, ce, &hm, &hw);
+            if ((l & 31) == 0) khint = find_msg(c, ch);           // the warp's first lane searches, the others walk forward
+            uint32_t k = find_msg_from(c, ch, khint);
+            if (fast) lane_scan_fast(c, ch, ce, k, &hm, &hw);
+            else lane_scan_slow(c, ch, ce, k, &hm, &hw);
             if (hw) counters[(uint64_t)hm * 8 + CNT_WORDS] += hw;
         }
     }

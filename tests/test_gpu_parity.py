@@ -39,7 +39,7 @@ def _meta_from_cases(cases):
 
 def test_dictionary_facts(eng):
     info = eng.dict_info()
-    assert 100 <= info["states"] <= 256 and info["warm_bytes"] == 16 and info["table_bytes"] == info["states"] * 512
+    assert 100 <= info["states"] <= 256 and info["warm_bytes"] == 16 and info["table_bytes"] == info["states"] * 516
     assert eng.dict_count(1) == 4 and eng.dict_count(2) == 5 and eng.dict_count(3) == 0
 
 
