@@ -188,9 +188,13 @@ def main():
     eng = mq.Engine(device=local)
     info = eng.dict_info()
 
-    pad = np.zeros(((total + 31) // 16) * 16, np.uint8)
-    pad[:total] = data
+    # the engine's preferred wire format: 16-byte aligned message starts + reset-pad fill
+    content_bytes = total
+    off, lens, pad = eng.pack_padded(off, data)
+    del data
+    total = int(off[-1])
     d_bytes = torch.from_numpy(pad).to(dev)
+    d_len = torch.from_numpy(lens.view(np.int32)).to(dev)
     d_off = torch.from_numpy(off.view(np.int64)).to(dev)
     d_meta = torch.from_numpy(meta.view(np.uint8).reshape(n, 16)).to(dev)
     d_res = torch.zeros((n, 16), dtype=torch.uint8, device=dev)
@@ -204,7 +208,8 @@ def main():
     torch.cuda.synchronize()
 
     def step():
-        adm = eng.submit_device(d_off.data_ptr(), d_bytes.data_ptr(), total, d_meta.data_ptr(), None, n, d_res.data_ptr(), d_ord.data_ptr())
+        adm = eng.submit_device_padded(d_off.data_ptr(), d_len.data_ptr(), d_bytes.data_ptr(), total, d_meta.data_ptr(), None, n,
+                                       d_res.data_ptr(), d_ord.data_ptr())
         t = eng.timings()
         if world > 1:
             eng.merge_allgather(rank_base, d_gord.data_ptr(), n * world)
@@ -259,6 +264,7 @@ def main():
     e2e = None
     if not args.skip_e2e:
         h_bytes = eng.host_array(len(pad)); h_bytes[:] = pad
+        h_len = eng.host_array(lens.nbytes, np.uint32); h_len[:] = lens
         h_off = eng.host_array(off.nbytes, np.uint64); h_off[:] = off
         h_meta = eng.host_array(meta.nbytes, np.uint8).view(mq.META_DTYPE); h_meta[:] = meta
         h_res = eng.host_array(n * 16, np.uint8).view(mq.RESULT_DTYPE)
@@ -267,7 +273,8 @@ def main():
         base = C.c_uint64()
 
         def e2e_step():
-            rc = lib.triage_submit(eng._h, 0, h_off.ctypes.data, h_bytes.ctypes.data, h_meta.ctypes.data, None, n, h_res.ctypes.data, C.byref(base))
+            rc = lib.triage_submit_padded(eng._h, 0, h_off.ctypes.data, h_len.ctypes.data, h_bytes.ctypes.data, h_meta.ctypes.data, None, n,
+                                          h_res.ctypes.data, C.byref(base))
             if rc != 0:
                 raise RuntimeError(lib.triage_last_error())
         e2e_steps = max(2, min(args.steps, 5))
@@ -284,17 +291,17 @@ def main():
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         e2e_s = float(tt[0])
         adm_now = int(h_res["accepted"].sum())
-        e2e = {"value": n * world / e2e_s, "unit": "msgs/s", "h2d_bytes_per_step": int(total + 8 * (n + 1) + 16 * n),
+        e2e = {"value": n * world / e2e_s, "unit": "msgs/s", "h2d_bytes_per_step": int(total + 8 * (n + 1) + 4 * n + 16 * n),
                "d2h_bytes_per_step": int(16 * n + 4 * adm_now), "ms_per_step": 1000 * e2e_s, "steps": e2e_steps,
-               "api": "triage_submit (C ABI, pinned host buffers from triage_host_alloc; H2D, kernels, D2H of results + order inside)"}
+               "api": "triage_submit_padded (C ABI, pinned host buffers from triage_host_alloc; H2D, kernels, D2H of results + order inside)"}
 
     if rank == 0:
         peak, peak_src = measured_peak()
         t_scan = sum(scan_ms) / len(scan_ms)
-        alg = total + 8 * (n + 1) + 32 * n     # sum(len) + offsets + 16 B meta in + 16 B result out
+        alg = total + 8 * (n + 1) + 4 * n + 32 * n     # arena (padded) + offsets + lengths + 16 B meta in + 16 B result out
         achieved = alg / (t_scan / 1000) / 1e9
         traffic = scan_traffic_from_profile()
-        roofline = {"bound": "hbm", "kernel": "scan_kernel<1024,48>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+        roofline = {"bound": "hbm", "kernel": "scan_padded_kernel (24 warps x 80 B/lane)", "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": achieved / peak, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg,
                     "kernel_ms": t_scan, "traffic": traffic["dram_bytes_per_launch"] if traffic else None,
                     "step_share": {"scan_ms": t_scan, "finalize_ms": sum(fin_ms) / len(fin_ms), "order_ms": sum(ord_ms) / len(ord_ms),
@@ -314,7 +321,7 @@ def main():
         line = {"metric": METRIC, "value": value, "unit": "msgs/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
                 "data": "synthetic", "config": workload_config(world) | {"messages_per_gpu": n, "global_messages": n * world,
-                                                                          "arena_bytes_per_gpu": total, "automaton_states": info["states"],
+                                                                          "arena_bytes_per_gpu": total, "content_bytes_per_gpu": content_bytes, "arena_layout": "padded16 (16-byte aligned starts, TAB reset pads)", "automaton_states": info["states"],
                                                                           "order_passes": passes},
                 "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
                 "timing": {"device_ms_total": dev_ms_max, "wall_ms_total": wall_ms_max, "admitted": adm}}

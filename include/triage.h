@@ -127,6 +127,22 @@ int32_t triage_submit(triage_engine *e, int32_t target_queue, const uint64_t *of
  * api/handlers.go:178-202).  target_queue = a queue id pushes the whole batch into that one queue with
  * item priority = int(msg.Priority): QueueManager.BatchPushMessages(queueName, msgs) (queue_manager.go:246-287). */
 
+/* -- padded arena: the engine's preferred wire format.  Message i starts at offsets[i] (a multiple of 16), holds
+ *    lengths[i] content bytes and is followed by 1..16 copies of triage_pad_byte() up to offsets[i+1]; offsets[n] is the
+ *    padded total.  The pad byte resets the automaton, so the scan never has to split a 16-byte group at a message
+ *    boundary.  A shim that copies Content into its arena anyway lays it out like this for free
+ *    (triage_pack_padded does it for an existing packed arena).  Same semantics and results as triage_submit.      */
+int32_t triage_pad_byte(triage_engine *e, int32_t *pad);      /* -1: this dictionary has none, use the packed calls */
+int32_t triage_pack_padded(const uint64_t *src_offsets, const uint8_t *src_bytes, uint32_t n, int32_t pad,
+                           uint64_t *dst_offsets, uint32_t *dst_lengths, uint8_t *dst_bytes, uint64_t *dst_total);
+int32_t triage_submit_padded(triage_engine *e, int32_t target_queue, const uint64_t *offsets, const uint32_t *lengths,
+                             const uint8_t *bytes, const triage_meta *meta, const uint64_t *enqueue_ns, uint32_t n,
+                             triage_result *out, uint64_t *handle_base);
+int32_t triage_submit_device_padded(triage_engine *e, const uint64_t *offsets_dev, const uint32_t *lengths_dev,
+                                    const uint8_t *bytes_dev, uint64_t total_bytes, const triage_meta *meta_dev,
+                                    const uint64_t *enqueue_ns_dev, uint32_t n, triage_result *results_dev,
+                                    uint32_t *order_dev, uint32_t *n_admitted);
+
 /* ProcessMessage only (preprocessor.go:56-114) for a batch: labels + analysis, no queue is touched. */
 int32_t triage_process(triage_engine *e, const uint64_t *offsets, const uint8_t *bytes,
                        const triage_meta *meta, uint32_t n, triage_result *out);

@@ -77,6 +77,13 @@ _SIGS = {
     "triage_process": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
     "triage_submit_device": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
                                          C.c_uint32, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32)]),
+    "triage_pad_byte": (C.c_int32, [C.c_void_p, C.POINTER(C.c_int32)]),
+    "triage_pack_padded": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                       C.POINTER(C.c_uint64)]),
+    "triage_submit_padded": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                         C.c_uint32, C.c_void_p, C.POINTER(C.c_uint64)]),
+    "triage_submit_device_padded": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p,
+                                                C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32)]),
     "triage_submit_device_static": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
                                                 C.c_uint32, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32)]),
     "triage_queue_create": (C.c_int32, [C.c_void_p, C.c_int64, C.POINTER(C.c_int32)]),
@@ -131,6 +138,21 @@ def pack_contents(contents):
         np.cumsum([len(c) for c in contents], out=offsets[1:])
     data = np.frombuffer(b"".join(contents), dtype=np.uint8).copy() if offsets[-1] else np.zeros(0, np.uint8)
     return offsets, data
+
+
+def pack_padded(offsets, data, pad: int, out_bytes=None):
+    n = len(offsets) - 1
+    dst_off = np.zeros(n + 1, np.uint64)
+    dst_len = np.zeros(max(n, 1), np.uint32)
+    total = C.c_uint64()
+    src = data if len(data) else np.zeros(1, np.uint8)
+    _check(lib().triage_pack_padded(_p(offsets), _p(src), n, pad, _p(dst_off), _p(dst_len), None, C.byref(total)))
+    if out_bytes is None:
+        out_bytes = np.empty(max(total.value, 16), np.uint8)
+    elif len(out_bytes) < total.value:
+        raise ValueError("out_bytes too small")
+    _check(lib().triage_pack_padded(_p(offsets), _p(src), n, pad, _p(dst_off), _p(dst_len), _p(out_bytes), C.byref(total)))
+    return dst_off, dst_len[:n], out_bytes[:total.value]
 
 
 class Engine:
@@ -197,6 +219,30 @@ class Engine:
         buf = data if len(data) else np.zeros(16, np.uint8)
         _check(lib().triage_submit(self._h, int(target_queue), _p(offsets), _p(buf), _p(meta), _p(ts), n, _p(out), C.byref(base)))
         return out, base.value
+
+    def pad_byte(self) -> int:
+        v = C.c_int32()
+        _check(lib().triage_pad_byte(self._h, C.byref(v)))
+        return v.value
+
+    def pack_padded(self, offsets, data, out_bytes=None):
+        """packed (offsets, bytes) -> padded layout (offsets u64[n+1], lengths u32[n], bytes u8[total]).  out_bytes: an
+        optional preallocated (e.g. pinned) uint8 array to fill."""
+        return pack_padded(offsets, data, self.pad_byte(), out_bytes)
+
+    def submit_padded(self, offsets, lengths, data, meta, ts=None, target_queue=0):
+        n = len(lengths)
+        out = np.zeros(n, dtype=RESULT_DTYPE)
+        base = C.c_uint64()
+        _check(lib().triage_submit_padded(self._h, int(target_queue), _p(offsets), _p(lengths), _p(data), _p(meta), _p(ts), n, _p(out),
+                                          C.byref(base)))
+        return out, base.value
+
+    def submit_device_padded(self, offsets_ptr, lengths_ptr, bytes_ptr, total, meta_ptr, ts_ptr, n, results_ptr, order_ptr) -> int:
+        adm = C.c_uint32()
+        _check(lib().triage_submit_device_padded(self._h, offsets_ptr, lengths_ptr, bytes_ptr, int(total), meta_ptr, ts_ptr, int(n),
+                                                 results_ptr, order_ptr, C.byref(adm)))
+        return adm.value
 
     def submit_device(self, offsets_ptr, bytes_ptr, total, meta_ptr, ts_ptr, n, results_ptr, order_ptr) -> int:
         adm = C.c_uint32()

@@ -489,8 +489,17 @@ std::string build_dfa(const std::vector<DictEntry> &dict, Dfa *out) {
     auto entry = [&](uint32_t st, uint32_t b) { return out->table[static_cast<size_t>(st) * 256 + b]; };
     std::vector<uint32_t> cand = {0x09, 0x0B, 0x0C, 0x0A, 0x0D, 0x20};
     for (uint32_t b = 0; b < 256; b++) cand.push_back(b);
-    out->head_pad = out->tail_pad = -1;
+    out->head_pad = out->tail_pad = out->reset_pad = -1;
     for (uint32_t b : cand) {
+        if (out->reset_pad < 0) {
+            bool ok = true;
+            for (uint32_t st = 0; st < nmin && ok; st++) {
+                uint16_t t = entry(st, b);
+                uint8_t emitted = static_cast<uint8_t>(((t >> 8) & 0x7F) | ((t & 0x8000) ? 0x80 : 0));
+                if (emitted != out->eom[st] || (t & 0xFF) != out->start_state) ok = false;
+            }
+            if (ok && out->eom[out->start_state] == 0) out->reset_pad = static_cast<int>(b);
+        }
         if (out->head_pad < 0 && entry(out->start_state, b) == out->start_state) out->head_pad = static_cast<int>(b);
         if (out->tail_pad < 0) {
             bool ok = true;

@@ -49,6 +49,7 @@ struct Dfa {
     // pad bytes for the scan's in-register boundary masking (-1: none exists for this dictionary)
     int head_pad = -1;   // START --head_pad--> START with no output
     int tail_pad = -1;   // from every state: reading it emits exactly that state's end-of-message output, then nothing
+    int reset_pad = -1;  // tail_pad that additionally lands in START from every state: the padded arena's fill byte
 };
 
 // returns "" on success, else a message (too many states / events for D8, bordered pattern, ...)

@@ -13,6 +13,7 @@
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/triage.h"
@@ -117,7 +118,7 @@ struct triage_engine {
     DevBuf<int64_t> d_maxsize;
     DevBuf<triage_meta> d_meta;
     DevBuf<triage_result> d_results;
-    DevBuf<uint32_t> d_counters, d_tile_first, d_order, d_perm_a, d_perm_b, d_blockhist, d_totals, d_small;
+    DevBuf<uint32_t> d_lengths, d_counters, d_tile_first, d_order, d_perm_a, d_perm_b, d_blockhist, d_totals, d_small;
     DevBuf<uint8_t> d_bucket, d_bucket2;
     uint32_t *h_small = nullptr;   // pinned: [0] flags, [1] n_admitted, [2..17] bucket counts, [32..] digit hist
     std::vector<uint32_t> h_order;
@@ -161,7 +162,8 @@ int32_t commit_dict(triage_engine *e) {
     DeviceDfa d{};
     d.n_states = dfa.n_states; d.n_events = (uint32_t)ev.size(); d.warm = dfa.warm_bytes;
     d.start_state = dfa.start_state; d.neutral_state = dfa.neutral_state;
-    d.head_pad = dfa.head_pad; d.tail_pad = dfa.tail_pad;
+    d.head_pad = dfa.head_pad; d.tail_pad = dfa.tail_pad; d.reset_pad = dfa.reset_pad;
+    if (d.reset_pad >= 0 && scan_padded_smem_bytes(d) > (size_t)e->max_smem_optin) d.reset_pad = -1;   // padded kernel would not fit
     ScanGeometry geom = pick_scan_geometry(d, (size_t)e->max_smem_optin);
     if (geom.nt == 0)
         return fail(TRIAGE_E_PATTERN, "dictionary automaton (" + std::to_string(dfa.n_states) + " states) does not fit in shared memory");
@@ -188,18 +190,25 @@ int32_t commit_dict(triage_engine *e) {
 // The whole device pipeline on e->stream.  All pointers are device pointers.
 enum RunMode { RUN_ROUTED = 0, RUN_SINGLE_QUEUE = 1, RUN_PROCESS_ONLY = 2 };
 
-int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, const uint8_t *bytes, uint64_t total,
+// lengths == nullptr: packed arena (message i = bytes[offsets[i], offsets[i+1])).  lengths != nullptr: padded arena
+// (16-byte aligned starts, 1..16 reset-pad bytes after every message, offsets[n] = padded total).
+int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, const uint32_t *lengths, const uint8_t *bytes, uint64_t total,
                    const triage_meta *meta, const uint64_t *ts, uint32_t n, triage_result *results, uint32_t *order,
                    const uint64_t pending[4], const int64_t max_size[4], uint32_t *n_admitted) {
     int32_t rc = commit_dict(e);
     if (rc) return rc;
     if ((reinterpret_cast<uintptr_t>(bytes) & 15) != 0) return fail(TRIAGE_E_ARG, "device arena must be 16-byte aligned");
+    const bool padded = lengths != nullptr;
+    if (padded && e->ddfa.reset_pad < 0)
+        return fail(TRIAGE_E_ARG, "this dictionary has no reset pad byte: use the packed (unpadded) entry points");
+    if (padded && (total & 15)) return fail(TRIAGE_E_ARG, "padded arena size must be a multiple of 16");
     cudaStream_t s = e->stream;
     uint32_t launches = 0;
     e->tm = triage_timings{};
     *n_admitted = 0;
     if (n == 0) return TRIAGE_OK;
-    const uint32_t ntiles = (uint32_t)((total + e->geom.tile - 1) / e->geom.tile);
+    const uint32_t tile_bytes = padded ? kPadMiniTile : e->geom.tile;
+    const uint32_t ntiles = (uint32_t)((total + tile_bytes - 1) / tile_bytes);
     const uint32_t nblocks = (n + kOrderBlock - 1) / kOrderBlock;
     CU(e->d_counters.ensure((size_t)n * CNT_STRIDE));
     CU(e->d_tile_first.ensure((size_t)ntiles + 2));
@@ -215,17 +224,19 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     CU(cudaEventRecord(e->ev[0], s));
     CU(cudaMemsetAsync(e->d_counters.p, 0, (size_t)n * CNT_STRIDE * sizeof(uint32_t), s));
     CU(cudaMemsetAsync(e->d_small.p, 0, (32 + 8 * 256) * sizeof(uint32_t), s));
-    ScanArgs sa{bytes, offsets, total, n, e->d_counters.p, e->d_tile_first.p, ntiles, e->geom.tile};
+    ScanArgs sa{bytes, offsets, total, n, e->d_counters.p, e->d_tile_first.p, ntiles, tile_bytes};
     if (ntiles) {
         CU(launch_tile_index(sa, s)); launches++;
         CU(cudaEventRecord(e->ev[1], s));
-        CU(launch_scan(sa, e->ddfa, e->geom, e->sm_count, s)); launches++;
+        if (padded) CU(launch_scan_padded(sa, e->ddfa, e->sm_count, s));
+        else CU(launch_scan(sa, e->ddfa, e->geom, e->sm_count, s));
+        launches++;
     } else {
         CU(cudaEventRecord(e->ev[1], s));
     }
     CU(cudaEventRecord(e->ev[2], s));
     const int32_t single = mode == RUN_SINGLE_QUEUE ? 1 : 0;
-    FinalizeArgs fa{e->d_counters.p, meta, offsets, ts, n, e->default_prio, mode == RUN_PROCESS_ONLY ? 0 : e->opts.rules_enabled,
+    FinalizeArgs fa{lengths, bytes, e->d_counters.p, meta, offsets, ts, n, e->default_prio, mode == RUN_PROCESS_ONLY ? 0 : e->opts.rules_enabled,
                     single, results, e->d_bucket.p, e->d_small.p};
     CU(launch_finalize(fa, s)); launches++;
     CU(cudaEventRecord(e->ev[3], s));
@@ -237,7 +248,7 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
         cudaEventElapsedTime(&ms0, e->ev[2], e->ev[3]); e->tm.finalize_ms = ms0;
         cudaEventElapsedTime(&ms0, e->ev[0], e->ev[4]); e->tm.total_ms = ms0;
         e->tm.launches = launches;
-        e->tm.scan_bytes = total + 8ull * (n + 1) + 32ull * n;
+        e->tm.scan_bytes = total + 8ull * (n + 1) + 32ull * n + (padded ? 4ull * n : 0);
         return TRIAGE_OK;
     }
     const uint8_t *bucket = e->d_bucket.p;
@@ -292,7 +303,7 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     cudaEventElapsedTime(&ms, e->ev[0], e->ev[4]); e->tm.total_ms = ms;
     e->tm.launches = launches;
     e->tm.order_passes = passes;
-    e->tm.scan_bytes = total + 8ull * (n + 1) + 32ull * n;
+    e->tm.scan_bytes = total + 8ull * (n + 1) + 32ull * n + (padded ? 4ull * n : 0);
     return TRIAGE_OK;
 }
 
@@ -341,7 +352,7 @@ void triage_destroy(triage_engine *e) {
     if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
     e->d_table.release(); e->d_events.release(); e->d_eom.release(); e->d_bytes.release(); e->d_offsets.release();
     e->d_ts.release(); e->d_pending.release(); e->d_maxsize.release(); e->d_meta.release(); e->d_results.release(); e->d_counters.release();
-    e->d_tile_first.release(); e->d_order.release(); e->d_perm_a.release(); e->d_perm_b.release(); e->d_blockhist.release();
+    e->d_tile_first.release(); e->d_lengths.release(); e->d_order.release(); e->d_perm_a.release(); e->d_perm_b.release(); e->d_blockhist.release();
     e->d_totals.release(); e->d_small.release(); e->d_bucket.release(); e->d_bucket2.release(); e->d_run_keys.release();
     e->d_all_keys.release(); e->d_header.release(); e->d_all_header.release(); e->d_run_gidx.release(); e->d_all_gidx.release();
     if (e->h_small) cudaFreeHost(e->h_small);
@@ -433,17 +444,21 @@ int32_t triage_submit_device(triage_engine *e, const uint64_t *offsets_dev, cons
     CU(cudaSetDevice(e->opts.device));
     const uint64_t pending[4] = {0, 0, 0, 0};
     const int64_t ms[4] = {e->opts.max_queue_size, e->opts.max_queue_size, e->opts.max_queue_size, e->opts.max_queue_size};
-    return run_device(e, RUN_ROUTED, offsets_dev, bytes_dev, total_bytes, meta_dev, enqueue_ns_dev, n, results_dev, order_dev, pending, ms,
-                      n_admitted);
+    return run_device(e, RUN_ROUTED, offsets_dev, nullptr, bytes_dev, total_bytes, meta_dev, enqueue_ns_dev, n, results_dev, order_dev,
+                      pending, ms, n_admitted);
 }
 
 namespace {
 
 // H2D of one batch into the engine's own buffers.  offsets are rebased to start at 0.
-int32_t upload_batch(triage_engine *e, const uint64_t *offsets, const uint8_t *bytes, const triage_meta *meta,
+int32_t upload_batch(triage_engine *e, const uint64_t *offsets, const uint32_t *lengths, const uint8_t *bytes, const triage_meta *meta,
                      const uint64_t *enqueue_ns, uint32_t n, uint64_t *total_out) {
     const uint64_t total = offsets[n] - offsets[0];
     if (total && !bytes) return fail(TRIAGE_E_ARG, "null arena");
+    if (lengths) {
+        if ((offsets[0] & 15) || (total & 15)) return fail(TRIAGE_E_ARG, "padded arena: offsets must be multiples of 16");
+        CU(e->d_lengths.ensure(n));
+    }
     cudaStream_t s = e->stream;
     CU(e->d_bytes.ensure(total + 32));
     CU(e->d_offsets.ensure((size_t)n + 1));
@@ -462,6 +477,7 @@ int32_t upload_batch(triage_engine *e, const uint64_t *offsets, const uint8_t *b
     CU(cudaMemsetAsync(e->d_bytes.p + total, 0, 32, s));   // the last tile's bulk copy rounds up to 16 bytes
     CU(cudaMemcpyAsync(e->d_offsets.p, off_src, ((size_t)n + 1) * 8, cudaMemcpyHostToDevice, s));
     CU(cudaMemcpyAsync(e->d_meta.p, meta, (size_t)n * sizeof(triage_meta), cudaMemcpyHostToDevice, s));
+    if (lengths) CU(cudaMemcpyAsync(e->d_lengths.p, lengths, (size_t)n * 4, cudaMemcpyHostToDevice, s));
     if (enqueue_ns) CU(cudaMemcpyAsync(e->d_ts.p, enqueue_ns, (size_t)n * 8, cudaMemcpyHostToDevice, s));
     CU(cudaStreamSynchronize(s));   // `rebased` goes out of scope; also separates the H2D time
     *total_out = total;
@@ -478,14 +494,14 @@ int32_t triage_process(triage_engine *e, const uint64_t *offsets, const uint8_t 
     if (n == 0) return TRIAGE_OK;
     auto t0 = std::chrono::steady_clock::now();
     uint64_t total = 0;
-    int32_t rc = upload_batch(e, offsets, bytes, meta, nullptr, n, &total);
+    int32_t rc = upload_batch(e, offsets, nullptr, bytes, meta, nullptr, n, &total);
     if (rc) return rc;
     auto t1 = std::chrono::steady_clock::now();
     const uint64_t pending[4] = {0, 0, 0, 0};
     const int64_t ms[4] = {0, 0, 0, 0};
     uint32_t n_adm = 0;
-    rc = run_device(e, RUN_PROCESS_ONLY, e->d_offsets.p, e->d_bytes.p, total, e->d_meta.p, nullptr, n, e->d_results.p, e->d_order.p,
-                    pending, ms, &n_adm);
+    rc = run_device(e, RUN_PROCESS_ONLY, e->d_offsets.p, nullptr, e->d_bytes.p, total, e->d_meta.p, nullptr, n, e->d_results.p,
+                    e->d_order.p, pending, ms, &n_adm);
     if (rc) return rc;
     auto t2 = std::chrono::steady_clock::now();
     CU(cudaMemcpyAsync(out, e->d_results.p, (size_t)n * sizeof(triage_result), cudaMemcpyDeviceToHost, e->stream));
@@ -496,8 +512,8 @@ int32_t triage_process(triage_engine *e, const uint64_t *offsets, const uint8_t 
     return TRIAGE_OK;
 }
 
-int32_t triage_submit(triage_engine *e, int32_t target_queue, const uint64_t *offsets, const uint8_t *bytes, const triage_meta *meta,
-                      const uint64_t *enqueue_ns, uint32_t n, triage_result *out, uint64_t *handle_base) {
+static int32_t submit_impl(triage_engine *e, int32_t target_queue, const uint64_t *offsets, const uint32_t *lengths, const uint8_t *bytes,
+                           const triage_meta *meta, const uint64_t *enqueue_ns, uint32_t n, triage_result *out, uint64_t *handle_base) {
     if (!e || (n && (!offsets || !meta))) return fail(TRIAGE_E_ARG, "null argument");
     CU(cudaSetDevice(e->opts.device));
     std::lock_guard<std::mutex> lock(e->mu);
@@ -507,7 +523,7 @@ int32_t triage_submit(triage_engine *e, int32_t target_queue, const uint64_t *of
     cudaStream_t s = e->stream;
     auto t0 = std::chrono::steady_clock::now();
     uint64_t total = 0;
-    int32_t rc = upload_batch(e, offsets, bytes, meta, enqueue_ns, n, &total);
+    int32_t rc = upload_batch(e, offsets, lengths, bytes, meta, enqueue_ns, n, &total);
     if (rc) return rc;
     auto t1 = std::chrono::steady_clock::now();
     uint64_t pending[4] = {0, 0, 0, 0};
@@ -519,8 +535,8 @@ int32_t triage_submit(triage_engine *e, int32_t target_queue, const uint64_t *of
         ms[0] = e->q[target_queue].max_size;
     }
     uint32_t n_adm = 0;
-    rc = run_device(e, target_queue ? RUN_SINGLE_QUEUE : RUN_ROUTED, e->d_offsets.p, e->d_bytes.p, total, e->d_meta.p,
-                    enqueue_ns ? e->d_ts.p : nullptr, n, e->d_results.p, e->d_order.p, pending, ms, &n_adm);
+    rc = run_device(e, target_queue ? RUN_SINGLE_QUEUE : RUN_ROUTED, e->d_offsets.p, lengths ? e->d_lengths.p : nullptr, e->d_bytes.p, total,
+                    e->d_meta.p, enqueue_ns ? e->d_ts.p : nullptr, n, e->d_results.p, e->d_order.p, pending, ms, &n_adm);
     if (rc) return rc;
     auto t2 = std::chrono::steady_clock::now();
     triage_result *res = out;
@@ -554,6 +570,72 @@ int32_t triage_submit(triage_engine *e, int32_t target_queue, const uint64_t *of
             std::inplace_merge(lq.items.begin() + lq.head, lq.items.begin() + run_begin[l], lq.items.end(), qless);
     }
     e->next_handle = base + n;
+    return TRIAGE_OK;
+}
+
+int32_t triage_submit(triage_engine *e, int32_t target_queue, const uint64_t *offsets, const uint8_t *bytes, const triage_meta *meta,
+                      const uint64_t *enqueue_ns, uint32_t n, triage_result *out, uint64_t *handle_base) {
+    return submit_impl(e, target_queue, offsets, nullptr, bytes, meta, enqueue_ns, n, out, handle_base);
+}
+
+int32_t triage_submit_padded(triage_engine *e, int32_t target_queue, const uint64_t *offsets, const uint32_t *lengths, const uint8_t *bytes,
+                             const triage_meta *meta, const uint64_t *enqueue_ns, uint32_t n, triage_result *out, uint64_t *handle_base) {
+    if (n && !lengths) return fail(TRIAGE_E_ARG, "null lengths");
+    return submit_impl(e, target_queue, offsets, lengths, bytes, meta, enqueue_ns, n, out, handle_base);
+}
+
+int32_t triage_submit_device_padded(triage_engine *e, const uint64_t *offsets_dev, const uint32_t *lengths_dev, const uint8_t *bytes_dev,
+                                    uint64_t total_bytes, const triage_meta *meta_dev, const uint64_t *enqueue_ns_dev, uint32_t n,
+                                    triage_result *results_dev, uint32_t *order_dev, uint32_t *n_admitted) {
+    if (!e || !n_admitted || (n && (!offsets_dev || !lengths_dev || !meta_dev || !results_dev || !order_dev))) return fail(TRIAGE_E_ARG, "null argument");
+    if (total_bytes && !bytes_dev) return fail(TRIAGE_E_ARG, "null arena");
+    CU(cudaSetDevice(e->opts.device));
+    const uint64_t pending[4] = {0, 0, 0, 0};
+    const int64_t ms[4] = {e->opts.max_queue_size, e->opts.max_queue_size, e->opts.max_queue_size, e->opts.max_queue_size};
+    return run_device(e, RUN_ROUTED, offsets_dev, lengths_dev, bytes_dev, total_bytes, meta_dev, enqueue_ns_dev, n, results_dev, order_dev,
+                      pending, ms, n_admitted);
+}
+
+int32_t triage_pad_byte(triage_engine *e, int32_t *pad) {
+    if (!e || !pad) return fail(TRIAGE_E_ARG, "null argument");
+    CU(cudaSetDevice(e->opts.device));
+    int32_t rc = commit_dict(e);
+    if (rc) return rc;
+    *pad = e->ddfa.reset_pad;
+    return TRIAGE_OK;
+}
+
+// Host-side arena builder for shims: packed (offsets, bytes) -> padded layout.  dst_bytes == NULL only computes
+// dst_offsets / dst_lengths / *dst_total so the caller can size its (pinned) arena.
+int32_t triage_pack_padded(const uint64_t *src_offsets, const uint8_t *src_bytes, uint32_t n, int32_t pad, uint64_t *dst_offsets,
+                           uint32_t *dst_lengths, uint8_t *dst_bytes, uint64_t *dst_total) {
+    if ((n && !src_offsets) || !dst_offsets || !dst_lengths || !dst_total || pad < 0 || pad > 255) return fail(TRIAGE_E_ARG, "bad argument");
+    uint64_t o = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        uint64_t len = src_offsets[i + 1] - src_offsets[i];
+        if (len > 0xFFFFFFFFull) return fail(TRIAGE_E_ARG, "message longer than 4 GiB");
+        dst_offsets[i] = o;
+        dst_lengths[i] = (uint32_t)len;
+        o += (len / 16 + 1) * 16;   // 1..16 pad bytes after every message
+    }
+    dst_offsets[n] = o;
+    *dst_total = o;
+    if (!dst_bytes) return TRIAGE_OK;
+    unsigned hw = std::thread::hardware_concurrency();
+    unsigned nthr = hw ? (hw > 32 ? 32 : hw) : 4;
+    if (nthr > n) nthr = n ? n : 1;
+    std::vector<std::thread> th;
+    for (unsigned t = 0; t < nthr; t++) {
+        th.emplace_back([=]() {
+            uint32_t lo = (uint32_t)((uint64_t)n * t / nthr), hi = (uint32_t)((uint64_t)n * (t + 1) / nthr);
+            for (uint32_t i = lo; i < hi; i++) {
+                uint64_t len = dst_lengths[i];
+                if (len) std::memcpy(dst_bytes + dst_offsets[i], src_bytes + src_offsets[i], len);
+                std::memset(dst_bytes + dst_offsets[i] + len, pad, dst_offsets[i + 1] - dst_offsets[i] - len);
+            }
+        });
+    }
+    for (auto &x : th) x.join();
     return TRIAGE_OK;
 }
 
@@ -915,7 +997,8 @@ extern "C" int32_t triage_submit_device_static(triage_engine *e, const uint64_t 
         CU(cudaEventRecord(e->ev[1], s));
     }
     CU(cudaEventRecord(e->ev[2], s));
-    FinalizeArgs fa{counters, meta_dev, offsets_dev, enqueue_ns_dev, n, e->default_prio, e->opts.rules_enabled, 0, results_dev, bucket, small};
+    FinalizeArgs fa{nullptr, nullptr, counters, meta_dev, offsets_dev, enqueue_ns_dev, n, e->default_prio, e->opts.rules_enabled, 0, results_dev,
+                    bucket, small};
     CU(launch_finalize(fa, s)); launches++;
     CU(cudaEventRecord(e->ev[3], s));
     const uint8_t *bk = bucket;

@@ -274,6 +274,165 @@ cudaError_t launch_scan(const ScanArgs &a, const DeviceDfa &d, const ScanGeometr
     return cudaErrorInvalidValue;
 }
 
+// ----------------------------------------------------------------------------- padded scan --
+// Warp-autonomous variant for the padded arena: every warp owns a double-buffered staging area, its own pair of
+// mbarriers and a small message list, takes 32*C-byte mini-tiles round-robin and never meets a CTA-wide barrier
+// after the automaton has been loaded.
+struct PadSmem { uint32_t table, events, stage0, list0, total, stage_bytes, list_bytes; };
+constexpr uint32_t kPadListCap = 34;
+__host__ __device__ inline PadSmem pad_layout(uint32_t n_states, uint32_t n_events, uint32_t warm) {
+    PadSmem L;
+    uint32_t o = 1024;   // mbarriers
+    L.table = o; o += ((n_states * kRowBytes + 127u) / 128u) * 128u;
+    L.events = o; o += ((n_events * 16u + 127u) / 128u) * 128u;
+    L.stage_bytes = ((warm + kPadMiniTile + 16u + 127u) / 128u) * 128u;
+    L.stage0 = o; o += kPadWarps * 2 * L.stage_bytes;
+    L.list_bytes = 160;
+    L.list0 = o; o += kPadWarps * 2 * L.list_bytes;
+    L.total = o;
+    return L;
+}
+size_t scan_padded_smem_bytes(const DeviceDfa &d) { return pad_layout(d.n_states, d.n_events, d.warm).total; }
+
+__global__ void __launch_bounds__(kPadWarps * 32, 1) scan_padded_kernel(ScanArgs a, DeviceDfa d) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    constexpr int C = kPadChunk;
+    constexpr uint32_t MT = kPadMiniTile;
+    const PadSmem L = pad_layout(d.n_states, d.n_events, d.warm);
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem) + warp * 2;
+    uint8_t *tbl = smem + L.table;
+    EventPacked *events = reinterpret_cast<EventPacked *>(smem + L.events);
+    auto stage_of = [&](uint32_t b) -> uint8_t * { return smem + L.stage0 + (warp * 2 + b) * L.stage_bytes; };
+    auto list_of = [&](uint32_t b) -> int32_t * { return reinterpret_cast<int32_t *>(smem + L.list0 + (warp * 2 + b) * L.list_bytes); };
+    const uint32_t warm = d.warm;
+
+    if (lane == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    {
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(d.table);
+        uint32_t *dst = reinterpret_cast<uint32_t *>(tbl);
+        for (uint32_t i = tid; i < d.n_states * (kRowBytes / 4); i += kPadWarps * 32) dst[i] = src[i];
+        const uint4 *es = reinterpret_cast<const uint4 *>(d.events);
+        uint4 *ed = reinterpret_cast<uint4 *>(events);
+        for (uint32_t i = tid; i < d.n_events; i += kPadWarps * 32) ed[i] = es[i];
+    }
+    __syncthreads();   // the only CTA-wide barrier
+
+    const uint32_t stride = gridDim.x * kPadWarps;
+    uint32_t t = blockIdx.x * kPadWarps + warp;
+    if (t >= a.ntiles) return;
+    const uint32_t nmine = (a.ntiles - t + stride - 1) / stride;
+
+    auto issue = [&](uint32_t mt, uint32_t buf) {   // one lane
+        uint64_t ts = (uint64_t)mt * MT;
+        uint64_t te = ts + MT < a.total ? ts + MT : a.total;
+        uint64_t cs = ts >= warm ? ts - warm : 0;
+        uint32_t dst_off = (uint32_t)(cs + warm - ts);
+        uint32_t bytes = (uint32_t)(((te - cs) + 15u) & ~(uint64_t)15u);
+        mbar_expect_tx(&bars[buf], bytes);
+        tma_load_1d(stage_of(buf) + dst_off, a.bytes + cs, bytes, &bars[buf]);
+    };
+
+    uint32_t first_cur = a.tile_first[t], last_cur = a.tile_first[t + 1];
+    if (lane == 0) issue(t, 0);
+    {
+        uint32_t cnt = last_cur - first_cur + 2;
+        if (cnt <= kPadListCap) {
+            const uint64_t ts = (uint64_t)t * MT;
+            if (lane < cnt) list_of(0)[lane] = rel_clamp(a.offsets[first_cur + lane], ts);
+            if (lane + 32 < cnt) list_of(0)[lane + 32] = rel_clamp(a.offsets[first_cur + lane + 32], ts);
+        }
+    }
+    uint32_t first_nxt = 0, last_nxt = 0;
+    if (nmine > 1) { first_nxt = a.tile_first[t + stride]; last_nxt = a.tile_first[t + stride + 1]; }
+    __syncwarp();
+
+    for (uint32_t k = 0; k < nmine; k++, t += stride) {
+        const uint32_t buf = k & 1;
+        const bool has_next = k + 1 < nmine;
+        if (has_next && lane == 0) issue(t + stride, buf ^ 1);
+        uint64_t n0 = 0, n1 = 0;
+        uint32_t cnt_nxt = 0, first_nn = 0, last_nn = 0;
+        if (has_next) {
+            cnt_nxt = last_nxt - first_nxt + 2;
+            if (cnt_nxt <= kPadListCap) {
+                if (lane < cnt_nxt) n0 = a.offsets[first_nxt + lane];
+                if (lane + 32 < cnt_nxt) n1 = a.offsets[first_nxt + lane + 32];
+            }
+            if (k + 2 < nmine) { first_nn = a.tile_first[t + 2 * stride]; last_nn = a.tile_first[t + 2 * stride + 1]; }
+        }
+        const uint64_t ts = (uint64_t)t * MT;
+        const int32_t len = (int32_t)((ts + MT < a.total ? ts + MT : a.total) - ts);
+        const uint32_t cnt_cur = last_cur - first_cur + 2;
+
+        LaneCtx c;
+        c.tbl = tbl; c.events = events; c.eom = nullptr; c.stage = stage_of(buf);
+        c.list = cnt_cur <= kPadListCap ? list_of(buf) : nullptr;
+        c.list_abs = a.offsets; c.tile_start = (int64_t)ts;
+        c.list_n = cnt_cur; c.msg_lo = first_cur; c.counters = a.counters; c.warm = (int32_t)warm;
+        c.start_state = d.start_state; c.neutral_state = d.neutral_state;
+        c.head_pad4 = c.tail_pad4 = 0;
+        c.tbl_s = smem_u32(tbl);
+
+        mbar_wait(&bars[buf], (k >> 1) & 1);
+
+        uint32_t hm = 0xFFFFFFFFu, hw = 0;
+        const int32_t chunk = (int32_t)(lane * C);
+        if (chunk < len) {
+            int32_t ce = chunk + C < len ? chunk + C : len;
+            lane_scan_padded(c, chunk, ce, find_msg(c, chunk), t == 0 && lane == 0, &hm, &hw);
+        }
+        {   // combine the head partials of neighbouring lanes that sit in the same message
+            const unsigned full = 0xFFFFFFFFu;
+            uint32_t prev = __shfl_up_sync(full, hm, 1);
+            bool head = lane == 0 || hm != prev;
+            uint32_t heads = __ballot_sync(full, head);
+            uint32_t v = hw;
+#pragma unroll
+            for (int dlt = 1; dlt < 32; dlt <<= 1) {
+                uint32_t tt = __shfl_up_sync(full, v, dlt);
+                if ((int)lane >= dlt) v += tt;
+            }
+            uint32_t above = heads & ~((2u << lane) - 1u);
+            uint32_t end = above ? (uint32_t)__ffs(above) - 2u : 31u;
+            uint32_t upto = __shfl_sync(full, v, end);
+            uint32_t before = __shfl_up_sync(full, v, 1);
+            if (lane == 0) before = 0;
+            if (head && hm != 0xFFFFFFFFu) {
+                uint32_t sum = upto - before;
+                if (sum) atomicAdd(a.counters + (uint64_t)hm * CNT_STRIDE + CNT_WORDS, sum);
+            }
+        }
+        if (has_next && cnt_nxt <= kPadListCap) {
+            const uint64_t tsn = ts + (uint64_t)stride * MT;
+            if (lane < cnt_nxt) list_of(buf ^ 1)[lane] = rel_clamp(n0, tsn);
+            if (lane + 32 < cnt_nxt) list_of(buf ^ 1)[lane + 32] = rel_clamp(n1, tsn);
+        }
+        first_cur = first_nxt; last_cur = last_nxt;
+        first_nxt = first_nn; last_nxt = last_nn;
+        __syncwarp();
+    }
+}
+
+cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, int sm_count, cudaStream_t s) {
+    if (a.ntiles == 0) return cudaSuccess;
+    size_t smem = scan_padded_smem_bytes(d);
+    static size_t configured = 0;
+    if (smem > configured) {
+        cudaError_t e = cudaFuncSetAttribute(scan_padded_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        configured = smem;
+    }
+    uint32_t need = (a.ntiles + kPadWarps - 1) / kPadWarps;
+    uint32_t grid = need < (uint32_t)sm_count ? need : (uint32_t)sm_count;
+    scan_padded_kernel<<<grid, kPadWarps * 32, smem, s>>>(a, d);
+    return cudaGetLastError();
+}
+
 // -------------------------------------------------------------------------------- finalize --
 __global__ void __launch_bounds__(256) finalize_kernel(FinalizeArgs a) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -281,7 +440,8 @@ __global__ void __launch_bounds__(256) finalize_kernel(FinalizeArgs a) {
     const uint4 c0 = reinterpret_cast<const uint4 *>(a.counters)[2 * (uint64_t)i];
     const uint4 c1 = reinterpret_cast<const uint4 *>(a.counters)[2 * (uint64_t)i + 1];
     const uint4 mraw = reinterpret_cast<const uint4 *>(a.meta)[i];
-    const uint64_t len = a.offsets[i + 1] - a.offsets[i];
+    const uint64_t off_i = a.offsets[i];
+    const uint64_t len = a.lengths ? (uint64_t)a.lengths[i] : a.offsets[i + 1] - off_i;
     const uint32_t preset = mraw.x & 0xFFu, up = (mraw.x >> 8) & 0xFFu, ud = (mraw.x >> 16) & 0xFFu, mp = mraw.x >> 24;
     const uint32_t mflags = mraw.y & 0xFFu;
     const uint32_t sc[5] = {0, c0.y, c0.z, c0.w, c1.x};
@@ -313,6 +473,7 @@ __global__ void __launch_bounds__(256) finalize_kernel(FinalizeArgs a) {
             words = c0.x;
             sentiment = c1.y > c1.z ? 1 : (c1.z > c1.y ? -1 : 0);
             question = c1.w ? 1 : 0;
+            if (a.lengths && a.bytes[off_i + len - 1] == '?') question = 1;   // HasSuffix(content, "?") (the unpadded scan does it itself)
             rflags |= TRIAGE_RF_HAS_ANALYSIS;
         }
     }

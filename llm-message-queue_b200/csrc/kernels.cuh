@@ -21,6 +21,7 @@ struct DeviceDfa {
     const uint8_t *eom;          // 256 (padded)
     uint32_t n_states, n_events, warm, start_state, neutral_state;
     int32_t head_pad, tail_pad;  // -1: no inert pad byte exists, use the byte-at-a-time boundary path
+    int32_t reset_pad;           // fill byte of the padded arena layout (-1: this dictionary has none)
 };
 
 struct ScanArgs {
@@ -34,7 +35,16 @@ struct ScanArgs {
     uint32_t tile_bytes;         // = geometry.tile
 };
 
+// padded-arena scan: warps are autonomous (own staging buffers, own mbarriers, no CTA barrier in the loop)
+constexpr uint32_t kPadWarps = 24;
+constexpr uint32_t kPadChunk = 80;
+constexpr uint32_t kPadMiniTile = 32 * kPadChunk;   // bytes per warp iteration
+size_t scan_padded_smem_bytes(const DeviceDfa &d);
+cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, int sm_count, cudaStream_t s);
+
 struct FinalizeArgs {
+    const uint32_t *lengths;     // padded layout: true content lengths (else nullptr: len = offsets[i+1]-offsets[i])
+    const uint8_t *bytes;        // padded layout: for the HasSuffix "?" test
     const uint32_t *counters;
     const triage_meta *meta;
     const uint64_t *offsets;

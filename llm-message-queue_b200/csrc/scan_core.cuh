@@ -245,6 +245,42 @@ TR_HD void lane_scan_fast(const LaneCtx &c, int32_t chunk, int32_t chunk_end, ui
     }
 }
 
+// ----------------------------------------------------------------------------------------- padded lane ---
+// Padded arena layout (the engine's preferred wire format): every message starts on a 16-byte boundary and is followed
+// by 1..16 copies of the dictionary's pad byte up to the next message.  The pad byte is a RESET symbol of the automaton
+// (from every state it emits that state's end-of-message output and lands in START), so a lane never needs to know where
+// messages end to keep its state right: boundaries only matter for attributing counts, and they always fall between
+// groups.  No masks, no end-of-message table, no second pass.  k = list index of the message containing `chunk`;
+// list holds the (padded) message starts.  at_arena_start: nothing precedes `chunk` (first lane of the first tile).
+TR_HD void lane_scan_padded(const LaneCtx &c, int32_t chunk, int32_t chunk_end, uint32_t k, bool at_arena_start,
+                            uint32_t *head_msg, uint32_t *head_words) {
+    uint32_t e = c.start_state;
+    if (!at_arena_start) {
+        e = c.neutral_state;
+        uint32_t wdummy = 0, evdummy = 0;
+        for (int32_t g = chunk - c.warm; g < chunk; g += 16) group16(c, load_quad(c, g), e, wdummy, evdummy);
+    }
+    int32_t mend = list_at(c, k + 1);
+    uint32_t msg = c.msg_lo + k;
+    uint32_t words = 0;
+    bool first = true;
+    *head_msg = msg;
+    *head_words = 0;
+    for (int32_t g = chunk; g < chunk_end; g += 16) {
+        if (g >= mend) {   // the previous message (and its pads) ended exactly here
+            if (first) { *head_words = words; first = false; }
+            else if (words) tr_add(c.counters + (uint64_t)msg * CNT_STRIDE + CNT_WORDS, words);
+            words = 0;
+            k++;
+            msg++;
+            mend = list_at(c, k + 1);
+        }
+        group16_counted(c, load_quad(c, g), e, words, msg);
+    }
+    if (first) *head_words = words;
+    else if (words) tr_add(c.counters + (uint64_t)msg * CNT_STRIDE + CNT_WORDS, words);
+}
+
 // ------------------------------------------------------------------------------------------- slow lane ---
 // Fallback for dictionaries without usable pad bytes: same walk, byte at a time around boundaries.
 TR_HD void step_slow(const LaneCtx &c, uint32_t byte, uint32_t &e, uint32_t &words, uint32_t msg, bool count) {

@@ -270,7 +270,11 @@ class QueueManager:
             if name not in self._ids:
                 raise ErrQueueNotFound
         offsets, data, meta = pack_messages(messages, preprocessor.user_priorities)
-        res, base = self.engine.submit(offsets, data, meta, enqueue_ns, 0)
+        if self.engine.pad_byte() >= 0:   # preferred wire format: 16-byte aligned starts + reset pads
+            poff, plen, pbytes = self.engine.pack_padded(offsets, data)
+            res, base = self.engine.submit_padded(poff, plen, pbytes, meta, enqueue_ns, 0)
+        else:
+            res, base = self.engine.submit(offsets, data, meta, enqueue_ns, 0)
         now = time.time()
         for i, (m, r) in enumerate(zip(messages, res)):
             apply_result(m, r, now)

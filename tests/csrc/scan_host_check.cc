@@ -124,3 +124,74 @@ extern "C" int hostcheck_table(const uint8_t *prios, const uint8_t *cis, const u
     info[0] = dfa.n_states; info[1] = dfa.start_state; info[2] = dfa.neutral_state; info[3] = dfa.warm_bytes;
     return 0;
 }
+
+// padded-arena variant: re-packs the input the way the engine's packer does (16-byte aligned starts, 1..16 reset pads
+// after every message), then walks warp mini-tiles of 32*chunk bytes with lane_scan_padded
+extern "C" int hostcheck_scan_padded(const uint8_t *prios, const uint8_t *cis, const uint32_t *lens, const uint8_t *lits, uint32_t n_pat,
+                                     const uint64_t *offsets, const uint8_t *bytes, uint32_t n_msgs, uint32_t chunk, int use_abs_list,
+                                     uint32_t *counters, uint32_t *info, char *err, uint32_t errcap)
+{
+    std::vector<DictEntry> dict;
+    size_t o = 0;
+    for (uint32_t i = 0; i < n_pat; i++) {
+        dict.push_back({prios[i], cis[i] != 0, std::string(reinterpret_cast<const char *>(lits + o), lens[i])});
+        o += lens[i];
+    }
+    Dfa dfa;
+    std::string e = build_dfa(dict, &dfa);
+    if (!e.empty()) { std::strncpy(err, e.c_str(), errcap - 1); err[errcap - 1] = 0; return 4; }
+    info[0] = dfa.n_states; info[1] = (uint32_t)dfa.reset_pad;
+    if (dfa.reset_pad < 0) { std::strncpy(err, "no reset pad", errcap - 1); return 5; }
+    if (n_msgs == 0) return 0;
+    std::vector<EventPacked> ev(dfa.events.size());
+    for (size_t i = 0; i < dfa.events.size(); i++) {
+        const EventVec &v = dfa.events[i];
+        ev[i] = {uint32_t(v.kw[0]) | uint32_t(v.kw[1]) << 16, uint32_t(v.kw[2]) | uint32_t(v.kw[3]) << 16,
+                 uint32_t(v.pos) | uint32_t(v.neg) << 8 | uint32_t(v.question) << 16, 0};
+    }
+    std::vector<uint8_t> tbl((size_t)dfa.n_states * kRowBytes, 0);
+    for (uint32_t st = 0; st < dfa.n_states; st++)
+        std::memcpy(tbl.data() + (size_t)st * kRowBytes, dfa.table.data() + (size_t)st * 256, 512);
+    // pack
+    std::vector<uint64_t> poff(n_msgs + 1, 0);
+    for (uint32_t i = 0; i < n_msgs; i++) poff[i + 1] = poff[i] + ((offsets[i + 1] - offsets[i]) / 16 + 1) * 16;
+    std::vector<uint8_t> arena(poff[n_msgs] + 32, (uint8_t)dfa.reset_pad);
+    for (uint32_t i = 0; i < n_msgs; i++) std::memcpy(arena.data() + poff[i], bytes + offsets[i], offsets[i + 1] - offsets[i]);
+    std::memset(counters, 0, sizeof(uint32_t) * 8 * n_msgs);
+    const uint64_t total = poff[n_msgs];
+    const uint64_t mt = 32ull * chunk;
+    const int32_t warm = (int32_t)dfa.warm_bytes;
+    std::vector<uint8_t> stage_raw(mt + warm + 64);
+    uint8_t *stage = stage_raw.data();
+    while (reinterpret_cast<uintptr_t>(stage) & 15) stage++;
+    for (uint64_t ts = 0; ts < total; ts += mt) {
+        uint64_t te = std::min(total, ts + mt);
+        std::memset(stage, 0xEE, mt + warm + 16);
+        uint64_t cs = ts >= (uint64_t)warm ? ts - warm : 0;
+        std::memcpy(stage + (cs - (ts - warm)), arena.data() + cs, te - cs);
+        uint32_t lo = 0, hi = n_msgs + 1;
+        while (lo < hi) { uint32_t mid = (lo + hi) / 2; if (poff[mid] > ts) hi = mid; else lo = mid + 1; }
+        uint32_t mlo = lo - 1, mhi = mlo;
+        while (poff[mhi + 1] < te) mhi++;
+        std::vector<int32_t> list;
+        for (uint32_t m = mlo; m <= mhi + 1; m++) list.push_back((int32_t)((int64_t)poff[m] - (int64_t)ts));
+        LaneCtx c;
+        c.tbl = tbl.data(); c.events = ev.data(); c.eom = dfa.eom.data(); c.stage = stage;
+        c.list = use_abs_list ? nullptr : list.data(); c.list_abs = poff.data(); c.tile_start = (int64_t)ts;
+        c.list_n = (uint32_t)list.size(); c.msg_lo = mlo; c.counters = counters; c.warm = warm;
+        c.start_state = dfa.start_state; c.neutral_state = dfa.neutral_state; c.tbl_s = 0; c.head_pad4 = c.tail_pad4 = 0;
+        int32_t len = (int32_t)(te - ts);
+        for (uint32_t l = 0; l < 32; l++) {
+            int32_t ch = (int32_t)(l * chunk);
+            if (ch >= len) break;
+            int32_t ce = std::min<int32_t>(ch + (int32_t)chunk, len);
+            uint32_t hm = 0, hw = 0;
+            lane_scan_padded(c, ch, ce, find_msg(c, ch), ts == 0 && l == 0, &hm, &hw);
+            if (hw) counters[(uint64_t)hm * 8 + CNT_WORDS] += hw;
+        }
+    }
+    // HasSuffix "?" is applied by the finalize kernel in the padded pipeline
+    for (uint32_t i = 0; i < n_msgs; i++)
+        if (offsets[i + 1] > offsets[i] && bytes[offsets[i + 1] - 1] == '?') counters[(uint64_t)i * 8 + CNT_Q] |= 1;
+    return 0;
+}

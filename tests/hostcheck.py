@@ -48,3 +48,22 @@ def scan(dict_entries, offsets, data, nt=64, chunk=48, use_abs_list=False, force
         raise ValueError(err.value.decode())
     return counters[:n], dict(states=int(info[0]), unminimised=int(info[1]), warm=int(info[2]), events=int(info[3]),
                                 head_pad=int(np.int32(info[4])), tail_pad=int(np.int32(info[5])))
+
+
+def scan_padded(dict_entries, offsets, data, chunk=80, use_abs_list=False):
+    """same counters through the padded-arena lane (engine's preferred layout)"""
+    n = len(offsets) - 1
+    prios = np.array([d[0] for d in dict_entries], np.uint8)
+    cis = np.array([1 if d[1] else 0 for d in dict_entries], np.uint8)
+    lens = np.array([len(d[2]) for d in dict_entries], np.uint32)
+    lits = np.frombuffer(b"".join(d[2] for d in dict_entries) or b"\0", np.uint8)
+    counters = np.zeros((max(n, 1), 8), np.uint32)
+    info = np.zeros(6, np.uint32)
+    err = C.create_string_buffer(256)
+    buf = data if len(data) else np.zeros(1, np.uint8)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    rc = lib().hostcheck_scan_padded(p(prios), p(cis), p(lens), p(lits), len(dict_entries), p(offsets), p(buf), n,
+                                     chunk, 1 if use_abs_list else 0, p(counters), p(info), err, 256)
+    if rc != 0:
+        raise ValueError(err.value.decode())
+    return counters[:n], dict(states=int(info[0]), reset_pad=int(np.int32(info[1])))

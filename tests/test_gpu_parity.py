@@ -223,3 +223,70 @@ def test_device_resident_entry_matches_host_entry(eng):
         _assert_same(res, exp, FIELDS + ("accepted", "admit"))
         assert adm == len(order)
         assert np.array_equal(d_ord.cpu().numpy()[:adm].astype(np.uint32), order)
+
+
+@pytest.mark.parametrize("seed,n,lo,hi,edge,mix", [
+    (111, 20000, 256, 4096, 50, 0),
+    (112, 50000, 0, 48, 3000, 0),          # tiny + empty messages: more than 34 messages per mini-tile (global-offset list path)
+    (113, 300, 32768, 131072, 200, 0),
+    (114, 30000, 256, 16384, 50, 1),
+    (115, 20000, 256, 4096, 10000, 0),
+    (116, 3, 1, 5, 0, 0),
+])
+def test_padded_arena_path_vs_c_oracle(seed, n, lo, hi, edge, mix):
+    """The engine's preferred wire format (16-byte aligned starts, reset-pad fill) through triage_pack_padded +
+    triage_submit_padded: same bits as the oracle, rules and capacity included."""
+    off, data, meta, ts = co.generate(seed, n, lo, hi, mix=mix, edge=edge)
+    exp, order = co.pipeline(co.Dict(), off, data, meta, ts, rules_on=True, max_size=7000, nthreads=os.cpu_count() or 4)
+    e = mq.Engine(device=0, rules_enabled=True, max_queue_size=7000)
+    try:
+        assert e.pad_byte() == 9
+        poff, plen, pbytes = e.pack_padded(off, data)
+        assert (poff % 16 == 0).all() and np.array_equal(plen, (off[1:] - off[:-1]).astype(np.uint32))
+        res, base = e.submit_padded(poff, plen, pbytes, meta, ts)
+        _assert_same(res, exp, FIELDS + ("accepted", "admit"), ctx=f"padded seed {seed}")
+        handles, _ = e.drain(n)
+        assert np.array_equal((handles - base).astype(np.uint32), order)
+    finally:
+        e.close()
+
+
+def test_padded_edge_cases_vs_golden(golden_dir):
+    cases = json.load(open(os.path.join(golden_dir, "edge_cases.json")))
+    contents = [bytes.fromhex(e["content_hex"]) for e in cases]
+    off, data = co.pack(contents)
+    e = mq.Engine(device=0)
+    try:
+        poff, plen, pbytes = e.pack_padded(off, data)
+        res, _ = e.submit_padded(poff, plen, pbytes, _meta_from_cases(cases))
+        for i, c in enumerate(cases):
+            x, r = c["expect"], res[i]
+            got = dict(label=int(r["label"]), reason=int(r["reason"]), analyzed=bool(r["flags"] & 1), tie=bool(r["flags"] & 2),
+                       words=int(r["words"]), sentiment=int(r["sentiment"]), question=bool(r["question"]),
+                       has_analysis=bool(r["flags"] & 4), score_rt=int(r["score_rt"]), score_hi=int(r["score_hi"]))
+            assert got == x, (i, c["note"], contents[i][:40], got, x)
+    finally:
+        e.close()
+
+
+def test_padded_full_size_c2_properties():
+    n = 1 << 20
+    off, data, meta, ts = co.generate(0xC0FFEE02, n, 256, 4096, edge=50)
+    e = mq.Engine(device=0)
+    try:
+        poff, plen, pbytes = e.pack_padded(off, data)
+        res, base = e.submit_padded(poff, plen, pbytes, meta, None)
+        handles, levels = e.drain(n)
+        order = (handles - base).astype(np.int64)
+        acc = np.nonzero(res["accepted"])[0]
+        assert np.array_equal(order, acc[np.argsort(res["label"][acc], kind="stable")])
+        rng = np.random.default_rng(1)
+        sample = np.sort(rng.choice(n, 20000, replace=False))
+        so, sd = co.pack([bytes(data[int(off[i]):int(off[i + 1])]) for i in sample])
+        exp = co.process_batch(co.Dict(), so, sd, meta[sample], nthreads=os.cpu_count() or 4)
+        _assert_same(res[sample], exp)
+        # and the packed path gives the very same records
+        res2, base2 = e.submit(off, data, meta, None)
+        assert res2.tobytes() == res.tobytes()
+    finally:
+        e.close()
