@@ -303,8 +303,8 @@ __global__ void __launch_bounds__(kPadWarps * 32, 1) scan_padded_kernel(ScanArgs
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem) + warp * 2;
     uint8_t *tbl = smem + L.table;
     EventPacked *events = reinterpret_cast<EventPacked *>(smem + L.events);
-    auto stage_of = [&](uint32_t b) -> uint8_t * { return smem + L.stage0 + (warp * 2 + b) * L.stage_bytes; };
-    auto list_of = [&](uint32_t b) -> int32_t * { return reinterpret_cast<int32_t *>(smem + L.list0 + (warp * 2 + b) * L.list_bytes); };
+    uint8_t *stage_base = smem + L.stage0 + warp * 2 * L.stage_bytes;
+    int32_t *list_base = reinterpret_cast<int32_t *>(smem + L.list0 + warp * 2 * L.list_bytes);
     const uint32_t warm = d.warm;
 
     if (lane == 0) {
@@ -326,32 +326,43 @@ __global__ void __launch_bounds__(kPadWarps * 32, 1) scan_padded_kernel(ScanArgs
     uint32_t t = blockIdx.x * kPadWarps + warp;
     if (t >= a.ntiles) return;
     const uint32_t nmine = (a.ntiles - t + stride - 1) / stride;
+    const uint32_t last_tile = a.ntiles - 1;
+    const uint32_t last_bytes = (uint32_t)(a.total - (uint64_t)last_tile * MT);   // multiple of 16 (padded arena)
 
-    auto issue = [&](uint32_t mt, uint32_t buf) {   // one lane
-        uint64_t ts = (uint64_t)mt * MT;
-        uint64_t te = ts + MT < a.total ? ts + MT : a.total;
-        uint64_t cs = ts >= warm ? ts - warm : 0;
-        uint32_t dst_off = (uint32_t)(cs + warm - ts);
-        uint32_t bytes = (uint32_t)(((te - cs) + 15u) & ~(uint64_t)15u);
+    // one lane: bulk copy of mini-tile mt (plus the warm-up bytes before it) into buffer buf
+    auto issue = [&](uint32_t mt, uint32_t buf) {
+        const uint8_t *src = a.bytes + (uint64_t)mt * MT;
+        uint32_t bytes = mt == last_tile ? last_bytes : MT;
+        uint8_t *dst = stage_base + buf * L.stage_bytes + warm;
+        if (mt != 0) { src -= warm; dst -= warm; bytes += warm; }
         mbar_expect_tx(&bars[buf], bytes);
-        tma_load_1d(stage_of(buf) + dst_off, a.bytes + cs, bytes, &bars[buf]);
+        tma_load_1d(dst, src, bytes, &bars[buf]);
     };
 
     uint32_t first_cur = a.tile_first[t], last_cur = a.tile_first[t + 1];
     if (lane == 0) issue(t, 0);
+    uint64_t ts = (uint64_t)t * MT;
     {
         uint32_t cnt = last_cur - first_cur + 2;
         if (cnt <= kPadListCap) {
-            const uint64_t ts = (uint64_t)t * MT;
-            if (lane < cnt) list_of(0)[lane] = rel_clamp(a.offsets[first_cur + lane], ts);
-            if (lane + 32 < cnt) list_of(0)[lane + 32] = rel_clamp(a.offsets[first_cur + lane + 32], ts);
+            if (lane < cnt) list_base[lane] = rel_clamp(a.offsets[first_cur + lane], ts);
+            if (lane + 32 < cnt) list_base[lane + 32] = rel_clamp(a.offsets[first_cur + lane + 32], ts);
         }
     }
     uint32_t first_nxt = 0, last_nxt = 0;
     if (nmine > 1) { first_nxt = a.tile_first[t + stride]; last_nxt = a.tile_first[t + stride + 1]; }
     __syncwarp();
 
-    for (uint32_t k = 0; k < nmine; k++, t += stride) {
+    LaneCtx c;
+    c.tbl = tbl; c.events = events; c.eom = nullptr;
+    c.list_abs = a.offsets; c.counters = a.counters; c.warm = (int32_t)warm;
+    c.start_state = d.start_state; c.neutral_state = d.neutral_state;
+    c.head_pad4 = c.tail_pad4 = 0;
+    c.tbl_s = smem_u32(tbl);
+    const int32_t chunk = (int32_t)(lane * C);
+    const uint64_t ts_step = (uint64_t)stride * MT;
+
+    for (uint32_t k = 0; k < nmine; k++, t += stride, ts += ts_step) {
         const uint32_t buf = k & 1;
         const bool has_next = k + 1 < nmine;
         if (has_next && lane == 0) issue(t + stride, buf ^ 1);
@@ -365,26 +376,27 @@ __global__ void __launch_bounds__(kPadWarps * 32, 1) scan_padded_kernel(ScanArgs
             }
             if (k + 2 < nmine) { first_nn = a.tile_first[t + 2 * stride]; last_nn = a.tile_first[t + 2 * stride + 1]; }
         }
-        const uint64_t ts = (uint64_t)t * MT;
-        const int32_t len = (int32_t)((ts + MT < a.total ? ts + MT : a.total) - ts);
+        const int32_t len = t == last_tile ? (int32_t)last_bytes : (int32_t)MT;
         const uint32_t cnt_cur = last_cur - first_cur + 2;
-
-        LaneCtx c;
-        c.tbl = tbl; c.events = events; c.eom = nullptr; c.stage = stage_of(buf);
-        c.list = cnt_cur <= kPadListCap ? list_of(buf) : nullptr;
-        c.list_abs = a.offsets; c.tile_start = (int64_t)ts;
-        c.list_n = cnt_cur; c.msg_lo = first_cur; c.counters = a.counters; c.warm = (int32_t)warm;
-        c.start_state = d.start_state; c.neutral_state = d.neutral_state;
-        c.head_pad4 = c.tail_pad4 = 0;
-        c.tbl_s = smem_u32(tbl);
+        const int32_t *lst = list_base + buf * (L.list_bytes / 4);
+        c.stage = stage_base + buf * L.stage_bytes;
+        c.list = cnt_cur <= kPadListCap ? lst : nullptr;
+        c.tile_start = (int64_t)ts;
+        c.list_n = cnt_cur; c.msg_lo = first_cur;
 
         mbar_wait(&bars[buf], (k >> 1) & 1);
 
         uint32_t hm = 0xFFFFFFFFu, hw = 0;
-        const int32_t chunk = (int32_t)(lane * C);
         if (chunk < len) {
             int32_t ce = chunk + C < len ? chunk + C : len;
-            lane_scan_padded(c, chunk, ce, find_msg(c, chunk), t == 0 && lane == 0, &hm, &hw);
+            uint32_t km;
+            if (c.list) {   // few messages per mini-tile: count the starts at or before this lane's chunk
+                km = 0;
+                for (uint32_t j = 1; j + 1 < cnt_cur; j++) km += lst[j] <= chunk ? 1u : 0u;
+            } else {
+                km = find_msg(c, chunk);
+            }
+            lane_scan_padded(c, chunk, ce, km, t == 0 && lane == 0, &hm, &hw);
         }
         {   // combine the head partials of neighbouring lanes that sit in the same message
             const unsigned full = 0xFFFFFFFFu;
@@ -408,9 +420,10 @@ __global__ void __launch_bounds__(kPadWarps * 32, 1) scan_padded_kernel(ScanArgs
             }
         }
         if (has_next && cnt_nxt <= kPadListCap) {
-            const uint64_t tsn = ts + (uint64_t)stride * MT;
-            if (lane < cnt_nxt) list_of(buf ^ 1)[lane] = rel_clamp(n0, tsn);
-            if (lane + 32 < cnt_nxt) list_of(buf ^ 1)[lane + 32] = rel_clamp(n1, tsn);
+            int32_t *ln = list_base + (buf ^ 1) * (L.list_bytes / 4);
+            const uint64_t tsn = ts + ts_step;
+            if (lane < cnt_nxt) ln[lane] = rel_clamp(n0, tsn);
+            if (lane + 32 < cnt_nxt) ln[lane + 32] = rel_clamp(n1, tsn);
         }
         first_cur = first_nxt; last_cur = last_nxt;
         first_nxt = first_nn; last_nxt = last_nn;

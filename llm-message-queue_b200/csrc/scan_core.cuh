@@ -150,14 +150,22 @@ TR_HD void group16_events(const LaneCtx &c, const Quad &q, uint32_t &e, uint32_t
     TR_STEPF4(q.a) TR_STEPF4(q.b) TR_STEPF4(q.c) TR_STEPF4(q.d)
 }
 
-// counted group: fast pass, replayed with event handling only when some transition carried an event
+TR_HD void half8_events(const LaneCtx &c, uint32_t wa, uint32_t wb, uint32_t &e, uint32_t &words, uint32_t msg) {
+    TR_STEPF4(wa) TR_STEPF4(wb)
+}
+
+// counted group: fast pass; a half whose transitions carried an event is replayed with event handling (the word
+// counts of the fast pass stand, the replay only applies the events)
 TR_HD void group16_counted(const LaneCtx &c, const Quad &q, uint32_t &e, uint32_t &words, uint32_t msg) {
-    uint32_t e0 = e, w0 = words, ev = 0;
-    group16(c, q, e, words, ev);
-    if (ev & 0x7F00u) {
-        e = e0;
-        words = w0;
-        group16_events(c, q, e, words, msg);
+    const uint32_t e0 = e;
+    uint32_t ev = 0, ev2 = 0;
+    TR_STEP4(q.a) TR_STEP4(q.b)
+    const uint32_t e8 = e;
+    { uint32_t &ev = ev2; TR_STEP4(q.c) TR_STEP4(q.d) }
+    if ((ev | ev2) & 0x7F00u) {
+        uint32_t wdummy = 0;
+        if (ev & 0x7F00u) { uint32_t er = e0; half8_events(c, q.a, q.b, er, wdummy, msg); }
+        if (ev2 & 0x7F00u) { uint32_t er = e8; half8_events(c, q.c, q.d, er, wdummy, msg); }
     }
 }
 
