@@ -156,6 +156,7 @@ def main():
     ap.add_argument("--messages", type=int, default=N_PER_GPU, help="messages per GPU (default: the BASELINE config)")
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--interleave-ts", action="store_true", help="(test) explicit enqueue times that interleave across ranks: exercises the general merge")
     ap.add_argument("--check", action="store_true", help="verify the (merged) dequeue order against a numpy reference after warm-up")
     args = ap.parse_args()
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
@@ -201,6 +202,11 @@ def main():
     d_ord = torch.zeros(n, dtype=torch.int32, device=dev)
     d_gord = torch.zeros(n * world, dtype=torch.int32, device=dev) if world > 1 else None
     rank_base = (np.arange(world, dtype=np.uint64) * np.uint64(n))
+    ts_host = None
+    d_ts = None
+    if args.interleave_ts:
+        ts_host = (np.arange(n, dtype=np.uint64) * np.uint64(world) + np.uint64(rank)) * np.uint64(10) + np.uint64(10**18)
+        d_ts = torch.from_numpy(ts_host.view(np.int64)).to(dev)
     if world > 1:
         uid = [mq.Engine.comm_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
@@ -208,8 +214,8 @@ def main():
     torch.cuda.synchronize()
 
     def step():
-        adm = eng.submit_device_padded(d_off.data_ptr(), d_len.data_ptr(), d_bytes.data_ptr(), total, d_meta.data_ptr(), None, n,
-                                       d_res.data_ptr(), d_ord.data_ptr())
+        adm = eng.submit_device_padded(d_off.data_ptr(), d_len.data_ptr(), d_bytes.data_ptr(), total, d_meta.data_ptr(),
+                                       d_ts.data_ptr() if d_ts is not None else None, n, d_res.data_ptr(), d_ord.data_ptr())
         t = eng.timings()
         if world > 1:
             eng.merge_allgather(rank_base, d_gord.data_ptr(), n * world)
@@ -231,7 +237,16 @@ def main():
             bucket_all = bucket
             got = d_ord.cpu().numpy().astype(np.int64)
         idx = np.nonzero(bucket_all != 255)[0]
-        want = idx[np.argsort(bucket_all[idx], kind="stable")]
+        if ts_host is not None:   # (bucket, enqueue time, rank, arrival) order
+            allts = [None] * world
+            if world > 1:
+                dist.all_gather_object(allts, ts_host)
+            else:
+                allts = [ts_host]
+            ts_all = np.concatenate(allts)
+            want = idx[np.lexsort((idx, ts_all[idx], bucket_all[idx]))]
+        else:
+            want = idx[np.argsort(bucket_all[idx], kind="stable")]
         ok = len(want) <= len(got) and np.array_equal(got[:len(want)], want)
         print(f"[check rank {rank}] merged order {'OK' if ok else 'MISMATCH'} ({len(want)} admitted of {n * world})", file=sys.stderr, flush=True)
         if not ok:

@@ -816,15 +816,10 @@ extern "C" int32_t triage_merge_allgather(triage_engine *e, const uint64_t *rank
     cudaStream_t s = e->stream;
     const uint32_t R = (uint32_t)e->nranks;
     const uint32_t n_adm = e->last_n_adm;
-    // 1. my sorted run and its header
-    CU(e->d_run_keys.ensure(std::max<size_t>(n_adm, 1)));
-    CU(e->d_run_gidx.ensure(std::max<size_t>(n_adm, 1)));
+    // 1. header of my run (counts and first/last time key per bucket), gathered from every rank
     CU(e->d_header.ensure(kHeaderWords));
     CU(e->d_all_header.ensure((size_t)R * kHeaderWords));
-    uint64_t stamp_base = 0;   // ts == NULL: arrival index is the time; rank_base keeps ranks in sequence order
-    CU(launch_build_run(e->last_order, n_adm, e->last_bucket, e->last_ts, stamp_base + rank_base[e->rank], rank_base[e->rank],
-                        e->d_run_keys.p, e->d_run_gidx.p, s));
-    CU(launch_header(e->d_run_keys.p, n_adm, e->last_counts, e->d_header.p, s));
+    CU(launch_header(e->last_order, n_adm, e->last_counts, e->last_ts, rank_base[e->rank], e->d_header.p, s));
     ncclResult_t r = g_nccl.AllGather(e->d_header.p, e->d_all_header.p, kHeaderWords, ncclUint64, e->comm, s);
     if (r != ncclSuccess) return fail(TRIAGE_E_CUDA, std::string("ncclAllGather(header): ") + g_nccl.GetErrorString(r));
     CU(cudaMemcpyAsync(e->h_header, e->d_all_header.p, (size_t)R * kHeaderWords * 8, cudaMemcpyDeviceToHost, s));
@@ -834,10 +829,16 @@ extern "C" int32_t triage_merge_allgather(triage_engine *e, const uint64_t *rank
     t.n_ranks = R;
     uint64_t total = 0;
     uint32_t cap = 1;
-    for (uint32_t q = 0; q < R; q++) { t.cnt[q] = (uint32_t)e->h_header[q * kHeaderWords]; total += t.cnt[q]; cap = std::max(cap, t.cnt[q]); }
+    for (uint32_t q = 0; q < R; q++) {
+        t.cnt[q] = (uint32_t)e->h_header[q * kHeaderWords];
+        t.base[q] = (uint32_t)rank_base[q];
+        total += t.cnt[q];
+        cap = std::max(cap, t.cnt[q]);
+    }
     t.cap = cap;
     *n_total = total;
     if (total > capacity) return fail(TRIAGE_E_ARG, "order_global_dev is too small");
+    if (cap > e->last_n) return fail(TRIAGE_E_ARG, "ranks must submit equally sized batches (order buffers are gathered at a common stride)");
     bool disjoint = true;   // per bucket, rank q's keys all <= rank q+1's keys?
     uint32_t dst = 0;
     for (uint32_t b = 0; b < 16; b++) {
@@ -857,19 +858,27 @@ extern "C" int32_t triage_merge_allgather(triage_engine *e, const uint64_t *rank
         uint32_t acc = 0;
         for (uint32_t b = 0; b < 16; b++) { t.lstart[q][b] = acc; acc += (uint32_t)e->h_header[(size_t)q * kHeaderWords + 1 + b]; }
     }
-    // 3. all-gather the runs (equal counts per rank: padded to the largest run)
-    CU(e->d_run_keys.ensure(cap, true));
-    CU(e->d_run_gidx.ensure(cap, true));
-    CU(e->d_all_keys.ensure((size_t)R * cap));
+    // 3. all-gather the local dequeue orders (4 bytes per message; the caller's order buffer holds >= cap entries)
     CU(e->d_all_gidx.ensure((size_t)R * cap));
-    r = g_nccl.AllGather(e->d_run_keys.p, e->d_all_keys.p, cap, ncclUint64, e->comm, s);
-    if (r != ncclSuccess) return fail(TRIAGE_E_CUDA, std::string("ncclAllGather(keys): ") + g_nccl.GetErrorString(r));
-    r = g_nccl.AllGather(e->d_run_gidx.p, e->d_all_gidx.p, cap, ncclUint32, e->comm, s);
-    if (r != ncclSuccess) return fail(TRIAGE_E_CUDA, std::string("ncclAllGather(gidx): ") + g_nccl.GetErrorString(r));
+    r = g_nccl.AllGather(e->last_order, e->d_all_gidx.p, cap, ncclUint32, e->comm, s);
+    if (r != ncclSuccess) return fail(TRIAGE_E_CUDA, std::string("ncclAllGather(order): ") + g_nccl.GetErrorString(r));
     // 4. merge: when the per-bucket key ranges of the ranks do not interleave (contiguous sequence shards, the
-    //    normal case) the merged order is pure offset arithmetic; otherwise rank every key by binary search
-    if (disjoint) CU(launch_concat(e->d_all_keys.p, e->d_all_gidx.p, t, order_global_dev, s));
-    else CU(launch_merge_strided(e->d_all_keys.p, e->d_all_gidx.p, t, order_global_dev, s));
+    //    normal case) the merged order is pure offset arithmetic; otherwise gather the time keys too and rank every
+    //    key by binary search in the other runs
+    if (disjoint) {
+        CU(launch_concat(e->d_all_gidx.p, t, order_global_dev, s));
+    } else {
+        CU(e->d_run_keys.ensure(cap));
+        CU(e->d_run_gidx.ensure(cap));
+        CU(e->d_all_keys.ensure((size_t)R * cap));
+        CU(launch_build_run(e->last_order, n_adm, e->last_bucket, e->last_ts, rank_base[e->rank], rank_base[e->rank], e->d_run_keys.p,
+                            e->d_run_gidx.p, s));
+        r = g_nccl.AllGather(e->d_run_keys.p, e->d_all_keys.p, cap, ncclUint64, e->comm, s);
+        if (r != ncclSuccess) return fail(TRIAGE_E_CUDA, std::string("ncclAllGather(keys): ") + g_nccl.GetErrorString(r));
+        r = g_nccl.AllGather(e->d_run_gidx.p, e->d_all_gidx.p, cap, ncclUint32, e->comm, s);
+        if (r != ncclSuccess) return fail(TRIAGE_E_CUDA, std::string("ncclAllGather(gidx): ") + g_nccl.GetErrorString(r));
+        CU(launch_merge_strided(e->d_all_keys.p, e->d_all_gidx.p, t, order_global_dev, s));
+    }
     CU(cudaStreamSynchronize(s));
     return TRIAGE_OK;
 }

@@ -721,31 +721,40 @@ cudaError_t launch_build_run(const uint32_t *order, uint32_t n_adm, const uint8_
     return cudaGetLastError();
 }
 
-// per-rank header for the merge: [0] admitted, [1..16] bucket counts, [17..32] first key, [33..48] last key per bucket
+// per-rank header for the merge: [0] admitted, [1..16] bucket counts, [17..32] first time key, [33..48] last time key per
+// bucket, read straight from the local order (key = enqueue time, or rank base + arrival index when times are implicit)
 struct Counts16 { uint32_t c[16]; };
-__global__ void header_kernel(const uint64_t *__restrict__ run_keys, uint32_t n_adm, Counts16 cnt, uint64_t *__restrict__ header) {
+__global__ void header_kernel(const uint32_t *__restrict__ order, uint32_t n_adm, Counts16 cnt, const uint64_t *__restrict__ ts,
+                              uint64_t ts_base, uint64_t *__restrict__ header) {
     uint32_t b = threadIdx.x;
     if (b == 0) header[0] = n_adm;
     if (b < 16) {
         uint32_t start = 0;
         for (uint32_t i = 0; i < b; i++) start += cnt.c[i];
         header[1 + b] = cnt.c[b];
-        header[17 + b] = cnt.c[b] ? run_keys[start] : 0;
-        header[33 + b] = cnt.c[b] ? run_keys[start + cnt.c[b] - 1] : 0;
+        uint64_t first = 0, last = 0;
+        if (cnt.c[b]) {
+            uint32_t i0 = order[start], i1 = order[start + cnt.c[b] - 1];
+            first = ts ? ts[i0] : ts_base + i0;
+            last = ts ? ts[i1] : ts_base + i1;
+        }
+        header[17 + b] = first;
+        header[33 + b] = last;
     }
 }
 
-cudaError_t launch_header(const uint64_t *run_keys, uint32_t n_adm, const uint32_t *counts16_host, uint64_t *header_dev, cudaStream_t s) {
+cudaError_t launch_header(const uint32_t *order, uint32_t n_adm, const uint32_t *counts16_host, const uint64_t *ts, uint64_t ts_base,
+                          uint64_t *header_dev, cudaStream_t s) {
     Counts16 c;
     for (int i = 0; i < 16; i++) c.c[i] = counts16_host[i];
-    header_kernel<<<1, 32, 0, s>>>(run_keys, n_adm, c, header_dev);
+    header_kernel<<<1, 32, 0, s>>>(order, n_adm, c, ts, ts_base, header_dev);
     return cudaGetLastError();
 }
 
 // fast merge: the ranks' key ranges do not interleave inside any bucket, so element j of (rank, bucket) goes to
 // dst[rank][bucket] + (j - lstart[rank][bucket])
-__global__ void __launch_bounds__(256) concat_kernel(const uint64_t *__restrict__ all_keys, const uint32_t *__restrict__ all_gidx,
-                                                     ConcatTables t, uint32_t *__restrict__ order_out) {
+__global__ void __launch_bounds__(256) concat_kernel(const uint32_t *__restrict__ all_order, ConcatTables t,
+                                                     uint32_t *__restrict__ order_out) {
     uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t q = blockIdx.y;
     if (j >= t.cnt[q]) return;
@@ -753,12 +762,12 @@ __global__ void __launch_bounds__(256) concat_kernel(const uint64_t *__restrict_
     uint32_t b = 0;
 #pragma unroll
     for (uint32_t i = 1; i < 16; i++) if (j >= t.lstart[q][i]) b = i;   // lstart is non-decreasing; the last i wins
-    order_out[t.dst[q][b] + (j - t.lstart[q][b])] = all_gidx[idx];
+    order_out[t.dst[q][b] + (j - t.lstart[q][b])] = all_order[idx] + t.base[q];   // local index -> global index
 }
 
-cudaError_t launch_concat(const uint64_t *all_keys, const uint32_t *all_gidx, const ConcatTables &t, uint32_t *order_out, cudaStream_t s) {
+cudaError_t launch_concat(const uint32_t *all_order, const ConcatTables &t, uint32_t *order_out, cudaStream_t s) {
     dim3 grid((t.cap + 255) / 256, t.n_ranks);
-    concat_kernel<<<grid, 256, 0, s>>>(all_keys, all_gidx, t, order_out);
+    concat_kernel<<<grid, 256, 0, s>>>(all_order, t, order_out);
     return cudaGetLastError();
 }
 

@@ -99,11 +99,13 @@ struct ConcatTables {
     uint32_t cap;                 // stride between ranks in the gathered buffers
     uint32_t n_ranks;
     uint32_t cnt[8];              // admitted per rank
+    uint32_t base[8];             // first global index of every rank
     uint32_t dst[8][16];          // destination of the first element of (rank, bucket)
     uint32_t lstart[8][16];       // start of bucket inside the rank's run
 };
-cudaError_t launch_header(const uint64_t *run_keys, uint32_t n_adm, const uint32_t *counts16_host, uint64_t *header_dev, cudaStream_t s);
-cudaError_t launch_concat(const uint64_t *all_keys, const uint32_t *all_gidx, const ConcatTables &t, uint32_t *order_out, cudaStream_t s);
+cudaError_t launch_header(const uint32_t *order, uint32_t n_adm, const uint32_t *counts16_host, const uint64_t *ts, uint64_t ts_base,
+                          uint64_t *header_dev, cudaStream_t s);
+cudaError_t launch_concat(const uint32_t *all_order, const ConcatTables &t, uint32_t *order_out, cudaStream_t s);
 cudaError_t launch_merge_strided(const uint64_t *all_keys, const uint32_t *all_gidx, const ConcatTables &t, uint32_t *order_out, cudaStream_t s);
 
 }  // namespace triage
