@@ -300,6 +300,7 @@ def main():
             t0 = time.perf_counter()
             e2e_step()
             dts.append(time.perf_counter() - t0)
+            e2e_tm = eng.timings()
             eng.drain(n)          # empty the level queues (host bookkeeping, outside the timed call)
         tt = torch.tensor([sum(dts) / len(dts)], dtype=torch.float64, device=dev)
         if world > 1:
@@ -308,6 +309,8 @@ def main():
         adm_now = int(h_res["accepted"].sum())
         e2e = {"value": n * world / e2e_s, "unit": "msgs/s", "h2d_bytes_per_step": int(total + 8 * (n + 1) + 4 * n + 16 * n),
                "d2h_bytes_per_step": int(16 * n + 4 * adm_now), "ms_per_step": 1000 * e2e_s, "steps": e2e_steps,
+               "breakdown_ms": {"h2d": e2e_tm["h2d_ms"], "kernels": e2e_tm["total_ms"], "d2h": e2e_tm["d2h_ms"],
+                                "host_queue_insert": 1000 * dts[-1] - e2e_tm["h2d_ms"] - e2e_tm["total_ms"] - e2e_tm["d2h_ms"]},
                "api": "triage_submit_padded (C ABI, pinned host buffers from triage_host_alloc; H2D, kernels, D2H of results + order inside)"}
 
     if rank == 0:

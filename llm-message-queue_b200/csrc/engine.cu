@@ -553,21 +553,48 @@ static int32_t submit_impl(triage_engine *e, int32_t target_queue, const uint64_
     uint64_t stamp0 = 0;
     if (!enqueue_ns) { stamp0 = std::max(now_ns(), e->next_stamp); e->next_stamp = stamp0 + n; }
     const uint64_t base = e->next_handle;
-    const int qlo = target_queue ? target_queue : 1, qhi = target_queue ? target_queue : 4;
-    std::vector<size_t> run_begin(e->q.size(), 0);
-    for (int l = qlo; l <= qhi; l++) run_begin[l] = e->q[l].items.size();
-    for (uint32_t k = 0; k < n_adm; k++) {
-        uint32_t i = e->h_order[k];
-        const triage_result &r = res[i];
-        QItem it{r.label, enqueue_ns ? enqueue_ns[i] : stamp0 + i, base + i};
-        e->q[target_queue ? target_queue : r.queue_level].items.push_back(it);
-    }
-    for (int l = qlo; l <= qhi; l++) {
-        LevelQueue &lq = e->q[l];
-        size_t added = lq.items.size() - run_begin[l];
+    // The device order is bucket-major: bucket b = (level-1)*4 + (prio-1) (routed) or min(prio, 15) (single queue), so every
+    // destination queue receives one contiguous slice of `order`, already sorted by (prio, time, sequence); the item
+    // priority is a function of the bucket, so res[] need not be read back per item.  Filled in parallel for big batches.
+    uint32_t bstart[17];
+    bstart[0] = 0;
+    for (int b = 0; b < 16; b++) bstart[b + 1] = bstart[b] + e->last_counts[b];
+    struct Slice { int q; uint32_t b_lo, b_hi; };   // buckets [b_lo, b_hi) go to queue q
+    std::vector<Slice> slices;
+    if (target_queue) slices.push_back({target_queue, 0, 16});
+    else for (int l = 1; l <= 4; l++) slices.push_back({l, (uint32_t)(l - 1) * 4, (uint32_t)l * 4});
+    const uint32_t *ord = e->h_order.data();
+    for (const Slice &sl : slices) {
+        LevelQueue &lq = e->q[sl.q];
+        const uint32_t lo = bstart[sl.b_lo], hi = bstart[sl.b_hi];
+        const size_t added = hi - lo;
+        if (!added) continue;
+        const size_t run_begin = lq.items.size();
+        lq.items.resize(run_begin + added);
+        QItem *dst = lq.items.data() + run_begin;
+        auto fill = [&](uint32_t k0, uint32_t k1) {
+            for (uint32_t b = sl.b_lo; b < sl.b_hi; b++) {
+                uint32_t s0 = std::max(bstart[b], k0), s1 = std::min(bstart[b + 1], k1);
+                const int32_t prio = target_queue ? (int32_t)b : (int32_t)(b & 3) + 1;
+                const bool lumped = target_queue && b == 15;   // single-queue mode lumps priorities >= 15 into the last bucket
+                for (uint32_t k = s0; k < s1; k++) {
+                    uint32_t i = ord[k];
+                    dst[k - lo] = QItem{lumped ? (int32_t)res[i].label : prio, enqueue_ns ? enqueue_ns[i] : stamp0 + i, base + i};
+                }
+            }
+        };
+        unsigned nthr = added > 65536 ? std::min(8u, std::max(1u, std::thread::hardware_concurrency())) : 1;
+        if (nthr <= 1) fill(lo, hi);
+        else {
+            std::vector<std::thread> th;
+            for (unsigned t = 0; t < nthr; t++)
+                th.emplace_back(fill, lo + (uint32_t)((uint64_t)added * t / nthr), lo + (uint32_t)((uint64_t)added * (t + 1) / nthr));
+            for (auto &x : th) x.join();
+        }
+        if (target_queue && e->last_counts[15]) std::stable_sort(dst + (bstart[15] - lo), dst + added, qless);
         lq.st.pending += (int64_t)added;
-        if (added && run_begin[l] > lq.head && qless(lq.items[run_begin[l]], lq.items[run_begin[l] - 1]))
-            std::inplace_merge(lq.items.begin() + lq.head, lq.items.begin() + run_begin[l], lq.items.end(), qless);
+        if (run_begin > lq.head && qless(lq.items[run_begin], lq.items[run_begin - 1]))
+            std::inplace_merge(lq.items.begin() + lq.head, lq.items.begin() + run_begin, lq.items.end(), qless);
     }
     e->next_handle = base + n;
     return TRIAGE_OK;
