@@ -47,23 +47,27 @@ uint32_t ascii_lower(uint32_t r) { return (r >= 'A' && r <= 'Z') ? r + 32 : r; }
 struct NfaNode {
     std::vector<std::pair<uint8_t, uint32_t>> edges;  // (byte, target)
     int accept_event = -1;                            // index into pattern events when a pattern ends here
+    int pattern = -1;                                 // which pattern's chain this node belongs to
 };
 
 struct Nfa {
     std::vector<NfaNode> nodes;  // node 0 = root (always active)
     std::vector<EventVec> accept;  // per accepting node event
+    std::vector<uint8_t> bordered; // per pattern: a proper prefix equals a suffix (after folding)
     uint32_t max_bytes = 1;
 
     Nfa() { nodes.emplace_back(); }
     uint32_t add_node() { nodes.emplace_back(); return static_cast<uint32_t>(nodes.size() - 1); }
 
     // one symbol = a set of alternative byte strings leading from `from` to a fresh node
-    uint32_t add_symbol(uint32_t from, const std::vector<std::string> &alts) {
+    uint32_t add_symbol(uint32_t from, const std::vector<std::string> &alts, int pattern) {
         uint32_t to = add_node();
+        nodes[to].pattern = pattern;
         for (const std::string &a : alts) {
             uint32_t cur = from;
             for (size_t k = 0; k < a.size(); k++) {
                 uint32_t nxt = (k + 1 == a.size()) ? to : add_node();
+                nodes[nxt].pattern = pattern;
                 nodes[cur].edges.emplace_back(static_cast<uint8_t>(a[k]), nxt);
                 cur = nxt;
             }
@@ -90,8 +94,10 @@ std::vector<std::string> symbol_alts(uint32_t r, const std::string &raw, FoldKin
     return alts;
 }
 
-uint32_t add_pattern(Nfa *nfa, const std::string &lit, FoldKind fold, const EventVec &ev) {
+uint32_t add_pattern(Nfa *nfa, const std::string &lit, FoldKind fold, const EventVec &ev, bool bordered) {
     uint32_t cur = 0, bytes = 0;
+    const int pattern = static_cast<int>(nfa->bordered.size());
+    nfa->bordered.push_back(bordered ? 1 : 0);
     for (size_t i = 0; i < lit.size();) {
         uint32_t r = 0, w = 1;
         decode_rune(lit, i, &r, &w);
@@ -99,7 +105,7 @@ uint32_t add_pattern(Nfa *nfa, const std::string &lit, FoldKind fold, const Even
         size_t longest = 0;
         for (auto &a : alts) longest = std::max(longest, a.size());
         bytes += static_cast<uint32_t>(longest);
-        cur = nfa->add_symbol(cur, alts);
+        cur = nfa->add_symbol(cur, alts, pattern);
         i += w;
     }
     nfa->nodes[cur].accept_event = static_cast<int>(nfa->accept.size());
@@ -218,11 +224,13 @@ void add_event(EventVec *a, const EventVec &b) {
     a->pos = static_cast<uint8_t>(a->pos + b.pos);
     a->neg = static_cast<uint8_t>(a->neg + b.neg);
     a->question = (a->question || b.question) ? 1 : 0;
+    a->risk = (a->risk || b.risk) ? 1 : 0;
 }
 
 struct Machine {
     Nfa nfa;
     SentTrie sent;
+    bool exact_nonoverlap = false;
 
     void ws_complete(Config *c, Out *o) const {
         if (c->in_field && c->sent != SentTrie::DEAD) {
@@ -252,11 +260,15 @@ struct Machine {
         Config c = in;
         // keyword / question NFA: consumes every byte, root is always active
         std::vector<uint32_t> nk;
+        std::vector<int> matched;   // self-overlapping patterns that completed on this byte
         auto follow = [&](uint32_t node) {
             for (auto &e : nfa.nodes[node].edges) {
                 if (e.first != b) continue;
                 const NfaNode &t = nfa.nodes[e.second];
-                if (t.accept_event >= 0) add_event(&o->ev, nfa.accept[t.accept_event]);
+                if (t.accept_event >= 0) {
+                    add_event(&o->ev, nfa.accept[t.accept_event]);
+                    if (nfa.bordered[t.pattern]) matched.push_back(t.pattern);
+                }
                 if (!t.edges.empty()) nk.push_back(e.second);
             }
         };
@@ -265,6 +277,12 @@ struct Machine {
         std::sort(nk.begin(), nk.end());
         // NOTE: duplicates are kept out — two NFA paths reaching the same node are the same thread
         nk.erase(std::unique(nk.begin(), nk.end()), nk.end());
+        for (int p : matched) {
+            // every other live thread of p started inside the occurrence that just ended
+            auto inside = [&](uint32_t n) { return nfa.nodes[n].pattern == p; };
+            if (exact_nonoverlap) nk.erase(std::remove_if(nk.begin(), nk.end(), inside), nk.end());   // search resumes at the match end
+            else if (std::any_of(nk.begin(), nk.end(), inside)) o->ev.risk = 1;                        // occurrences may overlap
+        }
         c.kw = nk;
         // whitespace / field context
         if (c.ws != WS_NONE) {
@@ -357,8 +375,14 @@ bool parse_regex_literal(const char *s, uint32_t len, bool *ci, std::string *lit
     return true;
 }
 
-std::string build_dfa(const std::vector<DictEntry> &dict, Dfa *out) {
+bool dict_has_bordered(const std::vector<DictEntry> &dict) {
+    for (const DictEntry &d : dict) if (literal_is_bordered(d.bytes, d.ci)) return true;
+    return false;
+}
+
+std::string build_dfa(const std::vector<DictEntry> &dict, Dfa *out, bool exact_nonoverlap) {
     Machine m;
+    m.exact_nonoverlap = exact_nonoverlap;
     for (const DictEntry &d : dict) {
         std::string e = validate_literal(d.bytes, d.ci);
         if (!e.empty()) return e;
@@ -366,14 +390,14 @@ std::string build_dfa(const std::vector<DictEntry> &dict, Dfa *out) {
         EventVec ev;
         std::memset(&ev, 0, sizeof(ev));
         ev.kw[d.prio - 1] = 1;
-        add_pattern(&m.nfa, d.bytes, d.ci ? FOLD_REGEXP : FOLD_NONE, ev);
+        add_pattern(&m.nfa, d.bytes, d.ci ? FOLD_REGEXP : FOLD_NONE, ev, literal_is_bordered(d.bytes, d.ci));
     }
     // preprocessor.go:51 — question words, matched as keyword + " " in strings.ToLower(content)
     for (const char *q : {"what", "how", "why", "when", "where", "who"}) {
         EventVec ev;
         std::memset(&ev, 0, sizeof(ev));
         ev.question = 1;
-        add_pattern(&m.nfa, std::string(q) + " ", FOLD_TOLOWER, ev);
+        add_pattern(&m.nfa, std::string(q) + " ", FOLD_TOLOWER, ev, false);
     }
     // preprocessor.go:49-50
     for (const char *w : {"good", "great", "excellent", "happy", "satisfied"}) m.sent.add(w, true);

@@ -27,9 +27,20 @@ struct DictEntry {
 struct EventVec {
     uint16_t kw[4];  // realtime, high, normal, low keyword matches ending on this byte
     uint8_t pos, neg, question;
+    uint8_t risk;    // a self-overlapping pattern matched while another of its threads was alive: occurrences may overlap,
+                     // the message needs the sequential exact recount (FindAllString counts without overlap)
     bool operator==(const EventVec &o) const;
     bool empty() const;
 };
+
+// 16-byte device form of an EventVec (scan_core.cuh EventPacked): x = kw_rt | kw_hi << 16, y = kw_norm | kw_low << 16,
+// z = pos | neg << 8 | question << 16 | risk << 24
+inline void pack_event(const EventVec &v, uint32_t out[4]) {
+    out[0] = uint32_t(v.kw[0]) | uint32_t(v.kw[1]) << 16;
+    out[1] = uint32_t(v.kw[2]) | uint32_t(v.kw[3]) << 16;
+    out[2] = uint32_t(v.pos) | uint32_t(v.neg) << 8 | uint32_t(v.question) << 16 | uint32_t(v.risk) << 24;
+    out[3] = 0;
+}
 
 // Dense table format "D8": entry(state, byte) is 16 bits:
 //   bits 0..7  next state      bits 8..14 event id (0 = none)      bit 15 word start
@@ -55,7 +66,11 @@ struct Dfa {
 // returns "" on success, else a message (too many states / events for D8, bordered pattern, ...)
 std::string validate_literal(const std::string &bytes, bool ci);
 bool literal_is_bordered(const std::string &bytes, bool ci);
-std::string build_dfa(const std::vector<DictEntry> &dict, Dfa *out);
+// exact_nonoverlap = false: the definite automaton the chunked scan uses (counts every occurrence, raises `risk`).
+// exact_nonoverlap = true: matching a self-overlapping pattern kills its other threads — FindAllString's leftmost
+// non-overlapping count, only valid when a message is walked sequentially from its start (not definite).
+std::string build_dfa(const std::vector<DictEntry> &dict, Dfa *out, bool exact_nonoverlap = false);
+bool dict_has_bordered(const std::vector<DictEntry> &dict);
 
 // "(?i)literal" / "literal" with backslash escapes -> DictEntry fields; false if not a literal
 bool parse_regex_literal(const char *s, uint32_t len, bool *ci, std::string *lit, std::string *err);

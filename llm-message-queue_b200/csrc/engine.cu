@@ -112,6 +112,11 @@ struct triage_engine {
     DevBuf<EventPacked> d_events;
     DevBuf<uint8_t> d_eom;
     DeviceDfa ddfa{};
+    // exact (sequential, non-overlapping) automaton, only when the dictionary has self-overlapping literals
+    bool has_bordered = false;
+    DevBuf<uint8_t> dx_table, dx_eom;
+    DevBuf<EventPacked> dx_events;
+    DeviceDfa dxdfa{};
     // batch buffers (triage_submit) and scratch
     DevBuf<uint8_t> d_bytes;
     DevBuf<uint64_t> d_offsets, d_ts, d_pending;
@@ -152,11 +157,7 @@ int32_t commit_dict(triage_engine *e) {
     if (!err.empty()) return fail(TRIAGE_E_PATTERN, err);
     if (dfa.warm_bytes > kMaxWarm) return fail(TRIAGE_E_PATTERN, "pattern too long for the scan's warm-up window");
     std::vector<EventPacked> ev(dfa.events.size());
-    for (size_t i = 0; i < dfa.events.size(); i++) {
-        const EventVec &v = dfa.events[i];
-        ev[i] = {uint32_t(v.kw[0]) | uint32_t(v.kw[1]) << 16, uint32_t(v.kw[2]) | uint32_t(v.kw[3]) << 16,
-                 uint32_t(v.pos) | uint32_t(v.neg) << 8 | uint32_t(v.question) << 16, 0};
-    }
+    for (size_t i = 0; i < dfa.events.size(); i++) pack_event(dfa.events[i], &ev[i].x);
     std::vector<uint8_t> eom(256, 0);
     std::copy(dfa.eom.begin(), dfa.eom.end(), eom.begin());
     DeviceDfa d{};
@@ -180,6 +181,30 @@ int32_t commit_dict(triage_engine *e) {
     CU(cudaMemcpy(e->d_events.p, ev.data(), ev.size() * sizeof(EventPacked), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(e->d_eom.p, eom.data(), 256, cudaMemcpyHostToDevice));
     d.table = e->d_table.p; d.events = e->d_events.p; d.eom = e->d_eom.p;
+    e->has_bordered = dict_has_bordered(e->dict);
+    if (e->has_bordered) {
+        Dfa xd;
+        err = build_dfa(e->dict, &xd, true);
+        if (!err.empty()) return fail(TRIAGE_E_PATTERN, "exact automaton: " + err);
+        std::vector<EventPacked> xev(xd.events.size());
+        for (size_t i = 0; i < xd.events.size(); i++) pack_event(xd.events[i], &xev[i].x);
+        std::vector<uint8_t> xeom(256, 0);
+        std::copy(xd.eom.begin(), xd.eom.end(), xeom.begin());
+        std::vector<uint8_t> xpad((size_t)xd.n_states * kRowBytes, 0);
+        for (uint32_t st = 0; st < xd.n_states; st++)
+            std::memcpy(xpad.data() + (size_t)st * kRowBytes, xd.table.data() + (size_t)st * 256, 512);
+        CU(e->dx_table.ensure(xpad.size()));
+        CU(e->dx_events.ensure(xev.size()));
+        CU(e->dx_eom.ensure(256));
+        CU(cudaMemcpy(e->dx_table.p, xpad.data(), xpad.size(), cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(e->dx_events.p, xev.data(), xev.size() * sizeof(EventPacked), cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(e->dx_eom.p, xeom.data(), 256, cudaMemcpyHostToDevice));
+        DeviceDfa x{};
+        x.table = e->dx_table.p; x.events = e->dx_events.p; x.eom = e->dx_eom.p;
+        x.n_states = xd.n_states; x.n_events = (uint32_t)xev.size(); x.start_state = xd.start_state; x.neutral_state = xd.neutral_state;
+        x.head_pad = x.tail_pad = x.reset_pad = -1; x.warm = 0;
+        e->dxdfa = x;
+    }
     e->ddfa = d;
     e->geom = geom;
     e->dfa = dfa;
@@ -234,6 +259,7 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     } else {
         CU(cudaEventRecord(e->ev[1], s));
     }
+    if (e->has_bordered && ntiles) { CU(launch_fixup(bytes, offsets, lengths, n, e->dxdfa, e->d_counters.p, s)); launches++; }
     CU(cudaEventRecord(e->ev[2], s));
     const int32_t single = mode == RUN_SINGLE_QUEUE ? 1 : 0;
     FinalizeArgs fa{lengths, bytes, e->d_counters.p, meta, offsets, ts, n, e->default_prio, mode == RUN_PROCESS_ONLY ? 0 : e->opts.rules_enabled,
@@ -350,7 +376,7 @@ void triage_destroy(triage_engine *e) {
     cudaSetDevice(e->opts.device);
     cudaStreamSynchronize(e->stream);
     if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
-    e->d_table.release(); e->d_events.release(); e->d_eom.release(); e->d_bytes.release(); e->d_offsets.release();
+    e->d_table.release(); e->d_events.release(); e->d_eom.release(); e->dx_table.release(); e->dx_events.release(); e->dx_eom.release(); e->d_bytes.release(); e->d_offsets.release();
     e->d_ts.release(); e->d_pending.release(); e->d_maxsize.release(); e->d_meta.release(); e->d_results.release(); e->d_counters.release();
     e->d_tile_first.release(); e->d_lengths.release(); e->d_order.release(); e->d_perm_a.release(); e->d_perm_b.release(); e->d_blockhist.release();
     e->d_totals.release(); e->d_small.release(); e->d_bucket.release(); e->d_bucket2.release(); e->d_run_keys.release();
@@ -380,8 +406,6 @@ int32_t triage_dict_add_literal(triage_engine *e, int32_t prio, const uint8_t *l
     std::string s(reinterpret_cast<const char *>(lit), len);
     std::string err = validate_literal(s, ci != 0);
     if (!err.empty()) return fail(TRIAGE_E_PATTERN, err);
-    if (literal_is_bordered(s, ci != 0))
-        return fail(TRIAGE_E_PATTERN, "self-overlapping literal (a proper prefix equals a suffix): non-overlapping match counting for it is not supported yet");
     e->dict.push_back({(uint8_t)prio, ci != 0, s});
     e->dict_dirty = true;
     return TRIAGE_OK;
@@ -1032,6 +1056,7 @@ extern "C" int32_t triage_submit_device_static(triage_engine *e, const uint64_t 
     } else {
         CU(cudaEventRecord(e->ev[1], s));
     }
+    if (e->has_bordered && ntiles) { CU(launch_fixup(bytes_dev, offsets_dev, nullptr, n, e->dxdfa, counters, s)); launches++; }
     CU(cudaEventRecord(e->ev[2], s));
     FinalizeArgs fa{nullptr, nullptr, counters, meta_dev, offsets_dev, enqueue_ns_dev, n, e->default_prio, e->opts.rules_enabled, 0, results_dev,
                     bucket, small};

@@ -446,6 +446,51 @@ cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, int sm_cou
     return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------------- fix-up --
+// Messages in which a self-overlapping keyword ("aa", "abab") may have overlapping occurrences are re-counted by one
+// thread each, walking the whole message from its start through the exact automaton (matching such a pattern kills its
+// other threads = FindAllString's leftmost non-overlapping count).  Rare by construction; HBM traffic negligible.
+__global__ void __launch_bounds__(128) fixup_kernel(const uint8_t *__restrict__ bytes, const uint64_t *__restrict__ offsets,
+                                                    const uint32_t *__restrict__ lengths, uint32_t n, DeviceDfa x,
+                                                    uint32_t *__restrict__ counters) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        uint32_t *cnt = counters + (uint64_t)i * CNT_STRIDE;
+        if (!(cnt[CNT_Q] & 2u)) continue;
+        const uint64_t off = offsets[i];
+        const uint64_t len = lengths ? (uint64_t)lengths[i] : offsets[i + 1] - off;
+        uint32_t acc[CNT_STRIDE] = {0, 0, 0, 0, 0, 0, 0, 0};
+        auto event = [&](uint32_t id) {
+            const EventPacked e = x.events[id];
+            acc[CNT_KW + 0] += e.x & 0xFFFFu; acc[CNT_KW + 1] += e.x >> 16;
+            acc[CNT_KW + 2] += e.y & 0xFFFFu; acc[CNT_KW + 3] += e.y >> 16;
+            acc[CNT_POS] += e.z & 0xFFu; acc[CNT_NEG] += (e.z >> 8) & 0xFFu;
+            if ((e.z >> 16) & 0xFFu) acc[CNT_Q] |= 1u;
+        };
+        uint32_t st = x.start_state;
+        for (uint64_t p = 0; p < len; p++) {
+            uint32_t e = *reinterpret_cast<const uint16_t *>(x.table + st * kRowBytes + 2u * bytes[off + p]);
+            st = e & 0xFFu;
+            acc[CNT_WORDS] += e >> 15;
+            if (e & 0x7F00u) event((e >> 8) & 0x7Fu);
+        }
+        const uint32_t eo = x.eom[st];
+        acc[CNT_WORDS] += eo >> 7;
+        if (eo & 0x7Fu) event(eo & 0x7Fu);
+        if (len && bytes[off + len - 1] == '?') acc[CNT_Q] |= 1u;
+#pragma unroll
+        for (int k = 0; k < CNT_STRIDE; k++) cnt[k] = acc[k];
+    }
+}
+
+cudaError_t launch_fixup(const uint8_t *bytes, const uint64_t *offsets, const uint32_t *lengths, uint32_t n, const DeviceDfa &exact,
+                         uint32_t *counters, cudaStream_t s) {
+    if (n == 0) return cudaSuccess;
+    uint32_t blocks = (n + 127) / 128;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    fixup_kernel<<<blocks, 128, 0, s>>>(bytes, offsets, lengths, n, exact, counters);
+    return cudaGetLastError();
+}
+
 // -------------------------------------------------------------------------------- finalize --
 __global__ void __launch_bounds__(256) finalize_kernel(FinalizeArgs a) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -485,7 +530,7 @@ __global__ void __launch_bounds__(256) finalize_kernel(FinalizeArgs a) {
         if (len > 0) {                                           // :199-249
             words = c0.x;
             sentiment = c1.y > c1.z ? 1 : (c1.z > c1.y ? -1 : 0);
-            question = c1.w ? 1 : 0;
+            question = (c1.w & 1u) ? 1 : 0;
             if (a.lengths && a.bytes[off_i + len - 1] == '?') question = 1;   // HasSuffix(content, "?") (the unpadded scan does it itself)
             rflags |= TRIAGE_RF_HAS_ANALYSIS;
         }

@@ -42,6 +42,10 @@ constexpr uint32_t kPadMiniTile = 32 * kPadChunk;   // bytes per warp iteration
 size_t scan_padded_smem_bytes(const DeviceDfa &d);
 cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, int sm_count, cudaStream_t s);
 
+// sequential exact recount of the messages the scan flagged (self-overlapping keywords); `exact` points at global memory
+cudaError_t launch_fixup(const uint8_t *bytes, const uint64_t *offsets, const uint32_t *lengths, uint32_t n, const DeviceDfa &exact,
+                         uint32_t *counters, cudaStream_t s);
+
 struct FinalizeArgs {
     const uint32_t *lengths;     // padded layout: true content lengths (else nullptr: len = offsets[i+1]-offsets[i])
     const uint8_t *bytes;        // padded layout: for the HasSuffix "?" test

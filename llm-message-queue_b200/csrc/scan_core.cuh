@@ -32,7 +32,8 @@ enum { CNT_WORDS = 0, CNT_KW = 1 /* ..4 */, CNT_POS = 5, CNT_NEG = 6, CNT_Q = 7,
 constexpr uint32_t kRowBytes = 516;
 constexpr uint32_t kDpMul = 0xACACAC02u;   // dot((byte, st, st, st), (2, 172, 172, 172)) = 2*byte + 516*st
 
-// events[id]: x = kw_rt | kw_hi << 16, y = kw_norm | kw_low << 16, z = pos | neg << 8 | question << 16
+// events[id]: x = kw_rt | kw_hi << 16, y = kw_norm | kw_low << 16, z = pos | neg << 8 | question << 16 | risk << 24
+// CNT_Q holds flags: bit 0 question, bit 1 overlap risk (message needs the sequential exact recount)
 struct EventPacked { uint32_t x, y, z, w; };
 struct alignas(16) Quad { uint32_t a, b, c, d; };
 
@@ -103,7 +104,8 @@ TR_COLD void apply_event_raw(const EventPacked *events, uint32_t *counters, uint
     if (e.y >> 16) tr_add(cnt + CNT_KW + 3, e.y >> 16);
     if (e.z & 0xFFu) tr_add(cnt + CNT_POS, e.z & 0xFFu);
     if ((e.z >> 8) & 0xFFu) tr_add(cnt + CNT_NEG, (e.z >> 8) & 0xFFu);
-    if (e.z >> 16) tr_or(cnt + CNT_Q, 1u);
+    if ((e.z >> 16) & 0xFFu) tr_or(cnt + CNT_Q, 1u);
+    if (e.z >> 24) tr_or(cnt + CNT_Q, 2u);
 }
 TR_HD void apply_event(const LaneCtx &c, uint32_t id, uint32_t msg) { apply_event_raw(c.events, c.counters, id, msg); }
 

@@ -36,9 +36,7 @@ int hostcheck_scan(const uint8_t *prios, const uint8_t *cis, const uint32_t *len
     if (n_msgs == 0) return 0;
     std::vector<EventPacked> ev(dfa.events.size());
     for (size_t i = 0; i < dfa.events.size(); i++) {
-        const EventVec &v = dfa.events[i];
-        ev[i] = {uint32_t(v.kw[0]) | uint32_t(v.kw[1]) << 16, uint32_t(v.kw[2]) | uint32_t(v.kw[3]) << 16,
-                 uint32_t(v.pos) | uint32_t(v.neg) << 8 | uint32_t(v.question) << 16, 0};
+        pack_event(dfa.events[i], &ev[i].x);
     }
     // padded rows, exactly as the engine uploads them
     std::vector<uint8_t> tbl((size_t)dfa.n_states * kRowBytes, 0);
@@ -145,9 +143,7 @@ extern "C" int hostcheck_scan_padded(const uint8_t *prios, const uint8_t *cis, c
     if (n_msgs == 0) return 0;
     std::vector<EventPacked> ev(dfa.events.size());
     for (size_t i = 0; i < dfa.events.size(); i++) {
-        const EventVec &v = dfa.events[i];
-        ev[i] = {uint32_t(v.kw[0]) | uint32_t(v.kw[1]) << 16, uint32_t(v.kw[2]) | uint32_t(v.kw[3]) << 16,
-                 uint32_t(v.pos) | uint32_t(v.neg) << 8 | uint32_t(v.question) << 16, 0};
+        pack_event(dfa.events[i], &ev[i].x);
     }
     std::vector<uint8_t> tbl((size_t)dfa.n_states * kRowBytes, 0);
     for (uint32_t st = 0; st < dfa.n_states; st++)
@@ -193,5 +189,41 @@ extern "C" int hostcheck_scan_padded(const uint8_t *prios, const uint8_t *cis, c
     // HasSuffix "?" is applied by the finalize kernel in the padded pipeline
     for (uint32_t i = 0; i < n_msgs; i++)
         if (offsets[i + 1] > offsets[i] && bytes[offsets[i + 1] - 1] == '?') counters[(uint64_t)i * 8 + CNT_Q] |= 1;
+    return 0;
+}
+
+
+// sequential walk of every message through the EXACT (non-overlapping) automaton: what the device fix-up kernel does
+extern "C" int hostcheck_exact(const uint8_t *prios, const uint8_t *cis, const uint32_t *lens, const uint8_t *lits, uint32_t n_pat,
+                               const uint64_t *offsets, const uint8_t *bytes, uint32_t n_msgs, uint32_t *counters, uint32_t *info)
+{
+    std::vector<DictEntry> dict;
+    size_t o = 0;
+    for (uint32_t i = 0; i < n_pat; i++) {
+        dict.push_back({prios[i], cis[i] != 0, std::string(reinterpret_cast<const char *>(lits + o), lens[i])});
+        o += lens[i];
+    }
+    Dfa x;
+    if (!build_dfa(dict, &x, true).empty()) return 4;
+    info[0] = x.n_states; info[1] = dict_has_bordered(dict) ? 1 : 0;
+    for (uint32_t i = 0; i < n_msgs; i++) {
+        uint32_t *acc = counters + (size_t)i * 8;
+        std::memset(acc, 0, 32);
+        uint32_t st = x.start_state;
+        auto event = [&](uint32_t id) {
+            const EventVec &v = x.events[id];
+            for (int k = 0; k < 4; k++) acc[CNT_KW + k] += v.kw[k];
+            acc[CNT_POS] += v.pos; acc[CNT_NEG] += v.neg; if (v.question) acc[CNT_Q] |= 1;
+        };
+        for (uint64_t p = offsets[i]; p < offsets[i + 1]; p++) {
+            uint16_t e = x.table[(size_t)st * 256 + bytes[p]];
+            st = e & 0xFF; acc[CNT_WORDS] += e >> 15;
+            if (e & 0x7F00) event((e >> 8) & 0x7F);
+        }
+        uint8_t eo = x.eom[st];
+        acc[CNT_WORDS] += eo >> 7;
+        if (eo & 0x7F) event(eo & 0x7F);
+        if (offsets[i + 1] > offsets[i] && bytes[offsets[i + 1] - 1] == '?') acc[CNT_Q] |= 1;
+    }
     return 0;
 }

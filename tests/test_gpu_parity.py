@@ -290,3 +290,37 @@ def test_padded_full_size_c2_properties():
         assert res2.tobytes() == res.tobytes()
     finally:
         e.close()
+
+
+def test_self_overlapping_keywords_count_without_overlap():
+    """AddKeywordPattern("haha"): FindAllString counts leftmost NON-overlapping matches (preprocessor.go:146).  The chunked
+    scan counts every occurrence and flags the message; the fix-up kernel recounts flagged messages sequentially."""
+    extra = [(4, False, b"haha"), (3, False, b"abab"), (2, True, b"aa"), (1, False, b"xyxyx")]
+    d = co.Dict()
+    e = mq.Engine(device=0)
+    try:
+        for p, ci, lit in extra:
+            assert d.add(p, lit, ci) == 0
+            e.add_literal(p, lit, ci)
+        rng = np.random.default_rng(9)
+        off, data, meta, ts = co.generate(91, 4000, 16, 900, edge=100)
+        contents = [bytes(data[int(off[i]):int(off[i + 1])]) for i in range(len(meta))]
+        # runs long enough to straddle lanes, mini-tiles and CTAs
+        for k in range(0, 4000, 7):
+            unit = [b"ha", b"ab", b"a", b"A", b"xy", b"aA"][k % 6]
+            reps = int(rng.integers(1, 4000 if k % 91 == 0 else 60))
+            pos = int(rng.integers(0, len(contents[k]) + 1))
+            contents[k] = contents[k][:pos] + unit * reps + contents[k][pos:]
+        off, data = co.pack(contents)
+        exp, order = co.pipeline(d, off, data, meta, ts, nthreads=os.cpu_count() or 4)
+        assert (exp["score_hi"] > 3).sum() > 100      # the case is exercised
+        res, base = e.submit(off, data, meta, ts)
+        _assert_same(res, exp, FIELDS + ("accepted", "admit"), ctx="packed")
+        e.drain(len(meta))
+        poff, plen, pbytes = e.pack_padded(off, data)
+        res, base = e.submit_padded(poff, plen, pbytes, meta, ts)
+        _assert_same(res, exp, FIELDS + ("accepted", "admit"), ctx="padded")
+        handles, _ = e.drain(len(meta))
+        assert np.array_equal((handles - base).astype(np.uint32), order)
+    finally:
+        e.close()
