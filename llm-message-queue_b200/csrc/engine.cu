@@ -109,6 +109,7 @@ struct triage_engine {
     Dfa dfa;
     DevBuf<uint8_t> d_table;
     ScanGeometry geom{0, 0, 0};
+    uint32_t pad_warps = 0;
     DevBuf<EventPacked> d_events;
     DevBuf<uint8_t> d_eom;
     DeviceDfa ddfa{};
@@ -164,7 +165,8 @@ int32_t commit_dict(triage_engine *e) {
     d.n_states = dfa.n_states; d.n_events = (uint32_t)ev.size(); d.warm = dfa.warm_bytes;
     d.start_state = dfa.start_state; d.neutral_state = dfa.neutral_state;
     d.head_pad = dfa.head_pad; d.tail_pad = dfa.tail_pad; d.reset_pad = dfa.reset_pad;
-    if (d.reset_pad >= 0 && scan_padded_smem_bytes(d) > (size_t)e->max_smem_optin) d.reset_pad = -1;   // padded kernel would not fit
+    const uint32_t pad_warps = d.reset_pad >= 0 ? pick_pad_warps(d, (size_t)e->max_smem_optin) : 0;
+    if (pad_warps == 0) d.reset_pad = -1;   // the padded kernel would not fit: packed entry points only
     ScanGeometry geom = pick_scan_geometry(d, (size_t)e->max_smem_optin);
     if (geom.nt == 0)
         return fail(TRIAGE_E_PATTERN, "dictionary automaton (" + std::to_string(dfa.n_states) + " states) does not fit in shared memory");
@@ -206,6 +208,7 @@ int32_t commit_dict(triage_engine *e) {
         e->dxdfa = x;
     }
     e->ddfa = d;
+    e->pad_warps = pad_warps;
     e->geom = geom;
     e->dfa = dfa;
     e->dict_dirty = false;
@@ -253,7 +256,7 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     if (ntiles) {
         CU(launch_tile_index(sa, s)); launches++;
         CU(cudaEventRecord(e->ev[1], s));
-        if (padded) CU(launch_scan_padded(sa, e->ddfa, e->sm_count, s));
+        if (padded) CU(launch_scan_padded(sa, e->ddfa, e->pad_warps, e->sm_count, s));
         else CU(launch_scan(sa, e->ddfa, e->geom, e->sm_count, s));
         launches++;
     } else {

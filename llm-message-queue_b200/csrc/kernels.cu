@@ -280,25 +280,33 @@ cudaError_t launch_scan(const ScanArgs &a, const DeviceDfa &d, const ScanGeometr
 // after the automaton has been loaded.
 struct PadSmem { uint32_t table, events, stage0, list0, total, stage_bytes, list_bytes; };
 constexpr uint32_t kPadListCap = 34;
-__host__ __device__ inline PadSmem pad_layout(uint32_t n_states, uint32_t n_events, uint32_t warm) {
+__host__ __device__ inline PadSmem pad_layout(uint32_t n_states, uint32_t n_events, uint32_t warm, uint32_t nw) {
     PadSmem L;
     uint32_t o = 1024;   // mbarriers
     L.table = o; o += ((n_states * kRowBytes + 127u) / 128u) * 128u;
     L.events = o; o += ((n_events * 16u + 127u) / 128u) * 128u;
     L.stage_bytes = ((warm + kPadMiniTile + 16u + 127u) / 128u) * 128u;
-    L.stage0 = o; o += kPadWarps * 2 * L.stage_bytes;
+    L.stage0 = o; o += nw * 2 * L.stage_bytes;
     L.list_bytes = 160;
-    L.list0 = o; o += kPadWarps * 2 * L.list_bytes;
+    L.list0 = o; o += nw * 2 * L.list_bytes;
     L.total = o;
     return L;
 }
-size_t scan_padded_smem_bytes(const DeviceDfa &d) { return pad_layout(d.n_states, d.n_events, d.warm).total; }
+size_t scan_padded_smem_bytes(const DeviceDfa &d, uint32_t nw) { return pad_layout(d.n_states, d.n_events, d.warm, nw).total; }
+// most warps per CTA whose staging buffers still fit next to the automaton (0: none)
+uint32_t pick_pad_warps(const DeviceDfa &d, size_t max_smem) {
+    for (uint32_t nw : {24u, 20u, 16u, 12u, 8u})
+        if (scan_padded_smem_bytes(d, nw) <= max_smem) return nw;
+    return 0;
+}
 
-__global__ void __launch_bounds__(kPadWarps * 32, 1) scan_padded_kernel(ScanArgs a, DeviceDfa d) {
+template <int NW>
+__global__ void __launch_bounds__(NW * 32, 1) scan_padded_kernel(ScanArgs a, DeviceDfa d) {
+    constexpr uint32_t kPadWarps = NW;
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int C = kPadChunk;
     constexpr uint32_t MT = kPadMiniTile;
-    const PadSmem L = pad_layout(d.n_states, d.n_events, d.warm);
+    const PadSmem L = pad_layout(d.n_states, d.n_events, d.warm, kPadWarps);
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem) + warp * 2;
     uint8_t *tbl = smem + L.table;
@@ -431,19 +439,31 @@ __global__ void __launch_bounds__(kPadWarps * 32, 1) scan_padded_kernel(ScanArgs
     }
 }
 
-cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, int sm_count, cudaStream_t s) {
-    if (a.ntiles == 0) return cudaSuccess;
-    size_t smem = scan_padded_smem_bytes(d);
+template <int NW>
+static cudaError_t launch_scan_padded_variant(const ScanArgs &a, const DeviceDfa &d, int sm_count, cudaStream_t s) {
+    size_t smem = scan_padded_smem_bytes(d, NW);
     static size_t configured = 0;
     if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(scan_padded_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(scan_padded_kernel<NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         configured = smem;
     }
-    uint32_t need = (a.ntiles + kPadWarps - 1) / kPadWarps;
+    uint32_t need = (a.ntiles + NW - 1) / NW;
     uint32_t grid = need < (uint32_t)sm_count ? need : (uint32_t)sm_count;
-    scan_padded_kernel<<<grid, kPadWarps * 32, smem, s>>>(a, d);
+    scan_padded_kernel<NW><<<grid, NW * 32, smem, s>>>(a, d);
     return cudaGetLastError();
+}
+
+cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, int sm_count, cudaStream_t s) {
+    if (a.ntiles == 0) return cudaSuccess;
+    switch (nw) {
+        case 24: return launch_scan_padded_variant<24>(a, d, sm_count, s);
+        case 20: return launch_scan_padded_variant<20>(a, d, sm_count, s);
+        case 16: return launch_scan_padded_variant<16>(a, d, sm_count, s);
+        case 12: return launch_scan_padded_variant<12>(a, d, sm_count, s);
+        case 8: return launch_scan_padded_variant<8>(a, d, sm_count, s);
+        default: return cudaErrorInvalidValue;
+    }
 }
 
 // ---------------------------------------------------------------------------------- fix-up --

@@ -36,11 +36,11 @@ struct ScanArgs {
 };
 
 // padded-arena scan: warps are autonomous (own staging buffers, own mbarriers, no CTA barrier in the loop)
-constexpr uint32_t kPadWarps = 24;
 constexpr uint32_t kPadChunk = 80;
 constexpr uint32_t kPadMiniTile = 32 * kPadChunk;   // bytes per warp iteration
-size_t scan_padded_smem_bytes(const DeviceDfa &d);
-cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, int sm_count, cudaStream_t s);
+size_t scan_padded_smem_bytes(const DeviceDfa &d, uint32_t nw);
+uint32_t pick_pad_warps(const DeviceDfa &d, size_t max_smem);   // 24 for the default dictionary; fewer when the table is large
+cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, int sm_count, cudaStream_t s);
 
 // sequential exact recount of the messages the scan flagged (self-overlapping keywords); `exact` points at global memory
 cudaError_t launch_fixup(const uint8_t *bytes, const uint64_t *offsets, const uint32_t *lengths, uint32_t n, const DeviceDfa &exact,

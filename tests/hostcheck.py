@@ -46,6 +46,7 @@ def scan(dict_entries, offsets, data, nt=64, chunk=48, use_abs_list=False, force
                               nt, chunk, (1 if use_abs_list else 0) | (2 if force_slow else 0), p(counters), p(info), err, 256)
     if rc != 0:
         raise ValueError(err.value.decode())
+    counters[:, 7] &= 1   # bit 1 = overlap-risk flag (self-overlapping keywords), not part of the analysis
     return counters[:n], dict(states=int(info[0]), unminimised=int(info[1]), warm=int(info[2]), events=int(info[3]),
                                 head_pad=int(np.int32(info[4])), tail_pad=int(np.int32(info[5])))
 
@@ -66,4 +67,6 @@ def scan_padded(dict_entries, offsets, data, chunk=80, use_abs_list=False):
                                      chunk, 1 if use_abs_list else 0, p(counters), p(info), err, 256)
     if rc != 0:
         raise ValueError(err.value.decode())
-    return counters[:n], dict(states=int(info[0]), reset_pad=int(np.int32(info[1])))
+    risk = (counters[:n, 7] & 2) != 0
+    counters[:, 7] &= 1
+    return counters[:n], dict(states=int(info[0]), reset_pad=int(np.int32(info[1])), risk=risk)
