@@ -221,6 +221,9 @@ def main():
             eng.merge_allgather(rank_base, d_gord.data_ptr(), n * world)
         return adm, t
 
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()          # samples every 200 ms from warm-up to the end of the e2e loop (the timed regions lie inside)
     for _ in range(args.warmup):
         step()
     if args.check:
@@ -251,10 +254,7 @@ def main():
         print(f"[check rank {rank}] merged order {'OK' if ok else 'MISMATCH'} ({len(want)} admitted of {n * world})", file=sys.stderr, flush=True)
         if not ok:
             raise SystemExit(3)
-    sampler = ClockSampler(local)
     barrier(); torch.cuda.synchronize()
-    if rank == 0:
-        sampler.start()
     eng.event_record(0)
     t_wall = time.perf_counter()
     scan_ms, fin_ms, ord_ms, launches, passes = [], [], [], 0, 0
@@ -267,7 +267,6 @@ def main():
     dev_ms = eng.event_elapsed_ms(0, 1)
     torch.cuda.synchronize(); barrier()
     wall_ms = 1000 * (time.perf_counter() - t_wall)
-    clocks = sampler.stop() if rank == 0 else None
     tt = torch.tensor([dev_ms, wall_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -313,6 +312,7 @@ def main():
                                 "host_queue_insert": 1000 * dts[-1] - e2e_tm["h2d_ms"] - e2e_tm["total_ms"] - e2e_tm["d2h_ms"]},
                "api": "triage_submit_padded (C ABI, pinned host buffers from triage_host_alloc; H2D, kernels, D2H of results + order inside)"}
 
+    clocks = sampler.stop() if rank == 0 else None
     if rank == 0:
         peak, peak_src = measured_peak()
         t_scan = sum(scan_ms) / len(scan_ms)
