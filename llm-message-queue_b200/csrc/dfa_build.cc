@@ -57,6 +57,7 @@ struct Nfa {
     uint32_t max_bytes = 1;
 
     Nfa() { nodes.emplace_back(); }
+    void finish() { for (auto &n : nodes) std::sort(n.edges.begin(), n.edges.end()); }
     uint32_t add_node() { nodes.emplace_back(); return static_cast<uint32_t>(nodes.size() - 1); }
 
     // one symbol = a set of alternative byte strings leading from `from` to a fresh node
@@ -262,8 +263,10 @@ struct Machine {
         std::vector<uint32_t> nk;
         std::vector<int> matched;   // self-overlapping patterns that completed on this byte
         auto follow = [&](uint32_t node) {
-            for (auto &e : nfa.nodes[node].edges) {
-                if (e.first != b) continue;
+            const auto &edges = nfa.nodes[node].edges;   // sorted by byte (Nfa::finish)
+            auto lo = std::lower_bound(edges.begin(), edges.end(), std::make_pair(b, uint32_t(0)));
+            for (auto it = lo; it != edges.end() && it->first == b; ++it) {
+                const auto &e = *it;
                 const NfaNode &t = nfa.nodes[e.second];
                 if (t.accept_event >= 0) {
                     add_event(&o->ev, nfa.accept[t.accept_event]);
@@ -403,6 +406,30 @@ std::string build_dfa(const std::vector<DictEntry> &dict, Dfa *out, bool exact_n
     for (const char *w : {"good", "great", "excellent", "happy", "satisfied"}) m.sent.add(w, true);
     for (const char *w : {"bad", "terrible", "awful", "angry", "frustrated"}) m.sent.add(w, false);
 
+    m.nfa.finish();
+    // ---- byte classes: bytes that nothing mentions behave identically (non-space, match nothing) ----
+    bool relevant[256] = {false};
+    for (const NfaNode &nd : m.nfa.nodes) for (auto &e : nd.edges) relevant[e.first] = true;
+    for (const auto &nd : m.sent.nodes) for (auto &kv : nd.next) relevant[kv.first] = true;
+    for (uint32_t b : {0x09u, 0x0Au, 0x0Bu, 0x0Cu, 0x0Du, 0x20u, 0xC2u, 0x85u, 0xA0u, 0xE1u, 0x9Au, 0xE2u, 0x81u, 0x9Fu, 0xE3u, 0xA8u, 0xA9u, 0xAFu}) relevant[b] = true;
+    for (uint32_t b = 0x80; b <= 0x8A; b++) relevant[b] = true;
+    uint8_t cls_of[256];
+    std::vector<uint8_t> rep;   // representative byte per class; class 0 = "other"
+    {
+        int other = -1;
+        for (int b = 0; b < 256; b++) if (!relevant[b]) { other = b; break; }
+        rep.push_back(static_cast<uint8_t>(other < 0 ? 0 : other));
+        for (int b = 0; b < 256; b++) {
+            if (relevant[b] || other < 0) { cls_of[b] = static_cast<uint8_t>(rep.size() < 256 ? rep.size() : 0); if (rep.size() < 256) rep.push_back(static_cast<uint8_t>(b)); }
+            else cls_of[b] = 0;
+        }
+        if (other < 0) {   // every byte value is mentioned somewhere: no shared class (class 0 is byte 0's own)
+            rep.clear();
+            for (int b = 0; b < 256; b++) { cls_of[b] = static_cast<uint8_t>(b); rep.push_back(static_cast<uint8_t>(b)); }
+        }
+    }
+    const uint32_t ncls = static_cast<uint32_t>(rep.size());
+
     // ---- reachable configurations (BFS) ----
     std::unordered_map<std::string, uint32_t> ids;
     std::vector<Config> cfgs;
@@ -429,19 +456,20 @@ std::string build_dfa(const std::vector<DictEntry> &dict, Dfa *out, bool exact_n
         return static_cast<uint32_t>(events.size() - 1);
     };
 
-    struct Trans { uint32_t next; uint32_t ev; bool ws; };
-    std::vector<Trans> trans;  // cfg-major, 256 per configuration
+    struct Trans { uint32_t next; uint16_t ev; uint8_t ws; };
+    std::vector<Trans> trans;  // cfg-major, ncls per configuration
     std::vector<uint32_t> eom_ev;
     std::vector<uint8_t> eom_ws;
-    constexpr uint32_t kHardCap = 1u << 16;
     for (uint32_t s = 0; s < cfgs.size(); s++) {
-        if (cfgs.size() > kHardCap) return "dictionary automaton exceeds 65536 configurations";
+        if (cfgs.size() > kMaxStatesW) return "dictionary automaton exceeds 2^20 states";
         Config cur = cfgs[s];
-        for (uint32_t b = 0; b < 256; b++) {
+        for (uint32_t c = 0; c < ncls; c++) {
             Out o;
             std::memset(&o.ev, 0, sizeof(o.ev));
-            Config nx = m.step(cur, static_cast<uint8_t>(b), &o);
-            trans.push_back({intern(nx), event_id(o.ev), o.word_start});
+            Config nx = m.step(cur, rep[c], &o);
+            uint32_t eid = event_id(o.ev);
+            if (eid > kMaxEventsW) return "dictionary automaton has too many distinct event vectors";
+            trans.push_back({intern(nx), static_cast<uint16_t>(eid), static_cast<uint8_t>(o.word_start ? 1 : 0)});
         }
         Out e = m.end_of_message(cur);
         eom_ev.push_back(event_id(e.ev));
@@ -450,89 +478,115 @@ std::string build_dfa(const std::vector<DictEntry> &dict, Dfa *out, bool exact_n
     uint32_t n = static_cast<uint32_t>(cfgs.size());
     out->n_states_unminimised = n;
 
-    // ---- minimise (Moore partition refinement on outputs + successor classes) ----
+    // ---- minimise (Moore partition refinement on outputs + successor classes); skipped for very large automata ----
     std::vector<uint32_t> cls(n, 0);
-    {
-        std::map<std::string, uint32_t> sig;
-        for (uint32_t s = 0; s < n; s++) {
-            std::string k;
-            k.append(reinterpret_cast<const char *>(&eom_ev[s]), 4);
-            k.push_back(static_cast<char>(eom_ws[s]));
-            for (uint32_t b = 0; b < 256; b++) {
-                const Trans &t = trans[s * 256 + b];
-                k.append(reinterpret_cast<const char *>(&t.ev), 4);
-                k.push_back(t.ws ? 1 : 0);
+    if (n <= 8192) {
+        {
+            std::map<std::string, uint32_t> sig;
+            for (uint32_t s = 0; s < n; s++) {
+                std::string k;
+                k.append(reinterpret_cast<const char *>(&eom_ev[s]), 4);
+                k.push_back(static_cast<char>(eom_ws[s]));
+                for (uint32_t c = 0; c < ncls; c++) {
+                    const Trans &t = trans[(size_t)s * ncls + c];
+                    k.append(reinterpret_cast<const char *>(&t.ev), 2);
+                    k.push_back(static_cast<char>(t.ws));
+                }
+                auto it = sig.emplace(k, static_cast<uint32_t>(sig.size())).first;
+                cls[s] = it->second;
             }
-            auto it = sig.emplace(k, static_cast<uint32_t>(sig.size())).first;
-            cls[s] = it->second;
         }
-    }
-    for (;;) {
-        std::map<std::string, uint32_t> sig;
-        std::vector<uint32_t> ncls(n);
-        for (uint32_t s = 0; s < n; s++) {
-            std::string k;
-            k.append(reinterpret_cast<const char *>(&cls[s]), 4);
-            for (uint32_t b = 0; b < 256; b++) k.append(reinterpret_cast<const char *>(&cls[trans[s * 256 + b].next]), 4);
-            auto it = sig.emplace(k, static_cast<uint32_t>(sig.size())).first;
-            ncls[s] = it->second;
+        for (;;) {
+            std::map<std::string, uint32_t> sig;
+            std::vector<uint32_t> ncl(n);
+            for (uint32_t s = 0; s < n; s++) {
+                std::string k;
+                k.append(reinterpret_cast<const char *>(&cls[s]), 4);
+                for (uint32_t c = 0; c < ncls; c++) k.append(reinterpret_cast<const char *>(&cls[trans[(size_t)s * ncls + c].next]), 4);
+                auto it = sig.emplace(k, static_cast<uint32_t>(sig.size())).first;
+                ncl[s] = it->second;
+            }
+            uint32_t before = *std::max_element(cls.begin(), cls.end()) + 1;
+            uint32_t after = static_cast<uint32_t>(sig.size());
+            cls.swap(ncl);
+            if (after == before) break;
         }
-        uint32_t before = *std::max_element(cls.begin(), cls.end()) + 1;
-        uint32_t after = static_cast<uint32_t>(sig.size());
-        cls.swap(ncls);
-        if (after == before) break;
+    } else {
+        for (uint32_t s = 0; s < n; s++) cls[s] = s;
     }
     uint32_t nmin = *std::max_element(cls.begin(), cls.end()) + 1;
-    if (nmin > kMaxStatesD8) return "dictionary automaton has " + std::to_string(nmin) + " states; this build supports " + std::to_string(kMaxStatesD8);
-    if (events.size() - 1 > kMaxEventsD8) return "dictionary automaton has too many distinct event vectors";
+    const bool wide = nmin > kMaxStatesD8 || events.size() - 1 > kMaxEventsD8;
 
     out->n_states = nmin;
-    out->table.assign(static_cast<size_t>(nmin) * 256, 0);
+    out->wide = wide;
+    out->n_classes = ncls;
+    std::memcpy(out->cls_of, cls_of, 256);
     out->eom.assign(nmin, 0);
+    out->table.clear();
+    out->wtable.clear();
+    if (!wide) out->table.assign(static_cast<size_t>(nmin) * 256, 0);
+    else out->wtable.assign(static_cast<size_t>(nmin) * ncls, 0);
     std::vector<bool> done(nmin, false);
+    std::vector<uint32_t> eom_full(nmin, 0);   // event id | ws << 31 (wide eom ids may exceed 7 bits)
     for (uint32_t s = 0; s < n; s++) {
         uint32_t c = cls[s];
         if (done[c]) continue;
         done[c] = true;
-        for (uint32_t b = 0; b < 256; b++) {
-            const Trans &t = trans[s * 256 + b];
-            out->table[static_cast<size_t>(c) * 256 + b] =
-                static_cast<uint16_t>(cls[t.next] | (t.ev << 8) | (t.ws ? 0x8000u : 0u));
+        if (!wide) {
+            for (uint32_t b = 0; b < 256; b++) {
+                const Trans &t = trans[(size_t)s * ncls + cls_of[b]];
+                out->table[static_cast<size_t>(c) * 256 + b] = static_cast<uint16_t>(cls[t.next] | (uint32_t(t.ev) << 8) | (t.ws ? 0x8000u : 0u));
+            }
+            out->eom[c] = static_cast<uint8_t>(eom_ev[s] | (eom_ws[s] ? 0x80u : 0u));
+        } else {
+            for (uint32_t k = 0; k < ncls; k++) {
+                const Trans &t = trans[(size_t)s * ncls + k];
+                out->wtable[static_cast<size_t>(c) * ncls + k] = cls[t.next] | (uint32_t(t.ev) << 20) | (t.ws ? 0x80000000u : 0u);
+            }
         }
-        out->eom[c] = static_cast<uint8_t>(eom_ev[s] | (eom_ws[s] ? 0x80u : 0u));
+        eom_full[c] = eom_ev[s] | (eom_ws[s] ? 0x80000000u : 0u);
     }
+    out->eom_w = eom_full;
     out->events = events;
     out->start_state = static_cast<uint8_t>(cls[start_id]);
     out->neutral_state = static_cast<uint8_t>(cls[neutral_id]);
+    out->start_state_w = cls[start_id];
+    out->neutral_state_w = cls[neutral_id];
     // longest byte distance an event can depend on: a keyword's own bytes, or for a sentiment word
     // the tail of a multi-byte whitespace before it (2), the word, and the whitespace after it (3)
     out->span = std::max<uint32_t>(m.nfa.max_bytes, m.sent.max_bytes + 5);
     out->warm_bytes = ((out->span - 1 + 15) / 16) * 16;
     if (out->warm_bytes == 0) out->warm_bytes = 16;
     // pad bytes (see scan_core.cuh): searched over all 256 values, whitespace first
-    auto entry = [&](uint32_t st, uint32_t b) { return out->table[static_cast<size_t>(st) * 256 + b]; };
+    struct TView { uint32_t next; uint32_t ev; bool ws; };
+    auto tv = [&](uint32_t st, uint32_t b) -> TView {
+        if (!wide) { uint16_t t = out->table[static_cast<size_t>(st) * 256 + b]; return {uint32_t(t & 0xFF), uint32_t((t >> 8) & 0x7F), (t & 0x8000) != 0}; }
+        uint32_t t = out->wtable[static_cast<size_t>(st) * ncls + cls_of[b]];
+        return {t & 0xFFFFFu, (t >> 20) & 0x7FFu, (t >> 31) != 0};
+    };
+    const uint32_t st0 = cls[start_id];
     std::vector<uint32_t> cand = {0x09, 0x0B, 0x0C, 0x0A, 0x0D, 0x20};
     for (uint32_t b = 0; b < 256; b++) cand.push_back(b);
     out->head_pad = out->tail_pad = out->reset_pad = -1;
     for (uint32_t b : cand) {
         if (out->reset_pad < 0) {
-            bool ok = true;
+            bool ok = eom_full[st0] == 0;
             for (uint32_t st = 0; st < nmin && ok; st++) {
-                uint16_t t = entry(st, b);
-                uint8_t emitted = static_cast<uint8_t>(((t >> 8) & 0x7F) | ((t & 0x8000) ? 0x80 : 0));
-                if (emitted != out->eom[st] || (t & 0xFF) != out->start_state) ok = false;
+                TView t = tv(st, b);
+                uint32_t emitted = t.ev | (t.ws ? 0x80000000u : 0u);
+                if (emitted != eom_full[st] || t.next != st0) ok = false;
             }
-            if (ok && out->eom[out->start_state] == 0) out->reset_pad = static_cast<int>(b);
+            if (ok) out->reset_pad = static_cast<int>(b);
         }
-        if (out->head_pad < 0 && entry(out->start_state, b) == out->start_state) out->head_pad = static_cast<int>(b);
+        if (out->head_pad < 0) { TView t = tv(st0, b); if (t.next == st0 && t.ev == 0 && !t.ws) out->head_pad = static_cast<int>(b); }
         if (out->tail_pad < 0) {
             bool ok = true;
             for (uint32_t st = 0; st < nmin && ok; st++) {
-                uint16_t t = entry(st, b);
-                uint8_t emitted = static_cast<uint8_t>(((t >> 8) & 0x7F) | ((t & 0x8000) ? 0x80 : 0));
-                if (emitted != out->eom[st]) { ok = false; break; }
-                uint32_t s1 = t & 0xFF;
-                if (entry(s1, b) != s1) ok = false;   // further pads: same state, no output
+                TView t = tv(st, b);
+                uint32_t emitted = t.ev | (t.ws ? 0x80000000u : 0u);
+                if (emitted != eom_full[st]) { ok = false; break; }
+                TView t2 = tv(t.next, b);
+                if (t2.next != t.next || t2.ev != 0 || t2.ws) ok = false;   // further pads: same state, no output
             }
             if (ok) out->tail_pad = static_cast<int>(b);
         }

@@ -47,10 +47,22 @@ inline void pack_event(const EventVec &v, uint32_t out[4]) {
 constexpr uint32_t kMaxStatesD8 = 256;
 constexpr uint32_t kMaxEventsD8 = 127;
 
+// Wide table format "W" (dictionaries beyond 256 states, e.g. 10 K keywords): bytes are first mapped to classes
+// (bytes no pattern, whitespace rune or fixed word mentions share class 0), entry(state, class) is 32 bits:
+//   bits 0..19 next state      bits 20..30 event id      bit 31 word start
+constexpr uint32_t kMaxStatesW = 1u << 20;
+constexpr uint32_t kMaxEventsW = 2047;
+
 struct Dfa {
     uint32_t n_states = 0;
-    std::vector<uint16_t> table;      // n_states * 256
-    std::vector<uint8_t> eom;         // per state: bit 7 word start, bits 0..6 event id, applied at end of message
+    bool wide = false;
+    std::vector<uint16_t> table;      // D8: n_states * 256
+    std::vector<uint32_t> wtable;     // W: n_states * n_classes
+    uint8_t cls_of[256] = {0};        // W: byte -> class
+    uint32_t n_classes = 0;
+    uint32_t start_state_w = 0, neutral_state_w = 0;   // W: state ids do not fit the 8-bit fields below
+    std::vector<uint8_t> eom;         // per state: bit 7 word start, bits 0..6 event id, applied at end of message (D8)
+    std::vector<uint32_t> eom_w;      // same, event id | word start << 31 (both formats)
     std::vector<EventVec> events;     // id -> counters (events[0] is all-zero)
     uint8_t start_state = 0;          // at a message start (field start, nothing pending)
     uint8_t neutral_state = 0;        // mid-field, no partial match: where a warm-up begins

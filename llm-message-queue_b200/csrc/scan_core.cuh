@@ -94,6 +94,11 @@ TR_HD uint32_t tr_next(const LaneCtx &c, uint32_t word, uint32_t entry, uint32_t
 #endif
 }
 
+// per-format accessors (D8 here; the wide format overloads them in scan_wide.cuh)
+TR_HD uint32_t tr_ws(const LaneCtx &, uint32_t e) { return e >> 15; }
+TR_HD uint32_t tr_evmask(const LaneCtx &) { return 0x7F00u; }
+TR_HD uint32_t tr_evid(const LaneCtx &, uint32_t e) { return (e >> 8) & 0x7Fu; }
+
 // rare: kept out of line so the 16x unrolled replay stays small
 TR_COLD void apply_event_raw(const EventPacked *events, uint32_t *counters, uint32_t id, uint32_t msg) {
     EventPacked e = events[id];
@@ -109,7 +114,8 @@ TR_COLD void apply_event_raw(const EventPacked *events, uint32_t *counters, uint
 }
 TR_HD void apply_event(const LaneCtx &c, uint32_t id, uint32_t msg) { apply_event_raw(c.events, c.counters, id, msg); }
 
-TR_HD int32_t list_at(const LaneCtx &c, uint32_t k) {
+template <class Ctx>
+TR_HD int32_t list_at(const Ctx &c, uint32_t k) {
     if (c.list) return c.list[k];
     int64_t r = (int64_t)c.list_abs[c.msg_lo + k] - c.tile_start;
     const int64_t lim = 1 << 30;
@@ -118,7 +124,8 @@ TR_HD int32_t list_at(const LaneCtx &c, uint32_t k) {
 
 // index k into list with list[k] <= pos < list[k+1]  (upper_bound - 1; empty messages repeat a value, so this lands on
 // the one non-empty message that contains pos)
-TR_HD uint32_t find_msg(const LaneCtx &c, int32_t pos) {
+template <class Ctx>
+TR_HD uint32_t find_msg(const Ctx &c, int32_t pos) {
     uint32_t lo = 0, hi = c.list_n;   // first index with list[idx] > pos
     while (lo < hi) {
         uint32_t mid = (lo + hi) >> 1;
@@ -134,40 +141,44 @@ TR_HD uint32_t find_msg_from(const LaneCtx &c, int32_t pos, uint32_t k) {
 
 // ------------------------------------------------------------------------------------------- group code ---
 #define TR_STEP(wd, k)                                                                      \
-    e = tr_next(c, wd, e, k); words += e >> 15; ev |= e;
+    e = tr_next(c, wd, e, k); words += tr_ws(c, e); ev |= e;
 #define TR_STEP4(wd) TR_STEP(wd, 0) TR_STEP(wd, 1) TR_STEP(wd, 2) TR_STEP(wd, 3)
 
 // 16 transitions, no branches: e = state entry, words += word starts, ev |= every entry seen
-TR_HD void group16(const LaneCtx &c, const Quad &q, uint32_t &e, uint32_t &words, uint32_t &ev) {
+template <class Ctx>
+TR_HD void group16(const Ctx &c, const Quad &q, uint32_t &e, uint32_t &words, uint32_t &ev) {
     TR_STEP4(q.a) TR_STEP4(q.b) TR_STEP4(q.c) TR_STEP4(q.d)
 }
 
 #define TR_STEPF(wd, k)                                                                     \
-    e = tr_next(c, wd, e, k); words += e >> 15;                                             \
-    if (e & 0x7F00u) apply_event(c, (e >> 8) & 0x7Fu, msg);
+    e = tr_next(c, wd, e, k); words += tr_ws(c, e);                                         \
+    if (e & tr_evmask(c)) apply_event(c, tr_evid(c, e), msg);
 #define TR_STEPF4(wd) TR_STEPF(wd, 0) TR_STEPF(wd, 1) TR_STEPF(wd, 2) TR_STEPF(wd, 3)
 
 // same 16 transitions with the (rare) events applied to message `msg`
-TR_HD void group16_events(const LaneCtx &c, const Quad &q, uint32_t &e, uint32_t &words, uint32_t msg) {
+template <class Ctx>
+TR_HD void group16_events(const Ctx &c, const Quad &q, uint32_t &e, uint32_t &words, uint32_t msg) {
     TR_STEPF4(q.a) TR_STEPF4(q.b) TR_STEPF4(q.c) TR_STEPF4(q.d)
 }
 
-TR_HD void half8_events(const LaneCtx &c, uint32_t wa, uint32_t wb, uint32_t &e, uint32_t &words, uint32_t msg) {
+template <class Ctx>
+TR_HD void half8_events(const Ctx &c, uint32_t wa, uint32_t wb, uint32_t &e, uint32_t &words, uint32_t msg) {
     TR_STEPF4(wa) TR_STEPF4(wb)
 }
 
 // counted group: fast pass; a half whose transitions carried an event is replayed with event handling (the word
 // counts of the fast pass stand, the replay only applies the events)
-TR_HD void group16_counted(const LaneCtx &c, const Quad &q, uint32_t &e, uint32_t &words, uint32_t msg) {
+template <class Ctx>
+TR_HD void group16_counted(const Ctx &c, const Quad &q, uint32_t &e, uint32_t &words, uint32_t msg) {
     const uint32_t e0 = e;
     uint32_t ev = 0, ev2 = 0;
     TR_STEP4(q.a) TR_STEP4(q.b)
     const uint32_t e8 = e;
     { uint32_t &ev = ev2; TR_STEP4(q.c) TR_STEP4(q.d) }
-    if ((ev | ev2) & 0x7F00u) {
+    if ((ev | ev2) & tr_evmask(c)) {
         uint32_t wdummy = 0;
-        if (ev & 0x7F00u) { uint32_t er = e0; half8_events(c, q.a, q.b, er, wdummy, msg); }
-        if (ev2 & 0x7F00u) { uint32_t er = e8; half8_events(c, q.c, q.d, er, wdummy, msg); }
+        if (ev & tr_evmask(c)) { uint32_t er = e0; half8_events(c, q.a, q.b, er, wdummy, msg); }
+        if (ev2 & tr_evmask(c)) { uint32_t er = e8; half8_events(c, q.c, q.d, er, wdummy, msg); }
     }
 }
 
@@ -186,7 +197,8 @@ TR_HD Quad mask_tail(Quad q, int32_t t, uint32_t pad4) {
     q.c = (q.c & ~m2) | (pad4 & m2); q.d = (q.d & ~m3) | (pad4 & m3);
     return q;
 }
-TR_HD Quad load_quad(const LaneCtx &c, int32_t p) { return *reinterpret_cast<const Quad *>(c.stage + p + c.warm); }
+template <class Ctx>
+TR_HD Quad load_quad(const Ctx &c, int32_t p) { return *reinterpret_cast<const Quad *>(c.stage + p + c.warm); }
 
 // ------------------------------------------------------------------------------------------- fast lane ---
 // Walks the lane's chunk [chunk, chunk_end) (tile-relative, chunk 16-aligned).  Every finished segment is flushed with
@@ -262,7 +274,8 @@ TR_HD void lane_scan_fast(const LaneCtx &c, int32_t chunk, int32_t chunk_end, ui
 // messages end to keep its state right: boundaries only matter for attributing counts, and they always fall between
 // groups.  No masks, no end-of-message table, no second pass.  k = list index of the message containing `chunk`;
 // list holds the (padded) message starts.  at_arena_start: nothing precedes `chunk` (first lane of the first tile).
-TR_HD void lane_scan_padded(const LaneCtx &c, int32_t chunk, int32_t chunk_end, uint32_t k, bool at_arena_start,
+template <class Ctx>
+TR_HD void lane_scan_padded(const Ctx &c, int32_t chunk, int32_t chunk_end, uint32_t k, bool at_arena_start,
                             uint32_t *head_msg, uint32_t *head_words) {
     uint32_t e = c.start_state;
     if (!at_arena_start) {

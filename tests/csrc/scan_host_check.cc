@@ -31,6 +31,7 @@ int hostcheck_scan(const uint8_t *prios, const uint8_t *cis, const uint32_t *len
     Dfa dfa;
     std::string e = build_dfa(dict, &dfa);
     if (!e.empty()) { std::strncpy(err, e.c_str(), errcap - 1); err[errcap - 1] = 0; return 4; }
+    if (dfa.wide) { std::strncpy(err, "automaton needs the wide table format", errcap - 1); return 6; }
     info[0] = dfa.n_states; info[1] = dfa.n_states_unminimised; info[2] = dfa.warm_bytes; info[3] = (uint32_t)dfa.events.size();
     info[4] = (uint32_t)dfa.head_pad; info[5] = (uint32_t)dfa.tail_pad;
     if (n_msgs == 0) return 0;
@@ -117,7 +118,7 @@ extern "C" int hostcheck_table(const uint8_t *prios, const uint8_t *cis, const u
     }
     Dfa dfa;
     std::string e = build_dfa(dict, &dfa);
-    if (!e.empty()) return 4;
+    if (!e.empty() || dfa.wide) return 4;
     std::memcpy(table, dfa.table.data(), dfa.table.size() * 2);
     info[0] = dfa.n_states; info[1] = dfa.start_state; info[2] = dfa.neutral_state; info[3] = dfa.warm_bytes;
     return 0;
@@ -138,6 +139,7 @@ extern "C" int hostcheck_scan_padded(const uint8_t *prios, const uint8_t *cis, c
     Dfa dfa;
     std::string e = build_dfa(dict, &dfa);
     if (!e.empty()) { std::strncpy(err, e.c_str(), errcap - 1); err[errcap - 1] = 0; return 4; }
+    if (dfa.wide) { std::strncpy(err, "automaton needs the wide table format", errcap - 1); return 6; }
     info[0] = dfa.n_states; info[1] = (uint32_t)dfa.reset_pad;
     if (dfa.reset_pad < 0) { std::strncpy(err, "no reset pad", errcap - 1); return 5; }
     if (n_msgs == 0) return 0;
@@ -204,7 +206,7 @@ extern "C" int hostcheck_exact(const uint8_t *prios, const uint8_t *cis, const u
         o += lens[i];
     }
     Dfa x;
-    if (!build_dfa(dict, &x, true).empty()) return 4;
+    if (!build_dfa(dict, &x, true).empty() || x.wide) return 4;
     info[0] = x.n_states; info[1] = dict_has_bordered(dict) ? 1 : 0;
     for (uint32_t i = 0; i < n_msgs; i++) {
         uint32_t *acc = counters + (size_t)i * 8;
@@ -224,6 +226,95 @@ extern "C" int hostcheck_exact(const uint8_t *prios, const uint8_t *cis, const u
         acc[CNT_WORDS] += eo >> 7;
         if (eo & 0x7F) event(eo & 0x7F);
         if (offsets[i + 1] > offsets[i] && bytes[offsets[i + 1] - 1] == '?') acc[CNT_Q] |= 1;
+    }
+    return 0;
+}
+
+// wide-format check: padded arena + lane_scan_padded<WideCtx> over warp mini-tiles (what scan_wide_kernel runs), and,
+// when the dictionary has self-overlapping literals, the sequential exact recount of flagged messages
+#include "../../llm-message-queue_b200/csrc/scan_wide.cuh"
+extern "C" int hostcheck_scan_wide(const uint8_t *prios, const uint8_t *cis, const uint32_t *lens, const uint8_t *lits, uint32_t n_pat,
+                                   const uint64_t *offsets, const uint8_t *bytes, uint32_t n_msgs, uint32_t chunk,
+                                   uint32_t *counters, uint32_t *info, char *err, uint32_t errcap)
+{
+    std::vector<DictEntry> dict;
+    size_t o = 0;
+    for (uint32_t i = 0; i < n_pat; i++) {
+        dict.push_back({prios[i], cis[i] != 0, std::string(reinterpret_cast<const char *>(lits + o), lens[i])});
+        o += lens[i];
+    }
+    Dfa dfa;
+    std::string e = build_dfa(dict, &dfa);
+    if (!e.empty()) { std::strncpy(err, e.c_str(), errcap - 1); err[errcap - 1] = 0; return 4; }
+    info[0] = dfa.n_states; info[1] = (uint32_t)dfa.reset_pad; info[2] = dfa.wide; info[3] = dfa.n_classes; info[4] = dfa.warm_bytes;
+    info[5] = (uint32_t)dfa.events.size();
+    if (!dfa.wide || dfa.reset_pad < 0) { std::strncpy(err, "not a wide automaton / no reset pad", errcap - 1); return 5; }
+    if (n_msgs == 0) return 0;
+    std::vector<EventPacked> ev(dfa.events.size());
+    for (size_t i = 0; i < dfa.events.size(); i++) pack_event(dfa.events[i], &ev[i].x);
+    std::vector<uint64_t> poff(n_msgs + 1, 0);
+    for (uint32_t i = 0; i < n_msgs; i++) poff[i + 1] = poff[i] + ((offsets[i + 1] - offsets[i]) / 16 + 1) * 16;
+    std::vector<uint8_t> arena(poff[n_msgs] + 32, (uint8_t)dfa.reset_pad);
+    for (uint32_t i = 0; i < n_msgs; i++) std::memcpy(arena.data() + poff[i], bytes + offsets[i], offsets[i + 1] - offsets[i]);
+    std::memset(counters, 0, sizeof(uint32_t) * 8 * n_msgs);
+    const uint64_t total = poff[n_msgs];
+    const uint64_t mt = 32ull * chunk;
+    const int32_t warm = (int32_t)dfa.warm_bytes;
+    std::vector<uint8_t> stage_raw(mt + warm + 64);
+    uint8_t *stage = stage_raw.data();
+    while (reinterpret_cast<uintptr_t>(stage) & 15) stage++;
+    for (uint64_t ts = 0; ts < total; ts += mt) {
+        uint64_t te = std::min(total, ts + mt);
+        uint64_t cs = ts >= (uint64_t)warm ? ts - warm : 0;
+        std::memcpy(stage + (cs - (ts - warm)), arena.data() + cs, te - cs);
+        uint32_t lo = 0, hi = n_msgs + 1;
+        while (lo < hi) { uint32_t mid = (lo + hi) / 2; if (poff[mid] > ts) hi = mid; else lo = mid + 1; }
+        uint32_t mlo = lo - 1, mhi = mlo;
+        while (poff[mhi + 1] < te) mhi++;
+        std::vector<int32_t> list;
+        for (uint32_t m = mlo; m <= mhi + 1; m++) list.push_back((int32_t)((int64_t)poff[m] - (int64_t)ts));
+        WideCtx c;
+        c.wtbl = dfa.wtable.data(); c.cls = dfa.cls_of; c.ncls = dfa.n_classes; c.events = ev.data(); c.stage = stage;
+        c.list = list.data(); c.list_abs = poff.data(); c.tile_start = (int64_t)ts; c.list_n = (uint32_t)list.size(); c.msg_lo = mlo;
+        c.counters = counters; c.warm = warm; c.start_state = dfa.start_state_w; c.neutral_state = dfa.neutral_state_w;
+        int32_t len = (int32_t)(te - ts);
+        for (uint32_t l = 0; l < 32; l++) {
+            int32_t ch = (int32_t)(l * chunk);
+            if (ch >= len) break;
+            int32_t ce = std::min<int32_t>(ch + (int32_t)chunk, len);
+            uint32_t hm = 0, hw = 0;
+            lane_scan_padded(c, ch, ce, find_msg(c, ch), ts == 0 && l == 0, &hm, &hw);
+            if (hw) counters[(uint64_t)hm * 8 + CNT_WORDS] += hw;
+        }
+    }
+    // exact recount of flagged messages (self-overlapping literals)
+    if (dict_has_bordered(dict)) {
+        Dfa x;
+        std::string e2 = build_dfa(dict, &x, true);
+        if (!e2.empty() || !x.wide) { std::strncpy(err, "exact automaton", errcap - 1); return 7; }
+        for (uint32_t i = 0; i < n_msgs; i++) {
+            uint32_t *acc = counters + (size_t)i * 8;
+            if (!(acc[CNT_Q] & 2)) continue;
+            std::memset(acc, 0, 32);
+            uint32_t st = x.start_state_w;
+            auto event = [&](uint32_t id) {
+                const EventVec &v = x.events[id];
+                for (int k = 0; k < 4; k++) acc[CNT_KW + k] += v.kw[k];
+                acc[CNT_POS] += v.pos; acc[CNT_NEG] += v.neg; if (v.question) acc[CNT_Q] |= 1;
+            };
+            for (uint64_t p = offsets[i]; p < offsets[i + 1]; p++) {
+                uint32_t t = x.wtable[(size_t)st * x.n_classes + x.cls_of[bytes[p]]];
+                st = t & 0xFFFFF; acc[CNT_WORDS] += t >> 31;
+                if (t & 0x7FF00000u) event((t >> 20) & 0x7FF);
+            }
+            uint32_t eo = x.eom_w[st];
+            acc[CNT_WORDS] += eo >> 31;
+            if (eo & 0x7FFFFFFF) event(eo & 0x7FFFFFFF);
+        }
+    }
+    for (uint32_t i = 0; i < n_msgs; i++) {
+        counters[(uint64_t)i * 8 + CNT_Q] &= 1;
+        if (offsets[i + 1] > offsets[i] && bytes[offsets[i + 1] - 1] == '?') counters[(uint64_t)i * 8 + CNT_Q] |= 1;
     }
     return 0;
 }

@@ -10,7 +10,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 SRC = [os.path.join(HERE, "csrc", "scan_host_check.cc"),
        os.path.join(ROOT, "llm-message-queue_b200", "csrc", "dfa_build.cc")]
-DEPS = SRC + [os.path.join(ROOT, "llm-message-queue_b200", "csrc", f) for f in ("dfa_build.h", "scan_core.cuh")]
+DEPS = SRC + [os.path.join(ROOT, "llm-message-queue_b200", "csrc", f) for f in ("dfa_build.h", "scan_core.cuh", "scan_wide.cuh")]
 LIB = os.path.join(HERE, "csrc", "libscan_host_check.so")
 
 DEFAULT_DICT = [(1, True, b"immediate"), (1, True, b"emergency"), (1, True, b"asap"), (1, True, b"right now"),
@@ -70,3 +70,23 @@ def scan_padded(dict_entries, offsets, data, chunk=80, use_abs_list=False):
     risk = (counters[:n, 7] & 2) != 0
     counters[:, 7] &= 1
     return counters[:n], dict(states=int(info[0]), reset_pad=int(np.int32(info[1])), risk=risk)
+
+
+def scan_wide(dict_entries, offsets, data, chunk=80):
+    """counters through the wide-table lane (large dictionaries) + exact recount of flagged messages"""
+    n = len(offsets) - 1
+    prios = np.array([d[0] for d in dict_entries], np.uint8)
+    cis = np.array([1 if d[1] else 0 for d in dict_entries], np.uint8)
+    lens = np.array([len(d[2]) for d in dict_entries], np.uint32)
+    lits = np.frombuffer(b"".join(d[2] for d in dict_entries) or b"\0", np.uint8)
+    counters = np.zeros((max(n, 1), 8), np.uint32)
+    info = np.zeros(6, np.uint32)
+    err = C.create_string_buffer(256)
+    buf = data if len(data) else np.zeros(1, np.uint8)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    rc = lib().hostcheck_scan_wide(p(prios), p(cis), p(lens), p(lits), len(dict_entries), p(offsets), p(buf), n, chunk,
+                                   p(counters), p(info), err, 256)
+    if rc != 0:
+        raise ValueError(err.value.decode())
+    return counters[:n], dict(states=int(info[0]), reset_pad=int(np.int32(info[1])), wide=bool(info[2]), classes=int(info[3]),
+                              warm=int(info[4]), events=int(info[5]))
