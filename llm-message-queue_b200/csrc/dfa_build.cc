@@ -61,8 +61,19 @@ struct Nfa {
     uint32_t add_node() { nodes.emplace_back(); return static_cast<uint32_t>(nodes.size() - 1); }
 
     // one symbol = a set of alternative byte strings leading from `from` to a fresh node
+    // children of shareable (non self-overlapping) patterns, keyed by (from node, alternatives): common prefixes
+    // become one trie path, so the live-thread sets stay as small as the pattern depth even for 10 K keywords
+    std::map<std::pair<uint32_t, std::string>, uint32_t> shared;
+
     uint32_t add_symbol(uint32_t from, const std::vector<std::string> &alts, int pattern) {
+        std::string key;
+        if (pattern < 0) {
+            for (const std::string &a : alts) { key += a; key.push_back('\0'); }
+            auto it = shared.find({from, key});
+            if (it != shared.end()) return it->second;
+        }
         uint32_t to = add_node();
+        if (pattern < 0) shared[{from, key}] = to;
         nodes[to].pattern = pattern;
         for (const std::string &a : alts) {
             uint32_t cur = from;
@@ -95,6 +106,8 @@ std::vector<std::string> symbol_alts(uint32_t r, const std::string &raw, FoldKin
     return alts;
 }
 
+void add_event(EventVec *a, const EventVec &b);
+
 uint32_t add_pattern(Nfa *nfa, const std::string &lit, FoldKind fold, const EventVec &ev, bool bordered) {
     uint32_t cur = 0, bytes = 0;
     const int pattern = static_cast<int>(nfa->bordered.size());
@@ -106,11 +119,15 @@ uint32_t add_pattern(Nfa *nfa, const std::string &lit, FoldKind fold, const Even
         size_t longest = 0;
         for (auto &a : alts) longest = std::max(longest, a.size());
         bytes += static_cast<uint32_t>(longest);
-        cur = nfa->add_symbol(cur, alts, pattern);
+        cur = nfa->add_symbol(cur, alts, bordered ? pattern : -1);   // only self-overlapping patterns need private chains
         i += w;
     }
-    nfa->nodes[cur].accept_event = static_cast<int>(nfa->accept.size());
-    nfa->accept.push_back(ev);
+    if (nfa->nodes[cur].accept_event >= 0) {   // a shared end node: another pattern with the same text ends here too
+        add_event(&nfa->accept[nfa->nodes[cur].accept_event], ev);
+    } else {
+        nfa->nodes[cur].accept_event = static_cast<int>(nfa->accept.size());
+        nfa->accept.push_back(ev);
+    }
     nfa->max_bytes = std::max(nfa->max_bytes, bytes);
     return cur;
 }
@@ -270,7 +287,7 @@ struct Machine {
                 const NfaNode &t = nfa.nodes[e.second];
                 if (t.accept_event >= 0) {
                     add_event(&o->ev, nfa.accept[t.accept_event]);
-                    if (nfa.bordered[t.pattern]) matched.push_back(t.pattern);
+                    if (t.pattern >= 0 && nfa.bordered[t.pattern]) matched.push_back(t.pattern);
                 }
                 if (!t.edges.empty()) nk.push_back(e.second);
             }
