@@ -138,6 +138,8 @@ int32_t triage_pack_padded(const uint64_t *src_offsets, const uint8_t *src_bytes
 int32_t triage_submit_padded(triage_engine *e, int32_t target_queue, const uint64_t *offsets, const uint32_t *lengths,
                              const uint8_t *bytes, const triage_meta *meta, const uint64_t *enqueue_ns, uint32_t n,
                              triage_result *out, uint64_t *handle_base);
+int32_t triage_process_padded(triage_engine *e, const uint64_t *offsets, const uint32_t *lengths, const uint8_t *bytes,
+                              const triage_meta *meta, uint32_t n, triage_result *out);   /* ProcessMessage only */
 int32_t triage_submit_device_padded(triage_engine *e, const uint64_t *offsets_dev, const uint32_t *lengths_dev,
                                     const uint8_t *bytes_dev, uint64_t total_bytes, const triage_meta *meta_dev,
                                     const uint64_t *enqueue_ns_dev, uint32_t n, triage_result *results_dev,

@@ -82,6 +82,7 @@ _SIGS = {
                                        C.POINTER(C.c_uint64)]),
     "triage_submit_padded": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                          C.c_uint32, C.c_void_p, C.POINTER(C.c_uint64)]),
+    "triage_process_padded": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
     "triage_submit_device_padded": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p,
                                                 C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32)]),
     "triage_submit_device_static": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
@@ -206,8 +207,14 @@ class Engine:
 
     # -- hot path -----------------------------------------------------------
     def process(self, offsets, data, meta):
+        """ProcessMessage for a batch given as a packed arena; dictionaries too large for the dense table are served
+        through the padded layout (re-packed here)."""
         n = len(offsets) - 1
         out = np.zeros(n, dtype=RESULT_DTYPE)
+        if n and self.dict_info()["states"] > 256:
+            poff, plen, pbytes = self.pack_padded(offsets, data)
+            _check(lib().triage_process_padded(self._h, _p(poff), _p(plen), _p(pbytes), _p(meta), n, _p(out)))
+            return out
         buf = data if len(data) else np.zeros(16, np.uint8)
         _check(lib().triage_process(self._h, _p(offsets), _p(buf), _p(meta), n, _p(out)))
         return out

@@ -76,6 +76,13 @@ struct DevBuf {
     void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
 };
 
+struct DfaBufs {
+    DevBuf<uint8_t> table, eom, cls;
+    DevBuf<EventPacked> events;
+    DevBuf<uint32_t> wtable, eomw;
+    void release() { table.release(); eom.release(); cls.release(); events.release(); wtable.release(); eomw.release(); }
+};
+
 struct QItem { int32_t prio; uint64_t ts; uint64_t handle; };
 inline bool qless(const QItem &a, const QItem &b) {   // queue.go:22-27 + handle (sequence) as the final tie-break
     if (a.prio != b.prio) return a.prio < b.prio;
@@ -107,16 +114,12 @@ struct triage_engine {
     std::vector<DictEntry> dict;
     bool dict_dirty = true;
     Dfa dfa;
-    DevBuf<uint8_t> d_table;
     ScanGeometry geom{0, 0, 0};
     uint32_t pad_warps = 0;
-    DevBuf<EventPacked> d_events;
-    DevBuf<uint8_t> d_eom;
+    DfaBufs dm, dx;   // device copies of the scan automaton and of the exact (sequential) one
     DeviceDfa ddfa{};
     // exact (sequential, non-overlapping) automaton, only when the dictionary has self-overlapping literals
     bool has_bordered = false;
-    DevBuf<uint8_t> dx_table, dx_eom;
-    DevBuf<EventPacked> dx_events;
     DeviceDfa dxdfa{};
     // batch buffers (triage_submit) and scratch
     DevBuf<uint8_t> d_bytes;
@@ -151,61 +154,75 @@ struct triage_engine {
 
 namespace {
 
+// host automaton -> device buffers (either table format) and the DeviceDfa view the kernels take
+int32_t upload_dfa(const Dfa &dfa, DfaBufs *b, DeviceDfa *out) {
+    std::vector<EventPacked> ev(dfa.events.size());
+    for (size_t i = 0; i < dfa.events.size(); i++) pack_event(dfa.events[i], &ev[i].x);
+    DeviceDfa d{};
+    d.n_states = dfa.n_states; d.n_events = (uint32_t)ev.size(); d.warm = dfa.warm_bytes;
+    d.head_pad = dfa.head_pad; d.tail_pad = dfa.tail_pad; d.reset_pad = dfa.reset_pad;
+    d.wide = dfa.wide ? 1 : 0;
+    CU(b->events.ensure(ev.size()));
+    CU(cudaMemcpy(b->events.p, ev.data(), ev.size() * sizeof(EventPacked), cudaMemcpyHostToDevice));
+    d.events = b->events.p;
+    if (!dfa.wide) {
+        d.start_state = dfa.start_state; d.neutral_state = dfa.neutral_state;
+        std::vector<uint8_t> eom(256, 0);
+        std::copy(dfa.eom.begin(), dfa.eom.end(), eom.begin());
+        // rows padded to kRowBytes so that row r starts at shared-memory bank r (mod 32)
+        std::vector<uint8_t> padded((size_t)dfa.n_states * kRowBytes, 0);
+        for (uint32_t st = 0; st < dfa.n_states; st++)
+            std::memcpy(padded.data() + (size_t)st * kRowBytes, dfa.table.data() + (size_t)st * 256, 512);
+        CU(b->table.ensure(padded.size()));
+        CU(b->eom.ensure(256));
+        CU(cudaMemcpy(b->table.p, padded.data(), padded.size(), cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(b->eom.p, eom.data(), 256, cudaMemcpyHostToDevice));
+        d.table = b->table.p; d.eom = b->eom.p;
+    } else {
+        d.start_state = dfa.start_state_w; d.neutral_state = dfa.neutral_state_w;
+        d.n_classes = dfa.n_classes;
+        CU(b->wtable.ensure(dfa.wtable.size()));
+        CU(b->cls.ensure(256));
+        CU(b->eomw.ensure(dfa.eom_w.size()));
+        CU(cudaMemcpy(b->wtable.p, dfa.wtable.data(), dfa.wtable.size() * 4, cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(b->cls.p, dfa.cls_of, 256, cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(b->eomw.p, dfa.eom_w.data(), dfa.eom_w.size() * 4, cudaMemcpyHostToDevice));
+        d.wtable = b->wtable.p; d.cls_of = b->cls.p; d.eom_w = b->eomw.p;
+    }
+    *out = d;
+    return TRIAGE_OK;
+}
+
 int32_t commit_dict(triage_engine *e) {
     if (!e->dict_dirty) return TRIAGE_OK;
     Dfa dfa;
     std::string err = build_dfa(e->dict, &dfa);
     if (!err.empty()) return fail(TRIAGE_E_PATTERN, err);
     if (dfa.warm_bytes > kMaxWarm) return fail(TRIAGE_E_PATTERN, "pattern too long for the scan's warm-up window");
-    std::vector<EventPacked> ev(dfa.events.size());
-    for (size_t i = 0; i < dfa.events.size(); i++) pack_event(dfa.events[i], &ev[i].x);
-    std::vector<uint8_t> eom(256, 0);
-    std::copy(dfa.eom.begin(), dfa.eom.end(), eom.begin());
-    DeviceDfa d{};
-    d.n_states = dfa.n_states; d.n_events = (uint32_t)ev.size(); d.warm = dfa.warm_bytes;
-    d.start_state = dfa.start_state; d.neutral_state = dfa.neutral_state;
-    d.head_pad = dfa.head_pad; d.tail_pad = dfa.tail_pad; d.reset_pad = dfa.reset_pad;
-    const uint32_t pad_warps = d.reset_pad >= 0 ? pick_pad_warps(d, (size_t)e->max_smem_optin) : 0;
-    if (pad_warps == 0) d.reset_pad = -1;   // the padded kernel would not fit: packed entry points only
-    ScanGeometry geom = pick_scan_geometry(d, (size_t)e->max_smem_optin);
-    if (geom.nt == 0)
-        return fail(TRIAGE_E_PATTERN, "dictionary automaton (" + std::to_string(dfa.n_states) + " states) does not fit in shared memory");
-    // rows padded to kRowBytes so that row r starts at shared-memory bank r (mod 32)
-    std::vector<uint8_t> padded((size_t)dfa.n_states * kRowBytes, 0);
-    for (uint32_t st = 0; st < dfa.n_states; st++)
-        std::memcpy(padded.data() + (size_t)st * kRowBytes, dfa.table.data() + (size_t)st * 256, 512);
-    CU(e->d_table.ensure(padded.size()));
-    CU(e->d_events.ensure(ev.size()));
-    CU(e->d_eom.ensure(256));
+    if (dfa.wide && dfa.reset_pad < 0)
+        return fail(TRIAGE_E_PATTERN, "large dictionary without a usable pad byte (every ASCII whitespace occurs in a pattern)");
     // the previous automaton may still be in use by a kernel on the stream
     CU(cudaStreamSynchronize(e->stream));
-    CU(cudaMemcpy(e->d_table.p, padded.data(), padded.size(), cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(e->d_events.p, ev.data(), ev.size() * sizeof(EventPacked), cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(e->d_eom.p, eom.data(), 256, cudaMemcpyHostToDevice));
-    d.table = e->d_table.p; d.events = e->d_events.p; d.eom = e->d_eom.p;
+    DeviceDfa d{};
+    int32_t rc = upload_dfa(dfa, &e->dm, &d);
+    if (rc) return rc;
+    const uint32_t pad_warps = d.reset_pad >= 0 ? pick_pad_warps(d, (size_t)e->max_smem_optin) : 0;
+    if (pad_warps == 0) d.reset_pad = -1;   // the padded kernel would not fit: packed entry points only
+    ScanGeometry geom{0, 0, 0};
+    if (!dfa.wide) {
+        geom = pick_scan_geometry(d, (size_t)e->max_smem_optin);
+        if (geom.nt == 0)
+            return fail(TRIAGE_E_PATTERN, "dictionary automaton (" + std::to_string(dfa.n_states) + " states) does not fit in shared memory");
+    } else if (pad_warps == 0) {
+        return fail(TRIAGE_E_PATTERN, "large dictionary: the padded scan does not fit in shared memory");
+    }
     e->has_bordered = dict_has_bordered(e->dict);
     if (e->has_bordered) {
         Dfa xd;
         err = build_dfa(e->dict, &xd, true);
         if (!err.empty()) return fail(TRIAGE_E_PATTERN, "exact automaton: " + err);
-        std::vector<EventPacked> xev(xd.events.size());
-        for (size_t i = 0; i < xd.events.size(); i++) pack_event(xd.events[i], &xev[i].x);
-        std::vector<uint8_t> xeom(256, 0);
-        std::copy(xd.eom.begin(), xd.eom.end(), xeom.begin());
-        std::vector<uint8_t> xpad((size_t)xd.n_states * kRowBytes, 0);
-        for (uint32_t st = 0; st < xd.n_states; st++)
-            std::memcpy(xpad.data() + (size_t)st * kRowBytes, xd.table.data() + (size_t)st * 256, 512);
-        CU(e->dx_table.ensure(xpad.size()));
-        CU(e->dx_events.ensure(xev.size()));
-        CU(e->dx_eom.ensure(256));
-        CU(cudaMemcpy(e->dx_table.p, xpad.data(), xpad.size(), cudaMemcpyHostToDevice));
-        CU(cudaMemcpy(e->dx_events.p, xev.data(), xev.size() * sizeof(EventPacked), cudaMemcpyHostToDevice));
-        CU(cudaMemcpy(e->dx_eom.p, xeom.data(), 256, cudaMemcpyHostToDevice));
-        DeviceDfa x{};
-        x.table = e->dx_table.p; x.events = e->dx_events.p; x.eom = e->dx_eom.p;
-        x.n_states = xd.n_states; x.n_events = (uint32_t)xev.size(); x.start_state = xd.start_state; x.neutral_state = xd.neutral_state;
-        x.head_pad = x.tail_pad = x.reset_pad = -1; x.warm = 0;
-        e->dxdfa = x;
+        rc = upload_dfa(xd, &e->dx, &e->dxdfa);
+        if (rc) return rc;
     }
     e->ddfa = d;
     e->pad_warps = pad_warps;
@@ -229,6 +246,8 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     const bool padded = lengths != nullptr;
     if (padded && e->ddfa.reset_pad < 0)
         return fail(TRIAGE_E_ARG, "this dictionary has no reset pad byte: use the packed (unpadded) entry points");
+    if (!padded && e->ddfa.wide)
+        return fail(TRIAGE_E_ARG, "a dictionary this large (more than 256 automaton states) needs the padded-arena entry points");
     if (padded && (total & 15)) return fail(TRIAGE_E_ARG, "padded arena size must be a multiple of 16");
     cudaStream_t s = e->stream;
     uint32_t launches = 0;
@@ -379,7 +398,7 @@ void triage_destroy(triage_engine *e) {
     cudaSetDevice(e->opts.device);
     cudaStreamSynchronize(e->stream);
     if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
-    e->d_table.release(); e->d_events.release(); e->d_eom.release(); e->dx_table.release(); e->dx_events.release(); e->dx_eom.release(); e->d_bytes.release(); e->d_offsets.release();
+    e->dm.release(); e->dx.release(); e->d_bytes.release(); e->d_offsets.release();
     e->d_ts.release(); e->d_pending.release(); e->d_maxsize.release(); e->d_meta.release(); e->d_results.release(); e->d_counters.release();
     e->d_tile_first.release(); e->d_lengths.release(); e->d_order.release(); e->d_perm_a.release(); e->d_perm_b.release(); e->d_blockhist.release();
     e->d_totals.release(); e->d_small.release(); e->d_bucket.release(); e->d_bucket2.release(); e->d_run_keys.release();
@@ -449,7 +468,7 @@ int32_t triage_dict_info(triage_engine *e, uint32_t *n_states, uint32_t *warm_by
     if (rc) return rc;
     if (n_states) *n_states = e->dfa.n_states;
     if (warm_bytes) *warm_bytes = e->dfa.warm_bytes;
-    if (table_bytes) *table_bytes = e->dfa.n_states * kRowBytes;
+    if (table_bytes) *table_bytes = e->dfa.wide ? e->dfa.n_states * e->dfa.n_classes * 4u : e->dfa.n_states * kRowBytes;
     return TRIAGE_OK;
 }
 
@@ -513,22 +532,22 @@ int32_t upload_batch(triage_engine *e, const uint64_t *offsets, const uint32_t *
 
 }  // namespace
 
-int32_t triage_process(triage_engine *e, const uint64_t *offsets, const uint8_t *bytes, const triage_meta *meta, uint32_t n,
-                       triage_result *out) {
+static int32_t process_impl(triage_engine *e, const uint64_t *offsets, const uint32_t *lengths, const uint8_t *bytes,
+                            const triage_meta *meta, uint32_t n, triage_result *out) {
     if (!e || (n && (!offsets || !meta || !out))) return fail(TRIAGE_E_ARG, "null argument");
     CU(cudaSetDevice(e->opts.device));
     std::lock_guard<std::mutex> lock(e->mu);
     if (n == 0) return TRIAGE_OK;
     auto t0 = std::chrono::steady_clock::now();
     uint64_t total = 0;
-    int32_t rc = upload_batch(e, offsets, nullptr, bytes, meta, nullptr, n, &total);
+    int32_t rc = upload_batch(e, offsets, lengths, bytes, meta, nullptr, n, &total);
     if (rc) return rc;
     auto t1 = std::chrono::steady_clock::now();
     const uint64_t pending[4] = {0, 0, 0, 0};
     const int64_t ms[4] = {0, 0, 0, 0};
     uint32_t n_adm = 0;
-    rc = run_device(e, RUN_PROCESS_ONLY, e->d_offsets.p, nullptr, e->d_bytes.p, total, e->d_meta.p, nullptr, n, e->d_results.p,
-                    e->d_order.p, pending, ms, &n_adm);
+    rc = run_device(e, RUN_PROCESS_ONLY, e->d_offsets.p, lengths ? e->d_lengths.p : nullptr, e->d_bytes.p, total, e->d_meta.p, nullptr, n,
+                    e->d_results.p, e->d_order.p, pending, ms, &n_adm);
     if (rc) return rc;
     auto t2 = std::chrono::steady_clock::now();
     CU(cudaMemcpyAsync(out, e->d_results.p, (size_t)n * sizeof(triage_result), cudaMemcpyDeviceToHost, e->stream));
@@ -537,6 +556,17 @@ int32_t triage_process(triage_engine *e, const uint64_t *offsets, const uint8_t 
     e->tm.h2d_ms = std::chrono::duration<float, std::milli>(t1 - t0).count();
     e->tm.d2h_ms = std::chrono::duration<float, std::milli>(t3 - t2).count();
     return TRIAGE_OK;
+}
+
+int32_t triage_process(triage_engine *e, const uint64_t *offsets, const uint8_t *bytes, const triage_meta *meta, uint32_t n,
+                       triage_result *out) {
+    return process_impl(e, offsets, nullptr, bytes, meta, n, out);
+}
+
+int32_t triage_process_padded(triage_engine *e, const uint64_t *offsets, const uint32_t *lengths, const uint8_t *bytes,
+                              const triage_meta *meta, uint32_t n, triage_result *out) {
+    if (n && !lengths) return fail(TRIAGE_E_ARG, "null lengths");
+    return process_impl(e, offsets, lengths, bytes, meta, n, out);
 }
 
 static int32_t submit_impl(triage_engine *e, int32_t target_queue, const uint64_t *offsets, const uint32_t *lengths, const uint8_t *bytes,
@@ -1019,6 +1049,7 @@ extern "C" int32_t triage_submit_device_static(triage_engine *e, const uint64_t 
         return fail(TRIAGE_E_ARG, "triage_submit_device_static: arena of " + std::to_string(total_bytes) + " bytes exceeds the static scratch limit of " +
                                       std::to_string(kStaticMaxBytes));
     if (e->dict_dirty) return fail(TRIAGE_E_ARG, "triage_submit_device_static: call triage_dict_commit first (committing allocates, this entry point must not)");
+    if (e->ddfa.wide) return fail(TRIAGE_E_ARG, "triage_submit_device_static: large dictionaries need the padded-arena entry points");
     if ((reinterpret_cast<uintptr_t>(bytes_dev) & 15) != 0) return fail(TRIAGE_E_ARG, "device arena must be 16-byte aligned");
     CU(cudaSetDevice(e->opts.device));
     unsigned char *base = nullptr;

@@ -14,6 +14,8 @@
 // 92-119, queue_manager.go:451-466, queue_factory.go:211-233, cmd/queue-manager/main.go:111-124.
 #include "kernels.cuh"
 
+#include <type_traits>
+
 namespace triage {
 
 // ------------------------------------------------------------------------------ PTX helpers --
@@ -280,11 +282,12 @@ cudaError_t launch_scan(const ScanArgs &a, const DeviceDfa &d, const ScanGeometr
 // after the automaton has been loaded.
 struct PadSmem { uint32_t table, events, stage0, list0, total, stage_bytes, list_bytes; };
 constexpr uint32_t kPadListCap = 34;
-__host__ __device__ inline PadSmem pad_layout(uint32_t n_states, uint32_t n_events, uint32_t warm, uint32_t nw) {
+__host__ __device__ inline PadSmem pad_layout(uint32_t n_states, uint32_t n_events, uint32_t warm, uint32_t nw, bool wide) {
     PadSmem L;
     uint32_t o = 1024;   // mbarriers
-    L.table = o; o += ((n_states * kRowBytes + 127u) / 128u) * 128u;
-    L.events = o; o += ((n_events * 16u + 127u) / 128u) * 128u;
+    // dense: the whole table and the event list; wide: only the 256-byte class map (table + events stay in global memory)
+    L.table = o; o += wide ? 256u : ((n_states * kRowBytes + 127u) / 128u) * 128u;
+    L.events = o; o += wide ? 0u : ((n_events * 16u + 127u) / 128u) * 128u;
     L.stage_bytes = ((warm + kPadMiniTile + 16u + 127u) / 128u) * 128u;
     L.stage0 = o; o += nw * 2 * L.stage_bytes;
     L.list_bytes = 160;
@@ -292,7 +295,7 @@ __host__ __device__ inline PadSmem pad_layout(uint32_t n_states, uint32_t n_even
     L.total = o;
     return L;
 }
-size_t scan_padded_smem_bytes(const DeviceDfa &d, uint32_t nw) { return pad_layout(d.n_states, d.n_events, d.warm, nw).total; }
+size_t scan_padded_smem_bytes(const DeviceDfa &d, uint32_t nw) { return pad_layout(d.n_states, d.n_events, d.warm, nw, d.wide != 0).total; }
 // most warps per CTA whose staging buffers still fit next to the automaton (0: none)
 uint32_t pick_pad_warps(const DeviceDfa &d, size_t max_smem) {
     for (uint32_t nw : {24u, 20u, 16u, 12u, 8u})
@@ -300,13 +303,13 @@ uint32_t pick_pad_warps(const DeviceDfa &d, size_t max_smem) {
     return 0;
 }
 
-template <int NW>
+template <int NW, bool WIDE>
 __global__ void __launch_bounds__(NW * 32, 1) scan_padded_kernel(ScanArgs a, DeviceDfa d) {
     constexpr uint32_t kPadWarps = NW;
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int C = kPadChunk;
     constexpr uint32_t MT = kPadMiniTile;
-    const PadSmem L = pad_layout(d.n_states, d.n_events, d.warm, kPadWarps);
+    const PadSmem L = pad_layout(d.n_states, d.n_events, d.warm, kPadWarps, WIDE);
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem) + warp * 2;
     uint8_t *tbl = smem + L.table;
@@ -320,7 +323,9 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_padded_kernel(ScanArgs a, Dev
         mbar_init(&bars[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    {
+    if constexpr (WIDE) {
+        for (uint32_t i = tid; i < 256; i += kPadWarps * 32) tbl[i] = d.cls_of[i];
+    } else {
         const uint32_t *src = reinterpret_cast<const uint32_t *>(d.table);
         uint32_t *dst = reinterpret_cast<uint32_t *>(tbl);
         for (uint32_t i = tid; i < d.n_states * (kRowBytes / 4); i += kPadWarps * 32) dst[i] = src[i];
@@ -361,12 +366,17 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_padded_kernel(ScanArgs a, Dev
     if (nmine > 1) { first_nxt = a.tile_first[t + stride]; last_nxt = a.tile_first[t + stride + 1]; }
     __syncwarp();
 
-    LaneCtx c;
-    c.tbl = tbl; c.events = events; c.eom = nullptr;
+    using Ctx = typename std::conditional<WIDE, WideCtx, LaneCtx>::type;
+    Ctx c;
+    if constexpr (WIDE) {
+        c.wtbl = d.wtable; c.cls = tbl; c.ncls = d.n_classes; c.events = d.events;
+    } else {
+        c.tbl = tbl; c.events = events; c.eom = nullptr;
+        c.head_pad4 = c.tail_pad4 = 0;
+        c.tbl_s = smem_u32(tbl);
+    }
     c.list_abs = a.offsets; c.counters = a.counters; c.warm = (int32_t)warm;
     c.start_state = d.start_state; c.neutral_state = d.neutral_state;
-    c.head_pad4 = c.tail_pad4 = 0;
-    c.tbl_s = smem_u32(tbl);
     const int32_t chunk = (int32_t)(lane * C);
     const uint64_t ts_step = (uint64_t)stride * MT;
 
@@ -439,23 +449,24 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_padded_kernel(ScanArgs a, Dev
     }
 }
 
-template <int NW>
+template <int NW, bool WIDE = false>
 static cudaError_t launch_scan_padded_variant(const ScanArgs &a, const DeviceDfa &d, int sm_count, cudaStream_t s) {
     size_t smem = scan_padded_smem_bytes(d, NW);
     static size_t configured = 0;
     if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(scan_padded_kernel<NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(scan_padded_kernel<NW, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         configured = smem;
     }
     uint32_t need = (a.ntiles + NW - 1) / NW;
     uint32_t grid = need < (uint32_t)sm_count ? need : (uint32_t)sm_count;
-    scan_padded_kernel<NW><<<grid, NW * 32, smem, s>>>(a, d);
+    scan_padded_kernel<NW, WIDE><<<grid, NW * 32, smem, s>>>(a, d);
     return cudaGetLastError();
 }
 
 cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, int sm_count, cudaStream_t s) {
     if (a.ntiles == 0) return cudaSuccess;
+    if (d.wide) return launch_scan_padded_variant<24, true>(a, d, sm_count, s);
     switch (nw) {
         case 24: return launch_scan_padded_variant<24>(a, d, sm_count, s);
         case 20: return launch_scan_padded_variant<20>(a, d, sm_count, s);
@@ -487,15 +498,27 @@ __global__ void __launch_bounds__(128) fixup_kernel(const uint8_t *__restrict__ 
             if ((e.z >> 16) & 0xFFu) acc[CNT_Q] |= 1u;
         };
         uint32_t st = x.start_state;
-        for (uint64_t p = 0; p < len; p++) {
-            uint32_t e = *reinterpret_cast<const uint16_t *>(x.table + st * kRowBytes + 2u * bytes[off + p]);
-            st = e & 0xFFu;
-            acc[CNT_WORDS] += e >> 15;
-            if (e & 0x7F00u) event((e >> 8) & 0x7Fu);
+        if (!x.wide) {
+            for (uint64_t p = 0; p < len; p++) {
+                uint32_t e = *reinterpret_cast<const uint16_t *>(x.table + st * kRowBytes + 2u * bytes[off + p]);
+                st = e & 0xFFu;
+                acc[CNT_WORDS] += e >> 15;
+                if (e & 0x7F00u) event((e >> 8) & 0x7Fu);
+            }
+            const uint32_t eo = x.eom[st];
+            acc[CNT_WORDS] += eo >> 7;
+            if (eo & 0x7Fu) event(eo & 0x7Fu);
+        } else {
+            for (uint64_t p = 0; p < len; p++) {
+                uint32_t e = x.wtable[(uint64_t)st * x.n_classes + x.cls_of[bytes[off + p]]];
+                st = e & 0xFFFFFu;
+                acc[CNT_WORDS] += e >> 31;
+                if (e & 0x7FF00000u) event((e >> 20) & 0x7FFu);
+            }
+            const uint32_t eo = x.eom_w[st];
+            acc[CNT_WORDS] += eo >> 31;
+            if (eo & 0x7FFFFFFFu) event(eo & 0x7FFFFFFFu);
         }
-        const uint32_t eo = x.eom[st];
-        acc[CNT_WORDS] += eo >> 7;
-        if (eo & 0x7Fu) event(eo & 0x7Fu);
         if (len && bytes[off + len - 1] == '?') acc[CNT_Q] |= 1u;
 #pragma unroll
         for (int k = 0; k < CNT_STRIDE; k++) cnt[k] = acc[k];

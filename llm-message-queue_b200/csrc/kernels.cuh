@@ -5,6 +5,7 @@
 
 #include "../../include/triage.h"
 #include "scan_core.cuh"
+#include "scan_wide.cuh"
 
 namespace triage {
 
@@ -22,6 +23,12 @@ struct DeviceDfa {
     uint32_t n_states, n_events, warm, start_state, neutral_state;
     int32_t head_pad, tail_pad;  // -1: no inert pad byte exists, use the byte-at-a-time boundary path
     int32_t reset_pad;           // fill byte of the padded arena layout (-1: this dictionary has none)
+    // wide format (more than 256 states): class map + 32-bit table in global memory, padded arena only
+    int32_t wide;
+    const uint32_t *wtable;      // n_states * n_classes
+    const uint8_t *cls_of;       // 256
+    const uint32_t *eom_w;       // n_states (fix-up kernel)
+    uint32_t n_classes;
 };
 
 struct ScanArgs {

@@ -75,7 +75,26 @@ def test_long_pattern_widens_the_warm_up():
 def test_unsupported_dictionaries_are_refused():
     with pytest.raises(ValueError):
         hc.scan(hc.DEFAULT_DICT + [(2, False, b"\xff")], *co.pack([b"x"]))
-    # enough distinct long patterns to overflow the 256-state dense table
+    # enough distinct long patterns to overflow the 256-state dense table: the dense-format harness refuses,
+    # the wide format takes over (test_large_dictionary_wide_format)
     many = hc.DEFAULT_DICT + [(4, False, (f"w{i:03d}" * 3).encode()) for i in range(40)]
     with pytest.raises(ValueError):
         hc.scan(many, *co.pack([b"x"]))
+
+
+def test_large_dictionary_wide_format():
+    """C5: 10 000 keywords on top of the defaults compile to the wide (class-compressed, 32-bit) table; the padded lane walk
+    plus the exact recount of flagged messages equals the oracle, self-overlapping keywords included."""
+    from tests import c5
+    entries = hc.DEFAULT_DICT + c5.dictionary()
+    d = co.Dict()
+    for p, ci, lit in entries[len(hc.DEFAULT_DICT):]:
+        assert d.add(p, lit, ci) == 0
+    off, data, meta, ts = co.generate(0xC0FFEE05, 250, 64, 900, mix=2, edge=100)
+    contents = c5.inject([bytes(data[int(off[i]):int(off[i + 1])]) for i in range(250)], entries[9:])
+    off, data = co.pack(contents)
+    cnt, info = hc.scan_wide(entries, off, data, chunk=80)
+    assert info["wide"] and info["states"] > 50000 and info["reset_pad"] == 9
+    exp = _expected(d, contents)
+    bad = np.nonzero((cnt != exp).any(axis=1))[0]
+    assert len(bad) == 0, (bad[:5], cnt[bad[:5]], exp[bad[:5]])

@@ -324,3 +324,35 @@ def test_self_overlapping_keywords_count_without_overlap():
         assert np.array_equal((handles - base).astype(np.uint32), order)
     finally:
         e.close()
+
+
+def test_c5_large_dictionary_10k_keywords():
+    """BASELINE configs[4]: 10 000 keywords added with AddKeywordPattern semantics (case-sensitive literals, ~1 %
+    self-overlapping) on top of the defaults, skewed traffic.  The automaton (tens of thousands of states) takes the
+    wide table format: class map in shared memory, transitions in L2-resident global memory."""
+    from tests import c5
+    entries = c5.dictionary()
+    d = co.Dict()
+    e = mq.Engine(device=0)
+    try:
+        for p, ci, lit in entries:
+            assert d.add(p, lit, ci) == 0
+            e.add_literal(p, lit, ci)
+        info = e.dict_info()
+        assert info["states"] > 50000
+        off, data, meta, ts = co.generate(0xC0FFEE05, 3000, 256, 2048, mix=2, edge=50)
+        contents = c5.inject([bytes(data[int(off[i]):int(off[i + 1])]) for i in range(len(meta))], entries)
+        off, data = co.pack(contents)
+        exp, order = co.pipeline(d, off, data, meta, ts, nthreads=os.cpu_count() or 4)
+        assert len(set(exp["label"].tolist())) >= 4
+        poff, plen, pbytes = e.pack_padded(off, data)
+        res, base = e.submit_padded(poff, plen, pbytes, meta, ts)
+        _assert_same(res, exp, FIELDS + ("accepted", "admit"), ctx="C5 padded")
+        handles, _ = e.drain(len(meta))
+        assert np.array_equal((handles - base).astype(np.uint32), order)
+        res2 = e.process(off, data, meta)            # the mirror's ProcessMessage path re-packs for large dictionaries
+        _assert_same(res2, exp, ctx="C5 process")
+        with pytest.raises(mq.TriageError):          # the packed submit says so instead of silently doing something else
+            e.submit(off, data, meta, ts)
+    finally:
+        e.close()
