@@ -1,0 +1,37 @@
+#!/usr/bin/env python
+"""Side measurements for DESIGN.md (not the bench contract): scan time of the other BASELINE configs on one B200.
+  python profiles/measure_configs.py c4|c5
+c4: 16 384 long-context payloads of 32-128 KB (quarter of SURVEY's 65 536), default dictionary.
+c5: 262 144 messages of 256-4096 B, 10 000-keyword dictionary (wide table format)."""
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import llm_message_queue_b200 as mq  # noqa: E402
+from oracle import c_oracle as co  # noqa: E402
+from tests import c5  # noqa: E402
+
+which = sys.argv[1] if len(sys.argv) > 1 else "c4"
+e = mq.Engine(device=0)
+if which == "c5":
+    for p, ci, lit in c5.dictionary():
+        e.add_literal(p, lit, ci)
+    off, data, meta, ts = co.generate(0xC0FFEE05, 1 << 18, 256, 4096, mix=2, edge=50)
+else:
+    off, data, meta, ts = co.generate(0xC0FFEE04, 1 << 14, 32768, 131072, edge=50)
+info = e.dict_info()
+poff, plen, pbytes = e.pack_padded(off, data)
+times = []
+for _ in range(6):
+    res, base = e.submit_padded(poff, plen, pbytes, meta, None)
+    e.drain(len(meta))
+    times.append(e.timings())
+t = times[-1]
+scan = min(x["scan_ms"] for x in times[2:])
+print(json.dumps({"config": which, "messages": len(meta), "arena_bytes": int(poff[-1]), "automaton_states": info["states"],
+                  "table_bytes": info["table_bytes"], "scan_ms": scan, "scan_GBps": t["scan_bytes"] / scan / 1e6,
+                  "finalize_ms": t["finalize_ms"], "order_ms": t["order_ms"], "msgs_per_s_device": len(meta) / (t["total_ms"] / 1e3)}))
