@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cstring>
 #include <map>
+#include <string>
 #include <unordered_map>
 
 namespace triage {
@@ -400,6 +401,133 @@ bool dict_has_bordered(const std::vector<DictEntry> &dict) {
     return false;
 }
 
+// ---- shared-memory placement of the dense table ---------------------------------------------------------------
+// The scan reads entry (state, byte) at byte offset state * 516 + 2 * byte of shared memory: bank = (state + byte / 2)
+// mod 32.  32 lanes in different states reading different bytes collide on banks; how often depends only on
+// state id mod 32 of the states the lanes are usually in.  place_states() renumbers the (minimised) states so that the
+// expected number of shared-memory wavefronts per 32-lane lookup is small for ordinary text: it walks the automaton over
+// a deterministic sample of English-like text (common words, the dictionary's own patterns, some capitals, digits and
+// punctuation), draws 32-lane groups from that walk and does coordinate descent on "most distinct words in one bank"
+// over the rotations of the hottest states.  Results never depend on the numbering; a workload unlike the sample only
+// sees the same conflict rate an arbitrary numbering would give.
+static const char kPriorWords[] =
+    "the of and to a in is it you that he was for on are with as i his they be at one have this from or had by hot but some "
+    "there we can out other were all your up use word said an each she which do their time if will way about many then them "
+    "would write like so these her long make thing see him two has look more day could go come did my sound no most number "
+    "over know water than call first people may down side been now find any new work part take get place made live after "
+    "back little only round man year came show every me give our under name very through just form much think say help low "
+    "line before turn cause same mean differ move right boy old too does tell sentence set three want air well also play "
+    "small end put home read hand port large spell add even land here must big high such follow act ask men change went "
+    "light kind off need house picture try us again animal point mother world near build self earth father head stand own "
+    "page should country found answer school grow study still learn plant cover food sun four thought let keep eye never "
+    "last door between city tree cross since hard start might story saw far sea draw left late run while press close night "
+    "real life few stop open seem together next white children begin got walk example ease paper often always music those "
+    "both mark book letter until mile river car feet care second group carry took rain eat room friend began idea fish "
+    "mountain north once base hear horse cut sure watch color face wood main enough plain girl usual young ready above ever "
+    "red list though feel talk bird body dog family direct pose leave song measure state product black short please thanks "
+    "hello team customer order account issue problem update server error request message service support system data";
+
+static std::vector<uint32_t> place_states(const std::vector<uint8_t> &next /* n * 256 */, uint32_t n, uint32_t start,
+                                          const std::vector<std::string> &patterns) {
+    std::vector<uint32_t> perm(n);
+    for (uint32_t i = 0; i < n; i++) perm[i] = i;
+    if (n <= 2) return perm;
+    uint64_t rng = 0x9E3779B97F4A7C15ull;
+    auto rnd = [&]() { rng = rng * 6364136223846793005ull + 1442695040888963407ull; return static_cast<uint32_t>(rng >> 33); };
+    std::vector<std::string> common;
+    for (const char *p = kPriorWords; *p;) {
+        const char *q = p;
+        while (*q && *q != ' ') q++;
+        common.emplace_back(p, q);
+        p = *q ? q + 1 : q;
+    }
+    std::string text;
+    while (text.size() < 48 * 1024) {
+        std::string w = (!patterns.empty() && rnd() % 100 < 4) ? patterns[rnd() % patterns.size()] : common[rnd() % common.size()];
+        uint32_t r = rnd() % 100;
+        if (r < 6) { if (!w.empty() && w[0] >= 'a' && w[0] <= 'z') w[0] = static_cast<char>(w[0] - 32); }
+        else if (r < 8) { for (char &ch : w) if (ch >= 'a' && ch <= 'z') ch = static_cast<char>(ch - 32); }
+        else if (r < 10) w = std::to_string(rnd() % 1000);
+        r = rnd() % 100;
+        if (r < 6) w.push_back(",.?!:"[rnd() % 5]);
+        text += w;
+        text.push_back(' ');
+    }
+    // walk: (state, word of the row) per text byte
+    std::vector<uint16_t> key(text.size());
+    std::vector<uint32_t> heat(n, 0);
+    uint32_t st = start;
+    for (size_t i = 0; i < text.size(); i++) {
+        uint8_t b = static_cast<uint8_t>(text[i]);
+        key[i] = static_cast<uint16_t>(st << 7 | b >> 1);
+        heat[st]++;
+        st = next[static_cast<size_t>(st) * 256 + b];
+    }
+    // 32-lane samples, de-duplicated (equal keys are one broadcast read)
+    constexpr uint32_t kSamples = 1024, kHot = 32, kSweeps = 2;
+    std::vector<std::vector<uint16_t>> samples(kSamples);
+    std::vector<std::vector<uint32_t>> uses(n);   // state -> samples containing it
+    for (uint32_t t = 0; t < kSamples; t++) {
+        std::vector<uint16_t> &v = samples[t];
+        for (int l = 0; l < 32; l++) v.push_back(key[rnd() % key.size()]);
+        std::sort(v.begin(), v.end());
+        v.erase(std::unique(v.begin(), v.end()), v.end());
+        uint32_t last = ~0u;
+        for (uint16_t k : v) if (static_cast<uint32_t>(k >> 7) != last) { last = k >> 7; uses[last].push_back(t); }
+    }
+    std::vector<uint32_t> order(n);
+    for (uint32_t i = 0; i < n; i++) order[i] = i;
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return heat[a] > heat[b]; });
+    std::vector<uint8_t> rot(n);
+    for (uint32_t i = 0; i < n; i++) rot[i] = static_cast<uint8_t>(i & 31);
+    auto sample_cost = [&](uint32_t t) {
+        uint8_t cnt[32] = {0};
+        uint32_t mx = 0;
+        for (uint16_t k : samples[t]) {
+            uint32_t b = (rot[k >> 7] + (k & 127u)) & 31u;
+            if (++cnt[b] > mx) mx = cnt[b];
+        }
+        return mx;
+    };
+    const uint32_t nhot = std::min<uint32_t>(kHot, n);
+    for (uint32_t sweep = 0; sweep < kSweeps; sweep++) {
+        for (uint32_t h = 0; h < nhot; h++) {
+            const uint32_t s = order[h];
+            if (heat[s] == 0) break;
+            uint32_t best_cost = ~0u, best_rot = rot[s];
+            const uint8_t keep = rot[s];
+            for (uint32_t r = 0; r < 32; r++) {
+                rot[s] = static_cast<uint8_t>((keep + r) & 31);   // the current rotation first: ties keep it
+                uint32_t c = 0;
+                for (uint32_t t : uses[s]) c += sample_cost(t);
+                if (c < best_cost) { best_cost = c; best_rot = rot[s]; }
+            }
+            rot[s] = static_cast<uint8_t>(best_rot);
+        }
+    }
+    // rotations -> ids: hot states take a free id with their residue (nearest residue if that one is used up)
+    std::vector<bool> taken(n, false);
+    std::vector<bool> placed(n, false);
+    for (uint32_t h = 0; h < nhot; h++) {
+        const uint32_t s = order[h];
+        if (heat[s] == 0) break;
+        for (uint32_t d = 0; d < 32 && !placed[s]; d++) {
+            for (uint32_t id = (rot[s] + d) & 31u; id < n; id += 32) {
+                if (!taken[id]) { taken[id] = true; perm[s] = id; placed[s] = true; break; }
+            }
+        }
+    }
+    uint32_t free_id = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        const uint32_t s = order[i];
+        if (placed[s]) continue;
+        while (taken[free_id]) free_id++;
+        taken[free_id] = true;
+        perm[s] = free_id;
+    }
+    return perm;
+}
+
 std::string build_dfa(const std::vector<DictEntry> &dict, Dfa *out, bool exact_nonoverlap) {
     Machine m;
     m.exact_nonoverlap = exact_nonoverlap;
@@ -533,6 +661,18 @@ std::string build_dfa(const std::vector<DictEntry> &dict, Dfa *out, bool exact_n
     }
     uint32_t nmin = *std::max_element(cls.begin(), cls.end()) + 1;
     const bool wide = nmin > kMaxStatesD8 || events.size() - 1 > kMaxEventsD8;
+    if (!wide) {   // renumber the states for few shared-memory bank conflicts (place_states)
+        std::vector<uint8_t> mnext(static_cast<size_t>(nmin) * 256, 0);
+        for (uint32_t s = 0; s < n; s++)
+            for (uint32_t b = 0; b < 256; b++)
+                mnext[static_cast<size_t>(cls[s]) * 256 + b] = static_cast<uint8_t>(cls[trans[(size_t)s * ncls + cls_of[b]].next]);
+        std::vector<std::string> pats;
+        for (const DictEntry &d : dict) pats.push_back(d.bytes);
+        for (const char *w : {"good", "great", "excellent", "happy", "satisfied", "bad", "terrible", "awful", "angry", "frustrated",
+                              "what", "how", "why", "when", "where", "who"}) pats.push_back(w);
+        std::vector<uint32_t> perm = place_states(mnext, nmin, cls[start_id], pats);
+        for (uint32_t s = 0; s < n; s++) cls[s] = perm[cls[s]];
+    }
 
     out->n_states = nmin;
     out->wide = wide;

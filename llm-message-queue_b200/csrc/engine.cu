@@ -8,6 +8,7 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <chrono>
 #include <cstdio>
 #include <cstring>
@@ -116,6 +117,7 @@ struct triage_engine {
     Dfa dfa;
     ScanGeometry geom{0, 0, 0};
     uint32_t pad_warps = 0;
+    uint32_t stream_variant = 0;   // > 0: the padded arena is scanned by the streaming kernel (warps * 10 + chains)
     DfaBufs dm, dx;   // device copies of the scan automaton and of the exact (sequential) one
     DeviceDfa ddfa{};
     // exact (sequential, non-overlapping) automaton, only when the dictionary has self-overlapping literals
@@ -206,7 +208,11 @@ int32_t commit_dict(triage_engine *e) {
     DeviceDfa d{};
     int32_t rc = upload_dfa(dfa, &e->dm, &d);
     if (rc) return rc;
-    const uint32_t pad_warps = d.reset_pad >= 0 ? pick_pad_warps(d, (size_t)e->max_smem_optin) : 0;
+    uint32_t pad_warps = d.reset_pad >= 0 ? pick_pad_warps(d, (size_t)e->max_smem_optin) : 0;
+    if (const char *w = getenv("TRIAGE_PAD_WARPS")) {   // tuning knob: fewer warps than fit (8, 12, 16, 20, 24)
+        uint32_t want = (uint32_t)atoi(w);
+        if (pad_warps && want >= 8 && want <= pad_warps && want % 4 == 0) pad_warps = want;
+    }
     if (pad_warps == 0) d.reset_pad = -1;   // the padded kernel would not fit: packed entry points only
     ScanGeometry geom{0, 0, 0};
     if (!dfa.wide) {
@@ -226,6 +232,12 @@ int32_t commit_dict(triage_engine *e) {
     }
     e->ddfa = d;
     e->pad_warps = pad_warps;
+    e->stream_variant = 0;
+    if (pad_warps && !dfa.wide) {
+        const char *v = getenv("TRIAGE_STREAM_VARIANT");   // tuning knob: 0 = staged kernel, else warps * 10 + chains
+        uint32_t variant = v ? (uint32_t)atoi(v) : 0u;
+        if (variant && scan_stream_smem_bytes(d, variant) <= (size_t)e->max_smem_optin) e->stream_variant = variant;
+    }
     e->geom = geom;
     e->dfa = dfa;
     e->dict_dirty = false;
@@ -254,7 +266,8 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     e->tm = triage_timings{};
     *n_admitted = 0;
     if (n == 0) return TRIAGE_OK;
-    const uint32_t tile_bytes = padded ? kPadMiniTile : e->geom.tile;
+    const bool use_stream = padded && e->stream_variant > 0;
+    const uint32_t tile_bytes = padded ? (use_stream ? scan_stream_super_bytes(e->stream_variant) : kPadMiniTile) : e->geom.tile;
     const uint32_t ntiles = (uint32_t)((total + tile_bytes - 1) / tile_bytes);
     const uint32_t nblocks = (n + kOrderBlock - 1) / kOrderBlock;
     CU(e->d_counters.ensure((size_t)n * CNT_STRIDE));
@@ -275,7 +288,8 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     if (ntiles) {
         CU(launch_tile_index(sa, s)); launches++;
         CU(cudaEventRecord(e->ev[1], s));
-        if (padded) CU(launch_scan_padded(sa, e->ddfa, e->pad_warps, e->sm_count, s));
+        if (use_stream) CU(launch_scan_stream(sa, e->ddfa, e->stream_variant, e->sm_count, s));
+        else if (padded) CU(launch_scan_padded(sa, e->ddfa, e->pad_warps, e->sm_count, s));
         else CU(launch_scan(sa, e->ddfa, e->geom, e->sm_count, s));
         launches++;
     } else {

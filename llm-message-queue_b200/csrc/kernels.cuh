@@ -49,6 +49,15 @@ size_t scan_padded_smem_bytes(const DeviceDfa &d, uint32_t nw);
 uint32_t pick_pad_warps(const DeviceDfa &d, size_t max_smem);   // 24 for the default dictionary; fewer when the table is large
 cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, int sm_count, cudaStream_t s);
 
+// streaming variant of the padded scan (dense table): a lane walks several 512-byte chunks interleaved, reading the
+// arena straight from global memory; `variant` = warps per CTA * 10 + chains per lane
+constexpr uint32_t kStreamChunk = 512;
+constexpr uint32_t kStreamListCap = 128;   // message starts of a super-tile kept in shared memory
+constexpr uint32_t kStreamRing = 4;         // 16-byte slots per lane and chain (3 steps of prefetch)
+size_t scan_stream_smem_bytes(const DeviceDfa &d, uint32_t variant);
+uint32_t scan_stream_super_bytes(uint32_t variant);
+cudaError_t launch_scan_stream(const ScanArgs &a, const DeviceDfa &d, uint32_t variant, int sm_count, cudaStream_t s);
+
 // sequential exact recount of the messages the scan flagged (self-overlapping keywords); `exact` points at global memory
 cudaError_t launch_fixup(const uint8_t *bytes, const uint64_t *offsets, const uint32_t *lengths, uint32_t n, const DeviceDfa &exact,
                          uint32_t *counters, cudaStream_t s);

@@ -304,6 +304,150 @@ TR_HD void lane_scan_padded(const Ctx &c, int32_t chunk, int32_t chunk_end, uint
     else if (words) tr_add(c.counters + (uint64_t)msg * CNT_STRIDE + CNT_WORDS, words);
 }
 
+// ------------------------------------------------------------------------------------------- long lanes ---
+// Padded arena, long per-lane chunks streamed through shared memory in windows: the lane keeps its automaton state,
+// word count and current message in registers from window to window, so the warm-up is paid once per chunk
+// (e.g. 16 bytes per 320) instead of once per window.
+struct LongLane {
+    uint32_t e, words, k, msg, head_msg, head_words;
+    int32_t mend;
+    bool first;
+};
+
+// warm_bytes: the c.warm bytes that precede the chunk (16-byte aligned), unused when at_arena_start
+template <class Ctx>
+TR_HD void long_begin(const Ctx &c, LongLane &L, uint32_t k, bool at_arena_start, const uint8_t *warm_bytes) {
+    L.e = c.start_state;
+    if (!at_arena_start) {
+        L.e = c.neutral_state;
+        uint32_t wdummy = 0, evdummy = 0;
+        for (int32_t g = 0; g < c.warm; g += 16) group16(c, *reinterpret_cast<const Quad *>(warm_bytes + g), L.e, wdummy, evdummy);
+    }
+    L.k = k;
+    L.mend = list_at(c, k + 1);
+    L.msg = c.msg_lo + k;
+    L.words = 0;
+    L.first = true;
+    L.head_msg = L.msg;
+    L.head_words = 0;
+}
+
+// the message (and its pads) that was current ended exactly at `pos`: flush its count, step to the next one.  Messages
+// take at least 16 bytes of the padded arena, so one check per 16-byte group is enough.
+template <class Ctx>
+TR_HD void long_boundary(const Ctx &c, LongLane &L, int32_t pos) {
+    if (pos >= L.mend) {
+        if (L.first) { L.head_words = L.words; L.first = false; }
+        else if (L.words) tr_add(c.counters + (uint64_t)L.msg * CNT_STRIDE + CNT_WORDS, L.words);
+        L.words = 0;
+        L.k++;
+        L.msg++;
+        L.mend = list_at(c, L.k + 1);
+    }
+}
+
+// win: this lane's bytes of the window (16-byte aligned), pos: their position relative to the list origin
+template <class Ctx>
+TR_HD void long_window(const Ctx &c, LongLane &L, const uint8_t *win, int32_t pos, int32_t nbytes) {
+    for (int32_t g = 0; g < nbytes; g += 16) {
+        long_boundary(c, L, pos + g);
+        group16_counted(c, *reinterpret_cast<const Quad *>(win + g), L.e, L.words, L.msg);
+    }
+}
+
+// Re-walks 8 bytes from entry e and applies the events met on the way (the counts of the fast pass stand).  Kept out of
+// line and rolled: with several chains per lane an inlined copy per chain and half pushes the loop out of the
+// instruction cache.
+template <class Ctx>
+TR_COLD void replay_half(const Ctx &c, uint32_t wa, uint32_t wb, uint32_t e, uint32_t msg) {
+#ifdef __CUDA_ARCH__
+#pragma unroll 1
+#endif
+    for (int i = 0; i < 8; i++) {
+        const uint32_t wd = i < 4 ? wa : wb;
+        e = tr_next(c, wd >> (8 * (i & 3)), e, 0);
+        if (e & tr_evmask(c)) apply_event(c, tr_evid(c, e), msg);
+    }
+}
+
+// N independent chains per lane, interleaved transition by transition: the walk of one chain is a dependent sequence
+// (table read -> index arithmetic -> table read), so N chains give the scheduler N reads in flight per lane.
+#define TR_STEPN(fld, k, EV)                                                                   \
+    _Pragma("unroll") for (int ch = 0; ch < N; ch++) {                                         \
+        L[ch].e = tr_next(c, q[ch].fld, L[ch].e, k); L[ch].words += tr_ws(c, L[ch].e); EV[ch] |= L[ch].e; }
+#define TR_STEPN4(fld, EV) TR_STEPN(fld, 0, EV) TR_STEPN(fld, 1, EV) TR_STEPN(fld, 2, EV) TR_STEPN(fld, 3, EV)
+
+template <int N, class Ctx>
+TR_HD void group16_counted_n(const Ctx &c, const Quad (&q)[N], LongLane (&L)[N]) {
+    uint32_t e0[N], e8[N], eva[N], evb[N], any = 0;
+#pragma unroll
+    for (int ch = 0; ch < N; ch++) { e0[ch] = L[ch].e; eva[ch] = 0; evb[ch] = 0; }
+    TR_STEPN4(a, eva) TR_STEPN4(b, eva)
+#pragma unroll
+    for (int ch = 0; ch < N; ch++) e8[ch] = L[ch].e;
+    TR_STEPN4(c, evb) TR_STEPN4(d, evb)
+#pragma unroll
+    for (int ch = 0; ch < N; ch++) any |= eva[ch] | evb[ch];
+    if (any & tr_evmask(c)) {
+#pragma unroll
+        for (int ch = 0; ch < N; ch++) {
+            if (eva[ch] & tr_evmask(c)) replay_half(c, q[ch].a, q[ch].b, e0[ch], L[ch].msg);
+            if (evb[ch] & tr_evmask(c)) replay_half(c, q[ch].c, q[ch].d, e8[ch], L[ch].msg);
+        }
+    }
+}
+
+TR_HD Quad stream_quad(const uint8_t *p) {
+#ifdef __CUDA_ARCH__
+    uint4 v = __ldg(reinterpret_cast<const uint4 *>(p));
+    Quad q; q.a = v.x; q.b = v.y; q.c = v.z; q.d = v.w;
+    return q;
+#else
+    return *reinterpret_cast<const Quad *>(p);
+#endif
+}
+TR_HD void stream_prefetch(const uint8_t *p) {
+#ifdef __CUDA_ARCH__
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+#else
+    (void)p;
+#endif
+}
+
+// Streams nbytes (a multiple of 16) of N chains straight from global memory: src[ch] is the chunk of chain ch, pos[ch]
+// its position relative to the list origin.  The next 16 bytes of every chain are loaded into registers while the
+// current ones are walked; `limit` is the end of the arena (prefetch hints stay below it).
+template <int N, class Ctx>
+TR_HD void long_stream_n(const Ctx &c, LongLane (&L)[N], const uint8_t *const (&src)[N], const int32_t (&pos)[N], int32_t nbytes,
+                         const uint8_t *limit) {
+    Quad cur[N], nxt[N];
+#pragma unroll
+    for (int ch = 0; ch < N; ch++) { cur[ch] = stream_quad(src[ch]); nxt[ch] = cur[ch]; }
+#pragma unroll 2
+    for (int32_t g = 0; g < nbytes; g += 16) {
+        if (g + 16 < nbytes) {
+#pragma unroll
+            for (int ch = 0; ch < N; ch++) nxt[ch] = stream_quad(src[ch] + g + 16);
+        }
+        if ((g & 127) == 0) {
+#pragma unroll
+            for (int ch = 0; ch < N; ch++)
+                if (src[ch] + g + 384 < limit) stream_prefetch(src[ch] + g + 384);
+        }
+#pragma unroll
+        for (int ch = 0; ch < N; ch++) long_boundary(c, L[ch], pos[ch] + g);
+        group16_counted_n<N>(c, cur, L);
+#pragma unroll
+        for (int ch = 0; ch < N; ch++) cur[ch] = nxt[ch];
+    }
+}
+
+template <class Ctx>
+TR_HD void long_end(const Ctx &c, LongLane &L) {
+    if (L.first) L.head_words = L.words;
+    else if (L.words) tr_add(c.counters + (uint64_t)L.msg * CNT_STRIDE + CNT_WORDS, L.words);
+}
+
 // ------------------------------------------------------------------------------------------- slow lane ---
 // Fallback for dictionaries without usable pad bytes: same walk, byte at a time around boundaries.
 TR_HD void step_slow(const LaneCtx &c, uint32_t byte, uint32_t &e, uint32_t &words, uint32_t msg, bool count) {

@@ -318,3 +318,160 @@ extern "C" int hostcheck_scan_wide(const uint8_t *prios, const uint8_t *cis, con
     }
     return 0;
 }
+
+// long-lane variant: 32 lanes x chunk_long bytes per warp iteration, streamed in windows of `window` bytes
+extern "C" int hostcheck_scan_long(const uint8_t *prios, const uint8_t *cis, const uint32_t *lens, const uint8_t *lits, uint32_t n_pat,
+                                   const uint64_t *offsets, const uint8_t *bytes, uint32_t n_msgs, uint32_t chunk_long, uint32_t window,
+                                   uint32_t *counters, char *err, uint32_t errcap)
+{
+    std::vector<DictEntry> dict;
+    size_t o = 0;
+    for (uint32_t i = 0; i < n_pat; i++) {
+        dict.push_back({prios[i], cis[i] != 0, std::string(reinterpret_cast<const char *>(lits + o), lens[i])});
+        o += lens[i];
+    }
+    Dfa dfa;
+    std::string e = build_dfa(dict, &dfa);
+    if (!e.empty() || dfa.wide || dfa.reset_pad < 0) { std::strncpy(err, "unsupported", errcap - 1); return 4; }
+    if (n_msgs == 0) return 0;
+    std::vector<EventPacked> ev(dfa.events.size());
+    for (size_t i = 0; i < dfa.events.size(); i++) pack_event(dfa.events[i], &ev[i].x);
+    std::vector<uint8_t> tbl((size_t)dfa.n_states * kRowBytes, 0);
+    for (uint32_t st = 0; st < dfa.n_states; st++)
+        std::memcpy(tbl.data() + (size_t)st * kRowBytes, dfa.table.data() + (size_t)st * 256, 512);
+    std::vector<uint64_t> poff(n_msgs + 1, 0);
+    for (uint32_t i = 0; i < n_msgs; i++) poff[i + 1] = poff[i] + ((offsets[i + 1] - offsets[i]) / 16 + 1) * 16;
+    std::vector<uint8_t> arena_raw(poff[n_msgs] + 64, (uint8_t)dfa.reset_pad);
+    uint8_t *arena = arena_raw.data();
+    while (reinterpret_cast<uintptr_t>(arena) & 15) arena++;
+    for (uint32_t i = 0; i < n_msgs; i++) std::memcpy(arena + poff[i], bytes + offsets[i], offsets[i + 1] - offsets[i]);
+    std::memset(counters, 0, sizeof(uint32_t) * 8 * n_msgs);
+    const uint64_t total = poff[n_msgs];
+    const uint64_t st_bytes = 32ull * chunk_long;
+    const int32_t warm = (int32_t)dfa.warm_bytes;
+    for (uint64_t ts = 0; ts < total; ts += st_bytes) {
+        uint64_t te = std::min(total, ts + st_bytes);
+        uint32_t lo = 0, hi = n_msgs + 1;
+        while (lo < hi) { uint32_t mid = (lo + hi) / 2; if (poff[mid] > ts) hi = mid; else lo = mid + 1; }
+        uint32_t mlo = lo - 1, mhi = mlo;
+        while (poff[mhi + 1] < te) mhi++;
+        std::vector<int32_t> list;
+        for (uint32_t m = mlo; m <= mhi + 1; m++) list.push_back((int32_t)((int64_t)poff[m] - (int64_t)ts));
+        LaneCtx c;
+        c.tbl = tbl.data(); c.events = ev.data(); c.eom = nullptr; c.stage = nullptr;
+        c.list = list.data(); c.list_abs = poff.data(); c.tile_start = (int64_t)ts; c.list_n = (uint32_t)list.size(); c.msg_lo = mlo;
+        c.counters = counters; c.warm = warm; c.start_state = dfa.start_state; c.neutral_state = dfa.neutral_state; c.tbl_s = 0;
+        c.head_pad4 = c.tail_pad4 = 0;
+        for (uint32_t l = 0; l < 32; l++) {
+            uint64_t cs = ts + (uint64_t)l * chunk_long;
+            if (cs >= te) break;
+            uint64_t ce = std::min<uint64_t>(cs + chunk_long, te);
+            LongLane L;
+            long_begin(c, L, find_msg(c, (int32_t)(cs - ts)), cs == 0, cs ? arena + cs - warm : arena);
+            for (uint64_t w = cs; w < ce; w += window)
+                long_window(c, L, arena + w, (int32_t)(w - ts), (int32_t)std::min<uint64_t>(window, ce - w));
+            long_end(c, L);
+            if (L.head_words) counters[(uint64_t)L.head_msg * 8 + CNT_WORDS] += L.head_words;
+        }
+    }
+    for (uint32_t i = 0; i < n_msgs; i++) {
+        counters[(uint64_t)i * 8 + CNT_Q] &= 1;
+        if (offsets[i + 1] > offsets[i] && bytes[offsets[i + 1] - 1] == '?') counters[(uint64_t)i * 8 + CNT_Q] |= 1;
+    }
+    return 0;
+}
+
+// streaming variant: a lane owns `nch` chunks of chunk_long bytes (chunk v = ch * 32 + lane of the super-tile) and walks
+// them interleaved with long_stream_n; a chunk cut short by the end of the arena is walked alone
+template <int N>
+static void stream_lane(const LaneCtx &c, const uint8_t *arena, uint64_t ts, uint64_t te, uint32_t l, uint32_t chunk_long, int32_t warm,
+                        uint32_t *counters)
+{
+    LongLane L[N];
+    const uint8_t *src[N];
+    int32_t pos[N], nb[N];
+    bool all_full = true;
+    for (int ch = 0; ch < N; ch++) {
+        uint64_t cs = ts + (uint64_t)(ch * 32 + l) * chunk_long;
+        nb[ch] = cs >= te ? 0 : (int32_t)std::min<uint64_t>(chunk_long, te - cs);
+        all_full = all_full && nb[ch] == (int32_t)chunk_long;
+        src[ch] = arena + cs;
+        pos[ch] = (int32_t)(cs - ts);
+        if (nb[ch]) long_begin(c, L[ch], find_msg(c, pos[ch]), cs == 0, cs ? arena + cs - warm : arena);
+    }
+    if (all_full) {
+        long_stream_n<N>(c, L, src, pos, (int32_t)chunk_long, arena + te);
+    } else {
+        for (int ch = 0; ch < N; ch++) {
+            if (!nb[ch]) continue;
+            LongLane L1[1] = {L[ch]};
+            const uint8_t *s1[1] = {src[ch]};
+            int32_t p1[1] = {pos[ch]};
+            long_stream_n<1>(c, L1, s1, p1, nb[ch], arena + te);
+            L[ch] = L1[0];
+        }
+    }
+    for (int ch = 0; ch < N; ch++) {
+        if (!nb[ch]) continue;
+        long_end(c, L[ch]);
+        if (L[ch].head_words) counters[(uint64_t)L[ch].head_msg * 8 + CNT_WORDS] += L[ch].head_words;
+    }
+}
+
+extern "C" int hostcheck_scan_stream(const uint8_t *prios, const uint8_t *cis, const uint32_t *lens, const uint8_t *lits, uint32_t n_pat,
+                                     const uint64_t *offsets, const uint8_t *bytes, uint32_t n_msgs, uint32_t chunk_long, uint32_t nch,
+                                     uint32_t *counters, char *err, uint32_t errcap)
+{
+    std::vector<DictEntry> dict;
+    size_t o = 0;
+    for (uint32_t i = 0; i < n_pat; i++) {
+        dict.push_back({prios[i], cis[i] != 0, std::string(reinterpret_cast<const char *>(lits + o), lens[i])});
+        o += lens[i];
+    }
+    Dfa dfa;
+    std::string e = build_dfa(dict, &dfa);
+    if (!e.empty() || dfa.wide || dfa.reset_pad < 0 || nch < 1 || nch > 4) { std::strncpy(err, "unsupported", errcap - 1); return 4; }
+    if (n_msgs == 0) return 0;
+    std::vector<EventPacked> ev(dfa.events.size());
+    for (size_t i = 0; i < dfa.events.size(); i++) pack_event(dfa.events[i], &ev[i].x);
+    std::vector<uint8_t> tbl((size_t)dfa.n_states * kRowBytes, 0);
+    for (uint32_t st = 0; st < dfa.n_states; st++)
+        std::memcpy(tbl.data() + (size_t)st * kRowBytes, dfa.table.data() + (size_t)st * 256, 512);
+    std::vector<uint64_t> poff(n_msgs + 1, 0);
+    for (uint32_t i = 0; i < n_msgs; i++) poff[i + 1] = poff[i] + ((offsets[i + 1] - offsets[i]) / 16 + 1) * 16;
+    std::vector<uint8_t> arena_raw(poff[n_msgs] + 64, (uint8_t)dfa.reset_pad);
+    uint8_t *arena = arena_raw.data();
+    while (reinterpret_cast<uintptr_t>(arena) & 15) arena++;
+    for (uint32_t i = 0; i < n_msgs; i++) std::memcpy(arena + poff[i], bytes + offsets[i], offsets[i + 1] - offsets[i]);
+    std::memset(counters, 0, sizeof(uint32_t) * 8 * n_msgs);
+    const uint64_t total = poff[n_msgs];
+    const uint64_t st_bytes = 32ull * chunk_long * nch;
+    const int32_t warm = (int32_t)dfa.warm_bytes;
+    for (uint64_t ts = 0; ts < total; ts += st_bytes) {
+        uint64_t te = std::min(total, ts + st_bytes);
+        uint32_t lo = 0, hi = n_msgs + 1;
+        while (lo < hi) { uint32_t mid = (lo + hi) / 2; if (poff[mid] > ts) hi = mid; else lo = mid + 1; }
+        uint32_t mlo = lo - 1, mhi = mlo;
+        while (poff[mhi + 1] < te) mhi++;
+        std::vector<int32_t> list;
+        for (uint32_t m = mlo; m <= mhi + 1; m++) list.push_back((int32_t)((int64_t)poff[m] - (int64_t)ts));
+        LaneCtx c;
+        c.tbl = tbl.data(); c.events = ev.data(); c.eom = nullptr; c.stage = nullptr;
+        c.list = list.data(); c.list_abs = poff.data(); c.tile_start = (int64_t)ts; c.list_n = (uint32_t)list.size(); c.msg_lo = mlo;
+        c.counters = counters; c.warm = warm; c.start_state = dfa.start_state; c.neutral_state = dfa.neutral_state; c.tbl_s = 0;
+        c.head_pad4 = c.tail_pad4 = 0;
+        for (uint32_t l = 0; l < 32; l++) {
+            switch (nch) {
+                case 1: stream_lane<1>(c, arena, ts, te, l, chunk_long, warm, counters); break;
+                case 2: stream_lane<2>(c, arena, ts, te, l, chunk_long, warm, counters); break;
+                case 3: stream_lane<3>(c, arena, ts, te, l, chunk_long, warm, counters); break;
+                default: stream_lane<4>(c, arena, ts, te, l, chunk_long, warm, counters); break;
+            }
+        }
+    }
+    for (uint32_t i = 0; i < n_msgs; i++) {
+        counters[(uint64_t)i * 8 + CNT_Q] &= 1;
+        if (offsets[i + 1] > offsets[i] && bytes[offsets[i + 1] - 1] == '?') counters[(uint64_t)i * 8 + CNT_Q] |= 1;
+    }
+    return 0;
+}

@@ -90,3 +90,39 @@ def scan_wide(dict_entries, offsets, data, chunk=80):
         raise ValueError(err.value.decode())
     return counters[:n], dict(states=int(info[0]), reset_pad=int(np.int32(info[1])), wide=bool(info[2]), classes=int(info[3]),
                               warm=int(info[4]), events=int(info[5]))
+
+
+def scan_long(dict_entries, offsets, data, chunk_long=320, window=80):
+    """counters through the long-lane walk (chunk_long bytes per lane, streamed in windows)"""
+    n = len(offsets) - 1
+    prios = np.array([d[0] for d in dict_entries], np.uint8)
+    cis = np.array([1 if d[1] else 0 for d in dict_entries], np.uint8)
+    lens = np.array([len(d[2]) for d in dict_entries], np.uint32)
+    lits = np.frombuffer(b"".join(d[2] for d in dict_entries) or b"\0", np.uint8)
+    counters = np.zeros((max(n, 1), 8), np.uint32)
+    err = C.create_string_buffer(256)
+    buf = data if len(data) else np.zeros(1, np.uint8)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    rc = lib().hostcheck_scan_long(p(prios), p(cis), p(lens), p(lits), len(dict_entries), p(offsets), p(buf), n, chunk_long, window,
+                                   p(counters), err, 256)
+    if rc != 0:
+        raise ValueError(err.value.decode())
+    return counters[:n]
+
+
+def scan_stream(dict_entries, offsets, data, chunk_long=512, nch=2):
+    """counters through the streaming walk (nch interleaved chains of chunk_long bytes per lane)"""
+    n = len(offsets) - 1
+    prios = np.array([d[0] for d in dict_entries], np.uint8)
+    cis = np.array([1 if d[1] else 0 for d in dict_entries], np.uint8)
+    lens = np.array([len(d[2]) for d in dict_entries], np.uint32)
+    lits = np.frombuffer(b"".join(d[2] for d in dict_entries) or b"\0", np.uint8)
+    counters = np.zeros((max(n, 1), 8), np.uint32)
+    err = C.create_string_buffer(256)
+    buf = data if len(data) else np.zeros(1, np.uint8)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    rc = lib().hostcheck_scan_stream(p(prios), p(cis), p(lens), p(lits), len(dict_entries), p(offsets), p(buf), n, chunk_long, nch,
+                                     p(counters), err, 256)
+    if rc != 0:
+        raise ValueError(err.value.decode())
+    return counters[:n]

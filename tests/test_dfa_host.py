@@ -98,3 +98,26 @@ def test_large_dictionary_wide_format():
     exp = _expected(d, contents)
     bad = np.nonzero((cnt != exp).any(axis=1))[0]
     assert len(bad) == 0, (bad[:5], cnt[bad[:5]], exp[bad[:5]])
+
+
+@pytest.mark.parametrize("walk", ["long-320-80", "long-48-16", "stream-512-2", "stream-512-1", "stream-64-3", "stream-1024-4"])
+def test_long_lane_walks(golden_dir, walk):
+    """padded arena, state carried along a long per-lane chunk: windowed (shared-memory staging) and streaming
+    (N interleaved chains read straight from the arena) variants, on the edge cases and on generated text"""
+    kind, a, b = walk.split("-")
+    run = (lambda off, data: hc.scan_long(hc.DEFAULT_DICT, off, data, chunk_long=int(a), window=int(b))) if kind == "long" else \
+          (lambda off, data: hc.scan_stream(hc.DEFAULT_DICT, off, data, chunk_long=int(a), nch=int(b)))
+    cases = json.load(open(os.path.join(golden_dir, "edge_cases.json")))
+    contents = [bytes.fromhex(e["content_hex"]) for e in cases]
+    off, data = co.pack(contents)
+    cnt = run(off, data)
+    exp = _expected(co.Dict(), contents)
+    bad = np.nonzero((cnt != exp).any(axis=1))[0]
+    assert len(bad) == 0, (bad[:5], cnt[bad[:5]], exp[bad[:5]])
+    for seed, n, lo, hi, edge in ((99, 2000, 1, 600, 2000), (6, 8000, 0, 40, 3000), (5, 200, 2000, 9000, 500)):
+        off, data, meta, ts = co.generate(seed, n, lo, hi, edge=edge)
+        contents = [bytes(data[int(off[i]):int(off[i + 1])]) for i in range(n)]
+        cnt = run(off, data)
+        exp = _expected(co.Dict(), contents)
+        bad = np.nonzero((cnt != exp).any(axis=1))[0]
+        assert len(bad) == 0, (seed, bad[:5], cnt[bad[:5]], exp[bad[:5]])
