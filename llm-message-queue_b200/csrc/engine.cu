@@ -285,7 +285,7 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
         use_rows = scan_rows_usable(probe);
     }
     const uint32_t tile_bytes = !padded ? e->geom.tile
-                              : use_rows ? scan_rows_super_bytes()
+                              : use_rows ? scan_rows_super_bytes(e->row_warps)
                               : use_long ? scan_long_super_bytes(e->long_variant)
                               : use_stream ? scan_stream_super_bytes(e->stream_variant) : 32u * scan_padded_chunk(e->pad_warps);
     const uint32_t ntiles = (uint32_t)((total + tile_bytes - 1) / tile_bytes);

@@ -15,6 +15,7 @@
 #include "kernels.cuh"
 
 #include <cuda.h>   // CUtensorMap + the cuTensorMapEncodeTiled prototype; the entry point is fetched at run time, libcuda is not linked
+#include <cstdlib>
 #include <type_traits>
 
 namespace triage {
@@ -717,24 +718,75 @@ cudaError_t launch_scan_long(const ScanArgs &a, const DeviceDfa &d, uint32_t var
 // would otherwise issue itself (cp.async) cost as much as the warm-up lookups they save.  The automaton state, word
 // count and current message stay in registers along the row.  The last, partial row of the arena is read straight from
 // global memory by the lane that owns it.
-constexpr uint32_t kRowLane = 320, kRowWin = 80, kRowWins = kRowLane / kRowWin;
-struct RowSmem { uint32_t table, events, warp0, total, warp_bytes, warm_off, list_off; };
+// geometry by warps per CTA (more warps = smaller windows so that the staging still fits): row bytes, window bytes
+__host__ __device__ constexpr uint32_t row_win(uint32_t nw) { return nw >= 32 ? 48u : nw >= 28 ? 64u : 80u; }
+__host__ __device__ constexpr uint32_t row_lane(uint32_t nw) { return nw >= 32 ? 336u : 320u; }
+constexpr uint32_t kRowListCap = 34;     // message starts of a tile kept in shared memory (lane, lane + 32)
+constexpr uint32_t kRowQueueCap = 24;    // deferred event replays per warp (12 bytes each)
+constexpr uint32_t kRowQueueFlush = 10;  // replayed by the whole warp once this many are waiting
+struct RowSmem { uint32_t table, events, warp0, aux0, total, warp_bytes, aux_bytes, warm_off, list_off, queue_off; };
+
+// Per-warp queue of "8 bytes whose walk met an event": (message | entry state << 24, bytes 0..3, bytes 4..7).  A lane
+// that meets an event in the fast pass only records it; the warp replays the recorded halves together (one per lane)
+// at the end of a window.  Full queue or message index >= 2^24: the lane replays on the spot.
+struct RowEventQueue {
+    uint32_t base_s;   // shared address: count word, then the slots
+    __device__ __forceinline__ void push(const LaneCtx &c, uint32_t e0, uint32_t wa, uint32_t wb, uint32_t msg) {
+        uint32_t slot = kRowQueueCap;
+        if ((msg >> 24) == 0) asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(slot) : "r"(base_s) : "memory");
+        if (slot < kRowQueueCap) {
+            const uint32_t at = base_s + 4 + slot * 12;
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(at), "r"(msg | (e0 << 24)) : "memory");
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(at + 4), "r"(wa) : "memory");
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(at + 8), "r"(wb) : "memory");
+        } else {
+            replay_half(c, wa, wb, e0 & 0xFFu, msg);
+        }
+    }
+    // whole warp, converged; force: also when only a few are waiting
+    __device__ __forceinline__ void flush(const LaneCtx &c, uint32_t lane, bool force) {
+        uint32_t n;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(n) : "r"(base_s) : "memory");
+        if (n == 0 || (!force && n < kRowQueueFlush)) return;
+        if (n > kRowQueueCap) n = kRowQueueCap;
+        if (lane < n) {
+            uint32_t m, wa, wb;
+            const uint32_t at = base_s + 4 + lane * 12;
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(m) : "r"(at) : "memory");
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(wa) : "r"(at + 4) : "memory");
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(wb) : "r"(at + 8) : "memory");
+            uint32_t e = m >> 24, wdummy = 0;
+            half8_events(c, wa, wb, e, wdummy, m & 0xFFFFFFu);
+        }
+        __syncwarp();
+        if (lane == 0) asm volatile("st.shared.u32 [%0], %1;" ::"r"(base_s), "r"(0u) : "memory");
+        __syncwarp();
+    }
+};
 __host__ __device__ inline RowSmem row_layout(uint32_t n_states, uint32_t n_events, uint32_t nw) {
     RowSmem L;
     uint32_t o = 1024;   // mbarriers
     L.table = o; o += ((n_states * kRowBytes + 127u) / 128u) * 128u;
     L.events = o; o += ((n_events * 16u + 127u) / 128u) * 128u;
-    L.warm_off = 2 * 32 * kRowWin;
-    L.list_off = L.warm_off + 512;
-    L.warp_bytes = L.list_off + 2 * 4 * kLongListCap;
+    // TMA destinations (two windows + the warm-up box, 128-byte aligned) of all warps first, the small per-warp areas after
+    L.warm_off = 2 * 32 * row_win(nw);
+    L.warp_bytes = L.warm_off + 512;
     L.warp0 = o; o += nw * L.warp_bytes;
+    L.list_off = 0;
+    L.queue_off = 2 * 4 * kRowListCap;
+    L.aux_bytes = ((L.queue_off + 4 + 12 * kRowQueueCap + 15u) / 16u) * 16u;
+    L.aux0 = o; o += nw * L.aux_bytes;
     L.total = o;
     return L;
 }
 size_t scan_rows_smem_bytes(const DeviceDfa &d, uint32_t nw) { return row_layout(d.n_states, d.n_events, nw).total; }
-uint32_t scan_rows_super_bytes() { return 32 * kRowLane; }
+uint32_t scan_rows_super_bytes(uint32_t nw) { return 32 * row_lane(nw); }
 uint32_t pick_row_warps(const DeviceDfa &d, size_t max_smem) {
     if (d.wide || d.warm != 16 || d.reset_pad < 0) return 0;
+    if (const char *w = getenv("TRIAGE_ROW_WARPS")) {   // tuning knob
+        uint32_t nw = (uint32_t)atoi(w);
+        if ((nw == 16 || nw == 20 || nw == 24 || nw == 28 || nw == 32) && scan_rows_smem_bytes(d, nw) <= max_smem) return nw;
+    }
     for (uint32_t nw : {24u, 20u, 16u})
         if (scan_rows_smem_bytes(d, nw) <= max_smem) return nw;
     return 0;
@@ -744,7 +796,7 @@ template <int NW>
 __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, DeviceDfa d, const __grid_constant__ CUtensorMap tm_win,
                                                               const __grid_constant__ CUtensorMap tm_warm, uint32_t nrows_full) {
     extern __shared__ __align__(128) uint8_t smem[];
-    constexpr int32_t CL = kRowLane, WIN = kRowWin, NWIN = kRowWins;
+    constexpr int32_t CL = (int32_t)row_lane(NW), WIN = (int32_t)row_win(NW), NWIN = CL / WIN;
     constexpr uint32_t SUPER = 32 * CL;
     const RowSmem L = row_layout(d.n_states, d.n_events, NW);
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -753,12 +805,16 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
     EventPacked *events = reinterpret_cast<EventPacked *>(smem + L.events);
     uint8_t *wbase = smem + L.warp0 + warp * L.warp_bytes;
     uint8_t *warm_buf = wbase + L.warm_off;
-    int32_t *list_base = reinterpret_cast<int32_t *>(wbase + L.list_off);
+    uint8_t *aux = smem + L.aux0 + warp * L.aux_bytes;
+    int32_t *list_base = reinterpret_cast<int32_t *>(aux + L.list_off);
 
+    RowEventQueue queue;
+    queue.base_s = smem_u32(aux + L.queue_off);
     if (lane == 0) {
         mbar_init(&bars[0], 1);
         mbar_init(&bars[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(queue.base_s), "r"(0u) : "memory");
     }
     {
         const uint32_t *src = reinterpret_cast<const uint32_t *>(d.table);
@@ -790,7 +846,7 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
     uint64_t ts = (uint64_t)t0 * SUPER;
     {
         uint32_t cnt = last_cur - first_cur + 2;
-        if (cnt <= kLongListCap) {
+        if (cnt <= kRowListCap) {
             if (lane < cnt) list_base[lane] = rel_clamp(a.offsets[first_cur + lane], ts);
             if (lane + 32 < cnt) list_base[lane + 32] = rel_clamp(a.offsets[first_cur + lane + 32], ts);
         }
@@ -815,15 +871,15 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
         uint32_t cnt_nxt = 0, first_nn = 0, last_nn = 0;
         if (has_next) {
             cnt_nxt = last_nxt - first_nxt + 2;
-            if (cnt_nxt <= kLongListCap) {
+            if (cnt_nxt <= kRowListCap) {
                 if (lane < cnt_nxt) n0 = a.offsets[first_nxt + lane];
                 if (lane + 32 < cnt_nxt) n1 = a.offsets[first_nxt + lane + 32];
             }
             if (sk + 2 < nmine) { first_nn = a.tile_first[t + 2 * stride]; last_nn = a.tile_first[t + 2 * stride + 1]; }
         }
         const uint32_t cnt_cur = last_cur - first_cur + 2;
-        const int32_t *lst = list_base + (sk & 1) * kLongListCap;
-        c.list = cnt_cur <= kLongListCap ? lst : nullptr;
+        const int32_t *lst = list_base + (sk & 1) * kRowListCap;
+        c.list = cnt_cur <= kRowListCap ? lst : nullptr;
         c.tile_start = (int64_t)ts;
         c.list_n = cnt_cur; c.msg_lo = first_cur;
         const uint32_t row = t * 32 + lane;
@@ -853,10 +909,11 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
 #pragma unroll 1
                 for (int32_t q = 0; q < WIN; q += 16) {
                     long_boundary(c, ll, pos + q);
-                    group16_counted(c, *reinterpret_cast<const Quad *>(wb + q), ll.e, ll.words, ll.msg);
+                    group16_sink(c, *reinterpret_cast<const Quad *>(wb + q), ll.e, ll.words, ll.msg, queue);
                 }
             }
             __syncwarp();   // every lane is done with this buffer before lane 0 refills it (two windows on)
+            queue.flush(c, lane, false);
         }
         if (tail_row) {
             const uint8_t *src = a.bytes + row_start;
@@ -890,8 +947,8 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
                 if (sum) atomicAdd(a.counters + (uint64_t)hm * CNT_STRIDE + CNT_WORDS, sum);
             }
         }
-        if (has_next && cnt_nxt <= kLongListCap) {
-            int32_t *ln = list_base + ((sk + 1) & 1) * kLongListCap;
+        if (has_next && cnt_nxt <= kRowListCap) {
+            int32_t *ln = list_base + ((sk + 1) & 1) * kRowListCap;
             const uint64_t tsn = ts + ts_step;
             if (lane < cnt_nxt) ln[lane] = rel_clamp(n0, tsn);
             if (lane + 32 < cnt_nxt) ln[lane + 32] = rel_clamp(n1, tsn);
@@ -900,6 +957,7 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
         first_nxt = first_nn; last_nxt = last_nn;
         __syncwarp();
     }
+    queue.flush(c, lane, true);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
@@ -934,18 +992,19 @@ static cudaError_t launch_scan_rows_variant(const ScanArgs &a, const DeviceDfa &
 
 // needs at least one full row and a 16-byte aligned arena; the caller falls back to the mini-tile kernel otherwise
 bool scan_rows_usable(const ScanArgs &a) {
-    return a.total >= kRowLane && (reinterpret_cast<uintptr_t>(a.bytes) & 15u) == 0 && encode_tiled_fn() != nullptr;
+    return a.total >= 336 && (reinterpret_cast<uintptr_t>(a.bytes) & 15u) == 0 && encode_tiled_fn() != nullptr;
 }
 
 cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, int sm_count, cudaStream_t s) {
     if (a.ntiles == 0) return cudaSuccess;
     EncodeTiledFn enc = encode_tiled_fn();
     if (!enc) return cudaErrorNotSupported;
-    const uint64_t nrows_full = a.total / kRowLane;
+    const uint32_t lane_bytes = row_lane(nw), win = row_win(nw);
+    const uint64_t nrows_full = a.total / lane_bytes;
     CUtensorMap tw, tm;
-    const cuuint64_t dims[2] = {kRowLane, nrows_full};
-    const cuuint64_t strides[1] = {kRowLane};
-    const cuuint32_t box_w[2] = {kRowWin, 32}, box_m[2] = {16, 32}, es[2] = {1, 1};
+    const cuuint64_t dims[2] = {lane_bytes, nrows_full};
+    const cuuint64_t strides[1] = {lane_bytes};
+    const cuuint32_t box_w[2] = {win, 32}, box_m[2] = {16, 32}, es[2] = {1, 1};
     void *base = const_cast<uint8_t *>(a.bytes);
     if (enc(&tw, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, base, dims, strides, box_w, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS ||
@@ -953,6 +1012,8 @@ cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw,
             CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
         return cudaErrorInvalidValue;
     switch (nw) {
+        case 32: return launch_scan_rows_variant<32>(a, d, tw, tm, (uint32_t)nrows_full, sm_count, s);
+        case 28: return launch_scan_rows_variant<28>(a, d, tw, tm, (uint32_t)nrows_full, sm_count, s);
         case 24: return launch_scan_rows_variant<24>(a, d, tw, tm, (uint32_t)nrows_full, sm_count, s);
         case 20: return launch_scan_rows_variant<20>(a, d, tw, tm, (uint32_t)nrows_full, sm_count, s);
         case 16: return launch_scan_rows_variant<16>(a, d, tw, tm, (uint32_t)nrows_full, sm_count, s);

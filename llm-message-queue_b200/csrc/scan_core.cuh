@@ -182,6 +182,21 @@ TR_HD void group16_counted(const Ctx &c, const Quad &q, uint32_t &e, uint32_t &w
     }
 }
 
+// same fast pass, but a half whose transitions carried an event is handed to `sink` (e.g. a per-warp queue that replays
+// many halves at once with all lanes, instead of one lane re-walking 8 bytes while 31 wait)
+template <class Ctx, class Sink>
+TR_HD void group16_sink(const Ctx &c, const Quad &q, uint32_t &e, uint32_t &words, uint32_t msg, Sink &sink) {
+    const uint32_t e0 = e;
+    uint32_t ev = 0, ev2 = 0;
+    TR_STEP4(q.a) TR_STEP4(q.b)
+    const uint32_t e8 = e;
+    { uint32_t &ev = ev2; TR_STEP4(q.c) TR_STEP4(q.d) }
+    if ((ev | ev2) & tr_evmask(c)) {
+        if (ev & tr_evmask(c)) sink.push(c, e0, q.a, q.b, msg);
+        if (ev2 & tr_evmask(c)) sink.push(c, e8, q.c, q.d, msg);
+    }
+}
+
 TR_HD uint32_t low_mask(int32_t nbytes) { return nbytes <= 0 ? 0u : (nbytes >= 4 ? 0xFFFFFFFFu : ((1u << (8 * nbytes)) - 1u)); }
 // bytes [0, h) of the group <- pad
 TR_HD Quad mask_head(Quad q, int32_t h, uint32_t pad4) {

@@ -25,7 +25,7 @@ __global__ void chain(const uint32_t *text, uint32_t *out, long long *cycles, in
         if (MODE == 0 || MODE == 1) *reinterpret_cast<uint16_t *>(smem + st * ROW + b * 2) = (uint16_t)(nx | ((b & 1) << 15));
         if (MODE == 2) *reinterpret_cast<uint32_t *>(smem + st * 1028 + b * 4) = nx * 1028 | ((b & 1u) << 31);     // pre-multiplied + flag
         if (MODE == 3) *reinterpret_cast<uint32_t *>(smem + st * 1028 + b * 4) = nx * 1028;                         // pure offset
-        if (MODE == 4) smem[st * 260 + b] = (uint8_t)nx;
+        if (MODE == 4 || MODE == 5) smem[st * 260 + b] = (uint8_t)nx;
     }
     __syncthreads();
     const uint32_t base = smem_u32(smem);
@@ -52,6 +52,10 @@ __global__ void chain(const uint32_t *text, uint32_t *out, long long *cycles, in
             } else if (MODE == 3) {    // 32-bit entries = pure row offset: IADD + LDS.32
                 uint32_t b4 = (w >> (8 * k) & 0xFFu) * 4u + base;
                 e = lds32(e + b4);
+            } else if (MODE == 5) {    // 8-bit entries = pure state: IMAD(e, 260, byte + base) + LDS.U8; flags from the state id
+                uint32_t pre = __dp4a(w, 1u << (8 * k), base);   // off the dependent chain
+                e = lds8(e * 260u + pre);
+                words = __umulhi(e, 0x1C0E070u) + words;           // + (e >= 146)
             } else if (MODE == 4) {    // 8-bit entries: PRMT + IDP + LDS.U8
                 uint32_t a = __dp4a(__byte_perm(w, e, 0x4440u | k), 0x00828201u, base);
                 e = lds8(a); words += e >> 7;
@@ -91,5 +95,6 @@ int main() {
     run<2>("u32 premultiplied+flag LOP+IADD", text, out, cyc, NST * 1028 + 64);
     run<3>("u32 pure offset IADD", text, out, cyc, NST * 1028 + 64);
     run<4>("u8 PRMT+IDP.4A", text, out, cyc, NST * 260 + 64);
+    run<5>("u8 pure state IMAD", text, out, cyc, NST * 260 + 64);
     return 0;
 }
