@@ -319,7 +319,7 @@ def main():
         alg = total + 8 * (n + 1) + 4 * n + 32 * n     # arena (padded) + offsets + lengths + 16 B meta in + 16 B result out
         achieved = alg / (t_scan / 1000) / 1e9
         traffic = scan_traffic_from_profile()
-        roofline = {"bound": "hbm", "kernel": "scan_padded_kernel (24 warps x 80 B/lane)", "achieved": achieved, "peak": peak, "unit": "GB/s",
+        roofline = {"bound": "hbm", "kernel": "scan_rows_kernel (24 warps, 320-byte rows per lane, 2-D TMA windows of 80 B x 32 rows)", "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": achieved / peak, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg,
                     "kernel_ms": t_scan, "traffic": traffic["dram_bytes_per_launch"] if traffic else None,
                     "step_share": {"scan_ms": t_scan, "finalize_ms": sum(fin_ms) / len(fin_ms), "order_ms": sum(ord_ms) / len(ord_ms),

@@ -118,8 +118,6 @@ struct triage_engine {
     ScanGeometry geom{0, 0, 0};
     uint32_t pad_warps = 0;
     uint32_t row_warps = 0;        // > 0: the padded arena is scanned by the row-lane kernel (2-D TMA), arenas of >= 1 row
-    uint32_t long_variant = 0;     // > 0: the padded arena is scanned by the long-lane kernel (warps * 100 + window bytes)
-    uint32_t stream_variant = 0;   // > 0: the padded arena is scanned by the streaming kernel (warps * 10 + chains)
     DfaBufs dm, dx;   // device copies of the scan automaton and of the exact (sequential) one
     DeviceDfa ddfa{};
     // exact (sequential, non-overlapping) automaton, only when the dictionary has self-overlapping literals
@@ -213,8 +211,7 @@ int32_t commit_dict(triage_engine *e) {
     uint32_t pad_warps = d.reset_pad >= 0 ? pick_pad_warps(d, (size_t)e->max_smem_optin) : 0;
     if (const char *w = getenv("TRIAGE_PAD_WARPS")) {   // tuning knob: fewer warps than fit (8, 12, 16, 20, 24)
         uint32_t want = (uint32_t)atoi(w);
-        if (pad_warps && want >= 8 && want <= 32 && want % 4 == 0 && !d.wide &&
-            scan_padded_smem_bytes(d, want) <= (size_t)e->max_smem_optin) pad_warps = want;
+        if (pad_warps && want >= 8 && want <= pad_warps && want % 4 == 0 && !d.wide) pad_warps = want;
     }
     if (pad_warps == 0) d.reset_pad = -1;   // the padded kernel would not fit: packed entry points only
     ScanGeometry geom{0, 0, 0};
@@ -235,19 +232,10 @@ int32_t commit_dict(triage_engine *e) {
     }
     e->ddfa = d;
     e->pad_warps = pad_warps;
-    e->stream_variant = 0;
-    e->long_variant = 0;
     e->row_warps = 0;
     if (pad_warps && !dfa.wide) {
         const char *rv = getenv("TRIAGE_ROWS");   // tuning knob: 0 = keep to the mini-tile kernel
         if (!rv || atoi(rv) != 0) e->row_warps = pick_row_warps(d, (size_t)e->max_smem_optin);
-        if (const char *lv = getenv("TRIAGE_LONG_VARIANT")) {   // tuning knob: warps * 100 + window bytes
-            uint32_t variant = (uint32_t)atoi(lv);
-            if (variant && scan_long_smem_bytes(d, variant) <= (size_t)e->max_smem_optin) e->long_variant = variant;
-        }
-        const char *v = getenv("TRIAGE_STREAM_VARIANT");   // tuning knob: 0 = staged kernel, else warps * 10 + chains
-        uint32_t variant = v ? (uint32_t)atoi(v) : 0u;
-        if (variant && scan_stream_smem_bytes(d, variant) <= (size_t)e->max_smem_optin) e->stream_variant = variant;
     }
     e->geom = geom;
     e->dfa = dfa;
@@ -277,17 +265,13 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     e->tm = triage_timings{};
     *n_admitted = 0;
     if (n == 0) return TRIAGE_OK;
-    const bool use_long = padded && e->long_variant > 0;
-    const bool use_stream = padded && !use_long && e->stream_variant > 0;
     bool use_rows = false;
-    if (padded && !use_long && !use_stream && e->row_warps > 0) {
+    if (padded && e->row_warps > 0) {
         ScanArgs probe{bytes, offsets, total, n, nullptr, nullptr, 0, 0};
         use_rows = scan_rows_usable(probe);
     }
     const uint32_t tile_bytes = !padded ? e->geom.tile
-                              : use_rows ? scan_rows_super_bytes(e->row_warps)
-                              : use_long ? scan_long_super_bytes(e->long_variant)
-                              : use_stream ? scan_stream_super_bytes(e->stream_variant) : 32u * scan_padded_chunk(e->pad_warps);
+                              : use_rows ? scan_rows_super_bytes(e->row_warps) : kPadMiniTile;
     const uint32_t ntiles = (uint32_t)((total + tile_bytes - 1) / tile_bytes);
     const uint32_t nblocks = (n + kOrderBlock - 1) / kOrderBlock;
     CU(e->d_counters.ensure((size_t)n * CNT_STRIDE));
@@ -309,8 +293,6 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
         CU(launch_tile_index(sa, s)); launches++;
         CU(cudaEventRecord(e->ev[1], s));
         if (use_rows) CU(launch_scan_rows(sa, e->ddfa, e->row_warps, e->sm_count, s));
-        else if (use_long) CU(launch_scan_long(sa, e->ddfa, e->long_variant, e->sm_count, s));
-        else if (use_stream) CU(launch_scan_stream(sa, e->ddfa, e->stream_variant, e->sm_count, s));
         else if (padded) CU(launch_scan_padded(sa, e->ddfa, e->pad_warps, e->sm_count, s));
         else CU(launch_scan(sa, e->ddfa, e->geom, e->sm_count, s));
         launches++;

@@ -41,12 +41,6 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
         "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
 // 1-D TMA bulk copy global -> shared, completion signalled on an mbarrier (SASS: UBLKCP)
-__device__ __forceinline__ void cp_async16(uint32_t dst_s, const void *src) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_s), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 __device__ __forceinline__ void tma_load_1d(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
                  "l"(src), "r"(bytes), "r"(smem_u32(bar))
@@ -298,24 +292,20 @@ cudaError_t launch_scan(const ScanArgs &a, const DeviceDfa &d, const ScanGeometr
 // after the automaton has been loaded.
 struct PadSmem { uint32_t table, events, stage0, list0, total, stage_bytes, list_bytes; };
 constexpr uint32_t kPadListCap = 34;
-__host__ __device__ inline PadSmem pad_layout(uint32_t n_states, uint32_t n_events, uint32_t warm, uint32_t nw, bool wide, uint32_t chunk = kPadChunk) {
+__host__ __device__ inline PadSmem pad_layout(uint32_t n_states, uint32_t n_events, uint32_t warm, uint32_t nw, bool wide) {
     PadSmem L;
     uint32_t o = 1024;   // mbarriers
     // dense: the whole table and the event list; wide: only the 256-byte class map (table + events stay in global memory)
     L.table = o; o += wide ? 256u : ((n_states * kRowBytes + 127u) / 128u) * 128u;
     L.events = o; o += wide ? 0u : ((n_events * 16u + 127u) / 128u) * 128u;
-    L.stage_bytes = ((warm + 32u * chunk + 16u + 127u) / 128u) * 128u;
+    L.stage_bytes = ((warm + kPadMiniTile + 16u + 127u) / 128u) * 128u;
     L.stage0 = o; o += nw * 2 * L.stage_bytes;
     L.list_bytes = 160;
     L.list0 = o; o += nw * 2 * L.list_bytes;
     L.total = o;
     return L;
 }
-// 28 and 32 warps run 64-byte chunks (smaller staging buffers, 64 / 72 registers per thread), the others 80-byte chunks
-uint32_t scan_padded_chunk(uint32_t nw) { return nw > 24 ? 64u : kPadChunk; }
-size_t scan_padded_smem_bytes(const DeviceDfa &d, uint32_t nw) {
-    return pad_layout(d.n_states, d.n_events, d.warm, nw, d.wide != 0, scan_padded_chunk(nw)).total;
-}
+size_t scan_padded_smem_bytes(const DeviceDfa &d, uint32_t nw) { return pad_layout(d.n_states, d.n_events, d.warm, nw, d.wide != 0).total; }
 // most warps per CTA whose staging buffers still fit next to the automaton (0: none)
 uint32_t pick_pad_warps(const DeviceDfa &d, size_t max_smem) {
     for (uint32_t nw : {24u, 20u, 16u, 12u, 8u})
@@ -323,13 +313,13 @@ uint32_t pick_pad_warps(const DeviceDfa &d, size_t max_smem) {
     return 0;
 }
 
-template <int NW, bool WIDE, int CH>
+template <int NW, bool WIDE>
 __global__ void __launch_bounds__(NW * 32, 1) scan_padded_kernel(ScanArgs a, DeviceDfa d) {
     constexpr uint32_t kPadWarps = NW;
     extern __shared__ __align__(128) uint8_t smem[];
-    constexpr int C = CH;
-    constexpr uint32_t MT = 32 * CH;
-    const PadSmem L = pad_layout(d.n_states, d.n_events, d.warm, kPadWarps, WIDE, CH);
+    constexpr int C = kPadChunk;
+    constexpr uint32_t MT = kPadMiniTile;
+    const PadSmem L = pad_layout(d.n_states, d.n_events, d.warm, kPadWarps, WIDE);
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem) + warp * 2;
     uint8_t *tbl = smem + L.table;
@@ -469,18 +459,18 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_padded_kernel(ScanArgs a, Dev
     }
 }
 
-template <int NW, bool WIDE = false, int CH = kPadChunk>
+template <int NW, bool WIDE = false>
 static cudaError_t launch_scan_padded_variant(const ScanArgs &a, const DeviceDfa &d, int sm_count, cudaStream_t s) {
     size_t smem = scan_padded_smem_bytes(d, NW);
     static size_t configured = 0;
     if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(scan_padded_kernel<NW, WIDE, CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(scan_padded_kernel<NW, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         configured = smem;
     }
     uint32_t need = (a.ntiles + NW - 1) / NW;
     uint32_t grid = need < (uint32_t)sm_count ? need : (uint32_t)sm_count;
-    scan_padded_kernel<NW, WIDE, CH><<<grid, NW * 32, smem, s>>>(a, d);
+    scan_padded_kernel<NW, WIDE><<<grid, NW * 32, smem, s>>>(a, d);
     return cudaGetLastError();
 }
 
@@ -488,8 +478,6 @@ cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, uint32_t n
     if (a.ntiles == 0) return cudaSuccess;
     if (d.wide) return launch_scan_padded_variant<24, true>(a, d, sm_count, s);
     switch (nw) {
-        case 32: return launch_scan_padded_variant<32, false, 64>(a, d, sm_count, s);
-        case 28: return launch_scan_padded_variant<28, false, 64>(a, d, sm_count, s);
         case 24: return launch_scan_padded_variant<24>(a, d, sm_count, s);
         case 20: return launch_scan_padded_variant<20>(a, d, sm_count, s);
         case 16: return launch_scan_padded_variant<16>(a, d, sm_count, s);
@@ -499,218 +487,8 @@ cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, uint32_t n
     }
 }
 
-// -------------------------------------------------------------------------------- long lanes --
-// Padded arena, dense table.  Like scan_padded_kernel, but a lane owns a long chunk (NWIN windows of WIN bytes) and
-// streams it through shared memory window by window, keeping the automaton state, word count and current message in
-// registers, so the 16-byte warm-up is paid once per chunk (5 % of the lookups instead of 20 %).  Every lane copies its
-// own window with 16-byte cp.async and is the only reader of it: the data path has no barrier.  Quad j of all lanes is
-// one contiguous 512-byte row of the buffer (conflict-free for the copies and for the 16-byte reads).
-struct LongSmem { uint32_t table, events, warp0, total, warp_bytes, buf_bytes, warm_off, list_off; };
-__host__ __device__ inline LongSmem long_layout(uint32_t n_states, uint32_t n_events, uint32_t warm, uint32_t nw, uint32_t win) {
-    LongSmem L;
-    uint32_t o = 0;
-    L.table = o; o += ((n_states * kRowBytes + 127u) / 128u) * 128u;
-    L.events = o; o += ((n_events * 16u + 127u) / 128u) * 128u;
-    L.buf_bytes = 32 * win;
-    L.warm_off = 2 * L.buf_bytes;
-    L.list_off = L.warm_off + 32 * warm;
-    L.warp_bytes = L.list_off + 2 * 4 * kLongListCap;
-    L.warp0 = o; o += nw * L.warp_bytes;
-    L.total = o;
-    return L;
-}
-// variant = warps per CTA * 100 + window bytes
-size_t scan_long_smem_bytes(const DeviceDfa &d, uint32_t variant) {
-    return long_layout(d.n_states, d.n_events, d.warm, variant / 100, variant % 100).total;
-}
-__host__ __device__ constexpr uint32_t long_windows(uint32_t win) { return win == 48 ? 7u : 320u / win; }   // chunk = 336 or 320 bytes
-uint32_t scan_long_super_bytes(uint32_t variant) { return 32u * (variant % 100) * long_windows(variant % 100); }
-
-template <int NW, int WIN>
-__global__ void __launch_bounds__(NW * 32, 1) scan_long_kernel(ScanArgs a, DeviceDfa d) {
-    extern __shared__ __align__(128) uint8_t smem[];
-    constexpr int32_t NWIN = (int32_t)long_windows(WIN), CL = WIN * NWIN, NQ = WIN / 16;
-    constexpr uint32_t SUPER = 32 * CL;
-    const LongSmem L = long_layout(d.n_states, d.n_events, d.warm, NW, WIN);
-    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    uint8_t *tbl = smem + L.table;
-    EventPacked *events = reinterpret_cast<EventPacked *>(smem + L.events);
-    uint8_t *wbase = smem + L.warp0 + warp * L.warp_bytes;
-    uint8_t *warm_buf = wbase + L.warm_off;
-    int32_t *list_base = reinterpret_cast<int32_t *>(wbase + L.list_off);
-    const uint32_t warm = d.warm;
-    {
-        const uint32_t *src = reinterpret_cast<const uint32_t *>(d.table);
-        uint32_t *dst = reinterpret_cast<uint32_t *>(tbl);
-        for (uint32_t i = tid; i < d.n_states * (kRowBytes / 4); i += NW * 32) dst[i] = src[i];
-        const uint4 *es = reinterpret_cast<const uint4 *>(d.events);
-        uint4 *ed = reinterpret_cast<uint4 *>(events);
-        for (uint32_t i = tid; i < d.n_events; i += NW * 32) ed[i] = es[i];
-    }
-    __syncthreads();   // the only CTA-wide barrier
-
-    const uint32_t stride = gridDim.x * NW;
-    const uint32_t t0 = blockIdx.x * NW + warp;
-    if (t0 >= a.ntiles) return;
-    const uint32_t nmine = (a.ntiles - t0 + stride - 1) / stride;
-    const uint64_t ts_step = (uint64_t)stride * SUPER;
-    const uint32_t win_s = smem_u32(wbase) + lane * 16;
-    const uint32_t warm_s = smem_u32(warm_buf) + lane * warm;
-
-    // window w of the chunk that starts at arena offset cs -> buffer buf (one commit group per call)
-    auto issue = [&](uint64_t cs, int32_t w, uint32_t buf) {
-        if (cs < a.total) {
-            const uint64_t ws = cs + (uint64_t)(w * WIN);
-            const uint64_t rem = a.total > ws ? a.total - ws : 0;
-            const uint8_t *src = a.bytes + ws;
-            const uint32_t dst = win_s + buf * L.buf_bytes;
-#pragma unroll
-            for (uint32_t q = 0; q < (uint32_t)NQ; q++)
-                if (q * 16 < rem) cp_async16(dst + q * 512, src + q * 16);
-            if (w == 0 && cs != 0)
-                for (uint32_t q = 0; q < warm; q += 16) cp_async16(warm_s + q, a.bytes + cs - warm + q);
-        }
-        cp_async_commit();
-    };
-
-    uint32_t first_cur = a.tile_first[t0], last_cur = a.tile_first[t0 + 1];
-    uint64_t ts = (uint64_t)t0 * SUPER;
-    issue(ts + (uint64_t)lane * CL, 0, 0);
-    {
-        uint32_t cnt = last_cur - first_cur + 2;
-        if (cnt <= kLongListCap) {
-            if (lane < cnt) list_base[lane] = rel_clamp(a.offsets[first_cur + lane], ts);
-            if (lane + 32 < cnt) list_base[lane + 32] = rel_clamp(a.offsets[first_cur + lane + 32], ts);
-        }
-    }
-    uint32_t first_nxt = 0, last_nxt = 0;
-    if (nmine > 1) { first_nxt = a.tile_first[t0 + stride]; last_nxt = a.tile_first[t0 + stride + 1]; }
-    __syncwarp();
-
-    LaneCtx c;
-    c.tbl = tbl; c.events = events; c.eom = nullptr; c.stage = nullptr;
-    c.list_abs = a.offsets; c.counters = a.counters; c.warm = (int32_t)warm;
-    c.start_state = d.start_state; c.neutral_state = d.neutral_state;
-    c.head_pad4 = c.tail_pad4 = 0;
-    c.tbl_s = smem_u32(tbl);
-    const int32_t chunk = (int32_t)(lane * CL);
-    uint32_t t = t0, buf = 0;
-
-    for (uint32_t sk = 0; sk < nmine; sk++, t += stride, ts += ts_step) {
-        const bool has_next = sk + 1 < nmine;
-        uint64_t n0 = 0, n1 = 0;
-        uint32_t cnt_nxt = 0, first_nn = 0, last_nn = 0;
-        if (has_next) {
-            cnt_nxt = last_nxt - first_nxt + 2;
-            if (cnt_nxt <= kLongListCap) {
-                if (lane < cnt_nxt) n0 = a.offsets[first_nxt + lane];
-                if (lane + 32 < cnt_nxt) n1 = a.offsets[first_nxt + lane + 32];
-            }
-            if (sk + 2 < nmine) { first_nn = a.tile_first[t + 2 * stride]; last_nn = a.tile_first[t + 2 * stride + 1]; }
-        }
-        const uint32_t cnt_cur = last_cur - first_cur + 2;
-        const int32_t *lst = list_base + (sk & 1) * kLongListCap;
-        c.list = cnt_cur <= kLongListCap ? lst : nullptr;
-        c.tile_start = (int64_t)ts;
-        c.list_n = cnt_cur; c.msg_lo = first_cur;
-        const uint64_t rem = a.total - ts;                       // bytes of the arena from this super-tile on
-        const int32_t len = rem < SUPER ? (int32_t)rem : (int32_t)SUPER;
-        const int32_t chunk_len = chunk < len ? (chunk + CL <= len ? CL : len - chunk) : 0;
-        const uint64_t cs = ts + (uint64_t)chunk;
-
-        LongLane ll;
-#pragma unroll 1
-        for (int32_t w = 0; w < NWIN; w++, buf ^= 1) {
-            if (w + 1 < NWIN) issue(cs, w + 1, buf ^ 1);
-            else if (has_next) issue(cs + ts_step, 0, buf ^ 1);
-            else cp_async_commit();
-            cp_async_wait<1>();   // everything but the window just issued has landed: this lane can read window w
-            if (w == 0 && chunk_len) {
-                uint32_t km;
-                if (c.list) {
-                    km = 0;
-                    for (uint32_t j = 1; j + 1 < cnt_cur; j++) km += lst[j] <= chunk ? 1u : 0u;
-                } else {
-                    km = find_msg(c, chunk);
-                }
-                long_begin(c, ll, km, t == 0 && lane == 0, warm_buf + lane * warm);
-            }
-            const int32_t woff = w * WIN;
-            const uint8_t *wb = wbase + buf * L.buf_bytes + lane * 16;
-#pragma unroll 1
-            for (int32_t q = 0; q < NQ; q++) {
-                if (woff + q * 16 < chunk_len) {
-                    long_boundary(c, ll, chunk + woff + q * 16);
-                    group16_counted(c, *reinterpret_cast<const Quad *>(wb + q * 512), ll.e, ll.words, ll.msg);
-                }
-            }
-        }
-        uint32_t hm = 0xFFFFFFFFu, hw = 0;
-        if (chunk_len) { long_end(c, ll); hm = ll.head_msg; hw = ll.head_words; }
-        {   // combine the head partials of neighbouring lanes that sit in the same message
-            const unsigned full = 0xFFFFFFFFu;
-            uint32_t prev = __shfl_up_sync(full, hm, 1);
-            bool head = lane == 0 || hm != prev;
-            uint32_t heads = __ballot_sync(full, head);
-            uint32_t v = hw;
-#pragma unroll
-            for (int dlt = 1; dlt < 32; dlt <<= 1) {
-                uint32_t tt = __shfl_up_sync(full, v, dlt);
-                if ((int)lane >= dlt) v += tt;
-            }
-            uint32_t above = heads & ~((2u << lane) - 1u);
-            uint32_t end = above ? (uint32_t)__ffs(above) - 2u : 31u;
-            uint32_t upto = __shfl_sync(full, v, end);
-            uint32_t before = __shfl_up_sync(full, v, 1);
-            if (lane == 0) before = 0;
-            if (head && hm != 0xFFFFFFFFu) {
-                uint32_t sum = upto - before;
-                if (sum) atomicAdd(a.counters + (uint64_t)hm * CNT_STRIDE + CNT_WORDS, sum);
-            }
-        }
-        if (has_next && cnt_nxt <= kLongListCap) {
-            int32_t *ln = list_base + ((sk + 1) & 1) * kLongListCap;
-            const uint64_t tsn = ts + ts_step;
-            if (lane < cnt_nxt) ln[lane] = rel_clamp(n0, tsn);
-            if (lane + 32 < cnt_nxt) ln[lane + 32] = rel_clamp(n1, tsn);
-        }
-        first_cur = first_nxt; last_cur = last_nxt;
-        first_nxt = first_nn; last_nxt = last_nn;
-        __syncwarp();
-    }
-    cp_async_wait<0>();
-}
-
-template <int NW, int WIN>
-static cudaError_t launch_scan_long_variant(const ScanArgs &a, const DeviceDfa &d, int sm_count, cudaStream_t s) {
-    size_t smem = scan_long_smem_bytes(d, NW * 100 + WIN);
-    static size_t configured = 0;
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(scan_long_kernel<NW, WIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        configured = smem;
-    }
-    uint32_t need = (a.ntiles + NW - 1) / NW;
-    uint32_t grid = need < (uint32_t)sm_count ? need : (uint32_t)sm_count;
-    scan_long_kernel<NW, WIN><<<grid, NW * 32, smem, s>>>(a, d);
-    return cudaGetLastError();
-}
-
-cudaError_t launch_scan_long(const ScanArgs &a, const DeviceDfa &d, uint32_t variant, int sm_count, cudaStream_t s) {
-    if (a.ntiles == 0) return cudaSuccess;
-    switch (variant) {
-        case 2480: return launch_scan_long_variant<24, 80>(a, d, sm_count, s);
-        case 2464: return launch_scan_long_variant<24, 64>(a, d, sm_count, s);
-        case 2864: return launch_scan_long_variant<28, 64>(a, d, sm_count, s);
-        case 2848: return launch_scan_long_variant<28, 48>(a, d, sm_count, s);
-        case 3248: return launch_scan_long_variant<32, 48>(a, d, sm_count, s);
-        case 3232: return launch_scan_long_variant<32, 32>(a, d, sm_count, s);
-        default: return cudaErrorInvalidValue;
-    }
-}
-
 // ---------------------------------------------------------------------------------- row lanes --
-// Padded arena, dense table, long lanes fed by the TMA: the arena is viewed as a matrix of kRowBytes320-byte rows, lane l
+// Padded arena, dense table, long lanes fed by the TMA: the arena is viewed as a matrix of 320-byte rows, lane l
 // of a warp owns row 32 * tile + l, and ONE tensor copy per warp and window brings the next 80-byte window of all 32
 // rows into shared memory (box 80 x 32), a second small one (box 16 x 32 at column 304 of the rows before) the warm-up
 // bytes of a new tile.  The load path issues no load/store-unit instructions at all - on this part the scan is bound by
@@ -718,9 +496,10 @@ cudaError_t launch_scan_long(const ScanArgs &a, const DeviceDfa &d, uint32_t var
 // would otherwise issue itself (cp.async) cost as much as the warm-up lookups they save.  The automaton state, word
 // count and current message stay in registers along the row.  The last, partial row of the arena is read straight from
 // global memory by the lane that owns it.
-// geometry by warps per CTA (more warps = smaller windows so that the staging still fits): row bytes, window bytes
-__host__ __device__ constexpr uint32_t row_win(uint32_t nw) { return nw >= 32 ? 48u : nw >= 28 ? 64u : 80u; }
-__host__ __device__ constexpr uint32_t row_lane(uint32_t nw) { return nw >= 32 ? 336u : 320u; }
+// row bytes and window bytes (28 warps x 64-byte windows and 32 x 48 were measured slower than 24 x 80: the 16-byte reads
+// of a 64-byte-pitch buffer collide on banks, and 64 registers per thread cost more than 8 more warps bring)
+__host__ __device__ constexpr uint32_t row_win(uint32_t) { return 80u; }
+__host__ __device__ constexpr uint32_t row_lane(uint32_t) { return 320u; }
 constexpr uint32_t kRowListCap = 34;     // message starts of a tile kept in shared memory (lane, lane + 32)
 constexpr uint32_t kRowQueueCap = 24;    // deferred event replays per warp (12 bytes each)
 constexpr uint32_t kRowQueueFlush = 10;  // replayed by the whole warp once this many are waiting
@@ -785,7 +564,7 @@ uint32_t pick_row_warps(const DeviceDfa &d, size_t max_smem) {
     if (d.wide || d.warm != 16 || d.reset_pad < 0) return 0;
     if (const char *w = getenv("TRIAGE_ROW_WARPS")) {   // tuning knob
         uint32_t nw = (uint32_t)atoi(w);
-        if ((nw == 16 || nw == 20 || nw == 24 || nw == 28 || nw == 32) && scan_rows_smem_bytes(d, nw) <= max_smem) return nw;
+        if ((nw == 16 || nw == 20 || nw == 24) && scan_rows_smem_bytes(d, nw) <= max_smem) return nw;
     }
     for (uint32_t nw : {24u, 20u, 16u})
         if (scan_rows_smem_bytes(d, nw) <= max_smem) return nw;
@@ -992,7 +771,7 @@ static cudaError_t launch_scan_rows_variant(const ScanArgs &a, const DeviceDfa &
 
 // needs at least one full row and a 16-byte aligned arena; the caller falls back to the mini-tile kernel otherwise
 bool scan_rows_usable(const ScanArgs &a) {
-    return a.total >= 336 && (reinterpret_cast<uintptr_t>(a.bytes) & 15u) == 0 && encode_tiled_fn() != nullptr;
+    return a.total >= row_lane(0) && (reinterpret_cast<uintptr_t>(a.bytes) & 15u) == 0 && encode_tiled_fn() != nullptr;
 }
 
 cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, int sm_count, cudaStream_t s) {
@@ -1012,271 +791,12 @@ cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw,
             CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
         return cudaErrorInvalidValue;
     switch (nw) {
-        case 32: return launch_scan_rows_variant<32>(a, d, tw, tm, (uint32_t)nrows_full, sm_count, s);
-        case 28: return launch_scan_rows_variant<28>(a, d, tw, tm, (uint32_t)nrows_full, sm_count, s);
         case 24: return launch_scan_rows_variant<24>(a, d, tw, tm, (uint32_t)nrows_full, sm_count, s);
         case 20: return launch_scan_rows_variant<20>(a, d, tw, tm, (uint32_t)nrows_full, sm_count, s);
         case 16: return launch_scan_rows_variant<16>(a, d, tw, tm, (uint32_t)nrows_full, sm_count, s);
         default: return cudaErrorInvalidValue;
     }
 }
-
-// ---------------------------------------------------------------------------- streaming lanes --
-// Padded arena, dense table.  A lane owns NCH chunks of kStreamChunk contiguous bytes (chunk v = ch * 32 + lane of the
-// warp's super-tile) and walks them interleaved, 16 bytes per chain and step, fed through lane-private cp.async rings
-// (long_ring_n).  The automaton state, word count and current message of every chain stay in registers for the whole
-// chunk, so the 16-byte warm-up is paid once per chunk; no barrier sits on the data path.
-struct StreamSmem { uint32_t table, events, lists, rings, total; };
-__host__ __device__ inline StreamSmem stream_layout(uint32_t n_states, uint32_t n_events, uint32_t nw, uint32_t nch) {
-    StreamSmem L;
-    uint32_t o = 0;
-    L.table = o; o += ((n_states * kRowBytes + 127u) / 128u) * 128u;
-    L.events = o; o += ((n_events * 16u + 127u) / 128u) * 128u;
-    L.lists = o; o += nw * 2u * 4u * kStreamListCap;
-    L.rings = o; o += nw * nch * kStreamRing * 512u;   // per warp, chain and ring slot: 32 lanes x 16 bytes
-    L.total = o;
-    return L;
-}
-size_t scan_stream_smem_bytes(const DeviceDfa &d, uint32_t variant) {
-    return stream_layout(d.n_states, d.n_events, variant / 10, variant % 10).total;
-}
-
-// Walks nbytes (a multiple of 16) of N chains.  Every lane feeds a private two-piece ring per chain with cp.async: a
-// piece is one 32-byte sector of the lane's chunk (two 16-byte copies issued together, so every DRAM sector is asked for
-// exactly once), one commit group per piece, one piece ahead.  The lane is the only reader of its slots, so the data
-// path needs no barrier; a 16-byte slot of all lanes is one contiguous 512-byte row (conflict-free).
-template <int N>
-__device__ __forceinline__ void ring_step(const LaneCtx &c, LongLane (&L)[N], const int32_t (&pos)[N], int32_t g, uint32_t slot_s) {
-    Quad q[N];
-#pragma unroll
-    for (int ch = 0; ch < N; ch++) {
-        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
-                     : "=r"(q[ch].a), "=r"(q[ch].b), "=r"(q[ch].c), "=r"(q[ch].d)
-                     : "r"(slot_s + ch * (kStreamRing * 512)) : "memory");
-    }
-#pragma unroll
-    for (int ch = 0; ch < N; ch++) long_boundary(c, L[ch], pos[ch] + g);
-    group16_counted_n<N>(c, q, L);
-}
-
-template <int N>
-__device__ __forceinline__ void long_ring_n(const LaneCtx &c, LongLane (&L)[N], const uint8_t *const (&src)[N], const int32_t (&pos)[N],
-                                            int32_t nbytes, uint32_t ring_s) {
-    static_assert(kStreamRing == 4, "two pieces of two 16-byte slots");
-    auto issue = [&](int32_t g, uint32_t piece_s) {   // piece = bytes [g, g + 32) of every chain
-#pragma unroll
-        for (int ch = 0; ch < N; ch++) {
-            cp_async16(piece_s + ch * (kStreamRing * 512), src[ch] + g);
-            if (g + 16 < nbytes) cp_async16(piece_s + ch * (kStreamRing * 512) + 512, src[ch] + g + 16);
-        }
-    };
-    issue(0, ring_s);
-    cp_async_commit();
-    uint32_t cur = 0;   // byte offset of the piece being read: 0 or 1024
-#pragma unroll 1
-    for (int32_t g = 0; g < nbytes; g += 32) {
-        if (g + 32 < nbytes) issue(g + 32, ring_s + (cur ^ 1024u));
-        cp_async_commit();
-        cp_async_wait<1>();   // the piece that holds step g has landed
-        ring_step<N>(c, L, pos, g, ring_s + cur);
-        if (g + 16 < nbytes) ring_step<N>(c, L, pos, g + 16, ring_s + cur + 512);
-        cur ^= 1024u;
-    }
-    cp_async_wait<0>();
-}
-
-template <int NW, int NCH>
-__global__ void __launch_bounds__(NW * 32, 1) scan_stream_kernel(ScanArgs a, DeviceDfa d) {
-    extern __shared__ __align__(128) uint8_t smem[];
-    constexpr int32_t CL = kStreamChunk;
-    constexpr uint32_t SUPER = NCH * 32 * kStreamChunk;
-    const StreamSmem S = stream_layout(d.n_states, d.n_events, NW, NCH);
-    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    uint8_t *tbl = smem + S.table;
-    EventPacked *events = reinterpret_cast<EventPacked *>(smem + S.events);
-    int32_t *list_base = reinterpret_cast<int32_t *>(smem + S.lists) + warp * 2 * kStreamListCap;
-    const uint32_t warm = d.warm;
-    const uint32_t ring_s = smem_u32(smem + S.rings) + warp * (NCH * kStreamRing * 512u) + lane * 16u;
-    {
-        const uint32_t *src = reinterpret_cast<const uint32_t *>(d.table);
-        uint32_t *dst = reinterpret_cast<uint32_t *>(tbl);
-        for (uint32_t i = tid; i < d.n_states * (kRowBytes / 4); i += NW * 32) dst[i] = src[i];
-        const uint4 *es = reinterpret_cast<const uint4 *>(d.events);
-        uint4 *ed = reinterpret_cast<uint4 *>(events);
-        for (uint32_t i = tid; i < d.n_events; i += NW * 32) ed[i] = es[i];
-    }
-    __syncthreads();   // the only CTA-wide barrier
-
-    const uint32_t stride = gridDim.x * NW;
-    const uint32_t t0 = blockIdx.x * NW + warp;
-    if (t0 >= a.ntiles) return;
-    const uint32_t nmine = (a.ntiles - t0 + stride - 1) / stride;
-    const uint8_t *limit = a.bytes + a.total;
-
-    uint32_t first_cur = a.tile_first[t0], last_cur = a.tile_first[t0 + 1];
-    uint64_t ts = (uint64_t)t0 * SUPER;
-    {
-        uint32_t cnt = last_cur - first_cur + 2;
-        if (cnt <= kStreamListCap)
-            for (uint32_t j = lane; j < cnt; j += 32) list_base[j] = rel_clamp(a.offsets[first_cur + j], ts);
-    }
-    uint32_t first_nxt = 0, last_nxt = 0;
-    if (nmine > 1) { first_nxt = a.tile_first[t0 + stride]; last_nxt = a.tile_first[t0 + stride + 1]; }
-    __syncwarp();
-
-    LaneCtx c;
-    c.tbl = tbl; c.events = events; c.eom = nullptr; c.stage = nullptr;
-    c.list_abs = a.offsets; c.counters = a.counters; c.warm = (int32_t)warm;
-    c.start_state = d.start_state; c.neutral_state = d.neutral_state;
-    c.head_pad4 = c.tail_pad4 = 0;
-    c.tbl_s = smem_u32(tbl);
-    const uint64_t ts_step = (uint64_t)stride * SUPER;
-    uint32_t t = t0;
-
-    for (uint32_t sk = 0; sk < nmine; sk++, t += stride, ts += ts_step) {
-        const bool has_next = sk + 1 < nmine;
-        const uint32_t cnt_cur = last_cur - first_cur + 2;
-        const int32_t *lst = list_base + (sk & 1) * kStreamListCap;
-        c.list = cnt_cur <= kStreamListCap ? lst : nullptr;
-        c.tile_start = (int64_t)ts;
-        c.list_n = cnt_cur; c.msg_lo = first_cur;
-        const uint64_t rem = a.total - ts;                       // bytes of the arena from this super-tile on
-        const int32_t len = rem < SUPER ? (int32_t)rem : (int32_t)SUPER;
-        const uint8_t *tile = a.bytes + ts;
-
-        if (has_next) {   // pull the first lines of the next super-tile's chunks towards L2
-            const uint8_t *nx = tile + ts_step;
-#pragma unroll
-            for (int ch = 0; ch < NCH; ch++) {
-                const uint8_t *p = nx + (ch * 32 + (int)lane) * CL;
-                if (p + 256 < limit) { stream_prefetch(p - 16); stream_prefetch(p + 128); stream_prefetch(p + 256); }
-            }
-        }
-
-        LongLane L[NCH];
-        const uint8_t *src[NCH];
-        int32_t pos[NCH], nb[NCH];
-        bool all_full = true;
-#pragma unroll
-        for (int ch = 0; ch < NCH; ch++) {
-            pos[ch] = (ch * 32 + (int)lane) * CL;
-            nb[ch] = pos[ch] >= len ? 0 : (len - pos[ch] < CL ? len - pos[ch] : CL);
-            all_full = all_full && nb[ch] == CL;
-            src[ch] = tile + pos[ch];
-        }
-        {   // the message every chunk starts in
-            uint32_t km[NCH];
-            if (c.list) {
-#pragma unroll
-                for (int ch = 0; ch < NCH; ch++) km[ch] = 0;
-                for (uint32_t j = 1; j + 1 < cnt_cur; j++) {
-                    const int32_t o = lst[j];
-#pragma unroll
-                    for (int ch = 0; ch < NCH; ch++) km[ch] += o <= pos[ch] ? 1u : 0u;
-                }
-            } else {
-#pragma unroll
-                for (int ch = 0; ch < NCH; ch++) km[ch] = nb[ch] ? find_msg(c, pos[ch]) : 0;
-            }
-#pragma unroll
-            for (int ch = 0; ch < NCH; ch++)
-                if (nb[ch]) long_begin(c, L[ch], km[ch], t == 0 && ch == 0 && lane == 0, src[ch] - warm);
-        }
-
-        // next list: loaded before the walk, stored after it
-        uint64_t nreg[kStreamListCap / 32];
-        uint32_t cnt_nxt = 0, first_nn = 0, last_nn = 0;
-        if (has_next) {
-            cnt_nxt = last_nxt - first_nxt + 2;
-            if (cnt_nxt <= kStreamListCap) {
-#pragma unroll
-                for (uint32_t j = 0; j < kStreamListCap / 32; j++)
-                    if (lane + 32 * j < cnt_nxt) nreg[j] = a.offsets[first_nxt + lane + 32 * j];
-            }
-            if (sk + 2 < nmine) { first_nn = a.tile_first[t + 2 * stride]; last_nn = a.tile_first[t + 2 * stride + 1]; }
-        }
-
-        if (all_full) {
-            long_ring_n<NCH>(c, L, src, pos, CL, ring_s);
-        } else {
-#pragma unroll
-            for (int ch = 0; ch < NCH; ch++) {
-                if (!nb[ch]) continue;
-                LongLane L1[1] = {L[ch]};
-                const uint8_t *s1[1] = {src[ch]};
-                const int32_t p1[1] = {pos[ch]};
-                long_ring_n<1>(c, L1, s1, p1, nb[ch], ring_s);
-                L[ch] = L1[0];
-            }
-        }
-
-#pragma unroll
-        for (int ch = 0; ch < NCH; ch++) {
-            uint32_t hm = 0xFFFFFFFFu, hw = 0;
-            if (nb[ch]) { long_end(c, L[ch]); hm = L[ch].head_msg; hw = L[ch].head_words; }
-            // combine the head partials of neighbouring lanes that sit in the same message
-            const unsigned full = 0xFFFFFFFFu;
-            uint32_t prev = __shfl_up_sync(full, hm, 1);
-            bool head = lane == 0 || hm != prev;
-            uint32_t heads = __ballot_sync(full, head);
-            uint32_t v = hw;
-#pragma unroll
-            for (int dlt = 1; dlt < 32; dlt <<= 1) {
-                uint32_t tt = __shfl_up_sync(full, v, dlt);
-                if ((int)lane >= dlt) v += tt;
-            }
-            uint32_t above = heads & ~((2u << lane) - 1u);
-            uint32_t end = above ? (uint32_t)__ffs(above) - 2u : 31u;
-            uint32_t upto = __shfl_sync(full, v, end);
-            uint32_t before = __shfl_up_sync(full, v, 1);
-            if (lane == 0) before = 0;
-            if (head && hm != 0xFFFFFFFFu) {
-                uint32_t sum = upto - before;
-                if (sum) atomicAdd(a.counters + (uint64_t)hm * CNT_STRIDE + CNT_WORDS, sum);
-            }
-        }
-        if (has_next && cnt_nxt <= kStreamListCap) {
-            int32_t *ln = list_base + ((sk + 1) & 1) * kStreamListCap;
-            const uint64_t tsn = ts + ts_step;
-#pragma unroll
-            for (uint32_t j = 0; j < kStreamListCap / 32; j++)
-                if (lane + 32 * j < cnt_nxt) ln[lane + 32 * j] = rel_clamp(nreg[j], tsn);
-        }
-        first_cur = first_nxt; last_cur = last_nxt;
-        first_nxt = first_nn; last_nxt = last_nn;
-        __syncwarp();
-    }
-}
-
-template <int NW, int NCH>
-static cudaError_t launch_scan_stream_variant(const ScanArgs &a, const DeviceDfa &d, int sm_count, cudaStream_t s) {
-    size_t smem = scan_stream_smem_bytes(d, NW * 10 + NCH);
-    static size_t configured = 0;
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(scan_stream_kernel<NW, NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        configured = smem;
-    }
-    uint32_t need = (a.ntiles + NW - 1) / NW;
-    uint32_t grid = need < (uint32_t)sm_count ? need : (uint32_t)sm_count;
-    scan_stream_kernel<NW, NCH><<<grid, NW * 32, smem, s>>>(a, d);
-    return cudaGetLastError();
-}
-
-// variant = warps per CTA * 10 + chains per lane
-cudaError_t launch_scan_stream(const ScanArgs &a, const DeviceDfa &d, uint32_t variant, int sm_count, cudaStream_t s) {
-    if (a.ntiles == 0) return cudaSuccess;
-    switch (variant) {
-        case 162: return launch_scan_stream_variant<16, 2>(a, d, sm_count, s);
-        case 202: return launch_scan_stream_variant<20, 2>(a, d, sm_count, s);
-        case 242: return launch_scan_stream_variant<24, 2>(a, d, sm_count, s);
-        case 163: return launch_scan_stream_variant<16, 3>(a, d, sm_count, s);
-        case 124: return launch_scan_stream_variant<12, 4>(a, d, sm_count, s);
-        case 241: return launch_scan_stream_variant<24, 1>(a, d, sm_count, s);
-        default: return cudaErrorInvalidValue;
-    }
-}
-uint32_t scan_stream_super_bytes(uint32_t variant) { return (variant % 10) * 32 * kStreamChunk; }
 
 // ---------------------------------------------------------------------------------- fix-up --
 // Messages in which a self-overlapping keyword ("aa", "abab") may have overlapping occurrences are re-counted by one

@@ -46,16 +46,8 @@ struct ScanArgs {
 constexpr uint32_t kPadChunk = 80;
 constexpr uint32_t kPadMiniTile = 32 * kPadChunk;   // bytes per warp iteration
 size_t scan_padded_smem_bytes(const DeviceDfa &d, uint32_t nw);
-uint32_t scan_padded_chunk(uint32_t nw);                       // bytes per lane and mini-tile for that warp count
 uint32_t pick_pad_warps(const DeviceDfa &d, size_t max_smem);   // 24 for the default dictionary; fewer when the table is large
 cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, int sm_count, cudaStream_t s);
-
-// long-lane variant of the padded scan (dense table): a lane streams a 320/336-byte chunk through shared memory in
-// windows; `variant` = warps per CTA * 100 + window bytes
-constexpr uint32_t kLongListCap = 64;      // message starts of a super-tile kept in shared memory (lane, lane + 32)
-size_t scan_long_smem_bytes(const DeviceDfa &d, uint32_t variant);
-uint32_t scan_long_super_bytes(uint32_t variant);
-cudaError_t launch_scan_long(const ScanArgs &a, const DeviceDfa &d, uint32_t variant, int sm_count, cudaStream_t s);
 
 // row-lane variant of the padded scan (dense table, 16-byte warm-up): 320-byte rows fed by 2-D TMA tile copies
 size_t scan_rows_smem_bytes(const DeviceDfa &d, uint32_t nw);
@@ -63,15 +55,6 @@ uint32_t scan_rows_super_bytes(uint32_t nw);
 uint32_t pick_row_warps(const DeviceDfa &d, size_t max_smem);   // 0: this automaton cannot use it
 bool scan_rows_usable(const ScanArgs &a);
 cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, int sm_count, cudaStream_t s);
-
-// streaming variant of the padded scan (dense table): a lane walks several 512-byte chunks interleaved, reading the
-// arena straight from global memory; `variant` = warps per CTA * 10 + chains per lane
-constexpr uint32_t kStreamChunk = 512;
-constexpr uint32_t kStreamListCap = 128;   // message starts of a super-tile kept in shared memory
-constexpr uint32_t kStreamRing = 4;         // 16-byte slots per lane and chain (3 steps of prefetch)
-size_t scan_stream_smem_bytes(const DeviceDfa &d, uint32_t variant);
-uint32_t scan_stream_super_bytes(uint32_t variant);
-cudaError_t launch_scan_stream(const ScanArgs &a, const DeviceDfa &d, uint32_t variant, int sm_count, cudaStream_t s);
 
 // sequential exact recount of the messages the scan flagged (self-overlapping keywords); `exact` points at global memory
 cudaError_t launch_fixup(const uint8_t *bytes, const uint64_t *offsets, const uint32_t *lengths, uint32_t n, const DeviceDfa &exact,

@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """Side measurements for DESIGN.md (not the bench contract): scan time of the other BASELINE configs on one B200.
-  python profiles/measure_configs.py c4|c5
+  python profiles/measure_configs.py c3|c4|c5
+c3: 1 Mi messages, mixed lengths (70 % 256-1024 B, 25 % 1-4 KB, 5 % 4-16 KB), default dictionary.
 c4: 16 384 long-context payloads of 32-128 KB (quarter of SURVEY's 65 536), default dictionary.
 c5: 262 144 messages of 256-4096 B, 10 000-keyword dictionary (wide table format)."""
 import json
@@ -21,6 +22,8 @@ if which == "c5":
     for p, ci, lit in c5.dictionary():
         e.add_literal(p, lit, ci)
     off, data, meta, ts = co.generate(0xC0FFEE05, 1 << 18, 256, 4096, mix=2, edge=50)
+elif which == "c3":
+    off, data, meta, ts = co.generate(0xC0FFEE03, 1 << 20, 256, 16384, mix=1, edge=50)
 else:
     off, data, meta, ts = co.generate(0xC0FFEE04, 1 << 14, 32768, 131072, edge=50)
 info = e.dict_info()

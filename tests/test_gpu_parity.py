@@ -251,6 +251,30 @@ def test_padded_arena_path_vs_c_oracle(seed, n, lo, hi, edge, mix):
         e.close()
 
 
+@pytest.mark.parametrize("rows", ["1", "0"])
+def test_padded_arena_sizes_around_row_and_tile_boundaries(rows, monkeypatch):
+    """The padded arena is scanned as 320-byte rows, 32 rows per tile (2-D TMA), with the partial last row read directly;
+    arenas shorter than one row go to the mini-tile kernel.  Sweep totals across those boundaries, with both kernels
+    (TRIAGE_ROWS=0 keeps to the mini-tile kernel): every result must equal the oracle's."""
+    monkeypatch.setenv("TRIAGE_ROWS", rows)
+    e = mq.Engine(device=0)
+    try:
+        seen = set()
+        for seed, n, lo, hi in [(1, 1, 1, 15), (2, 1, 290, 303), (3, 2, 140, 160), (4, 3, 100, 110), (5, 40, 200, 300), (6, 33, 300, 304),
+                                (7, 64, 150, 170), (8, 65, 304, 320), (9, 700, 0, 30), (10, 31, 305, 319), (11, 257, 1, 90), (12, 5, 2000, 2100)]:
+            off, data, meta, ts = co.generate(seed, n, lo, hi, edge=1500)
+            exp, order = co.pipeline(co.Dict(), off, data, meta, ts, nthreads=4)
+            poff, plen, pbytes = e.pack_padded(off, data)
+            seen.add((int(poff[-1]) % 320) // 16)
+            res, base = e.submit_padded(poff, plen, pbytes, meta, ts)
+            _assert_same(res, exp, FIELDS, ctx=f"rows={rows} seed {seed} total {int(poff[-1])}")
+            handles, _ = e.drain(n)
+            assert np.array_equal((handles - base).astype(np.uint32), order)
+        assert len(seen) >= 6   # several different tail-row lengths were hit
+    finally:
+        e.close()
+
+
 def test_padded_edge_cases_vs_golden(golden_dir):
     cases = json.load(open(os.path.join(golden_dir, "edge_cases.json")))
     contents = [bytes.fromhex(e["content_hex"]) for e in cases]
