@@ -55,6 +55,24 @@ __device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *tm, in
                  : "memory");
 }
 
+// Raises a kernel's dynamic shared-memory limit once per (kernel, device): the attribute is per device, and one process
+// may hold engines on several GPUs.
+constexpr int kMaxDevices = 64;
+struct SmemConfigured { size_t bytes[kMaxDevices] = {0}; };
+template <class Kernel>
+static cudaError_t ensure_dynamic_smem(Kernel kernel, size_t smem, SmemConfigured &done) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+    if (smem > done.bytes[dev]) {
+        e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        done.bytes[dev] = smem;
+    }
+    return cudaSuccess;
+}
+
 // ------------------------------------------------------------------------------ tile index --
 __global__ void tile_index_kernel(const uint64_t *__restrict__ offsets, uint32_t n, uint32_t ntiles, uint32_t tile_bytes,
                                   uint32_t *__restrict__ tile_first) {
@@ -260,12 +278,8 @@ ScanGeometry pick_scan_geometry(const DeviceDfa &d, size_t max_smem) {
 template <int NT, int C, bool FAST>
 static cudaError_t launch_scan_variant(const ScanArgs &a, const DeviceDfa &d, size_t smem, uint32_t grid, cudaStream_t s) {
     auto kern = scan_kernel<NT, C, FAST>;
-    static size_t configured = 0;
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        configured = smem;
-    }
+    static SmemConfigured configured;
+    if (cudaError_t e = ensure_dynamic_smem(kern, smem, configured)) return e;
     kern<<<grid, NT, smem, s>>>(a, d);
     return cudaGetLastError();
 }
@@ -462,12 +476,8 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_padded_kernel(ScanArgs a, Dev
 template <int NW, bool WIDE = false>
 static cudaError_t launch_scan_padded_variant(const ScanArgs &a, const DeviceDfa &d, int sm_count, cudaStream_t s) {
     size_t smem = scan_padded_smem_bytes(d, NW);
-    static size_t configured = 0;
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(scan_padded_kernel<NW, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        configured = smem;
-    }
+    static SmemConfigured configured;
+    if (cudaError_t e = ensure_dynamic_smem(scan_padded_kernel<NW, WIDE>, smem, configured)) return e;
     uint32_t need = (a.ntiles + NW - 1) / NW;
     uint32_t grid = need < (uint32_t)sm_count ? need : (uint32_t)sm_count;
     scan_padded_kernel<NW, WIDE><<<grid, NW * 32, smem, s>>>(a, d);
@@ -757,12 +767,8 @@ template <int NW>
 static cudaError_t launch_scan_rows_variant(const ScanArgs &a, const DeviceDfa &d, const CUtensorMap &tw, const CUtensorMap &tm,
                                             uint32_t nrows_full, int sm_count, cudaStream_t s) {
     size_t smem = scan_rows_smem_bytes(d, NW);
-    static size_t configured = 0;
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(scan_rows_kernel<NW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        configured = smem;
-    }
+    static SmemConfigured configured;
+    if (cudaError_t e = ensure_dynamic_smem(scan_rows_kernel<NW>, smem, configured)) return e;
     uint32_t need = (a.ntiles + NW - 1) / NW;
     uint32_t grid = need < (uint32_t)sm_count ? need : (uint32_t)sm_count;
     scan_rows_kernel<NW><<<grid, NW * 32, smem, s>>>(a, d, tw, tm, nrows_full);
@@ -971,28 +977,51 @@ __global__ void __launch_bounds__(kOrderBlock) split_hist_kernel(Dig dig, const 
 __global__ void __launch_bounds__(1024) split_scan_kernel(uint32_t *__restrict__ blockhist, uint32_t nblocks, uint32_t nb,
                                                           uint32_t *__restrict__ totals) {
     __shared__ uint32_t part[1024];
-    const uint64_t total = (uint64_t)nblocks * nb;   // digits >= nb never occur
-    const uint64_t per = (total + 1023) / 1024;
-    const uint64_t lo = per * threadIdx.x, hi = lo + per < total ? lo + per : total;
+    __shared__ uint32_t warp_sum[32];
+    const uint32_t total = nblocks * nb;   // digits >= nb never occur; nblocks * 256 fits 32 bits (n < 2^32)
+    const uint32_t per = (total + 1023) / 1024;
+    const uint32_t lo = per * threadIdx.x < total ? per * threadIdx.x : total, hi = lo + per < total ? lo + per : total;
+    const uint32_t dgt0 = lo / nblocks, b0 = lo - dgt0 * nblocks;   // one division per thread, then counted up
     uint32_t s = 0;
-    for (uint64_t j = lo; j < hi; j++) { uint32_t dgt = (uint32_t)(j / nblocks), b = (uint32_t)(j % nblocks); s += blockhist[(uint64_t)b * 256 + dgt]; }
-    part[threadIdx.x] = s;
-    __syncthreads();
-    // inclusive scan of part (Hillis-Steele)
-    for (uint32_t off = 1; off < 1024; off <<= 1) {
-        uint32_t v = threadIdx.x >= off ? part[threadIdx.x - off] : 0;
-        __syncthreads();
-        part[threadIdx.x] += v;
-        __syncthreads();
+    {
+        uint32_t dgt = dgt0, b = b0;
+        for (uint32_t j = lo; j < hi; j++) {
+            s += blockhist[b * 256 + dgt];
+            if (++b == nblocks) { b = 0; dgt++; }
+        }
     }
-    uint32_t run = threadIdx.x ? part[threadIdx.x - 1] : 0;
-    for (uint64_t j = lo; j < hi; j++) {
-        uint32_t dgt = (uint32_t)(j / nblocks), b = (uint32_t)(j % nblocks);
-        uint64_t idx = (uint64_t)b * 256 + dgt;
-        uint32_t c = blockhist[idx];
-        blockhist[idx] = run;
-        if (b == 0) totals[dgt] = run;
-        run += c;
+    // exclusive scan of the 1024 partial sums: warp shuffles, then the 32 warp totals
+    const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t incl = s;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+        if ((int)lane >= d) incl += t;
+    }
+    if (lane == 31) warp_sum[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        uint32_t w = warp_sum[lane], wi = w;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            uint32_t t = __shfl_up_sync(0xFFFFFFFFu, wi, d);
+            if ((int)lane >= d) wi += t;
+        }
+        warp_sum[lane] = wi - w;   // exclusive
+    }
+    __syncthreads();
+    uint32_t run = warp_sum[wid] + incl - s;
+    part[threadIdx.x] = run + s;
+    {
+        uint32_t dgt = dgt0, b = b0;
+        for (uint32_t j = lo; j < hi; j++) {
+            const uint32_t idx = b * 256 + dgt;
+            const uint32_t c = blockhist[idx];
+            blockhist[idx] = run;
+            if (b == 0) totals[dgt] = run;
+            run += c;
+            if (++b == nblocks) { b = 0; dgt++; }
+        }
     }
     __syncthreads();
     for (uint32_t dgt = nb + threadIdx.x; dgt <= 256; dgt += 1024) totals[dgt] = part[1023];
