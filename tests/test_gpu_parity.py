@@ -275,6 +275,33 @@ def test_padded_arena_sizes_around_row_and_tile_boundaries(rows, monkeypatch):
         e.close()
 
 
+def test_event_dense_content_overflows_the_replay_queue():
+    """Row-lane scan: events are queued per warp (24 slots) and replayed in bulk; content where almost every 8-byte half
+    carries an event overflows the queue, so lanes replay on the spot as well.  Both paths must add up to the oracle."""
+    rng = np.random.default_rng(17)
+    words = [b"asap", b"soon", b"urgent", b"good", b"bad", b"what", b"who", b"ASAP", "a\u017fap".encode(),
+             b"x", b"critical", b"happy", b"why"]
+    contents = []
+    for i in range(600):
+        k = int(rng.integers(1, 400))
+        parts = [words[int(j)] for j in rng.integers(0, len(words), k)]
+        sep = b" " if i % 3 else b"\n"
+        contents.append(sep.join(parts) + (b"?" if i % 5 == 0 else b""))
+    off, data = co.pack(contents)
+    n = len(contents)
+    _, _, meta, ts = co.generate(18, n, 1, 2)   # realistic meta records and enqueue times, own content
+    exp, order = co.pipeline(co.Dict(), off, data, meta, ts, nthreads=4)
+    e = mq.Engine(device=0)
+    try:
+        poff, plen, pbytes = e.pack_padded(off, data)
+        res, base = e.submit_padded(poff, plen, pbytes, meta, ts)
+        _assert_same(res, exp, FIELDS, ctx="event-dense")
+        handles, _ = e.drain(n)
+        assert np.array_equal((handles - base).astype(np.uint32), order)
+    finally:
+        e.close()
+
+
 def test_padded_edge_cases_vs_golden(golden_dir):
     cases = json.load(open(os.path.join(golden_dir, "edge_cases.json")))
     contents = [bytes.fromhex(e["content_hex"]) for e in cases]
