@@ -121,3 +121,30 @@ def test_long_lane_walks(golden_dir, walk):
         exp = _expected(co.Dict(), contents)
         bad = np.nonzero((cnt != exp).any(axis=1))[0]
         assert len(bad) == 0, (seed, bad[:5], cnt[bad[:5]], exp[bad[:5]])
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_dictionaries_vs_oracle(seed):
+    """differential: random literal dictionaries (small alphabets, mixed case sensitivity, UTF-8, folds) on text built
+    from their own literals and fragments; every counter of every message, packed and padded walks"""
+    from tests import randdict
+    entries, contents = randdict.make(1000 + seed, allow_bordered=False)
+    d = co.Dict()
+    for p, ci, lit in entries:
+        assert d.add(p, lit, ci) == 0
+    off, data = co.pack(contents)
+    exp = _expected(d, contents)
+    full = hc.DEFAULT_DICT + entries
+    try:
+        cnt, info = hc.scan(full, off, data, nt=8, chunk=48)
+    except ValueError as e:   # the automaton needs the wide format, or a literal uses the pad byte: other tests cover those
+        pytest.skip(str(e))
+    bad = np.nonzero((cnt != exp).any(axis=1))[0]
+    assert len(bad) == 0, (entries, bad[:3], [contents[i][:60] for i in bad[:3]], cnt[bad[:3]], exp[bad[:3]])
+    for walk in (lambda: hc.scan_padded(full, off, data)[0], lambda: hc.scan_stream(full, off, data, chunk_long=320, nch=1)):
+        try:
+            cnt = walk()
+        except ValueError as e:
+            continue
+        bad = np.nonzero((cnt != exp).any(axis=1))[0]
+        assert len(bad) == 0, (entries, bad[:3], [contents[i][:60] for i in bad[:3]], cnt[bad[:3]], exp[bad[:3]])

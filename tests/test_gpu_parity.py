@@ -302,6 +302,39 @@ def test_event_dense_content_overflows_the_replay_queue():
         e.close()
 
 
+@pytest.mark.parametrize("seed", range(8))
+def test_random_dictionaries_through_the_engine(seed):
+    """differential: random literal dictionaries (self-overlapping ones included: fix-up kernel) added on top of the
+    defaults, on text built from their own literals; labels, scores, analysis and dequeue order vs the oracle, through
+    both wire formats"""
+    from tests import randdict
+    entries, contents = randdict.make(2000 + seed, allow_bordered=True)
+    d = co.Dict()
+    e = mq.Engine(device=0)
+    try:
+        for p, ci, lit in entries:
+            assert d.add(p, lit, ci) == 0
+            e.add_literal(p, lit, ci)
+        off, data = co.pack(contents)
+        n = len(contents)
+        _, _, meta, ts = co.generate(3000 + seed, n, 1, 2)
+        exp, order = co.pipeline(d, off, data, meta, ts, nthreads=4)
+        e.commit()
+        if e.dict_info()["states"] <= 256:   # larger automata use the wide table format: padded arena only
+            res, base = e.submit(off, data, meta, ts)
+            _assert_same(res, exp, FIELDS, ctx=f"random dictionary {seed} (packed) {entries}")
+            handles, _ = e.drain(n)
+            assert np.array_equal((handles - base).astype(np.uint32), order)
+        if e.pad_byte() >= 0:
+            poff, plen, pbytes = e.pack_padded(off, data)
+            res, base = e.submit_padded(poff, plen, pbytes, meta, ts)
+            _assert_same(res, exp, FIELDS, ctx=f"random dictionary {seed} (padded) {entries}")
+            handles, _ = e.drain(n)
+            assert np.array_equal((handles - base).astype(np.uint32), order)
+    finally:
+        e.close()
+
+
 def test_padded_edge_cases_vs_golden(golden_dir):
     cases = json.load(open(os.path.join(golden_dir, "edge_cases.json")))
     contents = [bytes.fromhex(e["content_hex"]) for e in cases]
