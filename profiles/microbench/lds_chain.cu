@@ -22,7 +22,7 @@ __global__ void chain(const uint32_t *text, uint32_t *out, long long *cycles, in
     for (uint32_t i = tid; i < NST * 256; i += blockDim.x) {
         uint32_t st = i >> 8, b = i & 255;
         uint32_t nx = (st * 7 + b * 13 + 1) % NST;
-        if (MODE == 0 || MODE == 1) *reinterpret_cast<uint16_t *>(smem + st * ROW + b * 2) = (uint16_t)(nx | ((b & 1) << 15));
+        if (MODE == 0 || MODE == 1 || MODE == 6) *reinterpret_cast<uint16_t *>(smem + st * ROW + b * 2) = (uint16_t)(nx | ((b & 1) << 15));
         if (MODE == 2) *reinterpret_cast<uint32_t *>(smem + st * 1028 + b * 4) = nx * 1028 | ((b & 1u) << 31);     // pre-multiplied + flag
         if (MODE == 3) *reinterpret_cast<uint32_t *>(smem + st * 1028 + b * 4) = nx * 1028;                         // pure offset
         if (MODE == 4 || MODE == 5) smem[st * 260 + b] = (uint8_t)nx;
@@ -31,16 +31,26 @@ __global__ void chain(const uint32_t *text, uint32_t *out, long long *cycles, in
     const uint32_t base = smem_u32(smem);
     uint32_t e = tid % NST, words = 0;
     if (MODE == 2 || MODE == 3) e = (tid % NST) * 1028;
-    const uint32_t *tp = text + (same_byte ? 0 : (tid & 31) * 64);
+    // the lane's text: 8 words held in registers (a load from global memory inside the loop would be measured instead)
+    uint32_t tw[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) tw[j] = same_byte ? 0x61616161u : text[(tid & 31) * 64 + j + 8 * (tid >> 5)];
     long long t0 = clock64();
 #pragma unroll 1
-    for (int i = 0; i < STEPS / 4; i++) {
-        uint32_t w = same_byte ? 0x61616161u : tp[i & 63];
+    for (int i = 0; i < STEPS / 32; i++) {
+#pragma unroll
+      for (int j = 0; j < 8; j++) {
+        const uint32_t w = tw[j];
 #pragma unroll
         for (int k = 0; k < 4; k++) {
             if (MODE == 0) {           // PRMT + IDP.4A + LDS.U16 (the shipped sequence)
                 uint32_t a = __dp4a(__byte_perm(w, e, 0x4440u | k), 0xACACAC02u, base);
                 e = lds16(a); words += e >> 15;
+            } else if (MODE == 6) {    // shipped sequence, half of the lanes idle: is the limit per instruction or per lane?
+                if ((tid & 1) == 0) {
+                    uint32_t a = __dp4a(__byte_perm(w, e, 0x4440u | k), 0xACACAC02u, base);
+                    e = lds16(a); words += e >> 15;
+                }
             } else if (MODE == 1) {    // LOP + IMAD + LDS.U16
                 uint32_t b2 = (w >> (8 * k) & 0xFFu) * 2u;
                 uint32_t a = (e & 0xFFu) * ROW + b2 + base;
@@ -61,6 +71,7 @@ __global__ void chain(const uint32_t *text, uint32_t *out, long long *cycles, in
                 e = lds8(a); words += e >> 7;
             }
         }
+      }
     }
     long long t1 = clock64();
     out[blockIdx.x * blockDim.x + tid] = e + words;
@@ -96,5 +107,6 @@ int main() {
     run<3>("u32 pure offset IADD", text, out, cyc, NST * 1028 + 64);
     run<4>("u8 PRMT+IDP.4A", text, out, cyc, NST * 260 + 64);
     run<5>("u8 pure state IMAD", text, out, cyc, NST * 260 + 64);
+    run<6>("u16 PRMT+IDP.4A, 16 of 32 lanes", text, out, cyc, NST * ROW + 64);   // lookups/clk counts all 32 lanes: halve it
     return 0;
 }
