@@ -286,11 +286,9 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     OrderScratch sc{e->d_blockhist.p, e->d_totals.p, nblocks};
 
     CU(cudaEventRecord(e->ev[0], s));
-    CU(cudaMemsetAsync(e->d_counters.p, 0, (size_t)n * CNT_STRIDE * sizeof(uint32_t), s));
-    CU(cudaMemsetAsync(e->d_small.p, 0, (32 + 8 * 256) * sizeof(uint32_t), s));
     ScanArgs sa{bytes, offsets, total, n, e->d_counters.p, e->d_tile_first.p, ntiles, tile_bytes};
+    CU(launch_prepare(sa, e->d_small.p, 32 + 8 * 256, e->sm_count, s)); launches++;   // tile index + zeroed counters and scratch
     if (ntiles) {
-        CU(launch_tile_index(sa, s)); launches++;
         CU(cudaEventRecord(e->ev[1], s));
         if (use_rows) CU(launch_scan_rows(sa, e->ddfa, e->row_warps, e->sm_count, s));
         else if (padded) CU(launch_scan_padded(sa, e->ddfa, e->pad_warps, e->sm_count, s));

@@ -94,6 +94,34 @@ cudaError_t launch_tile_index(const ScanArgs &a, cudaStream_t s) {
     return cudaGetLastError();
 }
 
+// One launch before the scan: the tile index, and the zeroing of the per-message counters and of the small scratch
+// (two memsets and a kernel otherwise: ~45 us of a 1.2 ms step).  counters: n * CNT_STRIDE words, 16-byte aligned.
+__global__ void __launch_bounds__(256) prepare_kernel(const uint64_t *__restrict__ offsets, uint32_t n, uint32_t ntiles, uint32_t tile_bytes,
+                                                      uint32_t *__restrict__ tile_first, uint4 *__restrict__ counters4, uint64_t n_vec,
+                                                      uint32_t *__restrict__ small, uint32_t small_words) {
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nthreads = gridDim.x * blockDim.x;
+    for (uint32_t t = tid; t <= ntiles; t += nthreads) {
+        if (t == ntiles) { tile_first[t] = n - 1; continue; }
+        uint64_t pos = (uint64_t)t * tile_bytes;
+        uint32_t lo = 0, hi = n + 1;   // first index with offsets[idx] > pos
+        while (lo < hi) {
+            uint32_t mid = (lo + hi) >> 1;
+            if (offsets[mid] > pos) hi = mid; else lo = mid + 1;
+        }
+        tile_first[t] = lo - 1;
+    }
+    const uint4 z = make_uint4(0, 0, 0, 0);
+    for (uint64_t i = tid; i < n_vec; i += nthreads) counters4[i] = z;
+    for (uint32_t i = tid; i < small_words; i += nthreads) small[i] = 0;
+}
+
+cudaError_t launch_prepare(const ScanArgs &a, uint32_t *small, uint32_t small_words, int sm_count, cudaStream_t s) {
+    const uint64_t n_vec = (uint64_t)a.n * CNT_STRIDE / 4;   // CNT_STRIDE = 8 words per message
+    prepare_kernel<<<sm_count * 8, 256, 0, s>>>(a.offsets, a.n, a.ntiles, a.tile_bytes, a.tile_first, reinterpret_cast<uint4 *>(a.counters),
+                                                n_vec, small, small_words);
+    return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------------------------ scan --
 // shared memory layout (bytes): [0,16) two mbarriers | table | events | eom(256) | stage0 | stage1 | list0 | list1
 struct ScanSmem {

@@ -80,6 +80,8 @@ struct FinalizeArgs {
 ScanGeometry pick_scan_geometry(const DeviceDfa &d, size_t max_smem);
 size_t scan_smem_bytes(const DeviceDfa &d, const ScanGeometry &g);
 cudaError_t launch_tile_index(const ScanArgs &a, cudaStream_t s);
+// tile index + zeroing of a.counters (n * CNT_STRIDE words) and of `small` in one launch
+cudaError_t launch_prepare(const ScanArgs &a, uint32_t *small, uint32_t small_words, int sm_count, cudaStream_t s);
 cudaError_t launch_scan(const ScanArgs &a, const DeviceDfa &d, const ScanGeometry &g, int sm_count, cudaStream_t s);
 cudaError_t launch_finalize(const FinalizeArgs &a, cudaStream_t s);
 
