@@ -140,6 +140,15 @@ int32_t triage_submit_padded(triage_engine *e, int32_t target_queue, const uint6
                              triage_result *out, uint64_t *handle_base);
 int32_t triage_process_padded(triage_engine *e, const uint64_t *offsets, const uint32_t *lengths, const uint8_t *bytes,
                               const triage_meta *meta, uint32_t n, triage_result *out);   /* ProcessMessage only */
+/* Ring of two: starts the host->device copy of a batch on the engine's copy stream and returns at once.  A later
+ * triage_submit / triage_submit_padded with the SAME host pointers and n finds the batch on the device and only waits
+ * for that copy, so the shim can upload batch k+1 while batch k is scanned, ordered, read back and queued (the "pinned
+ * host ring buffers, async streams" of the design brief; the reference has no counterpart - its handlers push one
+ * message at a time).  lengths = NULL: packed arena.  The host buffers (pinned, triage_host_alloc) must stay unchanged
+ * until that submit returns; at most two prefetched batches are kept, a third replaces the older one.  Results are
+ * identical to a submit without prefetch.                                                                           */
+int32_t triage_prefetch(triage_engine *e, const uint64_t *offsets, const uint32_t *lengths, const uint8_t *bytes,
+                        const triage_meta *meta, const uint64_t *enqueue_ns, uint32_t n);
 int32_t triage_submit_device_padded(triage_engine *e, const uint64_t *offsets_dev, const uint32_t *lengths_dev,
                                     const uint8_t *bytes_dev, uint64_t total_bytes, const triage_meta *meta_dev,
                                     const uint64_t *enqueue_ns_dev, uint32_t n, triage_result *results_dev,

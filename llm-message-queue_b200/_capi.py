@@ -83,6 +83,7 @@ _SIGS = {
     "triage_submit_padded": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                          C.c_uint32, C.c_void_p, C.POINTER(C.c_uint64)]),
     "triage_process_padded": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
+    "triage_prefetch": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]),
     "triage_submit_device_padded": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p,
                                                 C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32)]),
     "triage_submit_device_static": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
@@ -244,6 +245,11 @@ class Engine:
         _check(lib().triage_submit_padded(self._h, int(target_queue), _p(offsets), _p(lengths), _p(data), _p(meta), _p(ts), n, _p(out),
                                           C.byref(base)))
         return out, base.value
+
+    def prefetch(self, offsets, lengths, data, meta, ts=None):
+        """start the host->device copy of a batch; a later submit / submit_padded with the same arrays skips the upload.
+        lengths=None: packed arena.  The arrays must stay alive and unchanged until that submit returns."""
+        _check(lib().triage_prefetch(self._h, _p(offsets), _p(lengths), _p(data), _p(meta), _p(ts), len(meta)))
 
     def submit_device_padded(self, offsets_ptr, lengths_ptr, bytes_ptr, total, meta_ptr, ts_ptr, n, results_ptr, order_ptr) -> int:
         adm = C.c_uint32()

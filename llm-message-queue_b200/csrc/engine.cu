@@ -100,6 +100,22 @@ struct LevelQueue {
     void compact() { if (head > 4096 && head * 2 > items.size()) { items.erase(items.begin(), items.begin() + head); head = 0; } }
 };
 
+// A batch whose host->device copy was started ahead of its submit (triage_prefetch): own device buffers, filled on the
+// copy stream, `ready` recorded behind the last copy.  Matched to the later submit by the caller's host pointers.
+struct PrefetchSlot {
+    DevBuf<uint8_t> bytes;
+    DevBuf<uint64_t> offsets, ts;
+    DevBuf<uint32_t> lengths;
+    DevBuf<triage_meta> meta;
+    std::vector<uint64_t> rebased;   // must outlive the asynchronous copy of the offsets
+    const void *k_offsets = nullptr, *k_bytes = nullptr, *k_meta = nullptr, *k_lengths = nullptr, *k_ts = nullptr;
+    uint32_t n = 0;
+    uint64_t total = 0;
+    cudaEvent_t ready = nullptr;
+    bool valid = false;
+    uint64_t seq = 0;                // age: the older valid slot is the one a new prefetch may reuse last
+};
+
 constexpr int kHeaderWords = 64;   // per-rank merge header (u64): n_adm, 16 counts, 16 first keys, 16 last keys
 
 }  // namespace
@@ -131,6 +147,9 @@ struct triage_engine {
     DevBuf<triage_result> d_results;
     DevBuf<uint32_t> d_lengths, d_counters, d_tile_first, d_order, d_perm_a, d_perm_b, d_blockhist, d_totals, d_small;
     DevBuf<uint8_t> d_bucket, d_bucket2;
+    PrefetchSlot pre[2];           // batches uploading ahead of their submit
+    cudaStream_t copy_stream = nullptr;
+    uint64_t pre_seq = 0;
     uint32_t *h_small = nullptr;   // pinned: [0] flags, [1] n_admitted, [2..17] bucket counts, [32..] digit hist
     std::vector<uint32_t> h_order;
     std::vector<triage_result> h_results_tmp;
@@ -399,6 +418,8 @@ int32_t triage_create(const triage_opts *opts, triage_engine **out) {
     cudaError_t ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
     for (int i = 0; i < 6 && ce == cudaSuccess; i++) ce = cudaEventCreate(&e->ev[i]);
     for (int i = 0; i < 4 && ce == cudaSuccess; i++) ce = cudaEventCreate(&e->user_ev[i]);
+    if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking);
+    for (int i = 0; i < 2 && ce == cudaSuccess; i++) ce = cudaEventCreateWithFlags(&e->pre[i].ready, cudaEventDisableTiming);
     if (ce == cudaSuccess) ce = cudaHostAlloc(reinterpret_cast<void **>(&e->h_small), (32 + 8 * 256) * sizeof(uint32_t), cudaHostAllocDefault);
     if (ce != cudaSuccess) { delete e; return fail(TRIAGE_E_CUDA, cudaGetErrorString(ce)); }
     e->q.resize(5);
@@ -413,6 +434,8 @@ void triage_destroy(triage_engine *e) {
     if (!e) return;
     cudaSetDevice(e->opts.device);
     cudaStreamSynchronize(e->stream);
+    if (e->copy_stream) cudaStreamSynchronize(e->copy_stream);
+    for (auto &ps : e->pre) { ps.bytes.release(); ps.offsets.release(); ps.ts.release(); ps.lengths.release(); ps.meta.release(); }
     if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
     e->dm.release(); e->dx.release(); e->d_bytes.release(); e->d_offsets.release();
     e->d_ts.release(); e->d_pending.release(); e->d_maxsize.release(); e->d_meta.release(); e->d_results.release(); e->d_counters.release();
@@ -423,6 +446,8 @@ void triage_destroy(triage_engine *e) {
     if (e->h_header) cudaFreeHost(e->h_header);
     for (auto &ev : e->ev) if (ev) cudaEventDestroy(ev);
     for (auto &ev : e->user_ev) if (ev) cudaEventDestroy(ev);
+    if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
+    for (auto &ps : e->pre) if (ps.ready) cudaEventDestroy(ps.ready);
     if (e->stream) cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -548,6 +573,59 @@ int32_t upload_batch(triage_engine *e, const uint64_t *offsets, const uint32_t *
 
 }  // namespace
 
+// triage_prefetch: start the host->device copy of a batch on the copy stream, into a slot of its own
+static int32_t prefetch_impl(triage_engine *e, const uint64_t *offsets, const uint32_t *lengths, const uint8_t *bytes,
+                             const triage_meta *meta, const uint64_t *enqueue_ns, uint32_t n) {
+    if (!e || (n && (!offsets || !meta))) return fail(TRIAGE_E_ARG, "null argument");
+    CU(cudaSetDevice(e->opts.device));
+    std::lock_guard<std::mutex> lock(e->mu);
+    if (n == 0) return TRIAGE_OK;
+    const uint64_t total = offsets[n] - offsets[0];
+    if (total && !bytes) return fail(TRIAGE_E_ARG, "null arena");
+    if (lengths && ((offsets[0] & 15) || (total & 15))) return fail(TRIAGE_E_ARG, "padded arena: offsets must be multiples of 16");
+    PrefetchSlot *ps = &e->pre[0];   // a free slot, else the older one
+    if (e->pre[0].valid && (!e->pre[1].valid || e->pre[1].seq < e->pre[0].seq)) ps = &e->pre[1];
+    cudaStream_t cs = e->copy_stream;
+    ps->valid = false;
+    CU(ps->bytes.ensure(total + 32));
+    CU(ps->offsets.ensure((size_t)n + 1));
+    CU(ps->meta.ensure(n));
+    if (lengths) CU(ps->lengths.ensure(n));
+    if (enqueue_ns) CU(ps->ts.ensure(n));
+    const uint64_t *off_src = offsets;
+    if (offsets[0] != 0) {
+        CU(cudaStreamSynchronize(cs));   // an earlier copy may still read the previous rebased offsets
+        ps->rebased.resize((size_t)n + 1);
+        for (uint32_t i = 0; i <= n; i++) ps->rebased[i] = offsets[i] - offsets[0];
+        off_src = ps->rebased.data();
+    }
+    if (total) CU(cudaMemcpyAsync(ps->bytes.p, bytes + offsets[0], total, cudaMemcpyHostToDevice, cs));
+    CU(cudaMemsetAsync(ps->bytes.p + total, 0, 32, cs));
+    CU(cudaMemcpyAsync(ps->offsets.p, off_src, ((size_t)n + 1) * 8, cudaMemcpyHostToDevice, cs));
+    CU(cudaMemcpyAsync(ps->meta.p, meta, (size_t)n * sizeof(triage_meta), cudaMemcpyHostToDevice, cs));
+    if (lengths) CU(cudaMemcpyAsync(ps->lengths.p, lengths, (size_t)n * 4, cudaMemcpyHostToDevice, cs));
+    if (enqueue_ns) CU(cudaMemcpyAsync(ps->ts.p, enqueue_ns, (size_t)n * 8, cudaMemcpyHostToDevice, cs));
+    CU(cudaEventRecord(ps->ready, cs));
+    ps->k_offsets = offsets; ps->k_bytes = bytes; ps->k_meta = meta; ps->k_lengths = lengths; ps->k_ts = enqueue_ns;
+    ps->n = n; ps->total = total;
+    ps->seq = ++e->pre_seq;
+    ps->valid = true;
+    return TRIAGE_OK;
+}
+
+// the slot that holds exactly this batch (same host pointers and sizes), oldest first; nullptr: not prefetched
+static PrefetchSlot *find_prefetched(triage_engine *e, const uint64_t *offsets, const uint32_t *lengths, const uint8_t *bytes,
+                                     const triage_meta *meta, const uint64_t *enqueue_ns, uint32_t n) {
+    PrefetchSlot *best = nullptr;
+    for (auto &ps : e->pre) {
+        if (!ps.valid || ps.n != n || ps.k_offsets != offsets || ps.k_bytes != bytes || ps.k_meta != meta || ps.k_lengths != lengths ||
+            ps.k_ts != enqueue_ns || ps.total != offsets[n] - offsets[0])
+            continue;
+        if (!best || ps.seq < best->seq) best = &ps;
+    }
+    return best;
+}
+
 static int32_t process_impl(triage_engine *e, const uint64_t *offsets, const uint32_t *lengths, const uint8_t *bytes,
                             const triage_meta *meta, uint32_t n, triage_result *out) {
     if (!e || (n && (!offsets || !meta || !out))) return fail(TRIAGE_E_ARG, "null argument");
@@ -596,8 +674,28 @@ static int32_t submit_impl(triage_engine *e, int32_t target_queue, const uint64_
     cudaStream_t s = e->stream;
     auto t0 = std::chrono::steady_clock::now();
     uint64_t total = 0;
-    int32_t rc = upload_batch(e, offsets, lengths, bytes, meta, enqueue_ns, n, &total);
-    if (rc) return rc;
+    int32_t rc = TRIAGE_OK;
+    const uint64_t *d_off = nullptr, *d_tsp = nullptr;
+    const uint32_t *d_len = nullptr;
+    const uint8_t *d_byt = nullptr;
+    const triage_meta *d_met = nullptr;
+    if (PrefetchSlot *ps = find_prefetched(e, offsets, lengths, bytes, meta, enqueue_ns, n)) {
+        // uploaded ahead by triage_prefetch: the compute stream only waits for the copy stream's event
+        CU(cudaStreamWaitEvent(s, ps->ready, 0));
+        CU(e->d_results.ensure(n));
+        CU(e->d_order.ensure(n));
+        total = ps->total;
+        d_off = ps->offsets.p; d_byt = ps->bytes.p; d_met = ps->meta.p;
+        d_len = lengths ? ps->lengths.p : nullptr;
+        d_tsp = enqueue_ns ? ps->ts.p : nullptr;
+        ps->valid = false;   // consumed (the buffers stay untouched until the next prefetch, i.e. after this call returns)
+    } else {
+        rc = upload_batch(e, offsets, lengths, bytes, meta, enqueue_ns, n, &total);
+        if (rc) return rc;
+        d_off = e->d_offsets.p; d_byt = e->d_bytes.p; d_met = e->d_meta.p;
+        d_len = lengths ? e->d_lengths.p : nullptr;
+        d_tsp = enqueue_ns ? e->d_ts.p : nullptr;
+    }
     auto t1 = std::chrono::steady_clock::now();
     uint64_t pending[4] = {0, 0, 0, 0};
     int64_t ms[4] = {0, 0, 0, 0};
@@ -608,8 +706,8 @@ static int32_t submit_impl(triage_engine *e, int32_t target_queue, const uint64_
         ms[0] = e->q[target_queue].max_size;
     }
     uint32_t n_adm = 0;
-    rc = run_device(e, target_queue ? RUN_SINGLE_QUEUE : RUN_ROUTED, e->d_offsets.p, lengths ? e->d_lengths.p : nullptr, e->d_bytes.p, total,
-                    e->d_meta.p, enqueue_ns ? e->d_ts.p : nullptr, n, e->d_results.p, e->d_order.p, pending, ms, &n_adm);
+    rc = run_device(e, target_queue ? RUN_SINGLE_QUEUE : RUN_ROUTED, d_off, d_len, d_byt, total, d_met, d_tsp, n, e->d_results.p,
+                    e->d_order.p, pending, ms, &n_adm);
     if (rc) return rc;
     auto t2 = std::chrono::steady_clock::now();
     triage_result *res = out;
@@ -682,6 +780,11 @@ int32_t triage_submit_padded(triage_engine *e, int32_t target_queue, const uint6
                              const triage_meta *meta, const uint64_t *enqueue_ns, uint32_t n, triage_result *out, uint64_t *handle_base) {
     if (n && !lengths) return fail(TRIAGE_E_ARG, "null lengths");
     return submit_impl(e, target_queue, offsets, lengths, bytes, meta, enqueue_ns, n, out, handle_base);
+}
+
+int32_t triage_prefetch(triage_engine *e, const uint64_t *offsets, const uint32_t *lengths, const uint8_t *bytes, const triage_meta *meta,
+                        const uint64_t *enqueue_ns, uint32_t n) {
+    return prefetch_impl(e, offsets, lengths, bytes, meta, enqueue_ns, n);
 }
 
 int32_t triage_submit_device_padded(triage_engine *e, const uint64_t *offsets_dev, const uint32_t *lengths_dev, const uint8_t *bytes_dev,

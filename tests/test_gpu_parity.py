@@ -335,6 +335,52 @@ def test_random_dictionaries_through_the_engine(seed):
         e.close()
 
 
+def test_prefetched_batches_give_the_same_results():
+    """triage_prefetch uploads batch k+1 while batch k is processed; the matching submit (same host arrays) must return
+    exactly what a plain submit returns — also when two batches are in flight, when a prefetch is never consumed, and
+    for the packed arena."""
+    batches = []
+    for seed, n, lo, hi in [(301, 6000, 64, 2000), (302, 9000, 0, 300), (303, 500, 2000, 9000)]:
+        off, data, meta, ts = co.generate(seed, n, lo, hi, edge=300)
+        batches.append((off, data, meta, ts))
+    ref, e = mq.Engine(device=0), mq.Engine(device=0)
+    try:
+        expected = []
+        for off, data, meta, ts in batches:
+            poff, plen, pbytes = ref.pack_padded(off, data)
+            res, base = ref.submit_padded(poff, plen, pbytes, meta, ts)
+            handles, _ = ref.drain(len(meta))
+            expected.append((res, (handles - base).astype(np.uint32)))
+        padded = [e.pack_padded(off, data) for off, data, _, _ in batches]
+        # ring of two: prefetch k+1 before submitting k
+        e.prefetch(padded[0][0], padded[0][1], padded[0][2], batches[0][2], batches[0][3])
+        for k, (off, data, meta, ts) in enumerate(batches):
+            if k + 1 < len(batches):
+                nx = padded[k + 1]
+                e.prefetch(nx[0], nx[1], nx[2], batches[k + 1][2], batches[k + 1][3])
+            poff, plen, pbytes = padded[k]
+            res, base = e.submit_padded(poff, plen, pbytes, meta, ts)
+            assert e.timings()["h2d_ms"] < 1.0   # no upload inside the call
+            handles, _ = e.drain(len(meta))
+            for f in res.dtype.names:
+                assert np.array_equal(res[f], expected[k][0][f]), (k, f)
+            assert np.array_equal((handles - base).astype(np.uint32), expected[k][1])
+        # a prefetch that is never consumed, then an unrelated plain submit, then the packed arena prefetched
+        e.prefetch(padded[1][0], padded[1][1], padded[1][2], batches[1][2], batches[1][3])
+        off, data, meta, ts = batches[2]
+        res, base = e.submit(off, data, meta, ts)
+        e.drain(len(meta))
+        assert all(np.array_equal(res[f], expected[2][0][f]) for f in res.dtype.names)
+        e.prefetch(off, None, data, meta, ts)
+        res, base = e.submit(off, data, meta, ts)
+        handles, _ = e.drain(len(meta))
+        assert all(np.array_equal(res[f], expected[2][0][f]) for f in res.dtype.names)
+        assert np.array_equal((handles - base).astype(np.uint32), expected[2][1])
+    finally:
+        ref.close()
+        e.close()
+
+
 def test_padded_edge_cases_vs_golden(golden_dir):
     cases = json.load(open(os.path.join(golden_dir, "edge_cases.json")))
     contents = [bytes.fromhex(e["content_hex"]) for e in cases]
