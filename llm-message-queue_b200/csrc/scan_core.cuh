@@ -320,9 +320,12 @@ TR_HD void lane_scan_padded(const Ctx &c, int32_t chunk, int32_t chunk_end, uint
 }
 
 // ------------------------------------------------------------------------------------------- long lanes ---
-// Padded arena, long per-lane chunks streamed through shared memory in windows: the lane keeps its automaton state,
-// word count and current message in registers from window to window, so the warm-up is paid once per chunk
-// (e.g. 16 bytes per 320) instead of once per window.
+// Padded arena, long per-lane chunks taken a window at a time: the lane keeps its automaton state, word count and
+// current message in registers from window to window, so the warm-up is paid once per chunk (16 bytes per 320) instead
+// of once per window.  scan_rows_kernel (kernels.cu) is built from long_begin / long_boundary / group16_sink / long_end
+// with its windows staged by the TMA, and reads the arena's partial last row with long_stream_n<1>; long_window and the
+// N-chain forms are the same walk in plain loops, kept for the host checks (tests/csrc) and measured as kernel variants
+// (several chains per lane bring nothing, the load/store unit is the limit).
 struct LongLane {
     uint32_t e, words, k, msg, head_msg, head_words;
     int32_t mend;
@@ -386,7 +389,8 @@ TR_COLD void replay_half(const Ctx &c, uint32_t wa, uint32_t wb, uint32_t e, uin
 }
 
 // N independent chains per lane, interleaved transition by transition: the walk of one chain is a dependent sequence
-// (table read -> index arithmetic -> table read), so N chains give the scheduler N reads in flight per lane.
+// (table read -> index arithmetic -> table read), so N chains give the scheduler N reads in flight per lane (N = 1 in
+// the shipped kernels).
 #define TR_STEPN(fld, k, EV)                                                                   \
     _Pragma("unroll") for (int ch = 0; ch < N; ch++) {                                         \
         L[ch].e = tr_next(c, q[ch].fld, L[ch].e, k); L[ch].words += tr_ws(c, L[ch].e); EV[ch] |= L[ch].e; }
