@@ -1001,58 +1001,95 @@ __global__ void __launch_bounds__(kOrderBlock) split_hist_kernel(Dig dig, const 
 }
 
 // exclusive scan in digit-major order over (digit, block); blockhist[b][d] <- global exclusive offset,
-// totals[d] <- offset of (d, block 0), totals[256] <- total kept
+// totals[d] <- offset of (d, block 0), totals[256] <- total kept.  One CTA; thread t owns histogram rows t, t + 1024, ...
+// and takes 16 digits of a row at a time (one 64-byte line, four 128-bit loads issued together): the 16 block-wide
+// scans of a digit group run on registers with warp shuffles.
 __global__ void __launch_bounds__(1024) split_scan_kernel(uint32_t *__restrict__ blockhist, uint32_t nblocks, uint32_t nb,
                                                           uint32_t *__restrict__ totals) {
-    __shared__ uint32_t part[1024];
-    __shared__ uint32_t warp_sum[32];
-    const uint32_t total = nblocks * nb;   // digits >= nb never occur; nblocks * 256 fits 32 bits (n < 2^32)
-    const uint32_t per = (total + 1023) / 1024;
-    const uint32_t lo = per * threadIdx.x < total ? per * threadIdx.x : total, hi = lo + per < total ? lo + per : total;
-    const uint32_t dgt0 = lo / nblocks, b0 = lo - dgt0 * nblocks;   // one division per thread, then counted up
-    uint32_t s = 0;
-    {
-        uint32_t dgt = dgt0, b = b0;
-        for (uint32_t j = lo; j < hi; j++) {
-            s += blockhist[b * 256 + dgt];
-            if (++b == nblocks) { b = 0; dgt++; }
-        }
-    }
-    // exclusive scan of the 1024 partial sums: warp shuffles, then the 32 warp totals
-    const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    uint32_t incl = s;
+    __shared__ uint32_t wt[32][17];     // per warp and digit of the group: warp total, then its exclusive prefix
+    __shared__ uint32_t group_tot[16];  // per digit of the group: total over the current chunk of 1024 rows
+    const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const unsigned full = 0xFFFFFFFFu;
+    uint32_t run = 0;                   // offset of (first digit of the group, block 0)
+    auto load_row = [&](uint32_t b, uint32_t d0, uint32_t (&v)[16]) {
+        if (b < nblocks) {
+            const uint4 *p = reinterpret_cast<const uint4 *>(blockhist + (size_t)b * 256 + d0);
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-        if ((int)lane >= d) incl += t;
-    }
-    if (lane == 31) warp_sum[wid] = incl;
-    __syncthreads();
-    if (wid == 0) {
-        uint32_t w = warp_sum[lane], wi = w;
+            for (int q = 0; q < 4; q++) { uint4 x = p[q]; v[4 * q] = x.x; v[4 * q + 1] = x.y; v[4 * q + 2] = x.z; v[4 * q + 3] = x.w; }
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            uint32_t t = __shfl_up_sync(0xFFFFFFFFu, wi, d);
-            if ((int)lane >= d) wi += t;
+            for (int j = 0; j < 16; j++) if (d0 + j >= nb) v[j] = 0;
+        } else {
+#pragma unroll
+            for (int j = 0; j < 16; j++) v[j] = 0;
         }
-        warp_sum[lane] = wi - w;   // exclusive
-    }
-    __syncthreads();
-    uint32_t run = warp_sum[wid] + incl - s;
-    part[threadIdx.x] = run + s;
-    {
-        uint32_t dgt = dgt0, b = b0;
-        for (uint32_t j = lo; j < hi; j++) {
-            const uint32_t idx = b * 256 + dgt;
-            const uint32_t c = blockhist[idx];
-            blockhist[idx] = run;
-            if (b == 0) totals[dgt] = run;
-            run += c;
-            if (++b == nblocks) { b = 0; dgt++; }
+    };
+    // block-wide exclusive scan of v[j] over the 1024 threads, for all 16 j; group_tot[j] <- sum over the threads
+    auto scan16 = [&](uint32_t (&v)[16], uint32_t (&ex)[16]) {
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+            uint32_t inc = v[j];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(full, inc, d); if ((int)lane >= d) inc += t; }
+            ex[j] = inc - v[j];
+            if (lane == 31) wt[wid][j] = inc;
         }
+        __syncthreads();
+        if (wid < 16) {   // warp j scans the 32 warp totals of digit j
+            uint32_t w = wt[lane][wid], inc = w;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(full, inc, d); if ((int)lane >= d) inc += t; }
+            wt[lane][wid] = inc - w;
+            if (lane == 31) group_tot[wid] = inc;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < 16; j++) ex[j] += wt[wid][j];
+    };
+    for (uint32_t d0 = 0; d0 < nb; d0 += 16) {
+        // pass 1 (only when the rows do not fit one chunk): totals of the group's digits over all rows
+        uint32_t dig_tot[16];
+        if (nblocks > 1024) {
+            uint32_t acc[16], ex[16];
+#pragma unroll
+            for (int j = 0; j < 16; j++) acc[j] = 0;
+            for (uint32_t b = tid; b < nblocks; b += 1024) {
+                uint32_t v[16];
+                load_row(b, d0, v);
+#pragma unroll
+                for (int j = 0; j < 16; j++) acc[j] += v[j];
+            }
+            scan16(acc, ex);
+#pragma unroll
+            for (int j = 0; j < 16; j++) dig_tot[j] = group_tot[j];
+            __syncthreads();
+        }
+        // pass 2: chunk by chunk, digit-major inside the group
+        uint32_t carry[16];
+#pragma unroll
+        for (int j = 0; j < 16; j++) carry[j] = 0;
+        for (uint32_t base = 0; base < nblocks; base += 1024) {
+            const uint32_t b = base + tid;
+            uint32_t v[16], ex[16];
+            load_row(b, d0, v);
+            scan16(v, ex);
+            if (nblocks <= 1024) {
+#pragma unroll
+                for (int j = 0; j < 16; j++) dig_tot[j] = group_tot[j];
+            }
+            uint32_t dbase = run;
+#pragma unroll
+            for (int j = 0; j < 16; j++) {
+                if (b < nblocks && d0 + j < nb) blockhist[(size_t)b * 256 + d0 + j] = dbase + carry[j] + ex[j];
+                if (b == 0 && d0 + j < nb) totals[d0 + j] = dbase;
+                carry[j] += group_tot[j];
+                dbase += dig_tot[j];
+            }
+            __syncthreads();   // group_tot / wt are reused by the next chunk
+        }
+#pragma unroll
+        for (int j = 0; j < 16; j++) run += dig_tot[j];
     }
-    __syncthreads();
-    for (uint32_t dgt = nb + threadIdx.x; dgt <= 256; dgt += 1024) totals[dgt] = part[1023];
+    for (uint32_t dgt = nb + tid; dgt <= 256; dgt += 1024) totals[dgt] = run;
 }
 
 struct ActPerm {
