@@ -350,6 +350,7 @@ __host__ __device__ inline PadSmem pad_layout(uint32_t n_states, uint32_t n_even
 size_t scan_padded_smem_bytes(const DeviceDfa &d, uint32_t nw) { return pad_layout(d.n_states, d.n_events, d.warm, nw, d.wide != 0).total; }
 // most warps per CTA whose staging buffers still fit next to the automaton (0: none)
 uint32_t pick_pad_warps(const DeviceDfa &d, size_t max_smem) {
+    if (d.wide && !getenv("TRIAGE_WIDE_24") && scan_padded_smem_bytes(d, 32) <= max_smem) return 32;
     for (uint32_t nw : {24u, 20u, 16u, 12u, 8u})
         if (scan_padded_smem_bytes(d, nw) <= max_smem) return nw;
     return 0;
@@ -514,7 +515,10 @@ static cudaError_t launch_scan_padded_variant(const ScanArgs &a, const DeviceDfa
 
 cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, int sm_count, cudaStream_t s) {
     if (a.ntiles == 0) return cudaSuccess;
-    if (d.wide) return launch_scan_padded_variant<24, true>(a, d, sm_count, s);
+    if (d.wide) {   // latency-bound on L1/L2 gathers: as many warps as the staging allows
+        if (nw >= 32) return launch_scan_padded_variant<32, true>(a, d, sm_count, s);
+        return launch_scan_padded_variant<24, true>(a, d, sm_count, s);
+    }
     switch (nw) {
         case 24: return launch_scan_padded_variant<24>(a, d, sm_count, s);
         case 20: return launch_scan_padded_variant<20>(a, d, sm_count, s);
