@@ -381,6 +381,32 @@ def test_prefetched_batches_give_the_same_results():
         e.close()
 
 
+def test_more_than_2_24_messages():
+    """Message indices beyond 2^24 do not fit the 24-bit field of the row-lane scan's deferred-event queue: those lanes
+    replay on the spot.  16.7 M empty messages followed by 3 000 keyword-dense ones: results and dequeue order of the
+    tail (and the counts of the whole batch) against the oracle."""
+    n_empty = (1 << 24) + 123
+    off_t, data_t, meta_t, _ = co.generate(77, 3000, 16, 700, edge=2000)
+    n = n_empty + len(meta_t)
+    off = np.zeros(n + 1, dtype=np.uint64)
+    off[n_empty:] = off_t
+    meta = np.zeros(n, dtype=mq.META_DTYPE)
+    meta["user_priority"] = 0
+    meta[n_empty:] = meta_t
+    ts = (np.arange(n, dtype=np.uint64) * np.uint64(7)) + np.uint64(10**15)
+    exp, order = co.pipeline(co.Dict(), off, data_t, meta, ts, nthreads=os.cpu_count() or 4)
+    e = mq.Engine(device=0)
+    try:
+        poff, plen, pbytes = e.pack_padded(off, data_t)
+        assert int(poff[-1]) >= 16 * n_empty
+        res, base = e.submit_padded(poff, plen, pbytes, meta, ts)
+        _assert_same(res, exp, FIELDS + ("accepted", "admit"), ctx="n > 2^24")
+        handles, _ = e.drain(n)
+        assert np.array_equal((handles - base).astype(np.uint32), order)
+    finally:
+        e.close()
+
+
 def test_padded_edge_cases_vs_golden(golden_dir):
     cases = json.load(open(os.path.join(golden_dir, "edge_cases.json")))
     contents = [bytes.fromhex(e["content_hex"]) for e in cases]
