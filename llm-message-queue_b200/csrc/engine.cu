@@ -289,8 +289,9 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
         ScanArgs probe{bytes, offsets, total, n, nullptr, nullptr, 0, 0};
         use_rows = scan_rows_usable(probe);
     }
+    const uint32_t row_bytes = use_rows ? scan_rows_lane_bytes(total, e->row_warps, e->sm_count) : 0;
     const uint32_t tile_bytes = !padded ? e->geom.tile
-                              : use_rows ? scan_rows_super_bytes(e->row_warps) : kPadMiniTile;
+                              : use_rows ? scan_rows_super_bytes(row_bytes) : kPadMiniTile;
     const uint32_t ntiles = (uint32_t)((total + tile_bytes - 1) / tile_bytes);
     const uint32_t nblocks = (n + kOrderBlock - 1) / kOrderBlock;
     CU(e->d_counters.ensure((size_t)n * CNT_STRIDE));
@@ -309,7 +310,7 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     CU(launch_prepare(sa, e->d_small.p, 32 + 8 * 256, e->sm_count, s)); launches++;   // tile index + zeroed counters and scratch
     if (ntiles) {
         CU(cudaEventRecord(e->ev[1], s));
-        if (use_rows) CU(launch_scan_rows(sa, e->ddfa, e->row_warps, e->sm_count, s));
+        if (use_rows) CU(launch_scan_rows(sa, e->ddfa, e->row_warps, row_bytes, e->d_small.p + 20, e->sm_count, s));   // d_small[20]: spare word, zeroed by prepare
         else if (padded) CU(launch_scan_padded(sa, e->ddfa, e->pad_warps, e->sm_count, s));
         else CU(launch_scan(sa, e->ddfa, e->geom, e->sm_count, s));
         launches++;

@@ -538,10 +538,19 @@ cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, uint32_t n
 // would otherwise issue itself (cp.async) cost as much as the warm-up lookups they save.  The automaton state, word
 // count and current message stay in registers along the row.  The last, partial row of the arena is read straight from
 // global memory by the lane that owns it.
-// row bytes and window bytes (28 warps x 64-byte windows and 32 x 48 were measured slower than 24 x 80: the 16-byte reads
-// of a 64-byte-pitch buffer collide on banks, and 64 registers per thread cost more than 8 more warps bring)
-__host__ __device__ constexpr uint32_t row_win(uint32_t) { return 80u; }
-__host__ __device__ constexpr uint32_t row_lane(uint32_t) { return 320u; }
+// Window: 80 bytes (28 warps x 64-byte windows and 32 x 48 were measured slower than 24 x 80: the 16-byte reads of a
+// 64-byte-pitch buffer collide on banks, and 64 registers per thread cost more than 8 more warps bring).  Row: 1280 bytes
+// for big arenas (warm-up 1.25 %, tile bookkeeping once per 40 KB: 0.955 ms on the bench config against 1.03 with 320),
+// 320 bytes when the arena would not give every warp a couple of 40 KB tiles.
+constexpr uint32_t kRowWin = 80, kRowLaneLong = 1280, kRowLaneShort = 320;
+__host__ __device__ constexpr uint32_t row_win(uint32_t) { return kRowWin; }
+uint32_t scan_rows_lane_bytes(uint64_t total, uint32_t nw, int sm_count) {
+    if (const char *v = getenv("TRIAGE_ROW_BYTES")) {   // test / tuning knob: force one of the two row lengths
+        const uint32_t want = (uint32_t)atoi(v);
+        if ((want == kRowLaneLong || want == kRowLaneShort) && total >= want) return want;
+    }
+    return total >= 2ull * 32 * kRowLaneLong * nw * (uint32_t)sm_count ? kRowLaneLong : kRowLaneShort;
+}
 constexpr uint32_t kRowListCap = 34;     // message starts of a tile kept in shared memory (lane, lane + 32)
 constexpr uint32_t kRowQueueCap = 24;    // deferred event replays per warp (12 bytes each)
 constexpr uint32_t kRowQueueFlush = 10;  // replayed by the whole warp once this many are waiting
@@ -601,7 +610,7 @@ __host__ __device__ inline RowSmem row_layout(uint32_t n_states, uint32_t n_even
     return L;
 }
 size_t scan_rows_smem_bytes(const DeviceDfa &d, uint32_t nw) { return row_layout(d.n_states, d.n_events, nw).total; }
-uint32_t scan_rows_super_bytes(uint32_t nw) { return 32 * row_lane(nw); }
+uint32_t scan_rows_super_bytes(uint32_t lane_bytes) { return 32 * lane_bytes; }
 uint32_t pick_row_warps(const DeviceDfa &d, size_t max_smem) {
     if (d.wide || d.warm != 16 || d.reset_pad < 0) return 0;
     if (const char *w = getenv("TRIAGE_ROW_WARPS")) {   // tuning knob
@@ -613,11 +622,12 @@ uint32_t pick_row_warps(const DeviceDfa &d, size_t max_smem) {
     return 0;
 }
 
-template <int NW>
+template <int NW, int LANE>
 __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, DeviceDfa d, const __grid_constant__ CUtensorMap tm_win,
-                                                              const __grid_constant__ CUtensorMap tm_warm, uint32_t nrows_full) {
+                                                              const __grid_constant__ CUtensorMap tm_warm, uint32_t nrows_full,
+                                                              uint32_t *__restrict__ tile_counter) {
     extern __shared__ __align__(128) uint8_t smem[];
-    constexpr int32_t CL = (int32_t)row_lane(NW), WIN = (int32_t)row_win(NW), NWIN = CL / WIN;
+    constexpr int32_t CL = LANE, WIN = (int32_t)row_win(NW), NWIN = CL / WIN;
     constexpr uint32_t SUPER = 32 * CL;
     const RowSmem L = row_layout(d.n_states, d.n_events, NW);
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -647,23 +657,29 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
     }
     __syncthreads();   // the only CTA-wide barrier
 
-    const uint32_t stride = gridDim.x * NW;
+    // Tiles are handed out dynamically: the first one per warp by position, every further one from a global counter
+    // (zeroed by prepare_kernel), fetched two tiles ahead so that the next tile's message list and first window can be
+    // prefetched while the current one is walked.
+    const uint32_t nwarps = gridDim.x * NW;
     const uint32_t t0 = blockIdx.x * NW + warp;
     if (t0 >= a.ntiles) return;
-    const uint32_t nmine = (a.ntiles - t0 + stride - 1) / stride;
-    const uint32_t nwin_total = nmine * NWIN;
+    auto grab = [&]() {
+        uint32_t v = 0;
+        if (lane == 0) v = atomicAdd(tile_counter, 1u) + nwarps;
+        return __shfl_sync(0xFFFFFFFFu, v, 0);
+    };
 
-    // window g of this warp: tile t0 + (g / NWIN) * stride, window g % NWIN -> buffer g & 1 (one lane issues)
-    auto issue = [&](uint32_t g) {
-        const uint32_t sk = g / NWIN, w = g % NWIN, buf = g & 1;
-        const int32_t row0 = (int32_t)((t0 + sk * stride) * 32u);
+    // window w of tile `tile` -> buffer buf (one lane issues)
+    auto issue = [&](uint32_t tile, uint32_t w, uint32_t buf) {
+        const int32_t row0 = (int32_t)(tile * 32u);
         mbar_expect_tx(&bars[buf], 32 * WIN + (w == 0 ? 512u : 0u));
         tma_load_2d(wbase + buf * (32 * WIN), &tm_win, (int32_t)(w * WIN), row0, &bars[buf]);
         if (w == 0) tma_load_2d(warm_buf, &tm_warm, CL - 16, row0 - 1, &bars[buf]);
     };
 
+    uint32_t t = t0, t_nxt = grab(), t_nn = grab();
     uint32_t first_cur = a.tile_first[t0], last_cur = a.tile_first[t0 + 1];
-    if (lane == 0) issue(0);
+    if (lane == 0) issue(t0, 0, 0);
     uint64_t ts = (uint64_t)t0 * SUPER;
     {
         uint32_t cnt = last_cur - first_cur + 2;
@@ -673,7 +689,7 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
         }
     }
     uint32_t first_nxt = 0, last_nxt = 0;
-    if (nmine > 1) { first_nxt = a.tile_first[t0 + stride]; last_nxt = a.tile_first[t0 + stride + 1]; }
+    if (t_nxt < a.ntiles) { first_nxt = a.tile_first[t_nxt]; last_nxt = a.tile_first[t_nxt + 1]; }
     __syncwarp();
 
     LaneCtx c;
@@ -683,11 +699,11 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
     c.head_pad4 = c.tail_pad4 = 0;
     c.tbl_s = smem_u32(tbl);
     const int32_t chunk = (int32_t)(lane * CL);
-    const uint64_t ts_step = (uint64_t)stride * SUPER;
-    uint32_t t = t0, g = 0;
+    uint32_t g = 0;
 
-    for (uint32_t sk = 0; sk < nmine; sk++, t += stride, ts += ts_step) {
-        const bool has_next = sk + 1 < nmine;
+    for (uint32_t sk = 0; t < a.ntiles; sk++) {
+        const bool has_next = t_nxt < a.ntiles;
+        ts = (uint64_t)t * SUPER;
         uint64_t n0 = 0, n1 = 0;
         uint32_t cnt_nxt = 0, first_nn = 0, last_nn = 0;
         if (has_next) {
@@ -696,7 +712,7 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
                 if (lane < cnt_nxt) n0 = a.offsets[first_nxt + lane];
                 if (lane + 32 < cnt_nxt) n1 = a.offsets[first_nxt + lane + 32];
             }
-            if (sk + 2 < nmine) { first_nn = a.tile_first[t + 2 * stride]; last_nn = a.tile_first[t + 2 * stride + 1]; }
+            if (t_nn < a.ntiles) { first_nn = a.tile_first[t_nn]; last_nn = a.tile_first[t_nn + 1]; }
         }
         const uint32_t cnt_cur = last_cur - first_cur + 2;
         const int32_t *lst = list_base + (sk & 1) * kRowListCap;
@@ -721,7 +737,10 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
         }
 #pragma unroll 1
         for (int32_t w = 0; w < NWIN; w++, g++) {
-            if (lane == 0 && g + 1 < nwin_total) issue(g + 1);
+            if (lane == 0) {
+                if (w + 1 < NWIN) issue(t, (uint32_t)w + 1, (g + 1) & 1);
+                else if (has_next) issue(t_nxt, 0, (g + 1) & 1);
+            }
             mbar_wait(&bars[g & 1], (g >> 1) & 1);
             if (full_row) {
                 if (w == 0) long_begin(c, ll, ll.k, row == 0, warm_buf + lane * 16);
@@ -770,12 +789,14 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
         }
         if (has_next && cnt_nxt <= kRowListCap) {
             int32_t *ln = list_base + ((sk + 1) & 1) * kRowListCap;
-            const uint64_t tsn = ts + ts_step;
+            const uint64_t tsn = (uint64_t)t_nxt * SUPER;
             if (lane < cnt_nxt) ln[lane] = rel_clamp(n0, tsn);
             if (lane + 32 < cnt_nxt) ln[lane + 32] = rel_clamp(n1, tsn);
         }
         first_cur = first_nxt; last_cur = last_nxt;
         first_nxt = first_nn; last_nxt = last_nn;
+        t = t_nxt; t_nxt = t_nn;
+        t_nn = t_nxt < a.ntiles ? grab() : t_nxt;   // warp-uniform: no more fetches once the counter has run past the end
         __syncwarp();
     }
     queue.flush(c, lane, true);
@@ -795,28 +816,30 @@ static EncodeTiledFn encode_tiled_fn() {
     return fn;
 }
 
-template <int NW>
+template <int NW, int LANE>
 static cudaError_t launch_scan_rows_variant(const ScanArgs &a, const DeviceDfa &d, const CUtensorMap &tw, const CUtensorMap &tm,
-                                            uint32_t nrows_full, int sm_count, cudaStream_t s) {
+                                            uint32_t nrows_full, uint32_t *tile_counter, int sm_count, cudaStream_t s) {
     size_t smem = scan_rows_smem_bytes(d, NW);
     static SmemConfigured configured;
-    if (cudaError_t e = ensure_dynamic_smem(scan_rows_kernel<NW>, smem, configured)) return e;
+    if (cudaError_t e = ensure_dynamic_smem(scan_rows_kernel<NW, LANE>, smem, configured)) return e;
     uint32_t need = (a.ntiles + NW - 1) / NW;
     uint32_t grid = need < (uint32_t)sm_count ? need : (uint32_t)sm_count;
-    scan_rows_kernel<NW><<<grid, NW * 32, smem, s>>>(a, d, tw, tm, nrows_full);
+    scan_rows_kernel<NW, LANE><<<grid, NW * 32, smem, s>>>(a, d, tw, tm, nrows_full, tile_counter);
     return cudaGetLastError();
 }
 
 // needs at least one full row and a 16-byte aligned arena; the caller falls back to the mini-tile kernel otherwise
 bool scan_rows_usable(const ScanArgs &a) {
-    return a.total >= row_lane(0) && (reinterpret_cast<uintptr_t>(a.bytes) & 15u) == 0 && encode_tiled_fn() != nullptr;
+    return a.total >= kRowLaneShort && (reinterpret_cast<uintptr_t>(a.bytes) & 15u) == 0 && encode_tiled_fn() != nullptr;
 }
 
-cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, int sm_count, cudaStream_t s) {
+cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, uint32_t lane_bytes, uint32_t *tile_counter, int sm_count,
+                             cudaStream_t s) {
     if (a.ntiles == 0) return cudaSuccess;
     EncodeTiledFn enc = encode_tiled_fn();
     if (!enc) return cudaErrorNotSupported;
-    const uint32_t lane_bytes = row_lane(nw), win = row_win(nw);
+    const uint32_t win = row_win(nw);
+    if (lane_bytes != kRowLaneLong && lane_bytes != kRowLaneShort) return cudaErrorInvalidValue;
     const uint64_t nrows_full = a.total / lane_bytes;
     CUtensorMap tw, tm;
     const cuuint64_t dims[2] = {lane_bytes, nrows_full};
@@ -828,10 +851,15 @@ cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw,
         enc(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, base, dims, strides, box_m, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
             CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
         return cudaErrorInvalidValue;
+    const bool lng = lane_bytes == kRowLaneLong;
+    const uint32_t nrows = (uint32_t)nrows_full;
     switch (nw) {
-        case 24: return launch_scan_rows_variant<24>(a, d, tw, tm, (uint32_t)nrows_full, sm_count, s);
-        case 20: return launch_scan_rows_variant<20>(a, d, tw, tm, (uint32_t)nrows_full, sm_count, s);
-        case 16: return launch_scan_rows_variant<16>(a, d, tw, tm, (uint32_t)nrows_full, sm_count, s);
+        case 24: return lng ? launch_scan_rows_variant<24, kRowLaneLong>(a, d, tw, tm, nrows, tile_counter, sm_count, s)
+                            : launch_scan_rows_variant<24, kRowLaneShort>(a, d, tw, tm, nrows, tile_counter, sm_count, s);
+        case 20: return lng ? launch_scan_rows_variant<20, kRowLaneLong>(a, d, tw, tm, nrows, tile_counter, sm_count, s)
+                            : launch_scan_rows_variant<20, kRowLaneShort>(a, d, tw, tm, nrows, tile_counter, sm_count, s);
+        case 16: return lng ? launch_scan_rows_variant<16, kRowLaneLong>(a, d, tw, tm, nrows, tile_counter, sm_count, s)
+                            : launch_scan_rows_variant<16, kRowLaneShort>(a, d, tw, tm, nrows, tile_counter, sm_count, s);
         default: return cudaErrorInvalidValue;
     }
 }

@@ -51,10 +51,13 @@ cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, uint32_t n
 
 // row-lane variant of the padded scan (dense table, 16-byte warm-up): 320-byte rows fed by 2-D TMA tile copies
 size_t scan_rows_smem_bytes(const DeviceDfa &d, uint32_t nw);
-uint32_t scan_rows_super_bytes(uint32_t nw);
+uint32_t scan_rows_lane_bytes(uint64_t total, uint32_t nw, int sm_count);   // row length for an arena of that size (1280 or 320)
+uint32_t scan_rows_super_bytes(uint32_t lane_bytes);
 uint32_t pick_row_warps(const DeviceDfa &d, size_t max_smem);   // 0: this automaton cannot use it
 bool scan_rows_usable(const ScanArgs &a);
-cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, int sm_count, cudaStream_t s);
+// tile_counter: one zeroed device word (tiles beyond the first per warp are handed out through it)
+cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, uint32_t lane_bytes, uint32_t *tile_counter, int sm_count,
+                             cudaStream_t s);
 
 // sequential exact recount of the messages the scan flagged (self-overlapping keywords); `exact` points at global memory
 cudaError_t launch_fixup(const uint8_t *bytes, const uint64_t *offsets, const uint32_t *lengths, uint32_t n, const DeviceDfa &exact,

@@ -251,17 +251,21 @@ def test_padded_arena_path_vs_c_oracle(seed, n, lo, hi, edge, mix):
         e.close()
 
 
-@pytest.mark.parametrize("rows", ["1", "0"])
+@pytest.mark.parametrize("rows", ["1", "0", "1280", "320"])
 def test_padded_arena_sizes_around_row_and_tile_boundaries(rows, monkeypatch):
     """The padded arena is scanned as 320-byte rows, 32 rows per tile (2-D TMA), with the partial last row read directly;
     arenas shorter than one row go to the mini-tile kernel.  Sweep totals across those boundaries, with both kernels
     (TRIAGE_ROWS=0 keeps to the mini-tile kernel): every result must equal the oracle's."""
-    monkeypatch.setenv("TRIAGE_ROWS", rows)
+    if rows in ("1280", "320"):   # force the long / short row length of the row-lane kernel whatever the arena size
+        monkeypatch.setenv("TRIAGE_ROW_BYTES", rows)
+    else:
+        monkeypatch.setenv("TRIAGE_ROWS", rows)
     e = mq.Engine(device=0)
     try:
         seen = set()
         for seed, n, lo, hi in [(1, 1, 1, 15), (2, 1, 290, 303), (3, 2, 140, 160), (4, 3, 100, 110), (5, 40, 200, 300), (6, 33, 300, 304),
-                                (7, 64, 150, 170), (8, 65, 304, 320), (9, 700, 0, 30), (10, 31, 305, 319), (11, 257, 1, 90), (12, 5, 2000, 2100)]:
+                                (7, 64, 150, 170), (8, 65, 304, 320), (9, 700, 0, 30), (10, 31, 305, 319), (11, 257, 1, 90), (12, 5, 2000, 2100),
+                                (13, 900, 100, 1500), (14, 41, 1200, 1290), (15, 3000, 16, 400)]:
             off, data, meta, ts = co.generate(seed, n, lo, hi, edge=1500)
             exp, order = co.pipeline(co.Dict(), off, data, meta, ts, nthreads=4)
             poff, plen, pbytes = e.pack_padded(off, data)
