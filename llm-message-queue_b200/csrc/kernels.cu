@@ -539,17 +539,23 @@ cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, uint32_t n
 // count and current message stay in registers along the row.  The last, partial row of the arena is read straight from
 // global memory by the lane that owns it.
 // Window: 80 bytes (28 warps x 64-byte windows and 32 x 48 were measured slower than 24 x 80: the 16-byte reads of a
-// 64-byte-pitch buffer collide on banks, and 64 registers per thread cost more than 8 more warps bring).  Row: 1280 bytes
-// for big arenas (warm-up 1.25 %, tile bookkeeping once per 40 KB: 0.955 ms on the bench config against 1.03 with 320),
-// 320 bytes when the arena would not give every warp a couple of 40 KB tiles.
-constexpr uint32_t kRowWin = 80, kRowLaneLong = 1280, kRowLaneShort = 320;
+// 64-byte-pitch buffer collide on banks, and 64 registers per thread cost more than 8 more warps bring).  Row: 1280, 640
+// or 320 bytes by arena size (longer rows: less warm-up, tile bookkeeping once per 40 / 20 / 10 KB).
+constexpr uint32_t kRowWin = 80, kRowLaneLong = 1280, kRowLaneMid = 640, kRowLaneShort = 320;
 __host__ __device__ constexpr uint32_t row_win(uint32_t) { return kRowWin; }
+// Longest row that still leaves every warp several tiles: tiles are handed out dynamically, so the kernel's tail is
+// half a tile per warp on average (1280-byte rows: 40 KB tiles, 0.955 ms on the 2.3 GB bench arena; 640: 0.98; 320: 1.03).
 uint32_t scan_rows_lane_bytes(uint64_t total, uint32_t nw, int sm_count) {
-    if (const char *v = getenv("TRIAGE_ROW_BYTES")) {   // test / tuning knob: force one of the two row lengths
+    if (const char *v = getenv("TRIAGE_ROW_BYTES")) {   // test / tuning knob: force a row length
         const uint32_t want = (uint32_t)atoi(v);
-        if ((want == kRowLaneLong || want == kRowLaneShort) && total >= want) return want;
+        if ((want == kRowLaneLong || want == kRowLaneMid || want == kRowLaneShort) && total >= want) return want;
     }
-    return total >= 2ull * 32 * kRowLaneLong * nw * (uint32_t)sm_count ? kRowLaneLong : kRowLaneShort;
+    const uint64_t warp_rows = (uint64_t)nw * (uint32_t)sm_count * 32;   // rows one round of tiles covers
+    // measured on one box: 2.29 GB (16 tiles of 40 KB per warp) 1280 -> 0.955 ms, 640 -> 0.98, 320 -> 1.03; 1.69 GB mixed
+    // lengths 0.783 / 0.778 / 0.810; 1.34 GB of 32-128 KB payloads 0.680 / 0.608 / 0.601; 575 MB 2.39 / 2.43 / 2.31 TB/s
+    if (total >= 12 * warp_rows * kRowLaneLong) return kRowLaneLong;
+    if (total >= 3 * warp_rows * kRowLaneMid) return kRowLaneMid;
+    return kRowLaneShort;
 }
 constexpr uint32_t kRowListCap = 34;     // message starts of a tile kept in shared memory (lane, lane + 32)
 constexpr uint32_t kRowQueueCap = 24;    // deferred event replays per warp (12 bytes each)
@@ -753,7 +759,7 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
                 }
             }
             __syncwarp();   // every lane is done with this buffer before lane 0 refills it (two windows on)
-            queue.flush(c, lane, false);
+            if ((w & 3) == 3) queue.flush(c, lane, false);   // the check is a shared-memory load: every fourth window
         }
         if (tail_row) {
             const uint8_t *src = a.bytes + row_start;
@@ -839,7 +845,7 @@ cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw,
     EncodeTiledFn enc = encode_tiled_fn();
     if (!enc) return cudaErrorNotSupported;
     const uint32_t win = row_win(nw);
-    if (lane_bytes != kRowLaneLong && lane_bytes != kRowLaneShort) return cudaErrorInvalidValue;
+    if (lane_bytes != kRowLaneLong && lane_bytes != kRowLaneMid && lane_bytes != kRowLaneShort) return cudaErrorInvalidValue;
     const uint64_t nrows_full = a.total / lane_bytes;
     CUtensorMap tw, tm;
     const cuuint64_t dims[2] = {lane_bytes, nrows_full};
@@ -851,17 +857,19 @@ cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw,
         enc(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, base, dims, strides, box_m, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
             CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
         return cudaErrorInvalidValue;
-    const bool lng = lane_bytes == kRowLaneLong;
     const uint32_t nrows = (uint32_t)nrows_full;
+#define TRIAGE_ROWS_CASE(NW_)                                                                                                        \
+    case NW_:                                                                                                                        \
+        if (lane_bytes == kRowLaneLong) return launch_scan_rows_variant<NW_, kRowLaneLong>(a, d, tw, tm, nrows, tile_counter, sm_count, s); \
+        if (lane_bytes == kRowLaneMid) return launch_scan_rows_variant<NW_, kRowLaneMid>(a, d, tw, tm, nrows, tile_counter, sm_count, s);   \
+        return launch_scan_rows_variant<NW_, kRowLaneShort>(a, d, tw, tm, nrows, tile_counter, sm_count, s);
     switch (nw) {
-        case 24: return lng ? launch_scan_rows_variant<24, kRowLaneLong>(a, d, tw, tm, nrows, tile_counter, sm_count, s)
-                            : launch_scan_rows_variant<24, kRowLaneShort>(a, d, tw, tm, nrows, tile_counter, sm_count, s);
-        case 20: return lng ? launch_scan_rows_variant<20, kRowLaneLong>(a, d, tw, tm, nrows, tile_counter, sm_count, s)
-                            : launch_scan_rows_variant<20, kRowLaneShort>(a, d, tw, tm, nrows, tile_counter, sm_count, s);
-        case 16: return lng ? launch_scan_rows_variant<16, kRowLaneLong>(a, d, tw, tm, nrows, tile_counter, sm_count, s)
-                            : launch_scan_rows_variant<16, kRowLaneShort>(a, d, tw, tm, nrows, tile_counter, sm_count, s);
+        TRIAGE_ROWS_CASE(24)
+        TRIAGE_ROWS_CASE(20)
+        TRIAGE_ROWS_CASE(16)
         default: return cudaErrorInvalidValue;
     }
+#undef TRIAGE_ROWS_CASE
 }
 
 // ---------------------------------------------------------------------------------- fix-up --

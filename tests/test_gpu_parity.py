@@ -251,12 +251,12 @@ def test_padded_arena_path_vs_c_oracle(seed, n, lo, hi, edge, mix):
         e.close()
 
 
-@pytest.mark.parametrize("rows", ["1", "0", "1280", "320"])
+@pytest.mark.parametrize("rows", ["1", "0", "1280", "640", "320"])
 def test_padded_arena_sizes_around_row_and_tile_boundaries(rows, monkeypatch):
     """The padded arena is scanned as 320-byte rows, 32 rows per tile (2-D TMA), with the partial last row read directly;
     arenas shorter than one row go to the mini-tile kernel.  Sweep totals across those boundaries, with both kernels
     (TRIAGE_ROWS=0 keeps to the mini-tile kernel): every result must equal the oracle's."""
-    if rows in ("1280", "320"):   # force the long / short row length of the row-lane kernel whatever the arena size
+    if rows in ("1280", "640", "320"):   # force the long / short row length of the row-lane kernel whatever the arena size
         monkeypatch.setenv("TRIAGE_ROW_BYTES", rows)
     else:
         monkeypatch.setenv("TRIAGE_ROWS", rows)
