@@ -530,10 +530,10 @@ cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, uint32_t n
 }
 
 // ---------------------------------------------------------------------------------- row lanes --
-// Padded arena, dense table, long lanes fed by the TMA: the arena is viewed as a matrix of 320-byte rows, lane l
+// Padded arena, dense table, long lanes fed by the TMA: the arena is viewed as a matrix of LANE-byte rows, lane l
 // of a warp owns row 32 * tile + l, and ONE tensor copy per warp and window brings the next 80-byte window of all 32
-// rows into shared memory (box 80 x 32), a second small one (box 16 x 32 at column 304 of the rows before) the warm-up
-// bytes of a new tile.  The load path issues no load/store-unit instructions at all - on this part the scan is bound by
+// rows into shared memory (box 80 x 32), a second small one (box 16 x 32 at column LANE - 16 of the rows before) the
+// warm-up bytes of a new tile.  The load path issues no load/store-unit instructions at all - on this part the scan is bound by
 // the rate at which the SM accepts shared-memory loads (profiles/microbench/lds_chain.cu), so the staging copies a lane
 // would otherwise issue itself (cp.async) cost as much as the warm-up lookups they save.  The automaton state, word
 // count and current message stay in registers along the row.  The last, partial row of the arena is read straight from
