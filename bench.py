@@ -314,10 +314,6 @@ def main():
             e2e_tm = eng.timings()
             eng.drain(n)          # empty the level queues (host bookkeeping, outside the timed call)
         serial_s = sum(dts) / len(dts)
-        if os.environ.get("BENCH_DEBUG"):
-            for i in (0, 1, 0, 1):
-                t0 = time.perf_counter(); submit(i); dt = time.perf_counter() - t0
-                print(f"[debug] serial submit ring[{i}] {1000*dt:.2f} ms h2d {eng.timings()['h2d_ms']:.2f}", file=sys.stderr); eng.drain(n)
         breakdown = {"h2d": e2e_tm["h2d_ms"], "kernels": e2e_tm["total_ms"], "d2h": e2e_tm["d2h_ms"],
                      "host_queue_insert": 1000 * dts[-1] - e2e_tm["h2d_ms"] - e2e_tm["total_ms"] - e2e_tm["d2h_ms"]}
         # (2) K batches through the ring from a cold start, wall clock over the whole loop (queue drains included, so nothing
@@ -332,9 +328,12 @@ def main():
             submit(k % 2)
             eng.drain(n)
         ring_s = (time.perf_counter() - t0) / e2e_steps
-        if os.environ.get("BENCH_DEBUG"):
-            same = np.array_equal(h_res["label"], d_res.cpu().numpy().view(mq.RESULT_DTYPE).reshape(n)["label"])
-            print(f"[debug] ring: {1000 * ring_s:.2f} ms per batch over {e2e_steps}, labels equal the device run: {bool(same)}", file=sys.stderr)
+        if args.check:   # the ring's results are the device-resident run's results
+            dev_res = d_res.cpu().numpy().view(mq.RESULT_DTYPE).reshape(n)
+            for f in ("label", "reason", "words", "sentiment", "question", "accepted"):
+                if not np.array_equal(h_res[f], dev_res[f]):
+                    raise SystemExit(f"[check rank {rank}] e2e ring: field {f} differs from the device-resident run")
+            print(f"[check rank {rank}] e2e ring results equal the device-resident run", file=sys.stderr)
         tt = torch.tensor([ring_s, serial_s], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
