@@ -174,7 +174,9 @@ int32_t triage_submit_device(triage_engine *e, const uint64_t *offsets_dev, cons
  *    HBM or cannot afford the allocator's implicit synchronisation.  Limits: at most 65536 messages and 256 MiB of arena
  *    per call (larger -> TRIAGE_E_ARG), the dictionary must already be committed with triage_dict_commit, and calls that
  *    overlap on one GPU race on the shared array (serialise them).  The first call on a device looks the array up with
- *    cudaGetSymbolAddress; make it before any stream capture.                                                        */
+ *    cudaGetSymbolAddress; make it before any stream capture.  It takes the packed arena and runs the packed-arena scan
+ *    (scan_kernel), which is about 2.5x slower per byte than the row kernel behind the padded entry points; dictionaries
+ *    that need the wide table format are refused (TRIAGE_E_ARG).                                                      */
 int32_t triage_submit_device_static(triage_engine *e, const uint64_t *offsets_dev, const uint8_t *bytes_dev,
                                     uint64_t total_bytes, const triage_meta *meta_dev,
                                     const uint64_t *enqueue_ns_dev, uint32_t n, triage_result *results_dev,
@@ -205,6 +207,10 @@ typedef struct {
     uint32_t launches;                              /* kernels launched by the last submit */
     uint32_t order_passes;                          /* radix digit passes executed */
     uint64_t scan_bytes;                            /* algorithmic bytes of the scan */
+    uint32_t scan_variant;                          /* kernel that ran: 1 packed-arena tiles, 2 padded mini-tiles, 3 row lanes (2-D TMA), 4 wide table */
+    uint32_t scan_row_bytes;                        /* row length of the row-lane scan (1280 / 640 / 320), else 0 */
+    uint32_t scan_warps;                            /* warps per CTA of that kernel */
+    uint32_t reserved;
 } triage_timings;
 int32_t triage_last_timings(triage_engine *e, triage_timings *t);
 /* CUDA events on the engine's own stream (torch.cuda.Event cannot see it): slots 0..3 */

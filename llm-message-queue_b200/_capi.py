@@ -36,7 +36,12 @@ class QStats(C.Structure):
 class Timings(C.Structure):
     _fields_ = [("scan_ms", C.c_float), ("finalize_ms", C.c_float), ("order_ms", C.c_float), ("total_ms", C.c_float),
                 ("h2d_ms", C.c_float), ("d2h_ms", C.c_float), ("launches", C.c_uint32), ("order_passes", C.c_uint32),
-                ("scan_bytes", C.c_uint64)]
+                ("scan_bytes", C.c_uint64), ("scan_variant", C.c_uint32), ("scan_row_bytes", C.c_uint32), ("scan_warps", C.c_uint32),
+                ("reserved", C.c_uint32)]
+
+SCAN_VARIANTS = {0: "none", 1: "scan_kernel (packed arena, CTA-wide tiles)", 2: "scan_padded_kernel (padded arena, mini-tiles)",
+                 3: "scan_rows_kernel (padded arena, row lanes, 2-D TMA windows of 80 B x 32 rows)",
+                 4: "scan_padded_kernel<wide> (class map in shared memory, transitions in L2)"}
 
 
 class TriageError(RuntimeError):

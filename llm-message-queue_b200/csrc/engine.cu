@@ -111,10 +111,35 @@ struct PrefetchSlot {
     const void *k_offsets = nullptr, *k_bytes = nullptr, *k_meta = nullptr, *k_lengths = nullptr, *k_ts = nullptr;
     uint32_t n = 0;
     uint64_t total = 0;
-    cudaEvent_t ready = nullptr;
+    cudaEvent_t ready = nullptr;     // behind the last copy
+    cudaEvent_t small_ready = nullptr;   // behind offsets / lengths / meta / times (copied first)
+    cudaEvent_t t_begin = nullptr, t_end = nullptr;   // timing events around the copies (h2d_ms)
+    std::vector<cudaEvent_t> chunk_ev;   // behind the copy of arena chunk i (kUploadChunk bytes each)
+    uint32_t n_chunks = 0;
     bool valid = false;
     uint64_t seq = 0;                // age: the older valid slot is the one a new prefetch may reuse last
 };
+
+// The arena travels in chunks so that the scan of chunk i runs while chunk i+1 is still on the PCIe link; the size is a
+// multiple of every tile size of the row-lane scan (32 rows of 320 / 640 / 1280 bytes).
+constexpr uint64_t kUploadChunk = 800ull * 40960ull;   // 31.25 MiB
+
+// what run_device needs to know about an upload that is still in flight (nullptr: everything is resident)
+struct UploadPlan {
+    const cudaEvent_t *chunk_ev;
+    uint32_t n_chunks;
+    cudaEvent_t small_ready, all_ready;
+};
+
+double trace_now_ms() {
+    static const auto t0 = std::chrono::steady_clock::now();
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+}
+bool trace_on() {
+    static const bool on = getenv("TRIAGE_TRACE") != nullptr;
+    return on;
+}
+#define TRACE(...) do { if (trace_on()) { fprintf(stderr, "[triage %9.3f ms] ", trace_now_ms()); fprintf(stderr, __VA_ARGS__); fputc('\n', stderr); } } while (0)
 
 constexpr int kHeaderWords = 64;   // per-rank merge header (u64): n_adm, 16 counts, 16 first keys, 16 last keys
 
@@ -148,6 +173,8 @@ struct triage_engine {
     DevBuf<uint32_t> d_lengths, d_counters, d_tile_first, d_order, d_perm_a, d_perm_b, d_blockhist, d_totals, d_small;
     DevBuf<uint8_t> d_bucket, d_bucket2;
     PrefetchSlot pre[2];           // batches uploading ahead of their submit
+    PrefetchSlot own;              // the batch a submit uploads itself (same chunked copy, same stream)
+    DevBuf<uint32_t> d_tilectr;    // one dynamic-tile counter per upload chunk
     cudaStream_t copy_stream = nullptr;
     uint64_t pre_seq = 0;
     uint32_t *h_small = nullptr;   // pinned: [0] flags, [1] n_admitted, [2..17] bucket counts, [32..] digit hist
@@ -269,7 +296,7 @@ enum RunMode { RUN_ROUTED = 0, RUN_SINGLE_QUEUE = 1, RUN_PROCESS_ONLY = 2 };
 // (16-byte aligned starts, 1..16 reset-pad bytes after every message, offsets[n] = padded total).
 int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, const uint32_t *lengths, const uint8_t *bytes, uint64_t total,
                    const triage_meta *meta, const uint64_t *ts, uint32_t n, triage_result *results, uint32_t *order,
-                   const uint64_t pending[4], const int64_t max_size[4], uint32_t *n_admitted) {
+                   const uint64_t pending[4], const int64_t max_size[4], uint32_t *n_admitted, const UploadPlan *plan = nullptr) {
     int32_t rc = commit_dict(e);
     if (rc) return rc;
     if ((reinterpret_cast<uintptr_t>(bytes) & 15) != 0) return fail(TRIAGE_E_ARG, "device arena must be 16-byte aligned");
@@ -289,7 +316,9 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
         ScanArgs probe{bytes, offsets, total, n, nullptr, nullptr, 0, 0};
         use_rows = scan_rows_usable(probe);
     }
-    const uint32_t row_bytes = use_rows ? scan_rows_lane_bytes(total, e->row_warps, e->sm_count) : 0;
+    // an upload in flight is scanned chunk by chunk: the row length is chosen for the chunk, not for the arena
+    const bool chunked = plan && use_rows && plan->n_chunks > 1;
+    const uint32_t row_bytes = use_rows ? scan_rows_lane_bytes(chunked ? kUploadChunk : total, e->row_warps, e->sm_count) : 0;
     const uint32_t tile_bytes = !padded ? e->geom.tile
                               : use_rows ? scan_rows_super_bytes(row_bytes) : kPadMiniTile;
     const uint32_t ntiles = (uint32_t)((total + tile_bytes - 1) / tile_bytes);
@@ -305,16 +334,37 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     CU(e->d_maxsize.ensure(4));
     OrderScratch sc{e->d_blockhist.p, e->d_totals.p, nblocks};
 
+    if (plan) CU(cudaStreamWaitEvent(s, plan->small_ready, 0));
     CU(cudaEventRecord(e->ev[0], s));
-    ScanArgs sa{bytes, offsets, total, n, e->d_counters.p, e->d_tile_first.p, ntiles, tile_bytes};
+    ScanArgs sa{bytes, offsets, total, n, e->d_counters.p, e->d_tile_first.p, ntiles, tile_bytes, 0, ntiles};
     CU(launch_prepare(sa, e->d_small.p, 32 + 8 * 256, e->sm_count, s)); launches++;   // tile index + zeroed counters and scratch
-    if (ntiles) {
+    e->tm.scan_variant = use_rows ? 3u : padded ? (e->ddfa.wide ? 4u : 2u) : 1u;
+    e->tm.scan_row_bytes = row_bytes;
+    e->tm.scan_warps = use_rows ? e->row_warps : padded ? e->pad_warps : e->geom.nt / 32;
+    if (ntiles && chunked) {
+        // scan of chunk i behind the copy of chunk i: the kernel walks the tiles of the part that has arrived
+        CU(e->d_tilectr.ensure(plan->n_chunks));
+        CU(cudaMemsetAsync(e->d_tilectr.p, 0, plan->n_chunks * sizeof(uint32_t), s));
+        CU(cudaEventRecord(e->ev[1], s));
+        const uint32_t tiles_per_chunk = (uint32_t)(kUploadChunk / tile_bytes);
+        for (uint32_t c = 0; c < plan->n_chunks; c++) {
+            sa.tile_begin = c * tiles_per_chunk;
+            sa.tile_end = std::min<uint64_t>(ntiles, (uint64_t)(c + 1) * tiles_per_chunk);
+            if (sa.tile_begin >= sa.tile_end) break;
+            CU(cudaStreamWaitEvent(s, plan->chunk_ev[c], 0));
+            CU(launch_scan_rows(sa, e->ddfa, e->row_warps, row_bytes, e->d_tilectr.p + c, e->sm_count, s));
+            launches++;
+        }
+        CU(cudaStreamWaitEvent(s, plan->all_ready, 0));
+    } else if (ntiles) {
+        if (plan) CU(cudaStreamWaitEvent(s, plan->all_ready, 0));
         CU(cudaEventRecord(e->ev[1], s));
         if (use_rows) CU(launch_scan_rows(sa, e->ddfa, e->row_warps, row_bytes, e->d_small.p + 20, e->sm_count, s));   // d_small[20]: spare word, zeroed by prepare
         else if (padded) CU(launch_scan_padded(sa, e->ddfa, e->pad_warps, e->sm_count, s));
         else CU(launch_scan(sa, e->ddfa, e->geom, e->sm_count, s));
         launches++;
     } else {
+        if (plan) CU(cudaStreamWaitEvent(s, plan->all_ready, 0));
         CU(cudaEventRecord(e->ev[1], s));
     }
     if (e->has_bordered && ntiles) { CU(launch_fixup(bytes, offsets, lengths, n, e->dxdfa, e->d_counters.p, s)); launches++; }
@@ -420,7 +470,12 @@ int32_t triage_create(const triage_opts *opts, triage_engine **out) {
     for (int i = 0; i < 6 && ce == cudaSuccess; i++) ce = cudaEventCreate(&e->ev[i]);
     for (int i = 0; i < 4 && ce == cudaSuccess; i++) ce = cudaEventCreate(&e->user_ev[i]);
     if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking);
-    for (int i = 0; i < 2 && ce == cudaSuccess; i++) ce = cudaEventCreateWithFlags(&e->pre[i].ready, cudaEventDisableTiming);
+    for (PrefetchSlot *ps : {&e->pre[0], &e->pre[1], &e->own}) {
+        if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&ps->ready, cudaEventDisableTiming);
+        if (ce == cudaSuccess) ce = cudaEventCreateWithFlags(&ps->small_ready, cudaEventDisableTiming);
+        if (ce == cudaSuccess) ce = cudaEventCreate(&ps->t_begin);
+        if (ce == cudaSuccess) ce = cudaEventCreate(&ps->t_end);
+    }
     if (ce == cudaSuccess) ce = cudaHostAlloc(reinterpret_cast<void **>(&e->h_small), (32 + 8 * 256) * sizeof(uint32_t), cudaHostAllocDefault);
     if (ce != cudaSuccess) { delete e; return fail(TRIAGE_E_CUDA, cudaGetErrorString(ce)); }
     e->q.resize(5);
@@ -436,7 +491,12 @@ void triage_destroy(triage_engine *e) {
     cudaSetDevice(e->opts.device);
     cudaStreamSynchronize(e->stream);
     if (e->copy_stream) cudaStreamSynchronize(e->copy_stream);
-    for (auto &ps : e->pre) { ps.bytes.release(); ps.offsets.release(); ps.ts.release(); ps.lengths.release(); ps.meta.release(); }
+    for (PrefetchSlot *ps : {&e->pre[0], &e->pre[1], &e->own}) {
+        ps->bytes.release(); ps->offsets.release(); ps->ts.release(); ps->lengths.release(); ps->meta.release();
+        for (cudaEvent_t ev : ps->chunk_ev) cudaEventDestroy(ev);
+        for (cudaEvent_t ev : {ps->ready, ps->small_ready, ps->t_begin, ps->t_end}) if (ev) cudaEventDestroy(ev);
+    }
+    e->d_tilectr.release();
     if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
     e->dm.release(); e->dx.release(); e->d_bytes.release(); e->d_offsets.release();
     e->d_ts.release(); e->d_pending.release(); e->d_maxsize.release(); e->d_meta.release(); e->d_results.release(); e->d_counters.release();
@@ -448,7 +508,6 @@ void triage_destroy(triage_engine *e) {
     for (auto &ev : e->ev) if (ev) cudaEventDestroy(ev);
     for (auto &ev : e->user_ev) if (ev) cudaEventDestroy(ev);
     if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
-    for (auto &ps : e->pre) if (ps.ready) cudaEventDestroy(ps.ready);
     if (e->stream) cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -574,18 +633,14 @@ int32_t upload_batch(triage_engine *e, const uint64_t *offsets, const uint32_t *
 
 }  // namespace
 
-// triage_prefetch: start the host->device copy of a batch on the copy stream, into a slot of its own
-static int32_t prefetch_impl(triage_engine *e, const uint64_t *offsets, const uint32_t *lengths, const uint8_t *bytes,
-                             const triage_meta *meta, const uint64_t *enqueue_ns, uint32_t n) {
-    if (!e || (n && (!offsets || !meta))) return fail(TRIAGE_E_ARG, "null argument");
-    CU(cudaSetDevice(e->opts.device));
-    std::lock_guard<std::mutex> lock(e->mu);
-    if (n == 0) return TRIAGE_OK;
+// Starts the host->device copy of one batch into `ps` on the copy stream and returns at once: the small arrays first
+// (the tile index needs the offsets), then the arena in kUploadChunk pieces with an event behind each, so that the scan
+// can follow the copy chunk by chunk.  The host buffers must stay unchanged until the copy has finished.
+static int32_t start_upload(triage_engine *e, PrefetchSlot *ps, const uint64_t *offsets, const uint32_t *lengths, const uint8_t *bytes,
+                            const triage_meta *meta, const uint64_t *enqueue_ns, uint32_t n) {
     const uint64_t total = offsets[n] - offsets[0];
     if (total && !bytes) return fail(TRIAGE_E_ARG, "null arena");
     if (lengths && ((offsets[0] & 15) || (total & 15))) return fail(TRIAGE_E_ARG, "padded arena: offsets must be multiples of 16");
-    PrefetchSlot *ps = &e->pre[0];   // a free slot, else the older one
-    if (e->pre[0].valid && (!e->pre[1].valid || e->pre[1].seq < e->pre[0].seq)) ps = &e->pre[1];
     cudaStream_t cs = e->copy_stream;
     ps->valid = false;
     CU(ps->bytes.ensure(total + 32));
@@ -593,6 +648,12 @@ static int32_t prefetch_impl(triage_engine *e, const uint64_t *offsets, const ui
     CU(ps->meta.ensure(n));
     if (lengths) CU(ps->lengths.ensure(n));
     if (enqueue_ns) CU(ps->ts.ensure(n));
+    const uint32_t n_chunks = (uint32_t)std::max<uint64_t>(1, (total + kUploadChunk - 1) / kUploadChunk);
+    while (ps->chunk_ev.size() < n_chunks) {
+        cudaEvent_t ev = nullptr;
+        CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        ps->chunk_ev.push_back(ev);
+    }
     const uint64_t *off_src = offsets;
     if (offsets[0] != 0) {
         CU(cudaStreamSynchronize(cs));   // an earlier copy may still read the previous rebased offsets
@@ -600,18 +661,39 @@ static int32_t prefetch_impl(triage_engine *e, const uint64_t *offsets, const ui
         for (uint32_t i = 0; i <= n; i++) ps->rebased[i] = offsets[i] - offsets[0];
         off_src = ps->rebased.data();
     }
-    if (total) CU(cudaMemcpyAsync(ps->bytes.p, bytes + offsets[0], total, cudaMemcpyHostToDevice, cs));
-    CU(cudaMemsetAsync(ps->bytes.p + total, 0, 32, cs));
+    TRACE("upload start: n=%u total=%llu chunks=%u", n, (unsigned long long)total, n_chunks);
+    CU(cudaEventRecord(ps->t_begin, cs));
     CU(cudaMemcpyAsync(ps->offsets.p, off_src, ((size_t)n + 1) * 8, cudaMemcpyHostToDevice, cs));
     CU(cudaMemcpyAsync(ps->meta.p, meta, (size_t)n * sizeof(triage_meta), cudaMemcpyHostToDevice, cs));
     if (lengths) CU(cudaMemcpyAsync(ps->lengths.p, lengths, (size_t)n * 4, cudaMemcpyHostToDevice, cs));
     if (enqueue_ns) CU(cudaMemcpyAsync(ps->ts.p, enqueue_ns, (size_t)n * 8, cudaMemcpyHostToDevice, cs));
+    CU(cudaEventRecord(ps->small_ready, cs));
+    const uint8_t *src = bytes + offsets[0];
+    for (uint32_t c = 0; c < n_chunks; c++) {
+        const uint64_t lo = (uint64_t)c * kUploadChunk, hi = std::min(total, lo + kUploadChunk);
+        if (hi > lo) CU(cudaMemcpyAsync(ps->bytes.p + lo, src + lo, hi - lo, cudaMemcpyHostToDevice, cs));
+        if (c + 1 == n_chunks) CU(cudaMemsetAsync(ps->bytes.p + total, 0, 32, cs));   // the last tile's bulk copy rounds up to 16 bytes
+        CU(cudaEventRecord(ps->chunk_ev[c], cs));
+    }
+    CU(cudaEventRecord(ps->t_end, cs));
     CU(cudaEventRecord(ps->ready, cs));
     ps->k_offsets = offsets; ps->k_bytes = bytes; ps->k_meta = meta; ps->k_lengths = lengths; ps->k_ts = enqueue_ns;
-    ps->n = n; ps->total = total;
+    ps->n = n; ps->total = total; ps->n_chunks = n_chunks;
     ps->seq = ++e->pre_seq;
     ps->valid = true;
     return TRIAGE_OK;
+}
+
+// triage_prefetch: start the host->device copy of a batch on the copy stream, into a slot of its own
+static int32_t prefetch_impl(triage_engine *e, const uint64_t *offsets, const uint32_t *lengths, const uint8_t *bytes,
+                             const triage_meta *meta, const uint64_t *enqueue_ns, uint32_t n) {
+    if (!e || (n && (!offsets || !meta))) return fail(TRIAGE_E_ARG, "null argument");
+    CU(cudaSetDevice(e->opts.device));
+    std::lock_guard<std::mutex> lock(e->mu);
+    if (n == 0) return TRIAGE_OK;
+    PrefetchSlot *ps = &e->pre[0];   // a free slot, else the older one
+    if (e->pre[0].valid && (!e->pre[1].valid || e->pre[1].seq < e->pre[0].seq)) ps = &e->pre[1];
+    return start_upload(e, ps, offsets, lengths, bytes, meta, enqueue_ns, n);
 }
 
 // the slot that holds exactly this batch (same host pointers and sizes), oldest first; nullptr: not prefetched
@@ -680,23 +762,22 @@ static int32_t submit_impl(triage_engine *e, int32_t target_queue, const uint64_
     const uint32_t *d_len = nullptr;
     const uint8_t *d_byt = nullptr;
     const triage_meta *d_met = nullptr;
-    if (PrefetchSlot *ps = find_prefetched(e, offsets, lengths, bytes, meta, enqueue_ns, n)) {
-        // uploaded ahead by triage_prefetch: the compute stream only waits for the copy stream's event
-        CU(cudaStreamWaitEvent(s, ps->ready, 0));
-        CU(e->d_results.ensure(n));
-        CU(e->d_order.ensure(n));
-        total = ps->total;
-        d_off = ps->offsets.p; d_byt = ps->bytes.p; d_met = ps->meta.p;
-        d_len = lengths ? ps->lengths.p : nullptr;
-        d_tsp = enqueue_ns ? ps->ts.p : nullptr;
-        ps->valid = false;   // consumed (the buffers stay untouched until the next prefetch, i.e. after this call returns)
-    } else {
-        rc = upload_batch(e, offsets, lengths, bytes, meta, enqueue_ns, n, &total);
+    PrefetchSlot *ps = find_prefetched(e, offsets, lengths, bytes, meta, enqueue_ns, n);
+    const bool prefetched = ps != nullptr;
+    TRACE("submit enter: n=%u prefetched=%d", n, prefetched ? 1 : 0);
+    if (!ps) {   // not uploaded ahead: start the same chunked copy now, the scan below follows it chunk by chunk
+        ps = &e->own;
+        rc = start_upload(e, ps, offsets, lengths, bytes, meta, enqueue_ns, n);
         if (rc) return rc;
-        d_off = e->d_offsets.p; d_byt = e->d_bytes.p; d_met = e->d_meta.p;
-        d_len = lengths ? e->d_lengths.p : nullptr;
-        d_tsp = enqueue_ns ? e->d_ts.p : nullptr;
     }
+    CU(e->d_results.ensure(n));
+    CU(e->d_order.ensure(n));
+    total = ps->total;
+    d_off = ps->offsets.p; d_byt = ps->bytes.p; d_met = ps->meta.p;
+    d_len = lengths ? ps->lengths.p : nullptr;
+    d_tsp = enqueue_ns ? ps->ts.p : nullptr;
+    ps->valid = false;   // consumed (the buffers stay untouched until the next upload into this slot, i.e. after this call returns)
+    const UploadPlan plan{ps->chunk_ev.data(), ps->n_chunks, ps->small_ready, ps->ready};
     auto t1 = std::chrono::steady_clock::now();
     uint64_t pending[4] = {0, 0, 0, 0};
     int64_t ms[4] = {0, 0, 0, 0};
@@ -708,9 +789,10 @@ static int32_t submit_impl(triage_engine *e, int32_t target_queue, const uint64_
     }
     uint32_t n_adm = 0;
     rc = run_device(e, target_queue ? RUN_SINGLE_QUEUE : RUN_ROUTED, d_off, d_len, d_byt, total, d_met, d_tsp, n, e->d_results.p,
-                    e->d_order.p, pending, ms, &n_adm);
+                    e->d_order.p, pending, ms, &n_adm, &plan);
     if (rc) return rc;
     auto t2 = std::chrono::steady_clock::now();
+    TRACE("submit: kernels done (scan %.3f ms incl. waiting for chunks)", e->tm.scan_ms);
     triage_result *res = out;
     if (!res) { e->h_results_tmp.resize(n); res = e->h_results_tmp.data(); }
     e->h_order.resize(n_adm);
@@ -718,8 +800,13 @@ static int32_t submit_impl(triage_engine *e, int32_t target_queue, const uint64_
     if (n_adm) CU(cudaMemcpyAsync(e->h_order.data(), e->d_order.p, (size_t)n_adm * 4, cudaMemcpyDeviceToHost, s));
     CU(cudaStreamSynchronize(s));
     auto t3 = std::chrono::steady_clock::now();
-    e->tm.h2d_ms = std::chrono::duration<float, std::milli>(t1 - t0).count();
+    // h2d_ms: the copy engine's time for this batch when the call uploaded it itself (0: it was prefetched, the copy ran
+    // under the previous batch); the scan of that case overlaps the copy, so scan_ms includes waiting for chunks
+    e->tm.h2d_ms = 0;
+    if (!prefetched) { float hm = 0; if (cudaEventElapsedTime(&hm, ps->t_begin, ps->t_end) == cudaSuccess) e->tm.h2d_ms = hm; }
+    (void)t0; (void)t1;
     e->tm.d2h_ms = std::chrono::duration<float, std::milli>(t3 - t2).count();
+    TRACE("submit: results on the host (d2h %.3f ms)", e->tm.d2h_ms);
     // queue.go:105-116: admitted messages enter their queue; the device order is already
     // (queue, item priority, time, sequence), so each queue receives one sorted run
     uint64_t stamp0 = 0;
@@ -769,6 +856,7 @@ static int32_t submit_impl(triage_engine *e, int32_t target_queue, const uint64_
             std::inplace_merge(lq.items.begin() + lq.head, lq.items.begin() + run_begin, lq.items.end(), qless);
     }
     e->next_handle = base + n;
+    TRACE("submit exit (queues filled)");
     return TRIAGE_OK;
 }
 
@@ -1250,10 +1338,15 @@ extern "C" int32_t triage_submit_device_static(triage_engine *e, const uint64_t 
         }
         CU(launch_partition_u8(bk, perm, n, 16, true, order_dev, small + 2, sc, s)); launches += 4;
         CU(cudaEventRecord(e->ev[4], s));
+        CU(cudaMemcpyAsync(e->h_small, small, 32 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
         CU(cudaMemcpyAsync(e->h_small + 1, totals + 256, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
         CU(cudaStreamSynchronize(s));
     }
     *n_admitted = e->h_small[1];
+    // what triage_merge_allgather reads of "the last device submit" (the bucket bytes live in the shared array: merge
+    // before the next static call on this GPU)
+    for (int b = 0; b < 16; b++) e->last_counts[b] = e->h_small[2 + b];
+    e->last_order = order_dev; e->last_bucket = bk; e->last_ts = enqueue_ns_dev; e->last_n = n; e->last_n_adm = *n_admitted;
     float ms_ = 0;
     cudaEventElapsedTime(&ms_, e->ev[1], e->ev[2]); e->tm.scan_ms = ms_;
     cudaEventElapsedTime(&ms_, e->ev[2], e->ev[3]); e->tm.finalize_ms = ms_;

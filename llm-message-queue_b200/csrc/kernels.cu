@@ -666,12 +666,15 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
     // Tiles are handed out dynamically: the first one per warp by position, every further one from a global counter
     // (zeroed by prepare_kernel), fetched two tiles ahead so that the next tile's message list and first window can be
     // prefetched while the current one is walked.
+    // One launch walks the tiles [a.tile_begin, t_end): the whole arena, or the part of it that has already arrived when
+    // the upload is pipelined chunk by chunk (engine.cu, submit from host buffers).
     const uint32_t nwarps = gridDim.x * NW;
-    const uint32_t t0 = blockIdx.x * NW + warp;
-    if (t0 >= a.ntiles) return;
+    const uint32_t t_end = a.tile_end;
+    const uint32_t t0 = a.tile_begin + blockIdx.x * NW + warp;
+    if (t0 >= t_end) return;
     auto grab = [&]() {
         uint32_t v = 0;
-        if (lane == 0) v = atomicAdd(tile_counter, 1u) + nwarps;
+        if (lane == 0) v = atomicAdd(tile_counter, 1u) + nwarps + a.tile_begin;
         return __shfl_sync(0xFFFFFFFFu, v, 0);
     };
 
@@ -695,7 +698,7 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
         }
     }
     uint32_t first_nxt = 0, last_nxt = 0;
-    if (t_nxt < a.ntiles) { first_nxt = a.tile_first[t_nxt]; last_nxt = a.tile_first[t_nxt + 1]; }
+    if (t_nxt < t_end) { first_nxt = a.tile_first[t_nxt]; last_nxt = a.tile_first[t_nxt + 1]; }
     __syncwarp();
 
     LaneCtx c;
@@ -707,8 +710,8 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
     const int32_t chunk = (int32_t)(lane * CL);
     uint32_t g = 0;
 
-    for (uint32_t sk = 0; t < a.ntiles; sk++) {
-        const bool has_next = t_nxt < a.ntiles;
+    for (uint32_t sk = 0; t < t_end; sk++) {
+        const bool has_next = t_nxt < t_end;
         ts = (uint64_t)t * SUPER;
         uint64_t n0 = 0, n1 = 0;
         uint32_t cnt_nxt = 0, first_nn = 0, last_nn = 0;
@@ -718,7 +721,7 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
                 if (lane < cnt_nxt) n0 = a.offsets[first_nxt + lane];
                 if (lane + 32 < cnt_nxt) n1 = a.offsets[first_nxt + lane + 32];
             }
-            if (t_nn < a.ntiles) { first_nn = a.tile_first[t_nn]; last_nn = a.tile_first[t_nn + 1]; }
+            if (t_nn < t_end) { first_nn = a.tile_first[t_nn]; last_nn = a.tile_first[t_nn + 1]; }
         }
         const uint32_t cnt_cur = last_cur - first_cur + 2;
         const int32_t *lst = list_base + (sk & 1) * kRowListCap;
@@ -802,7 +805,7 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
         first_cur = first_nxt; last_cur = last_nxt;
         first_nxt = first_nn; last_nxt = last_nn;
         t = t_nxt; t_nxt = t_nn;
-        t_nn = t_nxt < a.ntiles ? grab() : t_nxt;   // warp-uniform: no more fetches once the counter has run past the end
+        t_nn = t_nxt < t_end ? grab() : t_nxt;   // warp-uniform: no more fetches once the counter has run past the end
         __syncwarp();
     }
     queue.flush(c, lane, true);
@@ -828,7 +831,7 @@ static cudaError_t launch_scan_rows_variant(const ScanArgs &a, const DeviceDfa &
     size_t smem = scan_rows_smem_bytes(d, NW);
     static SmemConfigured configured;
     if (cudaError_t e = ensure_dynamic_smem(scan_rows_kernel<NW, LANE>, smem, configured)) return e;
-    uint32_t need = (a.ntiles + NW - 1) / NW;
+    uint32_t need = (a.tile_end - a.tile_begin + NW - 1) / NW;
     uint32_t grid = need < (uint32_t)sm_count ? need : (uint32_t)sm_count;
     scan_rows_kernel<NW, LANE><<<grid, NW * 32, smem, s>>>(a, d, tw, tm, nrows_full, tile_counter);
     return cudaGetLastError();
@@ -841,7 +844,7 @@ bool scan_rows_usable(const ScanArgs &a) {
 
 cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, uint32_t lane_bytes, uint32_t *tile_counter, int sm_count,
                              cudaStream_t s) {
-    if (a.ntiles == 0) return cudaSuccess;
+    if (a.tile_end <= a.tile_begin) return cudaSuccess;
     EncodeTiledFn enc = encode_tiled_fn();
     if (!enc) return cudaErrorNotSupported;
     const uint32_t win = row_win(nw);

@@ -40,6 +40,7 @@ struct ScanArgs {
     uint32_t *tile_first;        // ntiles + 1 (scratch)
     uint32_t ntiles;
     uint32_t tile_bytes;         // = geometry.tile
+    uint32_t tile_begin, tile_end;   // row-lane scan only: the tiles this launch walks (the whole arena: 0, ntiles)
 };
 
 // padded-arena scan: warps are autonomous (own staging buffers, own mbarriers, no CTA barrier in the loop)
@@ -49,7 +50,7 @@ size_t scan_padded_smem_bytes(const DeviceDfa &d, uint32_t nw);
 uint32_t pick_pad_warps(const DeviceDfa &d, size_t max_smem);   // 24 for the default dictionary; fewer when the table is large
 cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, int sm_count, cudaStream_t s);
 
-// row-lane variant of the padded scan (dense table, 16-byte warm-up): 320-byte rows fed by 2-D TMA tile copies
+// row-lane variant of the padded scan (dense table, 16-byte warm-up): rows of 1280 / 640 / 320 bytes fed by 2-D TMA tile copies
 size_t scan_rows_smem_bytes(const DeviceDfa &d, uint32_t nw);
 uint32_t scan_rows_lane_bytes(uint64_t total, uint32_t nw, int sm_count);   // row length for an arena of that size (1280, 640 or 320)
 uint32_t scan_rows_super_bytes(uint32_t lane_bytes);

@@ -55,6 +55,9 @@ def apply_result(msg: Message, r, now: float) -> Message:
         msg.metadata = {}
     if not (r["flags"] & _capi.RF_ANALYZED):   # :63-65 explicit priority respected, nothing else touched
         return msg
+    # ProcessMessage sets Priority and QueueName from the PRE-rule priority (:103-105); the rules of PushMessage run
+    # later and only change Priority.  On the submit path r["label"] is post-rule and r["queue_level"] pre-rule.
+    pre_rule = int(r["queue_level"]) if 1 <= int(r["queue_level"]) <= 4 else int(r["label"])
     msg.priority = int(r["label"])
     if r["reason"]:
         msg.metadata["priority_reason"] = _REASONS[int(r["reason"])]
@@ -64,7 +67,7 @@ def apply_result(msg: Message, r, now: float) -> Message:
         msg.metadata["contains_question"] = "true" if r["question"] else "false"
     msg.metadata["analyzed"] = True
     if msg.queue_name == "":
-        msg.queue_name = priority_name(msg.priority)
+        msg.queue_name = priority_name(pre_rule)
     if not msg.created_at:
         msg.created_at = now
     msg.updated_at = now

@@ -142,8 +142,13 @@ class PriorityAdjustRule:   # queue_manager.go:47-51
 
 def builtin_priority_rules() -> list[PriorityAdjustRule]:
     """queue_factory.go:211-233"""
-    return [PriorityAdjustRule(lambda m: "vip_user" in (m.metadata or {}), 2, "vip"),
-            PriorityAdjustRule(lambda m: len(m.content_bytes()) > 10000, 4, "long")]
+    def vip(m):
+        return "vip_user" in (m.metadata or {})
+
+    def long_content(m):
+        return len(m.content_bytes()) > 10000
+    vip._builtin = long_content._builtin = True   # marks the predicates the device implements (batch_triage checks it)
+    return [PriorityAdjustRule(vip, 2, "vip"), PriorityAdjustRule(long_content, 4, "long")]
 
 
 @dataclass
@@ -269,6 +274,19 @@ class QueueManager:
         for name in LEVELS:
             if name not in self._ids:
                 raise ErrQueueNotFound
+        if not self._rules_are_device_rules():
+            # a custom rule list (arbitrary Python predicates) cannot run in the kernel: same semantics as the reference
+            # loop - ProcessMessage for the batch on the device, then PushMessage per message, which applies the rules
+            # (queue_manager.go:451-466) exactly as push_message does
+            preprocessor.process_messages(messages)
+            res = []
+            for m in messages:
+                try:
+                    self.push_message(priority_name(m.priority), m)
+                    res.append(True)
+                except QueueError:
+                    res.append(False)
+            return res
         offsets, data, meta = pack_messages(messages, preprocessor.user_priorities)
         if self.engine.pad_byte() >= 0:   # preferred wire format: 16-byte aligned starts + reset pads
             poff, plen, pbytes = self.engine.pack_padded(offsets, data)
@@ -283,6 +301,17 @@ class QueueManager:
             if r["accepted"]:
                 self._msgs[base + i] = m
         return res
+
+    def _rules_are_device_rules(self) -> bool:
+        """True when the configured rule list is what the device evaluates: none, or exactly the two built-in rules of
+        queue_factory.go:211-233 with builtin_rules set (the engine was told so in __init__)."""
+        rules = self.config.priority_adjust_rules
+        if not rules:
+            return not self.config.builtin_rules
+        if not self.config.builtin_rules or len(rules) != 2:
+            return False
+        return [(r.new_priority, r.description) for r in rules] == [(r.new_priority, r.description) for r in builtin_priority_rules()] \
+            and all(getattr(r.condition, "_builtin", False) for r in rules)
 
     def drain(self, max_items: int) -> list[Message]:
         handles, _ = self.engine.drain(max_items)

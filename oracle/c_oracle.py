@@ -50,6 +50,7 @@ def lib():
         L.orc_dict_add.restype = C.c_int
         L.orc_dict_add.argtypes = [vp, C.c_int, C.c_char_p, C.c_uint32, C.c_int]
         L.orc_dict_free.argtypes = [vp]
+        L.orc_dict_set_fast.argtypes = [vp, C.c_int]
         L.orc_scores.argtypes = [vp, C.c_char_p, C.c_uint64, C.POINTER(C.c_uint32)]
         L.orc_analyze.argtypes = [C.c_char_p, C.c_uint64, C.POINTER(C.c_uint32), C.POINTER(C.c_int32),
                                   C.POINTER(C.c_int32), C.POINTER(C.c_int)]
@@ -81,6 +82,11 @@ class Dict:
 
     def add(self, prio: int, literal: bytes, ci: bool) -> int:
         return lib().orc_dict_add(self.h, prio, literal, len(literal), 1 if ci else 0)
+
+    def set_fast(self, on=True):
+        """one-pass scoring for border-free case-sensitive literals (same numbers; for the full-size 10 K-keyword goldens).
+        Call after the last add()."""
+        lib().orc_dict_set_fast(self.h, 1 if on else 0)
 
     def __del__(self):
         try:

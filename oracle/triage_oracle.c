@@ -64,9 +64,21 @@ typedef struct {
     uint32_t *runes;
 } pat_t;
 
+/* "fast" mode (orc_dict_set_fast): same scores as the per-pattern passes, computed in one pass for the patterns where
+ * that is provably the same number.  A case-sensitive literal without a border (no proper prefix equal to a suffix)
+ * cannot overlap itself, so its leftmost non-overlapping count is its occurrence count; those literals go into one
+ * byte trie that is walked from every rune start.  Every other pattern ((?i) literals, self-overlapping literals)
+ * keeps its own count_nonoverlap pass.  Used for the full-size goldens of the 10 000-keyword config, where 10 000
+ * passes per message are out of reach; tests/test_oracle.py checks it against the per-pattern mode.              */
+typedef struct { uint32_t child_base; uint32_t add[5]; uint8_t has_add; } tnode_t;
 struct orc_dict {
     pat_t *pats;
     uint32_t n, cap;
+    int fast;
+    /* fast mode: open-addressed (node, byte) -> node map + per node score increments */
+    uint64_t *tkeys; uint32_t *tvals; uint32_t tmask;
+    tnode_t *tnodes; uint32_t tn;
+    uint32_t *slow_idx; uint32_t nslow;
 };
 
 /* regexp (?i) on a literal rune: unicode.SimpleFold orbit membership.
@@ -113,6 +125,7 @@ int orc_dict_add(orc_dict *d, int prio, const uint8_t *lit, uint32_t len, int ci
         d->cap = d->cap ? d->cap * 2 : 16;
         d->pats = (pat_t *)realloc(d->pats, sizeof(pat_t) * d->cap);
     }
+    d->fast = 0;   /* the trie of the fast mode is stale now: orc_dict_set_fast again after the last add */
     d->pats[d->n].prio = prio;
     d->pats[d->n].ci = ci;
     d->pats[d->n].nrunes = nr;
@@ -126,6 +139,7 @@ void orc_dict_free(orc_dict *d)
     if (!d) return;
     for (uint32_t i = 0; i < d->n; i++) free(d->pats[i].runes);
     free(d->pats);
+    free(d->tkeys); free(d->tvals); free(d->tnodes); free(d->slow_idx);
     free(d);
 }
 
@@ -158,10 +172,118 @@ static uint32_t count_nonoverlap(const pat_t *p, const uint8_t *s, uint64_t n)
     return count;
 }
 
+/* ------------------------------------------------------ fast mode -------- */
+static int pat_bordered(const pat_t *p)
+{
+    /* prefix function over (folded) runes: non-zero at the end = a proper prefix equals a suffix */
+    uint32_t m = p->nrunes;
+    if (m < 2) return 0;
+    uint32_t *pi = (uint32_t *)calloc(m, sizeof(uint32_t));
+    for (uint32_t i = 1; i < m; i++) {
+        uint32_t k = pi[i - 1];
+        while (k > 0 && p->runes[i] != p->runes[k]) k = pi[k - 1];
+        if (p->runes[i] == p->runes[k]) k++;
+        pi[i] = k;
+    }
+    int b = pi[m - 1] > 0;
+    free(pi);
+    return b;
+}
+static uint32_t encode_rune(uint32_t r, uint8_t out[4])
+{
+    if (r < 0x80) { out[0] = (uint8_t)r; return 1; }
+    if (r < 0x800) { out[0] = (uint8_t)(0xC0 | (r >> 6)); out[1] = (uint8_t)(0x80 | (r & 0x3F)); return 2; }
+    if (r < 0x10000) { out[0] = (uint8_t)(0xE0 | (r >> 12)); out[1] = (uint8_t)(0x80 | ((r >> 6) & 0x3F)); out[2] = (uint8_t)(0x80 | (r & 0x3F)); return 3; }
+    out[0] = (uint8_t)(0xF0 | (r >> 18)); out[1] = (uint8_t)(0x80 | ((r >> 12) & 0x3F)); out[2] = (uint8_t)(0x80 | ((r >> 6) & 0x3F));
+    out[3] = (uint8_t)(0x80 | (r & 0x3F));
+    return 4;
+}
+static uint32_t tmap_get(const orc_dict *d, uint32_t node, uint8_t b)
+{
+    uint64_t key = ((uint64_t)node << 8 | b) + 1;
+    uint64_t h = key * 0x9E3779B97F4A7C15ull;
+    for (uint32_t i = (uint32_t)(h >> 40) & d->tmask;; i = (i + 1) & d->tmask) {
+        if (d->tkeys[i] == key) return d->tvals[i];
+        if (d->tkeys[i] == 0) return 0;
+    }
+}
+static void tmap_put(orc_dict *d, uint32_t node, uint8_t b, uint32_t val)
+{
+    uint64_t key = ((uint64_t)node << 8 | b) + 1;
+    uint64_t h = key * 0x9E3779B97F4A7C15ull;
+    uint32_t i = (uint32_t)(h >> 40) & d->tmask;
+    while (d->tkeys[i] != 0) i = (i + 1) & d->tmask;
+    d->tkeys[i] = key;
+    d->tvals[i] = val;
+}
+void orc_dict_set_fast(orc_dict *d, int on)
+{
+    free(d->tkeys); free(d->tvals); free(d->tnodes); free(d->slow_idx);
+    d->tkeys = NULL; d->tvals = NULL; d->tnodes = NULL; d->slow_idx = NULL;
+    d->fast = 0; d->tn = 0; d->nslow = 0;
+    if (!on) return;
+    uint64_t total_bytes = 1;
+    for (uint32_t i = 0; i < d->n; i++) total_bytes += 4ull * d->pats[i].nrunes;
+    uint32_t cap = 16;
+    while (cap < total_bytes * 2) cap <<= 1;
+    d->tmask = cap - 1;
+    d->tkeys = (uint64_t *)calloc(cap, sizeof(uint64_t));
+    d->tvals = (uint32_t *)calloc(cap, sizeof(uint32_t));
+    d->tnodes = (tnode_t *)calloc(total_bytes + 1, sizeof(tnode_t));
+    d->slow_idx = (uint32_t *)malloc(sizeof(uint32_t) * (d->n ? d->n : 1));
+    d->tn = 1;   /* node 0 = root; child id 0 = absent */
+    for (uint32_t i = 0; i < d->n; i++) {
+        const pat_t *p = &d->pats[i];
+        if (p->ci || pat_bordered(p)) { d->slow_idx[d->nslow++] = i; continue; }
+        uint32_t node = 0;
+        for (uint32_t k = 0; k < p->nrunes; k++) {
+            uint8_t enc[4];
+            uint32_t w = encode_rune(p->runes[k], enc);
+            for (uint32_t j = 0; j < w; j++) {
+                uint32_t nx = tmap_get(d, node, enc[j]);
+                if (!nx) { nx = d->tn++; tmap_put(d, node, enc[j], nx); }
+                node = nx;
+            }
+        }
+        d->tnodes[node].add[p->prio]++;
+        d->tnodes[node].has_add = 1;
+    }
+    d->fast = 1;
+}
+static void scores_fast(const orc_dict *d, const uint8_t *s, uint64_t n, uint32_t scores[5])
+{
+    for (uint32_t k = 0; k < d->nslow; k++) {
+        const pat_t *p = &d->pats[d->slow_idx[k]];
+        if (p->ci) { scores[p->prio] += count_nonoverlap(p, s, n); continue; }
+        /* self-overlapping case-sensitive literal: leftmost non-overlapping occurrences by byte search.  A byte-level
+         * occurrence of a valid UTF-8 literal always starts and ends on rune boundaries of the text (its first byte
+         * is ASCII or a lead byte, never a continuation byte), so this is the rune-level count.                    */
+        uint8_t enc[64 * 4];
+        uint32_t m = 0;
+        if (p->nrunes > 64) { scores[p->prio] += count_nonoverlap(p, s, n); continue; }
+        for (uint32_t r = 0; r < p->nrunes; r++) m += encode_rune(p->runes[r], enc + m);
+        const uint8_t *q = s, *end = s + n;
+        while ((q = (const uint8_t *)memmem(q, (size_t)(end - q), enc, m)) != NULL) { scores[p->prio]++; q += m; }
+    }
+    if (d->tn <= 1) return;
+    for (uint64_t i = 0; i < n;) {
+        uint32_t node = 0;
+        for (uint64_t j = i; j < n; j++) {
+            node = tmap_get(d, node, s[j]);
+            if (!node) break;
+            if (d->tnodes[node].has_add) for (int p = 1; p <= 4; p++) scores[p] += d->tnodes[node].add[p];
+        }
+        uint32_t w;
+        (void)decode_rune(s + i, n - i, &w);   /* matches start at rune starts only (regexp works on runes) */
+        i += w;
+    }
+}
+
 /* preprocessor.go:141-149 */
 void orc_scores(const orc_dict *d, const uint8_t *s, uint64_t n, uint32_t scores[5])
 {
     for (int p = 0; p < 5; p++) scores[p] = 0;
+    if (d->fast) { scores_fast(d, s, n, scores); return; }
     for (uint32_t i = 0; i < d->n; i++) scores[d->pats[i].prio] += count_nonoverlap(&d->pats[i], s, n);
 }
 

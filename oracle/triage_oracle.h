@@ -77,6 +77,9 @@ orc_dict *orc_dict_new(int with_defaults);
 /* literal pattern; ci = 1 for a "(?i)" literal.  returns 0 ok, 4 unsupported */
 int  orc_dict_add(orc_dict *d, int prio, const uint8_t *lit, uint32_t len, int ci);
 void orc_dict_free(orc_dict *d);
+/* on = 1: one-pass scoring for border-free case-sensitive literals (same numbers as the per-pattern passes; see
+ * triage_oracle.c "fast mode"); call after the last orc_dict_add.  The timed CPU baseline never uses it.        */
+void orc_dict_set_fast(orc_dict *d, int on);
 uint32_t orc_dict_size(const orc_dict *d);
 
 /* a5: per-priority scores for one content; scores[1..4] */

@@ -33,6 +33,7 @@ def test_library_has_sm100a_code_and_tma():
     assert "sm_100a" in out
     sass = subprocess.run(["cuobjdump", "-sass", mq._capi.LIB_PATH], capture_output=True, text=True).stdout
     assert "UBLKCP" in sass          # cp.async.bulk (1-D TMA) staging of the arena tiles
+    assert "UTMALDG" in sass         # cp.async.bulk.tensor.2d: the row-lane scan's window copies
     assert "SYNCS" in sass           # mbarrier
 
 

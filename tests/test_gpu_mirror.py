@@ -164,3 +164,49 @@ def test_batch_triage_is_process_then_push_for_the_whole_batch():
     assert msgs[5].metadata["contains_question"] == "true" and "analyzed" not in (msgs[4].metadata or {})
     assert qm.drain(10) == [msgs[2], msgs[1], msgs[3], msgs[0], msgs[5], msgs[4]]
     assert qm.drain(1) == []
+
+
+def test_batch_triage_with_rules_sets_queue_name_from_the_pre_rule_priority():
+    """queue_manager.go:451-466 mutates msg.Priority inside PushMessage, after ProcessMessage has already named the queue
+    from the pre-rule priority (preprocessor.go:103-105): a VIP message about something "right now" sits in queue
+    "realtime" with Priority High."""
+    qm = QueueManager(QueueManagerConfig(default_max_size=0, builtin_rules=True))
+    for name in ("realtime", "high", "normal", "low"):
+        qm.create_queue(name)
+    p = Preprocessor(engine=qm.engine)
+    vip = new_message("c", "u", "do it right now", Priority.NORMAL)
+    vip.metadata = {"vip_user": True}
+    long_msg = new_message("c", "u", "urgent " + "z" * 10001, Priority.NORMAL)
+    plain = new_message("c", "u", "nothing", Priority.NORMAL)
+    qm.batch_triage([vip, long_msg, plain], p)
+    assert (int(vip.priority), vip.queue_name) == (2, "realtime")
+    assert (int(long_msg.priority), long_msg.queue_name) == (4, "high")
+    assert (int(plain.priority), plain.queue_name) == (3, "normal")
+    assert qm.drain(5) == [vip, long_msg, plain]
+
+
+def test_batch_triage_with_a_custom_rule_list_applies_it_like_push_message():
+    """A custom PriorityAdjustRule list cannot run in the kernel; batch_triage then processes the batch on the device and
+    pushes message by message, so the rules act exactly as in push_message (first match wins, queue_manager.go:451-466)."""
+    from llm_message_queue_b200 import PriorityAdjustRule, builtin_priority_rules
+    rules = [PriorityAdjustRule(lambda m: "escalate" in (m.metadata or {}), 1, "escalate")] + builtin_priority_rules()
+    qm = QueueManager(QueueManagerConfig(default_max_size=0, priority_adjust_rules=rules, builtin_rules=True))
+    for name in ("realtime", "high", "normal", "low"):
+        qm.create_queue(name)
+    p = Preprocessor(engine=qm.engine)
+    a = new_message("c", "u", "nothing special", Priority.NORMAL)
+    a.metadata = {"escalate": 1, "vip_user": 1}
+    b = new_message("c", "u", "nothing special either", Priority.NORMAL)
+    b.metadata = {"vip_user": 1}
+    c = new_message("c", "u", "this is urgent", Priority.NORMAL)
+    qm.batch_triage([a, b, c], p)
+    assert [int(m.priority) for m in (a, b, c)] == [1, 2, 2]
+    assert [m.queue_name for m in (a, b, c)] == ["normal", "normal", "high"]
+    via_push = QueueManager(QueueManagerConfig(default_max_size=0, priority_adjust_rules=rules, builtin_rules=True))
+    for name in ("realtime", "high", "normal", "low"):
+        via_push.create_queue(name)
+    a2 = new_message("c", "u", "nothing special", Priority.NORMAL)
+    a2.metadata = {"escalate": 1, "vip_user": 1}
+    via_push.push_message("normal", a2)
+    assert int(a2.priority) == int(a.priority)
+    assert qm.drain(5) == [c, a, b]      # queue high first; inside "normal" the item priorities 1 < 2 decide

@@ -1,7 +1,7 @@
 """CPU test (gloo, world_size 2) of the N>1 host logic: contiguous sharding, rank bases, and the contract of the
 merge — all-gathered per-rank sorted runs merged by (bucket, time key, rank) equal the whole-job dequeue order.
-The per-rank engine is played by the oracle here; the GPU merge kernels are checked against the same reference merge
-in the gpu-marked test below."""
+The per-rank engine is played by the oracle here; the GPU merge kernels (concat_kernel, merge_strided_kernel) are checked
+against the same reference merge and against the whole-job oracle order in tests/test_gpu_multigpu.py (two GPUs)."""
 import os
 import socket
 

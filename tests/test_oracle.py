@@ -131,3 +131,35 @@ def test_custom_patterns_case_sensitive_and_bordered():
         pc = P.scores(po.decode(c))
         assert sc[1:] == [pc.get(p, 0) for p in (1, 2, 3, 4)], c
     assert co.scores(d, b"hahahaha")[4] == 2 and co.scores(d, b"hahaha")[4] == 1
+
+
+def test_fast_mode_of_the_oracle_gives_the_per_pattern_scores():
+    """orc_dict_set_fast (one trie pass for border-free case-sensitive literals, byte search for self-overlapping ones) is
+    what produced the full-size digests of the 10 000-keyword config; it must equal the per-pattern passes that follow
+    preprocessor.go:144-149 literally - checked here on traffic that carries the dictionary, self-overlaps included."""
+    from tests import c5
+    entries = c5.dictionary(2500)
+    slow, fast = co.Dict(), co.Dict()
+    for p, ci, lit in entries:
+        assert slow.add(p, lit, ci) == 0 and fast.add(p, lit, ci) == 0
+    for lit in (b"na\xc3\xafve", "étéété".encode(), b"zz"):   # non-ASCII literals, bordered ones
+        assert slow.add(3, lit, False) == 0 and fast.add(3, lit, False) == 0
+    fast.set_fast()
+    off, data, meta, ts = co.generate(0xFA57, 400, 64, 1500, mix=2, edge=400)
+    contents = c5.inject([bytes(data[int(off[i]):int(off[i + 1])]) for i in range(len(meta))], entries)
+    contents[3] += "naïve étéétéété zzzzz \xc3".encode("latin-1", "ignore") + b"\xc3\xa9t\xc3" + "été".encode()
+    off, data = co.pack(contents)
+    a = co.process_batch(slow, off, data, meta, nthreads=4)
+    b = co.process_batch(fast, off, data, meta, nthreads=4)
+    assert a.tobytes() == b.tobytes()
+    assert (a["label"] == 4).sum() > 50 and len(set(a["label"].tolist())) >= 3
+
+
+def test_full_size_digests_are_committed_for_every_config():
+    from tests import fullsize
+    dig = fullsize.load()
+    for name, cfg in fullsize.CONFIGS.items():
+        assert name in dig and dig[name]["messages"] == cfg[1]
+        for f in fullsize.FIELDS + ("order",):
+            assert len(dig[name][f]) == 64
+    assert dig["c4_rules"]["label_histogram"][4] > 16000      # rules on: every non-VIP long message -> Low
