@@ -31,7 +31,7 @@ extern "C" {
 #define TRIAGE_E_NOT_FOUND   1   /* ErrQueueNotFound */
 #define TRIAGE_E_FULL        2   /* ErrQueueFull     */
 #define TRIAGE_E_EMPTY       3   /* ErrQueueEmpty    */
-#define TRIAGE_E_PATTERN     4   /* AddKeywordPattern: not a (optionally "(?i)") literal, or unsupported */
+#define TRIAGE_E_PATTERN     4   /* AddKeywordPattern: pattern outside the supported regexp subset */
 #define TRIAGE_E_ARG         5
 #define TRIAGE_E_CUDA        100 /* CUDA / NCCL failure, see triage_last_error() */
 
@@ -99,8 +99,12 @@ const char *triage_last_error(void);
 /* -- dictionary.  Replaces the pattern table built in NewPreprocessor (preprocessor.go:28-43),
  *    AddKeywordPattern (:176-184), SetDefaultPriority (:187) and GetKeywordPatterns (:192). */
 int32_t triage_dict_reset(triage_engine *e, int32_t with_defaults);
-/* regexp source as AddKeywordPattern receives it: optional "(?i)" then a literal (metacharacters
- * must be backslash-escaped).  Anything else -> TRIAGE_E_PATTERN (stated API deviation). */
+/* regexp source as AddKeywordPattern receives it (preprocessor.go:176-184 hands it to regexp.Compile).  A plain,
+ * optionally "(?i)"-prefixed literal joins the scan automaton.  Anything else is compiled as a regular expression of the
+ * supported RE2 subset - leading (?i)/(?s), classes, ".", \d \w \s, groups, alternation, ? * + {n,m} and their lazy
+ * forms - and counted on the device with FindAllString's leftmost-first, non-overlapping semantics (csrc/regex_vm.h).
+ * Outside the subset (anchors, \b, named groups, POSIX classes, patterns that can match "", non-ASCII under (?i), more
+ * than 64 instructions) -> TRIAGE_E_PATTERN with the reason: the stated API deviation, never a silent approximation. */
 int32_t triage_dict_add_pattern(triage_engine *e, int32_t prio, const char *regex, uint32_t len);
 int32_t triage_dict_add_literal(triage_engine *e, int32_t prio, const uint8_t *lit, uint32_t len, int32_t ci);
 int32_t triage_dict_commit(triage_engine *e);            /* compile + upload the automaton */
@@ -199,6 +203,39 @@ int32_t triage_queue_size(triage_engine *e, int32_t level, uint64_t *size);     
 int32_t triage_stats(triage_engine *e, int32_t level, triage_qstats *st);         /* GetStats, :165 */
 int32_t triage_complete(triage_engine *e, int32_t level);                         /* CompleteMessage, :197 */
 int32_t triage_fail(triage_engine *e, int32_t level);                             /* FailMessage, :205 */
+
+/* -- batch consumer side.  triage_drain_queue = QueueManager.BatchPopMessages(queueName, count) (queue_manager.go:326-367):
+ *    pops from ONE queue until it is empty or max is reached, under one lock and with one statistics update
+ *    (Pending -= k, Processing += k; queue.go:132-136 k times).  triage_complete_batch / triage_fail_batch =
+ *    CompleteMessage / FailMessage (queue.go:197-211) for k messages of a Worker.processBatch round (worker.go:128-158). */
+int32_t triage_drain_queue(triage_engine *e, int32_t queue, uint32_t max, uint64_t *handles, uint32_t *n_out);
+int32_t triage_complete_batch(triage_engine *e, int32_t queue, uint32_t k);
+int32_t triage_fail_batch(triage_engine *e, int32_t queue, uint32_t k);
+/* Retry of failed messages, Worker.handleFailure (worker.go:208-229), and DeadLetterQueue.Requeue / BatchRequeue
+ * (dead_letter_queue.go:187-258): QueueManager.PushMessage(queueName, message) for n messages that already have handles,
+ * in the given order - capacity rule per message (queue.go:101-103; accepted[i] = 0 where the queue was full, n_accepted
+ * = the count BatchRequeue returns), a fresh enqueue time each (enqueue_ns NULL: stamped strictly increasing, queue.go:108),
+ * so a retry goes behind everything of its priority that is already waiting.  item_priority = int(msg.Priority) after the
+ * shim applied its rules.  The accepted messages are ordered by (priority, time, arrival) - on the device for batches of
+ * 32768 and more (the LSD radix passes of the submit path), on the host below that - and merged into the queue as one run. */
+int32_t triage_requeue(triage_engine *e, int32_t queue, const uint64_t *handles, const int32_t *item_priority, const uint64_t *enqueue_ns,
+                       uint32_t n, uint8_t *accepted, uint32_t *n_accepted);
+/* DelayedQueue (delayed_queue.go): Schedule(message, readyAt) (:98-111) for n messages; the engine keeps them ordered by
+ * ReadyAt (Less, :37-39; equal times: arrival).  triage_release_due plays the run loop (:113-170) at time `now` (0 = the
+ * wall clock): every item whose ReadyAt has passed goes, earliest first, to processFn = PushMessage into the queue it
+ * was scheduled for, stamped at the release; handles/queues (nullable, room for max entries; max = 0: no limit)
+ * receive what was released, n_rejected counts pushes a full or deleted queue turned away.  This is where
+ * Worker.handleFailure's ScheduledAt (worker.go:220-229) becomes effective - the reference leaves that as a comment.
+ * triage_delayed_peek = DelayedQueue.Peek (earliest item; TRIAGE_E_EMPTY when none). */
+int32_t triage_schedule(triage_engine *e, int32_t queue, const uint64_t *handles, const int32_t *item_priority, const uint64_t *ready_at_ns,
+                        uint32_t n);
+int32_t triage_release_due(triage_engine *e, uint64_t now_ns, uint64_t *handles, int32_t *queues, uint32_t max, uint32_t *n_released,
+                           uint32_t *n_rejected);
+int32_t triage_delayed_peek(triage_engine *e, uint64_t *handle, uint64_t *ready_at_ns);
+int32_t triage_delayed_size(triage_engine *e, uint64_t *n);
+/* ExponentialBackoff.NextBackoff(retryCount) (worker.go:274-290) in nanoseconds: initial * factor^(retryCount-1) in float64,
+ * capped at max, truncated like time.Duration(backoff). */
+int64_t triage_backoff_ns(int64_t initial_ns, int64_t max_ns, double factor, int32_t retry_count);
 
 /* -- instrumentation: device times (CUDA events on the engine's stream) of the last submit */
 typedef struct {

@@ -11,7 +11,11 @@ from .preprocessor import Preprocessor, new_preprocessor
 from .priorityqueue import (ErrQueueEmpty, ErrQueueFull, ErrQueueNotFound, MultiLevelQueue, PriorityAdjustRule,
                             QueueError, QueueManager, QueueManagerConfig, QueueStats, builtin_priority_rules)
 
-__all__ = ["_capi", "Engine", "TriageError", "build", "META_DTYPE", "RESULT_DTYPE", "Message", "Priority", "new_message",
+from .consumer import (DeadLetterItem, DeadLetterQueue, DelayedQueue, ErrIndexOutOfRange, ExponentialBackoff,  # noqa: E402
+                       FixedBackoff, handle_failures)
+
+__all__ = ["ExponentialBackoff", "FixedBackoff", "DelayedQueue", "DeadLetterQueue", "DeadLetterItem", "ErrIndexOutOfRange", "handle_failures",
+           "_capi", "Engine", "TriageError", "build", "META_DTYPE", "RESULT_DTYPE", "Message", "Priority", "new_message",
            "priority_name", "Preprocessor", "new_preprocessor", "MultiLevelQueue", "QueueManager", "QueueManagerConfig",
            "QueueStats", "QueueError", "ErrQueueEmpty", "ErrQueueFull", "ErrQueueNotFound", "PriorityAdjustRule",
            "builtin_priority_rules"]

@@ -104,6 +104,15 @@ _SIGS = {
     "triage_stats": (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(QStats)]),
     "triage_complete": (C.c_int32, [C.c_void_p, C.c_int32]),
     "triage_fail": (C.c_int32, [C.c_void_p, C.c_int32]),
+    "triage_drain_queue": (C.c_int32, [C.c_void_p, C.c_int32, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint32)]),
+    "triage_complete_batch": (C.c_int32, [C.c_void_p, C.c_int32, C.c_uint32]),
+    "triage_fail_batch": (C.c_int32, [C.c_void_p, C.c_int32, C.c_uint32]),
+    "triage_requeue": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint32)]),
+    "triage_schedule": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]),
+    "triage_release_due": (C.c_int32, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+    "triage_delayed_peek": (C.c_int32, [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "triage_delayed_size": (C.c_int32, [C.c_void_p, C.POINTER(C.c_uint64)]),
+    "triage_backoff_ns": (C.c_int64, [C.c_int64, C.c_int64, C.c_double, C.c_int32]),
     "triage_last_timings": (C.c_int32, [C.c_void_p, C.POINTER(Timings)]),
     "triage_event_record": (C.c_int32, [C.c_void_p, C.c_int32]),
     "triage_event_elapsed_ms": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_float)]),
@@ -343,6 +352,55 @@ class Engine:
     def fail(self, q: int):
         _check(lib().triage_fail(self._h, int(q)))
 
+    # -- batch consumer, retries, delayed items --------------------------------
+    def drain_queue(self, q: int, max_items: int):
+        """BatchPopMessages: handles popped from one queue, until it is empty or max_items"""
+        handles = np.zeros(max(max_items, 1), np.uint64)
+        k = C.c_uint32()
+        _check(lib().triage_drain_queue(self._h, int(q), int(max_items), _p(handles), C.byref(k)))
+        return handles[:k.value]
+
+    def complete_batch(self, q: int, k: int):
+        _check(lib().triage_complete_batch(self._h, int(q), int(k)))
+
+    def fail_batch(self, q: int, k: int):
+        _check(lib().triage_fail_batch(self._h, int(q), int(k)))
+
+    def requeue(self, q: int, handles, item_priority, enqueue_ns=None):
+        """PushMessage for messages that already have handles (retries, dead-letter requeue) -> accepted u8[n]"""
+        handles = np.ascontiguousarray(handles, np.uint64)
+        prio = np.ascontiguousarray(item_priority, np.int32)
+        ts = None if enqueue_ns is None else np.ascontiguousarray(enqueue_ns, np.uint64)
+        acc = np.zeros(max(len(handles), 1), np.uint8)
+        k = C.c_uint32()
+        _check(lib().triage_requeue(self._h, int(q), _p(handles), _p(prio), _p(ts), len(handles), _p(acc), C.byref(k)))
+        return acc[:len(handles)]
+
+    def schedule(self, q: int, handles, item_priority, ready_at_ns):
+        handles = np.ascontiguousarray(handles, np.uint64)
+        prio = np.ascontiguousarray(item_priority, np.int32)
+        ready = np.ascontiguousarray(ready_at_ns, np.uint64)
+        _check(lib().triage_schedule(self._h, int(q), _p(handles), _p(prio), _p(ready), len(handles)))
+
+    def release_due(self, now_ns: int = 0, max_items: int = 0):
+        """-> (handles released in ReadyAt order, their queues, number a full or deleted queue turned away)"""
+        cap = max_items if max_items else max(self.delayed_size(), 1)
+        handles = np.zeros(cap, np.uint64)
+        queues = np.zeros(cap, np.int32)
+        k, r = C.c_uint32(), C.c_uint32()
+        _check(lib().triage_release_due(self._h, int(now_ns), _p(handles), _p(queues), int(max_items), C.byref(k), C.byref(r)))
+        return handles[:k.value], queues[:k.value], r.value
+
+    def delayed_peek(self):
+        h, t = C.c_uint64(), C.c_uint64()
+        _check(lib().triage_delayed_peek(self._h, C.byref(h), C.byref(t)))
+        return h.value, t.value
+
+    def delayed_size(self) -> int:
+        n = C.c_uint64()
+        _check(lib().triage_delayed_size(self._h, C.byref(n)))
+        return n.value
+
     # -- multi-GPU ------------------------------------------------------------
     @staticmethod
     def comm_unique_id() -> bytes:
@@ -357,3 +415,8 @@ class Engine:
         tot = C.c_uint64()
         _check(lib().triage_merge_allgather(self._h, _p(rank_base), order_global_ptr, int(capacity), C.byref(tot)))
         return tot.value
+
+
+def backoff_ns(initial_ns: int, max_ns: int, factor: float, retry_count: int) -> int:
+    """ExponentialBackoff.NextBackoff (worker.go:274-290) in nanoseconds"""
+    return int(lib().triage_backoff_ns(int(initial_ns), int(max_ns), float(factor), int(retry_count)))

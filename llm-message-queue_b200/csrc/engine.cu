@@ -20,6 +20,7 @@
 #include "../../include/triage.h"
 #include "dfa_build.h"
 #include "kernels.cuh"
+#include "regex_vm.h"
 
 using namespace triage;
 
@@ -154,6 +155,12 @@ struct triage_engine {
     cudaEvent_t user_ev[4]{};
     int32_t default_prio = TRIAGE_PRIO_NORMAL;
     std::vector<DictEntry> dict;
+    RegexSet regex;                // AddKeywordPattern patterns that are not plain literals (regex_vm.h)
+    DevBuf<RegexProgram> d_rx_prog;
+    DevBuf<RegexInst> d_rx_inst;
+    DevBuf<RegexClass> d_rx_cls;
+    DevBuf<uint32_t> d_rx_rng;
+    RegexView rxview{};            // device view, n_programs == 0: none
     bool dict_dirty = true;
     Dfa dfa;
     ScanGeometry geom{0, 0, 0};
@@ -185,6 +192,14 @@ struct triage_engine {
     std::vector<LevelQueue> q;   // q[0] unused; 1..4 = realtime/high/normal/low; further ids from triage_queue_create
     uint64_t next_handle = 1;
     uint64_t next_stamp = 0;
+    // DelayedQueue (delayed_queue.go): items waiting for their ReadyAt, sorted by (ready_at, arrival) from `dhead`
+    struct Delayed { uint64_t ready_at, seq, handle; int32_t queue, prio; };
+    std::vector<Delayed> delayed;
+    size_t dhead = 0;
+    uint64_t delayed_seq = 0;
+    DevBuf<uint64_t> d_keys;       // device sorter for big requeue / schedule batches
+    DevBuf<uint8_t> d_kprio;
+    DevBuf<uint32_t> d_korder;
     triage_timings tm{};
     // last device run (for the multi-GPU merge)
     const uint32_t *last_order = nullptr;
@@ -275,6 +290,19 @@ int32_t commit_dict(triage_engine *e) {
         if (!err.empty()) return fail(TRIAGE_E_PATTERN, "exact automaton: " + err);
         rc = upload_dfa(xd, &e->dx, &e->dxdfa);
         if (rc) return rc;
+    }
+    e->rxview = RegexView{};
+    if (!e->regex.empty()) {
+        const RegexSet &r = e->regex;
+        CU(e->d_rx_prog.ensure(r.programs.size()));
+        CU(e->d_rx_inst.ensure(r.insts.size()));
+        CU(e->d_rx_cls.ensure(r.classes.size()));
+        CU(e->d_rx_rng.ensure(r.ranges.size() + 2));
+        CU(cudaMemcpy(e->d_rx_prog.p, r.programs.data(), r.programs.size() * sizeof(RegexProgram), cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(e->d_rx_inst.p, r.insts.data(), r.insts.size() * sizeof(RegexInst), cudaMemcpyHostToDevice));
+        CU(cudaMemcpy(e->d_rx_cls.p, r.classes.data(), r.classes.size() * sizeof(RegexClass), cudaMemcpyHostToDevice));
+        if (!r.ranges.empty()) CU(cudaMemcpy(e->d_rx_rng.p, r.ranges.data(), r.ranges.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+        e->rxview = RegexView{e->d_rx_prog.p, e->d_rx_inst.p, e->d_rx_cls.p, e->d_rx_rng.p, (uint32_t)r.programs.size()};
     }
     e->ddfa = d;
     e->pad_warps = pad_warps;
@@ -368,6 +396,7 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
         CU(cudaEventRecord(e->ev[1], s));
     }
     if (e->has_bordered && ntiles) { CU(launch_fixup(bytes, offsets, lengths, n, e->dxdfa, e->d_counters.p, s)); launches++; }
+    if (e->rxview.n_programs && ntiles) { CU(launch_regex_count(e->rxview, bytes, offsets, lengths, n, e->d_counters.p, e->sm_count, s)); launches++; }
     CU(cudaEventRecord(e->ev[2], s));
     const int32_t single = mode == RUN_SINGLE_QUEUE ? 1 : 0;
     FinalizeArgs fa{lengths, bytes, e->d_counters.p, meta, offsets, ts, n, e->default_prio, mode == RUN_PROCESS_ONLY ? 0 : e->opts.rules_enabled,
@@ -498,6 +527,8 @@ void triage_destroy(triage_engine *e) {
     }
     e->d_tilectr.release();
     if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
+    e->d_rx_prog.release(); e->d_rx_inst.release(); e->d_rx_cls.release(); e->d_rx_rng.release();
+    e->d_keys.release(); e->d_kprio.release(); e->d_korder.release();
     e->dm.release(); e->dx.release(); e->d_bytes.release(); e->d_offsets.release();
     e->d_ts.release(); e->d_pending.release(); e->d_maxsize.release(); e->d_meta.release(); e->d_results.release(); e->d_counters.release();
     e->d_tile_first.release(); e->d_lengths.release(); e->d_order.release(); e->d_perm_a.release(); e->d_perm_b.release(); e->d_blockhist.release();
@@ -515,6 +546,7 @@ void triage_destroy(triage_engine *e) {
 int32_t triage_dict_reset(triage_engine *e, int32_t with_defaults) {
     if (!e) return fail(TRIAGE_E_ARG, "null engine");
     e->dict.clear();
+    e->regex.clear();
     if (with_defaults) {
         for (const char *w : {"immediate", "emergency", "asap", "right now"}) e->dict.push_back({TRIAGE_PRIO_REALTIME, true, w});
         for (const char *w : {"urgent", "important", "priority", "critical", "soon"}) e->dict.push_back({TRIAGE_PRIO_HIGH, true, w});
@@ -536,10 +568,17 @@ int32_t triage_dict_add_literal(triage_engine *e, int32_t prio, const uint8_t *l
 
 int32_t triage_dict_add_pattern(triage_engine *e, int32_t prio, const char *regex, uint32_t len) {
     if (!e || !regex) return fail(TRIAGE_E_ARG, "null argument");
+    if (prio < 1 || prio > 4) return fail(TRIAGE_E_PATTERN, "priority must be 1..4");
     bool ci = false;
     std::string lit, err;
-    if (!parse_regex_literal(regex, len, &ci, &lit, &err)) return fail(TRIAGE_E_PATTERN, err);
-    return triage_dict_add_literal(e, prio, reinterpret_cast<const uint8_t *>(lit.data()), (uint32_t)lit.size(), ci ? 1 : 0);
+    // plain (optionally "(?i)") literals go into the scan automaton; anything else is compiled as a regular expression
+    // of the supported subset (regex_vm.h) and counted by the regex kernel
+    if (parse_regex_literal(regex, len, &ci, &lit, &err))
+        return triage_dict_add_literal(e, prio, reinterpret_cast<const uint8_t *>(lit.data()), (uint32_t)lit.size(), ci ? 1 : 0);
+    err = regex_compile(regex, len, (uint32_t)prio, &e->regex);
+    if (!err.empty()) return fail(TRIAGE_E_PATTERN, "regexp outside the supported subset: " + err);
+    e->dict_dirty = true;
+    return TRIAGE_OK;
 }
 
 int32_t triage_dict_commit(triage_engine *e) {
@@ -552,6 +591,7 @@ int32_t triage_dict_count(triage_engine *e, int32_t prio, uint32_t *n) {
     if (!e || !n) return fail(TRIAGE_E_ARG, "null argument");
     uint32_t c = 0;
     for (auto &d : e->dict) if (d.prio == prio) c++;
+    for (auto &r : e->regex.programs) if ((int32_t)r.prio == prio) c++;
     *n = c;
     return TRIAGE_OK;
 }
@@ -1049,6 +1089,265 @@ int32_t triage_fail(triage_engine *e, int32_t level) {
     return TRIAGE_OK;
 }
 
+}  // extern "C"
+
+namespace {
+
+// Stable order of n items by (bucket, 64-bit key, index) on the device: the LSD radix passes and the bucket split that
+// order a submit whose enqueue times are not monotone (run_device), applied to keys that come from the host.  Used for
+// large retry / schedule batches; order_out receives the permutation.  bucket == nullptr: one bucket.
+int32_t device_sort_keys(triage_engine *e, const uint8_t *bucket, const uint64_t *keys, uint32_t n, uint32_t *order_out) {
+    cudaStream_t s = e->stream;
+    const uint32_t nblocks = (n + kOrderBlock - 1) / kOrderBlock;
+    CU(e->d_keys.ensure(n));
+    CU(e->d_kprio.ensure(n));
+    CU(e->d_korder.ensure(n));
+    CU(e->d_perm_a.ensure(n));
+    CU(e->d_perm_b.ensure(n));
+    CU(e->d_blockhist.ensure((size_t)nblocks * 256));
+    CU(e->d_totals.ensure(260));
+    CU(e->d_small.ensure(32 + 8 * 256));
+    OrderScratch sc{e->d_blockhist.p, e->d_totals.p, nblocks};
+    CU(cudaMemcpyAsync(e->d_keys.p, keys, (size_t)n * 8, cudaMemcpyHostToDevice, s));
+    if (bucket) CU(cudaMemcpyAsync(e->d_kprio.p, bucket, n, cudaMemcpyHostToDevice, s));
+    else CU(cudaMemsetAsync(e->d_kprio.p, 0, n, s));
+    CU(cudaMemsetAsync(e->d_small.p, 0, (32 + 8 * 256) * sizeof(uint32_t), s));
+    CU(launch_key_digit_hist(e->d_keys.p, nullptr, n, e->d_small.p + 32, s));
+    CU(cudaMemcpyAsync(e->h_small + 32, e->d_small.p + 32, 8 * 256 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    const uint32_t *perm = nullptr;
+    uint32_t *bufs[2] = {e->d_perm_a.p, e->d_perm_b.p};
+    int which = 0;
+    for (uint32_t b = 0; b < 8; b++) {
+        bool trivial = false;
+        for (uint32_t d = 0; d < 256; d++) if (e->h_small[32 + b * 256 + d] == n) trivial = true;
+        if (trivial) continue;   // every key has the same digit here
+        CU(launch_partition_key(e->d_keys.p, 8 * b, perm, n, bufs[which], sc, s));
+        perm = bufs[which];
+        which ^= 1;
+    }
+    CU(launch_partition_u8(e->d_kprio.p, perm, n, 16, false, e->d_korder.p, nullptr, sc, s));
+    CU(cudaMemcpyAsync(order_out, e->d_korder.p, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    return TRIAGE_OK;
+}
+
+constexpr uint32_t kDeviceSortMin = 1u << 15;   // below this a host sort is faster than the round trip
+
+// order of items by (bucket, key, index); buckets must be < 16 for the device path
+int32_t sort_keys(triage_engine *e, const uint8_t *bucket, const uint64_t *keys, uint32_t n, std::vector<uint32_t> *order) {
+    order->resize(n);
+    if (n >= kDeviceSortMin) {
+        bool fits = true;
+        if (bucket) for (uint32_t i = 0; i < n && fits; i++) fits = bucket[i] < 16;
+        if (fits && cudaSetDevice(e->opts.device) == cudaSuccess) return device_sort_keys(e, bucket, keys, n, order->data());
+    }
+    for (uint32_t i = 0; i < n; i++) (*order)[i] = i;
+    std::stable_sort(order->begin(), order->end(), [&](uint32_t a, uint32_t b) {
+        const uint32_t ba = bucket ? bucket[a] : 0, bb = bucket ? bucket[b] : 0;
+        if (ba != bb) return ba < bb;
+        return keys[a] < keys[b];
+    });
+    return TRIAGE_OK;
+}
+
+// PushMessage for items that already have handles: capacity in arrival order (queue.go:101-103), then one sorted run
+// merged into the queue.  prio: item priorities; ts: enqueue times.  Caller holds e->mu.
+int32_t push_run(triage_engine *e, int32_t queue, const uint64_t *handles, const int32_t *prio, const uint64_t *ts, uint32_t n,
+                 uint8_t *accepted, uint32_t *n_accepted) {
+    LevelQueue &lq = e->q[queue];
+    std::vector<uint32_t> adm;
+    adm.reserve(n);
+    for (uint32_t i = 0; i < n; i++) {
+        const bool ok = lq.max_size <= 0 || (int64_t)(lq.size() + adm.size()) < lq.max_size;
+        if (accepted) accepted[i] = ok ? 1 : 0;
+        if (ok) adm.push_back(i);
+    }
+    *n_accepted = (uint32_t)adm.size();
+    if (adm.empty()) return TRIAGE_OK;
+    std::vector<uint8_t> bucket(adm.size());
+    std::vector<uint64_t> keys(adm.size());
+    bool small_prio = true;
+    for (size_t k = 0; k < adm.size(); k++) {
+        const int32_t p = prio[adm[k]];
+        if (p < 0 || p > 15) small_prio = false;
+        bucket[k] = (uint8_t)(p < 0 ? 0 : (p > 15 ? 15 : p));
+        keys[k] = ts[adm[k]];
+    }
+    std::vector<uint32_t> order;
+    if (small_prio) {
+        int32_t rc = sort_keys(e, bucket.data(), keys.data(), (uint32_t)adm.size(), &order);
+        if (rc) return rc;
+    } else {   // priorities outside 0..15: plain comparison sort on the real values
+        order.resize(adm.size());
+        for (uint32_t i = 0; i < order.size(); i++) order[i] = i;
+        std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) {
+            if (prio[adm[a]] != prio[adm[b]]) return prio[adm[a]] < prio[adm[b]];
+            return keys[a] < keys[b];
+        });
+    }
+    const size_t run_begin = lq.items.size();
+    lq.items.resize(run_begin + adm.size());
+    for (size_t k = 0; k < adm.size(); k++) {
+        const uint32_t i = adm[order[k]];
+        lq.items[run_begin + k] = QItem{prio[i], ts[i], handles[i]};
+    }
+    // equal (priority, time): the queue's total order falls back to the handle; the run above is stable by arrival
+    std::stable_sort(lq.items.begin() + run_begin, lq.items.end(), qless);
+    if (run_begin > lq.head && qless(lq.items[run_begin], lq.items[run_begin - 1]))
+        std::inplace_merge(lq.items.begin() + lq.head, lq.items.begin() + run_begin, lq.items.end(), qless);
+    lq.st.pending += (int64_t)adm.size();
+    return TRIAGE_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+// QueueManager.BatchPopMessages(queueName, count) (queue_manager.go:326-367): pops until the queue is empty
+int32_t triage_drain_queue(triage_engine *e, int32_t queue, uint32_t max, uint64_t *handles, uint32_t *n_out) {
+    if (!e || !n_out || (max && !handles)) return fail(TRIAGE_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lock(e->mu);
+    *n_out = 0;
+    if (!queue_ok(e, queue)) return fail(TRIAGE_E_NOT_FOUND, "queue not found");   // :330-333
+    LevelQueue &lq = e->q[queue];
+    uint32_t k = 0;
+    while (k < max && lq.size()) handles[k++] = lq.items[lq.head++].handle;
+    lq.st.pending -= k;
+    lq.st.processing += k;
+    lq.compact();
+    *n_out = k;
+    return TRIAGE_OK;
+}
+
+int32_t triage_complete_batch(triage_engine *e, int32_t queue, uint32_t k) {
+    if (!e) return fail(TRIAGE_E_ARG, "null engine");
+    std::lock_guard<std::mutex> lock(e->mu);
+    if (!queue_ok(e, queue)) return TRIAGE_OK;   // updateStats ignores unknown queues (queue.go:192)
+    e->q[queue].st.processing -= k;
+    e->q[queue].st.completed += k;
+    return TRIAGE_OK;
+}
+
+int32_t triage_fail_batch(triage_engine *e, int32_t queue, uint32_t k) {
+    if (!e) return fail(TRIAGE_E_ARG, "null engine");
+    std::lock_guard<std::mutex> lock(e->mu);
+    if (!queue_ok(e, queue)) return TRIAGE_OK;
+    e->q[queue].st.processing -= k;
+    e->q[queue].st.failed += k;
+    return TRIAGE_OK;
+}
+
+int32_t triage_requeue(triage_engine *e, int32_t queue, const uint64_t *handles, const int32_t *item_priority, const uint64_t *enqueue_ns,
+                       uint32_t n, uint8_t *accepted, uint32_t *n_accepted) {
+    if (!e || !n_accepted || (n && (!handles || !item_priority))) return fail(TRIAGE_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lock(e->mu);
+    *n_accepted = 0;
+    if (!queue_ok(e, queue)) return fail(TRIAGE_E_NOT_FOUND, "queue not found");
+    if (n == 0) return TRIAGE_OK;
+    std::vector<uint64_t> stamped;
+    if (!enqueue_ns) {   // queue.go:108: time.Now() inside Push, strictly increasing in push order
+        stamped.resize(n);
+        const uint64_t t0 = std::max(now_ns(), e->next_stamp);
+        for (uint32_t i = 0; i < n; i++) stamped[i] = t0 + i;
+        e->next_stamp = t0 + n;
+        enqueue_ns = stamped.data();
+    }
+    return push_run(e, queue, handles, item_priority, enqueue_ns, n, accepted, n_accepted);
+}
+
+int32_t triage_schedule(triage_engine *e, int32_t queue, const uint64_t *handles, const int32_t *item_priority, const uint64_t *ready_at_ns,
+                        uint32_t n) {
+    if (!e || (n && (!handles || !item_priority || !ready_at_ns))) return fail(TRIAGE_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lock(e->mu);
+    if (!queue_ok(e, queue)) return fail(TRIAGE_E_NOT_FOUND, "queue not found");
+    if (n == 0) return TRIAGE_OK;
+    std::vector<uint32_t> order;
+    int32_t rc = sort_keys(e, nullptr, ready_at_ns, n, &order);   // DelayedQueue.Less: ReadyAt only (delayed_queue.go:37-39)
+    if (rc) return rc;
+    if (e->dhead > 4096 && e->dhead * 2 > e->delayed.size()) { e->delayed.erase(e->delayed.begin(), e->delayed.begin() + e->dhead); e->dhead = 0; }
+    const size_t run_begin = e->delayed.size();
+    e->delayed.resize(run_begin + n);
+    const uint64_t seq0 = e->delayed_seq;
+    for (uint32_t k = 0; k < n; k++) {
+        const uint32_t i = order[k];
+        e->delayed[run_begin + k] = triage_engine::Delayed{ready_at_ns[i], seq0 + i, handles[i], queue, item_priority[i]};
+    }
+    e->delayed_seq += n;
+    auto less = [](const triage_engine::Delayed &a, const triage_engine::Delayed &b) {
+        if (a.ready_at != b.ready_at) return a.ready_at < b.ready_at;
+        return a.seq < b.seq;
+    };
+    if (run_begin > e->dhead && less(e->delayed[run_begin], e->delayed[run_begin - 1]))
+        std::inplace_merge(e->delayed.begin() + e->dhead, e->delayed.begin() + run_begin, e->delayed.end(), less);
+    return TRIAGE_OK;
+}
+
+int32_t triage_delayed_size(triage_engine *e, uint64_t *n) {
+    if (!e || !n) return fail(TRIAGE_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lock(e->mu);
+    *n = e->delayed.size() - e->dhead;
+    return TRIAGE_OK;
+}
+
+int32_t triage_delayed_peek(triage_engine *e, uint64_t *handle, uint64_t *ready_at_ns) {
+    if (!e || !handle || !ready_at_ns) return fail(TRIAGE_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lock(e->mu);
+    if (e->delayed.size() == e->dhead) return fail(TRIAGE_E_EMPTY, "nothing is scheduled");
+    *handle = e->delayed[e->dhead].handle;
+    *ready_at_ns = e->delayed[e->dhead].ready_at;
+    return TRIAGE_OK;
+}
+
+int32_t triage_release_due(triage_engine *e, uint64_t now, uint64_t *handles, int32_t *queues, uint32_t max, uint32_t *n_released,
+                           uint32_t *n_rejected) {
+    if (!e || !n_released) return fail(TRIAGE_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lock(e->mu);
+    *n_released = 0;
+    if (n_rejected) *n_rejected = 0;
+    if (now == 0) now = now_ns();
+    // the run loop of delayed_queue.go:113-170 hands every item whose ReadyAt has passed to processFn, earliest first;
+    // processFn here is PushMessage into the queue the item was scheduled for, stamped at the release
+    size_t end = e->dhead;
+    while (end < e->delayed.size() && e->delayed[end].ready_at <= now && (max == 0 || end - e->dhead < max)) end++;
+    const uint32_t due = (uint32_t)(end - e->dhead);
+    if (!due) return TRIAGE_OK;
+    uint64_t t0 = std::max(now_ns(), e->next_stamp);
+    e->next_stamp = t0 + due;
+    uint32_t released = 0, rejected = 0;
+    // group by destination queue, keeping the ReadyAt order inside each
+    std::vector<int32_t> qs;
+    for (size_t k = e->dhead; k < end; k++) if (std::find(qs.begin(), qs.end(), e->delayed[k].queue) == qs.end()) qs.push_back(e->delayed[k].queue);
+    for (int32_t q : qs) {
+        std::vector<uint64_t> h, ts;
+        std::vector<int32_t> pr;
+        for (size_t k = e->dhead; k < end; k++) if (e->delayed[k].queue == q) { h.push_back(e->delayed[k].handle); pr.push_back(e->delayed[k].prio); ts.push_back(t0 + (k - e->dhead)); }
+        if (!queue_ok(e, q)) { rejected += (uint32_t)h.size(); continue; }   // the queue was deleted meanwhile: PushMessage fails
+        std::vector<uint8_t> acc(h.size());
+        uint32_t na = 0;
+        int32_t rc = push_run(e, q, h.data(), pr.data(), ts.data(), (uint32_t)h.size(), acc.data(), &na);
+        if (rc) return rc;
+        for (size_t k = 0; k < h.size(); k++) {
+            if (!acc[k]) { rejected++; continue; }
+            if (handles && (max == 0 || released < max)) { handles[released] = h[k]; if (queues) queues[released] = q; }
+            released++;
+        }
+    }
+    e->dhead = end;
+    *n_released = released;
+    if (n_rejected) *n_rejected = rejected;
+    return TRIAGE_OK;
+}
+
+// ExponentialBackoff.NextBackoff (worker.go:274-290): float64 arithmetic exactly as written there
+int64_t triage_backoff_ns(int64_t initial_ns, int64_t max_ns, double factor, int32_t retry_count) {
+    if (retry_count <= 0) return initial_ns;
+    double backoff = (double)initial_ns;
+    for (int32_t i = 1; i < retry_count; i++) backoff *= factor;
+    if (backoff > (double)max_ns) return max_ns;
+    return (int64_t)backoff;
+}
+
 int32_t triage_last_timings(triage_engine *e, triage_timings *t) {
     if (!e || !t) return fail(TRIAGE_E_ARG, "null argument");
     *t = e->tm;
@@ -1299,6 +1598,7 @@ extern "C" int32_t triage_submit_device_static(triage_engine *e, const uint64_t 
         CU(cudaEventRecord(e->ev[1], s));
     }
     if (e->has_bordered && ntiles) { CU(launch_fixup(bytes_dev, offsets_dev, nullptr, n, e->dxdfa, counters, s)); launches++; }
+    if (e->rxview.n_programs && ntiles) { CU(launch_regex_count(e->rxview, bytes_dev, offsets_dev, nullptr, n, counters, e->sm_count, s)); launches++; }
     CU(cudaEventRecord(e->ev[2], s));
     FinalizeArgs fa{nullptr, nullptr, counters, meta_dev, offsets_dev, enqueue_ns_dev, n, e->default_prio, e->opts.rules_enabled, 0, results_dev,
                     bucket, small};

@@ -932,6 +932,34 @@ cudaError_t launch_fixup(const uint8_t *bytes, const uint64_t *offsets, const ui
     return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------------------ regex patterns --
+// AddKeywordPattern with a real regular expression (regex_vm.h): one message per thread walks every compiled pattern over
+// its own bytes (ordered-thread simulation, regex_walk.cuh) and adds len(FindAllString) to the pattern's priority score.
+// Runs after the scan and the fix-up (which overwrites the counters of the messages it recounts) and before finalize.
+// Not a fast path: a dictionary pays for it only if it holds such patterns.
+__global__ void __launch_bounds__(128) regex_count_kernel(RegexView v, const uint8_t *__restrict__ bytes, const uint64_t *__restrict__ offsets,
+                                                          const uint32_t *__restrict__ lengths, uint32_t n, uint32_t *__restrict__ counters) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint64_t off = offsets[i];
+        const uint64_t len = lengths ? (uint64_t)lengths[i] : offsets[i + 1] - off;
+        if (len == 0) continue;
+        for (uint32_t p = 0; p < v.n_programs; p++) {
+            const uint32_t c = rx_count(v, p, bytes + off, len);
+            if (c) counters[(uint64_t)i * CNT_STRIDE + CNT_KW + (v.programs[p].prio - 1)] += c;
+        }
+    }
+}
+
+cudaError_t launch_regex_count(const RegexView &v, const uint8_t *bytes, const uint64_t *offsets, const uint32_t *lengths, uint32_t n,
+                               uint32_t *counters, int sm_count, cudaStream_t s) {
+    if (n == 0 || v.n_programs == 0) return cudaSuccess;
+    uint32_t blocks = (n + 127) / 128;
+    const uint32_t cap = (uint32_t)sm_count * 16;
+    if (blocks > cap) blocks = cap;
+    regex_count_kernel<<<blocks, 128, 0, s>>>(v, bytes, offsets, lengths, n, counters);
+    return cudaGetLastError();
+}
+
 // -------------------------------------------------------------------------------- finalize --
 __global__ void __launch_bounds__(256) finalize_kernel(FinalizeArgs a) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;

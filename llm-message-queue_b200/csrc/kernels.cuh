@@ -6,6 +6,7 @@
 #include "../../include/triage.h"
 #include "scan_core.cuh"
 #include "scan_wide.cuh"
+#include "regex_walk.cuh"
 
 namespace triage {
 
@@ -63,6 +64,10 @@ cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw,
 // sequential exact recount of the messages the scan flagged (self-overlapping keywords); `exact` points at global memory
 cudaError_t launch_fixup(const uint8_t *bytes, const uint64_t *offsets, const uint32_t *lengths, uint32_t n, const DeviceDfa &exact,
                          uint32_t *counters, cudaStream_t s);
+
+// regex patterns of the dictionary (regex_vm.h): adds every pattern's FindAllString count to its priority's score counter
+cudaError_t launch_regex_count(const RegexView &v, const uint8_t *bytes, const uint64_t *offsets, const uint32_t *lengths, uint32_t n,
+                               uint32_t *counters, int sm_count, cudaStream_t s);
 
 struct FinalizeArgs {
     const uint32_t *lengths;     // padded layout: true content lengths (else nullptr: len = offsets[i+1]-offsets[i])

@@ -234,15 +234,42 @@ class QueueManager:
         return self._msgs.pop(h)
 
     def batch_pop_messages(self, queue_name: str, count: int) -> list[Message]:
-        if queue_name not in self._ids:
+        qid = self._ids.get(queue_name)
+        if qid is None:
             raise ErrQueueNotFound
-        out = []
-        for _ in range(count):   # :336-342: stops at the first error, returns what it has
-            try:
-                out.append(self.pop_message(queue_name))
-            except QueueError:
-                break
-        return out
+        # :336-342 pops until the queue is empty and returns what it has: one engine call, one statistics update
+        return [self._msgs.pop(int(h)) for h in self.engine.drain_queue(qid, count)]
+
+    def requeue_batch(self, queue_name: str, messages: list[Message]) -> list[bool]:
+        """PushMessage(queue_name, m) for messages that are pushed AGAIN (worker.go:229 retries, dead-letter requeue): rules
+        applied per message, capacity in the given order, fresh enqueue times - one engine call.  -> accepted per message"""
+        qid = self._ids.get(queue_name)
+        if qid is None:
+            raise ErrQueueNotFound
+        if not messages:
+            return []
+        for m in messages:
+            self._apply_rules(m)
+        handles = [self._new_handle() for _ in messages]
+        acc = self.engine.requeue(qid, handles, [int(m.priority) for m in messages])
+        for h, m, a in zip(handles, messages, acc):
+            if a:
+                self._msgs[h] = m
+        return [bool(a) for a in acc]
+
+    def complete_batch(self, queue_name: str, k: int) -> None:
+        qid = self._ids.get(queue_name)
+        if qid is not None:
+            self.engine.complete_batch(qid, k)
+
+    def fail_batch(self, queue_name: str, k: int) -> None:
+        qid = self._ids.get(queue_name)
+        if qid is not None:
+            self.engine.fail_batch(qid, k)
+
+    def _new_handle(self) -> int:
+        self._requeue_handles = getattr(self, "_requeue_handles", 1 << 61) + 1   # disjoint from the engine's own handles
+        return self._requeue_handles
 
     def complete_message(self, queue_name: str, message_id: str = "", processing_time: float = 0.0) -> None:
         qid = self._ids.get(queue_name)

@@ -30,7 +30,7 @@ class GenCfg(C.Structure):
 
 
 def build(force: bool = False) -> str:
-    src = [os.path.join(_HERE, f) for f in ("triage_oracle.c", "gen.c", "triage_oracle.h")]
+    src = [os.path.join(_HERE, f) for f in ("triage_oracle.c", "regex_oracle.c", "gen.c", "triage_oracle.h")]
     if force or not os.path.exists(_LIB_PATH) or any(os.path.getmtime(s) > os.path.getmtime(_LIB_PATH) for s in src):
         subprocess.check_call(["make", "-C", _HERE, "-s", "-B"])
     return _LIB_PATH
@@ -51,6 +51,13 @@ def lib():
         L.orc_dict_add.argtypes = [vp, C.c_int, C.c_char_p, C.c_uint32, C.c_int]
         L.orc_dict_free.argtypes = [vp]
         L.orc_dict_set_fast.argtypes = [vp, C.c_int]
+        L.orc_dict_add_regex.restype = C.c_int
+        L.orc_dict_add_regex.argtypes = [vp, C.c_int, C.c_char_p, C.c_uint32]
+        L.orc_regex_compile.restype = vp
+        L.orc_regex_compile.argtypes = [C.c_char_p, C.c_uint32]
+        L.orc_regex_free.argtypes = [vp]
+        L.orc_regex_count.restype = C.c_uint32
+        L.orc_regex_count.argtypes = [vp, C.c_char_p, C.c_uint64]
         L.orc_scores.argtypes = [vp, C.c_char_p, C.c_uint64, C.POINTER(C.c_uint32)]
         L.orc_analyze.argtypes = [C.c_char_p, C.c_uint64, C.POINTER(C.c_uint32), C.POINTER(C.c_int32),
                                   C.POINTER(C.c_int32), C.POINTER(C.c_int)]
@@ -61,6 +68,8 @@ def lib():
         L.orc_pipeline.argtypes = [vp, C.c_int, u64p, vp, vp, u64p, C.c_uint32, C.c_int, C.c_int64, vp, vp, C.c_int]
         L.orc_generate.restype = C.c_uint64
         L.orc_generate.argtypes = [C.POINTER(GenCfg), u64p, vp, vp, u64p]
+        L.orc_next_backoff_ns.restype = C.c_int64
+        L.orc_next_backoff_ns.argtypes = [C.c_int64, C.c_int64, C.c_double, C.c_int]
         L.orc_heap_new.restype = vp
         L.orc_heap_free.argtypes = [vp]
         L.orc_heap_push.argtypes = [vp, C.c_int, C.c_uint64, C.c_uint32]
@@ -82,6 +91,10 @@ class Dict:
 
     def add(self, prio: int, literal: bytes, ci: bool) -> int:
         return lib().orc_dict_add(self.h, prio, literal, len(literal), 1 if ci else 0)
+
+    def add_regex(self, prio: int, pattern: bytes) -> int:
+        """AddKeywordPattern(prio, pattern) with a regular expression (RE2 subset); 0 ok, 4 outside the subset"""
+        return lib().orc_dict_add_regex(self.h, prio, pattern, len(pattern))
 
     def set_fast(self, on=True):
         """one-pass scoring for border-free case-sensitive literals (same numbers; for the full-size 10 K-keyword goldens).
@@ -149,3 +162,18 @@ def analyze(content: bytes):
     w, p, n, q = C.c_uint32(), C.c_int32(), C.c_int32(), C.c_int()
     lib().orc_analyze(content, len(content), C.byref(w), C.byref(p), C.byref(n), C.byref(q))
     return w.value, p.value, n.value, bool(q.value)
+
+
+def regex_count(pattern: bytes, content: bytes):
+    """len(FindAllString(content, -1)) by the C restatement; None when the pattern is outside its subset"""
+    h = lib().orc_regex_compile(pattern, len(pattern))
+    if not h:
+        return None
+    try:
+        return lib().orc_regex_count(h, content, len(content))
+    finally:
+        lib().orc_regex_free(h)
+
+
+def next_backoff_ns(initial_ns, max_ns, factor, retry_count):
+    return int(lib().orc_next_backoff_ns(int(initial_ns), int(max_ns), float(factor), int(retry_count)))

@@ -79,6 +79,109 @@ class Pattern:
         self.rx = re.compile("".join(parts))
 
 
+_PERL = {"d": "0-9", "w": "0-9A-Za-z_", "s": "\\t\\n\\f\\r "}   # RE2: ASCII only (Python's own \\d \\w \\s are Unicode-wide)
+
+
+def _fold_members(lo: int, hi: int) -> str:
+    """what "(?i)" adds to the ASCII range lo..hi: the other case, plus U+212A for k and U+017F for s"""
+    out = []
+    for c in range(lo, hi + 1):
+        ch = chr(c)
+        if ch.isascii() and ch.isalpha():
+            out.append(ch.swapcase())
+            if ch.lower() == "k":
+                out.append("\u212a")
+            if ch.lower() == "s":
+                out.append("\u017f")
+    return "".join(re.escape(x) for x in out)
+
+
+def go_regex_to_py(pattern: str) -> "re.Pattern":
+    """Go (RE2) pattern of the subset the engine accepts -> an equivalent Python `re` pattern with every class written out
+    (no re.IGNORECASE, no re.ASCII): a token-level rewrite, Python's backtracking engine then supplies the
+    leftmost-first semantics.  Raises ValueError for what this rewrite does not cover."""
+    fold = dotall = False
+    i = 0
+    m = re.match(r"\(\?([is]+)\)", pattern)
+    if m:
+        fold, dotall, i = "i" in m.group(1), "s" in m.group(1), m.end()
+    out = []
+    n = len(pattern)
+
+    def escape_item(j):
+        """after a backslash at pattern[j]: -> (text for inside a class or None, code point or None, next index)"""
+        c = pattern[j]
+        if c in _PERL:
+            return _PERL[c], None, j + 1
+        if c in "DWS":
+            return None, None, j + 1
+        if c in "ntrfv":
+            return None, ord({"n": "\n", "t": "\t", "r": "\r", "f": "\f", "v": "\v"}[c]), j + 1
+        if c == "x":
+            return None, int(pattern[j + 1:j + 3], 16), j + 3
+        if not c.isalnum():
+            return None, ord(c), j + 1
+        raise ValueError("escape outside the subset")
+
+    while i < n:
+        c = pattern[i]
+        if c == "\\":
+            txt, cp, j = escape_item(i + 1)
+            if txt is not None:
+                out.append("[" + txt + "]")
+            elif cp is None:
+                out.append("[^" + _PERL[pattern[i + 1].lower()] + "]")
+            else:
+                out.append("[" + re.escape(chr(cp)) + (_fold_members(cp, cp) if fold and cp < 128 else "") + "]")
+            i = j
+        elif c == "[":
+            i += 1
+            neg = i < n and pattern[i] == "^"
+            if neg:
+                i += 1
+            body, first = [], True
+            while True:
+                if pattern[i] == "]" and not first:
+                    i += 1
+                    break
+                first = False
+                if pattern[i] == "\\":
+                    txt, cp, i = escape_item(i + 1)
+                    if txt is not None:
+                        body.append(txt)
+                        continue
+                    if cp is None:
+                        raise ValueError("negated Perl class inside a class: not covered by the rewrite")
+                    lo = cp
+                else:
+                    lo = ord(pattern[i]); i += 1
+                hi = lo
+                if pattern[i] == "-" and pattern[i + 1] != "]":
+                    i += 1
+                    if pattern[i] == "\\":
+                        _, hi, i = escape_item(i + 1)
+                    else:
+                        hi = ord(pattern[i]); i += 1
+                body.append(re.escape(chr(lo)) + ("-" + re.escape(chr(hi)) if hi != lo else ""))
+                if fold:
+                    if hi >= 128:
+                        raise ValueError("non-ASCII under (?i)")
+                    body.append(_fold_members(lo, hi))
+            out.append("[" + ("^" if neg else "") + "".join(body) + "]")
+        elif c == ".":
+            out.append("[\\s\\S]" if dotall else "[^\\n]")
+            i += 1
+        elif c in "()|?*+{},^$" or c.isdigit() and False:
+            out.append(c)
+            i += 1
+        else:
+            if fold and ord(c) >= 128:
+                raise ValueError("non-ASCII under (?i)")
+            out.append("[" + re.escape(c) + _fold_members(ord(c), ord(c)) + "]" if fold and c.isascii() and c.isalpha() else re.escape(c))
+            i += 1
+    return re.compile("".join(out))
+
+
 class PyOracle:
     def __init__(self, with_defaults: bool = True, default_prio: int = NORMAL):
         self.patterns: list[Pattern] = []
@@ -91,6 +194,12 @@ class PyOracle:
 
     def add(self, prio: int, literal: str, ci: bool) -> None:
         self.patterns.append(Pattern(prio, literal, ci))
+
+    def add_regex(self, prio: int, pattern: str) -> None:
+        """AddKeywordPattern(prio, pattern) with a regular expression (preprocessor.go:176-184)"""
+        p = Pattern(prio, "x", False)
+        p.rx = go_regex_to_py(pattern)
+        self.patterns.append(p)
 
     # -- a5 --------------------------------------------------------------
     def scores(self, s: str) -> dict[int, int]:

@@ -79,6 +79,8 @@ struct orc_dict {
     uint64_t *tkeys; uint32_t *tvals; uint32_t tmask;
     tnode_t *tnodes; uint32_t tn;
     uint32_t *slow_idx; uint32_t nslow;
+    /* AddKeywordPattern with a regular expression (regex_oracle.c) */
+    orc_regex **rx; int *rx_prio; uint32_t nrx, rxcap;
 };
 
 /* regexp (?i) on a literal rune: unicode.SimpleFold orbit membership.
@@ -140,6 +142,8 @@ void orc_dict_free(orc_dict *d)
     for (uint32_t i = 0; i < d->n; i++) free(d->pats[i].runes);
     free(d->pats);
     free(d->tkeys); free(d->tvals); free(d->tnodes); free(d->slow_idx);
+    for (uint32_t i = 0; i < d->nrx; i++) orc_regex_free(d->rx[i]);
+    free(d->rx); free(d->rx_prio);
     free(d);
 }
 
@@ -283,8 +287,24 @@ static void scores_fast(const orc_dict *d, const uint8_t *s, uint64_t n, uint32_
 void orc_scores(const orc_dict *d, const uint8_t *s, uint64_t n, uint32_t scores[5])
 {
     for (int p = 0; p < 5; p++) scores[p] = 0;
+    for (uint32_t i = 0; i < d->nrx; i++) scores[d->rx_prio[i]] += orc_regex_count(d->rx[i], s, n);
     if (d->fast) { scores_fast(d, s, n, scores); return; }
     for (uint32_t i = 0; i < d->n; i++) scores[d->pats[i].prio] += count_nonoverlap(&d->pats[i], s, n);
+}
+
+/* preprocessor.go:176-184 with a pattern that is not a plain literal; 0 ok, 4 outside the restated subset */
+int orc_dict_add_regex(orc_dict *d, int prio, const uint8_t *pattern, uint32_t len)
+{
+    if (prio < 1 || prio > 4) return 4;
+    orc_regex *re = orc_regex_compile(pattern, len);
+    if (!re) return 4;
+    if (d->nrx == d->rxcap) {
+        d->rxcap = d->rxcap ? d->rxcap * 2 : 8;
+        d->rx = (orc_regex **)realloc(d->rx, sizeof(orc_regex *) * d->rxcap);
+        d->rx_prio = (int *)realloc(d->rx_prio, sizeof(int) * d->rxcap);
+    }
+    d->rx[d->nrx] = re; d->rx_prio[d->nrx] = prio; d->nrx++;
+    return 0;
 }
 
 /* ----------------------------------------------------------- analysis ---- */
@@ -568,4 +588,14 @@ uint32_t orc_pipeline(const orc_dict *d, int default_prio, const uint64_t *offse
 {
     orc_process_batch(d, default_prio, offsets, bytes, meta, n, out, nthreads);
     return orc_admit_and_order(out, meta, offsets, ts, n, rules_on, max_size, order_out);
+}
+
+/* ExponentialBackoff.NextBackoff, internal/priorityqueue/worker.go:274-290: float64 product, cap, truncation */
+int64_t orc_next_backoff_ns(int64_t initial_ns, int64_t max_ns, double factor, int retry_count)
+{
+    if (retry_count <= 0) return initial_ns;                    /* :275-277 */
+    double backoff = (double)initial_ns;                        /* :280 */
+    for (int i = 1; i < retry_count; i++) backoff *= factor;    /* :281-283 */
+    if (backoff > (double)max_ns) return max_ns;                /* :285-287 */
+    return (int64_t)backoff;                                    /* :289 time.Duration(backoff) */
 }

@@ -81,6 +81,13 @@ void orc_dict_free(orc_dict *d);
  * triage_oracle.c "fast mode"); call after the last orc_dict_add.  The timed CPU baseline never uses it.        */
 void orc_dict_set_fast(orc_dict *d, int on);
 uint32_t orc_dict_size(const orc_dict *d);
+/* AddKeywordPattern(prio, pattern) with a regular expression (regex_oracle.c: RE2 subset, leftmost-first,
+ * non-overlapping count on runes).  0 ok, 4 outside the restated subset. */
+typedef struct orc_regex orc_regex;
+orc_regex *orc_regex_compile(const uint8_t *pattern, uint32_t len);
+void orc_regex_free(orc_regex *re);
+uint32_t orc_regex_count(const orc_regex *re, const uint8_t *s, uint64_t n);
+int orc_dict_add_regex(orc_dict *d, int prio, const uint8_t *pattern, uint32_t len);
 
 /* a5: per-priority scores for one content; scores[1..4] */
 void orc_scores(const orc_dict *d, const uint8_t *s, uint64_t n, uint32_t scores[5]);
@@ -102,6 +109,9 @@ uint32_t orc_pipeline(const orc_dict *d, int default_prio, const uint64_t *offse
                       const uint8_t *bytes, const orc_meta *meta, const uint64_t *ts, uint32_t n,
                       int rules_on, int64_t max_size, orc_result *out, uint32_t *order_out,
                       int nthreads);
+
+/* worker.go:274-290 */
+int64_t orc_next_backoff_ns(int64_t initial_ns, int64_t max_ns, double factor, int retry_count);
 
 /* container/heap exposed for the queue KATs */
 typedef struct orc_heap orc_heap;

@@ -475,3 +475,15 @@ extern "C" int hostcheck_scan_stream(const uint8_t *prios, const uint8_t *cis, c
     }
     return 0;
 }
+
+// ---- AddKeywordPattern regex subset: compile + the host build of the device walk (regex_walk.cuh) ----
+#include "../../llm-message-queue_b200/csrc/regex_vm.h"
+// returns 0 and the count, or 4 and the reason the pattern is outside the subset
+extern "C" int hostcheck_regex_count(const char *pattern, uint32_t plen, const uint8_t *s, uint64_t n, uint32_t *count, char *err, uint32_t err_cap)
+{
+    triage::RegexSet set;
+    std::string e = triage::regex_compile(pattern, plen, 1, &set);
+    if (!e.empty()) { snprintf(err, err_cap, "%s", e.c_str()); return 4; }
+    *count = triage::regex_count_host(set, 0, s, n);
+    return 0;
+}

@@ -9,8 +9,10 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 SRC = [os.path.join(HERE, "csrc", "scan_host_check.cc"),
-       os.path.join(ROOT, "llm-message-queue_b200", "csrc", "dfa_build.cc")]
-DEPS = SRC + [os.path.join(ROOT, "llm-message-queue_b200", "csrc", f) for f in ("dfa_build.h", "scan_core.cuh", "scan_wide.cuh")]
+       os.path.join(ROOT, "llm-message-queue_b200", "csrc", "dfa_build.cc"),
+       os.path.join(ROOT, "llm-message-queue_b200", "csrc", "regex_vm.cc")]
+DEPS = SRC + [os.path.join(ROOT, "llm-message-queue_b200", "csrc", f)
+              for f in ("dfa_build.h", "scan_core.cuh", "scan_wide.cuh", "regex_vm.h", "regex_walk.cuh")]
 LIB = os.path.join(HERE, "csrc", "libscan_host_check.so")
 
 DEFAULT_DICT = [(1, True, b"immediate"), (1, True, b"emergency"), (1, True, b"asap"), (1, True, b"right now"),
@@ -126,3 +128,14 @@ def scan_stream(dict_entries, offsets, data, chunk_long=512, nch=2):
     if rc != 0:
         raise ValueError(err.value.decode())
     return counters[:n]
+
+
+def regex_count(pattern: bytes, content: bytes):
+    """len(FindAllString) of the engine's regex subset through the host build of the device walk; ValueError(reason) when
+    the pattern is outside the subset"""
+    cnt = C.c_uint32()
+    err = C.create_string_buffer(256)
+    rc = lib().hostcheck_regex_count(pattern, len(pattern), content if content else b"\0", len(content), C.byref(cnt), err, 256)
+    if rc != 0:
+        raise ValueError(err.value.decode())
+    return cnt.value

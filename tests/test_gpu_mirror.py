@@ -67,13 +67,17 @@ def test_setters_and_added_patterns():
     assert m.priority == Priority.REALTIME and m.metadata["priority_reason"] == "user_default"
     assert p.add_keyword_pattern(Priority.LOW, "newsletter") is None          # case-sensitive, as regexp.Compile(pattern) is
     assert p.add_keyword_pattern(Priority.LOW, "(?i)unsubscribe") is None
-    assert isinstance(p.add_keyword_pattern(Priority.LOW, "a|b"), ValueError)  # the stated deviation: literals only
+    assert isinstance(p.add_keyword_pattern(Priority.LOW, "^dear"), ValueError)  # the stated deviation: outside the regex subset (anchors)
+    assert isinstance(p.add_keyword_pattern(Priority.LOW, "x*"), ValueError)     # ... and patterns that match the empty string
     assert p.add_keyword_pattern(Priority.LOW, "haha") is None                  # self-overlapping literal: counted without overlap
     assert p.get_keyword_patterns(Priority.LOW) == ["newsletter", "(?i)unsubscribe", "haha"] and len(p.get_keyword_patterns(Priority.HIGH)) == 5
     m = p.process_message(new_message("c", "u", "weekly newsletter, UNSUBSCRIBE here. Newsletter", Priority.NORMAL))
     assert m.priority == Priority.LOW and m.queue_name == "low"
     m = p.process_message(new_message("c", "u", "urgent urgent hahahahaha", Priority.NORMAL))   # haha x2 (not 4) ties with urgent x2
     assert m.priority == Priority.HIGH
+    assert p.add_keyword_pattern(Priority.REALTIME, "(?i)p[0-9]+ (incident|outage)s?") is None   # a real regexp (RE2 subset)
+    m = p.process_message(new_message("c", "u", "weekly newsletter about the P1 Incident and the p23 outages", Priority.NORMAL))
+    assert m.priority == Priority.REALTIME and m.metadata["priority_reason"] == "content_keywords"
     p.set_default_priority(Priority.LOW)
     m = p.process_message(new_message("c", "u", "plain text", 0))
     assert m.priority == Priority.LOW and m.metadata["priority_reason"] == "content_keywords"

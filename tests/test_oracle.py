@@ -163,3 +163,20 @@ def test_full_size_digests_are_committed_for_every_config():
         for f in fullsize.FIELDS + ("order",):
             assert len(dig[name][f]) == 64
     assert dig["c4_rules"]["label_histogram"][4] > 16000      # rules on: every non-VIP long message -> Low
+
+
+def test_next_backoff_three_ways():
+    """ExponentialBackoff.NextBackoff (worker.go:274-290): the engine's C-ABI function (pure arithmetic, no GPU), the C
+    oracle and the formula written out here agree bit for bit, cap and truncation included."""
+    import llm_message_queue_b200 as mq
+    for initial, mx, factor in ((10**9, 60 * 10**9, 2.0), (10**8, 10**10, 1.5), (250 * 10**6, 3 * 10**9, 1.1), (1, 2**62, 3.7), (5 * 10**9, 10**9, 2.0)):
+        for rc in range(-1, 40):
+            if rc <= 0:
+                want = initial
+            else:
+                b = float(initial)
+                for _ in range(1, rc):
+                    b *= factor
+                want = mx if b > float(mx) else int(b)
+            assert co.next_backoff_ns(initial, mx, factor, rc) == want
+            assert mq._capi.backoff_ns(initial, mx, factor, rc) == want
