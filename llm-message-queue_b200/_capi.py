@@ -41,7 +41,9 @@ class Timings(C.Structure):
 
 SCAN_VARIANTS = {0: "none", 1: "scan_kernel (packed arena, CTA-wide tiles)", 2: "scan_padded_kernel (padded arena, mini-tiles)",
                  3: "scan_rows_kernel (padded arena, row lanes, 2-D TMA windows of 80 B x 32 rows)",
-                 4: "scan_padded_kernel<wide> (class map in shared memory, transitions in L2)"}
+                 4: "scan_padded_kernel<wide> (class map in shared memory, transitions in L2)",
+                 5: "scan_pair_kernel (padded arena, row lanes fed by 2-D TMA, filter automaton over class pairs: 8 lookups per 16 bytes, "
+                    "SIMD word count, flagged groups walked exactly)"}
 
 
 class TriageError(RuntimeError):

@@ -427,32 +427,17 @@ static const char kPriorWords[] =
     "red list though feel talk bird body dog family direct pose leave song measure state product black short please thanks "
     "hello team customer order account issue problem update server error request message service support system data";
 
+// deterministic sample of English-like text: common words, the dictionary's own patterns (4 %), some capitals, digits, punctuation
+static std::string prior_sample_text(const std::vector<std::string> &patterns, uint64_t &rng);
+
 static std::vector<uint32_t> place_states(const std::vector<uint8_t> &next /* n * 256 */, uint32_t n, uint32_t start,
                                           const std::vector<std::string> &patterns) {
     std::vector<uint32_t> perm(n);
     for (uint32_t i = 0; i < n; i++) perm[i] = i;
     if (n <= 2) return perm;
     uint64_t rng = 0x9E3779B97F4A7C15ull;
+    const std::string text = prior_sample_text(patterns, rng);
     auto rnd = [&]() { rng = rng * 6364136223846793005ull + 1442695040888963407ull; return static_cast<uint32_t>(rng >> 33); };
-    std::vector<std::string> common;
-    for (const char *p = kPriorWords; *p;) {
-        const char *q = p;
-        while (*q && *q != ' ') q++;
-        common.emplace_back(p, q);
-        p = *q ? q + 1 : q;
-    }
-    std::string text;
-    while (text.size() < 48 * 1024) {
-        std::string w = (!patterns.empty() && rnd() % 100 < 4) ? patterns[rnd() % patterns.size()] : common[rnd() % common.size()];
-        uint32_t r = rnd() % 100;
-        if (r < 6) { if (!w.empty() && w[0] >= 'a' && w[0] <= 'z') w[0] = static_cast<char>(w[0] - 32); }
-        else if (r < 8) { for (char &ch : w) if (ch >= 'a' && ch <= 'z') ch = static_cast<char>(ch - 32); }
-        else if (r < 10) w = std::to_string(rnd() % 1000);
-        r = rnd() % 100;
-        if (r < 6) w.push_back(",.?!:"[rnd() % 5]);
-        text += w;
-        text.push_back(' ');
-    }
     // walk: (state, word of the row) per text byte
     std::vector<uint16_t> key(text.size());
     std::vector<uint32_t> heat(n, 0);
@@ -527,6 +512,204 @@ static std::vector<uint32_t> place_states(const std::vector<uint8_t> &next /* n 
     }
     return perm;
 }
+
+static std::string prior_sample_text(const std::vector<std::string> &patterns, uint64_t &rng) {
+    auto rnd = [&]() { rng = rng * 6364136223846793005ull + 1442695040888963407ull; return static_cast<uint32_t>(rng >> 33); };
+    std::vector<std::string> common;
+    for (const char *p = kPriorWords; *p;) {
+        const char *q = p;
+        while (*q && *q != ' ') q++;
+        common.emplace_back(p, q);
+        p = *q ? q + 1 : q;
+    }
+    std::string text;
+    while (text.size() < 48 * 1024) {
+        std::string w = (!patterns.empty() && rnd() % 100 < 4) ? patterns[rnd() % patterns.size()] : common[rnd() % common.size()];
+        uint32_t r = rnd() % 100;
+        if (r < 6) { if (!w.empty() && w[0] >= 'a' && w[0] <= 'z') w[0] = static_cast<char>(w[0] - 32); }
+        else if (r < 8) { for (char &ch : w) if (ch >= 'a' && ch <= 'z') ch = static_cast<char>(ch - 32); }
+        else if (r < 10) w = std::to_string(rnd() % 1000);
+        r = rnd() % 100;
+        if (r < 6) w.push_back(",.?!:"[rnd() % 5]);
+        text += w;
+        text.push_back(' ');
+    }
+    return text;
+}
+
+// ---- filter automaton of the two-bytes-per-lookup lane (scan_pair.cuh) --------------------------------------------
+namespace {
+
+struct ClassPattern { std::vector<uint16_t> sym; };   // per symbol: the set of 4-bit classes (bit mask) that continue it
+
+inline uint32_t class4(uint32_t b, uint32_t mul, uint32_t shift) { return (((b & 31u) * mul) >> shift) & 15u; }
+
+// all-ASCII ways to complete an event, as class strings
+std::vector<ClassPattern> class_patterns(const std::vector<DictEntry> &dict, uint32_t mul, uint32_t shift) {
+    std::vector<ClassPattern> out;
+    auto letter = [&](uint32_t ch, bool fold) {
+        uint16_t m = static_cast<uint16_t>(1u << class4(ch, mul, shift));
+        if (fold && is_ascii_letter(ch)) m |= static_cast<uint16_t>(1u << class4(ch ^ 0x20u, mul, shift));
+        return m;
+    };
+    uint16_t ws = 0;
+    for (uint32_t b : {0x09u, 0x0Au, 0x0Bu, 0x0Cu, 0x0Du, 0x20u}) ws |= static_cast<uint16_t>(1u << class4(b, mul, shift));
+    for (const DictEntry &d : dict) {
+        ClassPattern p;
+        bool ascii = true;
+        for (unsigned char ch : d.bytes) { if (ch >= 0x80) { ascii = false; break; } p.sym.push_back(letter(ch, d.ci)); }
+        if (ascii && !p.sym.empty()) out.push_back(p);   // an occurrence of a non-ASCII literal always lies in groups walked exactly
+    }
+    for (const char *q : {"what", "how", "why", "when", "where", "who"}) {
+        ClassPattern p;
+        for (const char *c = q; *c; c++) p.sym.push_back(letter(static_cast<unsigned char>(*c), true));
+        p.sym.push_back(static_cast<uint16_t>(1u << class4(' ', mul, shift)));
+        out.push_back(p);
+    }
+    for (const char *w : {"good", "great", "excellent", "happy", "satisfied", "bad", "terrible", "awful", "angry", "frustrated"}) {
+        ClassPattern p;
+        p.sym.push_back(ws);                               // field start: ASCII whitespace (or a reset pad) before the word
+        for (const char *c = w; *c; c++) p.sym.push_back(letter(static_cast<unsigned char>(*c), true));
+        p.sym.push_back(ws);                               // the event is emitted on the whitespace (or pad) that ends the field
+        out.push_back(p);
+    }
+    return out;
+}
+
+// subset construction over the 16 classes, composition into class pairs, minimisation.  false: too many states
+bool determinise_pairs(const std::vector<ClassPattern> &pats, PairFilter *out) {
+    std::map<std::vector<uint32_t>, uint32_t> ids;
+    std::vector<std::vector<uint32_t>> states;
+    struct T { uint32_t next; bool fired; };
+    std::vector<T> single;   // state-major, 16 per state
+    auto intern = [&](const std::vector<uint32_t> &v) {
+        auto it = ids.find(v);
+        if (it != ids.end()) return it->second;
+        const uint32_t id = static_cast<uint32_t>(states.size());
+        ids.emplace(v, id);
+        states.push_back(v);
+        return id;
+    };
+    intern({});
+    for (uint32_t s = 0; s < states.size(); s++) {
+        if (states.size() > 4096) return false;
+        const std::vector<uint32_t> cur = states[s];
+        for (uint32_t c = 0; c < 16; c++) {
+            std::vector<uint32_t> nx;
+            bool fired = false;
+            auto advance = [&](uint32_t p, uint32_t idx) {
+                if (!((pats[p].sym[idx] >> c) & 1u)) return;
+                if (idx + 1 == pats[p].sym.size()) fired = true;
+                else nx.push_back(p << 8 | (idx + 1));
+            };
+            for (uint32_t pos : cur) advance(pos >> 8, pos & 0xFFu);
+            for (uint32_t p = 0; p < pats.size(); p++) advance(p, 0);   // an occurrence may start at every byte
+            std::sort(nx.begin(), nx.end());
+            nx.erase(std::unique(nx.begin(), nx.end()), nx.end());
+            single.push_back(T{intern(nx), fired});
+        }
+    }
+    const uint32_t n1 = static_cast<uint32_t>(states.size());
+    // pairs, restricted to what is reachable from the root in steps of two
+    std::vector<T> pair(static_cast<size_t>(n1) * 256);
+    for (uint32_t s = 0; s < n1; s++)
+        for (uint32_t c0 = 0; c0 < 16; c0++) {
+            const T a = single[s * 16 + c0];
+            for (uint32_t c1 = 0; c1 < 16; c1++) {
+                const T b = single[a.next * 16 + c1];
+                pair[static_cast<size_t>(s) * 256 + (c0 | c1 << 4)] = T{b.next, a.fired || b.fired};
+            }
+        }
+    std::vector<int> reach(n1, -1);
+    std::vector<uint32_t> order{0};
+    reach[0] = 0;
+    for (size_t k = 0; k < order.size(); k++)
+        for (uint32_t x = 0; x < 256; x++) {
+            const uint32_t t = pair[static_cast<size_t>(order[k]) * 256 + x].next;
+            if (reach[t] < 0) { reach[t] = static_cast<int>(order.size()); order.push_back(t); }
+        }
+    const uint32_t n = static_cast<uint32_t>(order.size());
+    // Moore refinement
+    std::vector<uint32_t> cls(n, 0);
+    {
+        std::map<std::string, uint32_t> sig;
+        for (uint32_t i = 0; i < n; i++) {
+            std::string k(256, '0');
+            for (uint32_t x = 0; x < 256; x++) if (pair[static_cast<size_t>(order[i]) * 256 + x].fired) k[x] = '1';
+            cls[i] = sig.emplace(k, static_cast<uint32_t>(sig.size())).first->second;
+        }
+    }
+    for (;;) {
+        std::map<std::string, uint32_t> sig;
+        std::vector<uint32_t> ncl(n);
+        for (uint32_t i = 0; i < n; i++) {
+            std::string k(reinterpret_cast<const char *>(&cls[i]), 4);
+            for (uint32_t x = 0; x < 256; x++) {
+                const uint32_t t = cls[reach[pair[static_cast<size_t>(order[i]) * 256 + x].next]];
+                k.append(reinterpret_cast<const char *>(&t), 4);
+            }
+            ncl[i] = sig.emplace(k, static_cast<uint32_t>(sig.size())).first->second;
+        }
+        const uint32_t before = *std::max_element(cls.begin(), cls.end()) + 1, after = static_cast<uint32_t>(sig.size());
+        cls.swap(ncl);
+        if (after == before) break;
+    }
+    const uint32_t nmin = *std::max_element(cls.begin(), cls.end()) + 1;
+    if (nmin > 256) return false;
+    out->n_states = nmin;
+    out->start = cls[0];
+    out->table.assign(static_cast<size_t>(nmin) * 256, 0);
+    for (uint32_t i = 0; i < n; i++)
+        for (uint32_t x = 0; x < 256; x++) {
+            const T t = pair[static_cast<size_t>(order[i]) * 256 + x];
+            out->table[static_cast<size_t>(cls[i]) * 256 + x] = static_cast<uint16_t>(cls[reach[t.next]] | (t.fired ? 0x8000u : 0u));
+        }
+    return true;
+}
+
+double pair_fire_rate(const PairFilter &f, const std::string &text) {
+    uint32_t st = f.start, groups = 0, fired_groups = 0;
+    for (size_t g = 0; g + 16 <= text.size(); g += 16) {
+        bool fired = false;
+        for (size_t j = 0; j < 16; j += 2) {
+            const uint32_t x = class4(static_cast<unsigned char>(text[g + j]), f.mul, f.shift) |
+                               class4(static_cast<unsigned char>(text[g + j + 1]), f.mul, f.shift) << 4;
+            const uint16_t e = f.table[static_cast<size_t>(st) * 256 + x];
+            st = e & 0xFFu;
+            fired = fired || (e & 0x8000u);
+        }
+        groups++;
+        fired_groups += fired ? 1 : 0;
+    }
+    return groups ? static_cast<double>(fired_groups) / groups : 0.0;
+}
+
+void build_pair_filter(const std::vector<DictEntry> &dict, const Dfa &exact, PairFilter *out) {
+    *out = PairFilter();
+    // the lane relies on a 16-byte warm-up, on reset pads that are ASCII whitespace, and on the dense exact table
+    if (exact.wide || exact.warm_bytes != 16 || exact.span > 17) return;
+    if (!(exact.reset_pad == 0x20 || (exact.reset_pad >= 0x09 && exact.reset_pad <= 0x0D))) return;
+    std::vector<std::string> pats;
+    for (const DictEntry &d : dict) pats.push_back(d.bytes);
+    uint64_t rng = 0xD1B54A32D192ED03ull;
+    const std::string text = prior_sample_text(pats, rng);
+    static const uint32_t cand[][2] = {{1, 0}, {5, 2}, {3, 2}, {5, 1}, {3, 0}, {7, 1}};
+    PairFilter best;
+    for (const auto &mk : cand) {
+        PairFilter f;
+        f.mul = mk[0]; f.shift = mk[1];
+        if (!determinise_pairs(class_patterns(dict, f.mul, f.shift), &f)) continue;
+        f.sample_fire_rate = pair_fire_rate(f, text);
+        f.ok = true;
+        // the first candidate needs no multiply on the device: keep it unless another one is clearly more selective
+        if (!best.ok || f.sample_fire_rate * 1.5 + 0.002 < best.sample_fire_rate) best = f;
+    }
+    // the sample carries the dictionary's own patterns in 4 % of its words (about one group in eight fires by design);
+    // a filter that flags much more than that flags ordinary text and is no filter
+    if (best.ok && best.sample_fire_rate < 0.30) *out = best;
+}
+
+}  // namespace
 
 std::string build_dfa(const std::vector<DictEntry> &dict, Dfa *out, bool exact_nonoverlap) {
     Machine m;
@@ -748,6 +931,7 @@ std::string build_dfa(const std::vector<DictEntry> &dict, Dfa *out, bool exact_n
             if (ok) out->tail_pad = static_cast<int>(b);
         }
     }
+    if (!exact_nonoverlap) build_pair_filter(dict, *out, &out->filter);
     return "";
 }
 

@@ -53,7 +53,21 @@ constexpr uint32_t kMaxEventsD8 = 127;
 constexpr uint32_t kMaxStatesW = 1u << 20;
 constexpr uint32_t kMaxEventsW = 2047;
 
+// Filter automaton of the two-bytes-per-lookup scan lane (scan_pair.cuh): bytes are mapped to 4-bit classes by
+// arithmetic, ((b & 31) * mul >> shift) & 15, the automaton recognises the class strings of every all-ASCII way to
+// complete an event (keyword literal, question word + " ", whitespace + sentiment word + whitespace) and consumes two
+// classes per table entry: entry(state, c0 | c1 << 4) = next state | fired << 15.  It over-approximates (bytes sharing
+// a class are not told apart); what it flags is re-walked through the exact automaton.
+struct PairFilter {
+    bool ok = false;                  // false: this dictionary keeps to the one-lookup-per-byte lanes
+    uint32_t n_states = 0, start = 0;
+    uint32_t mul = 1, shift = 0;
+    std::vector<uint16_t> table;      // n_states * 256
+    double sample_fire_rate = 0;      // flagged 16-byte groups on the compiler's sample text (diagnostics)
+};
+
 struct Dfa {
+    PairFilter filter;
     uint32_t n_states = 0;
     bool wide = false;
     std::vector<uint16_t> table;      // D8: n_states * 256

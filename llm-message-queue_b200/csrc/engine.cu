@@ -79,10 +79,10 @@ struct DevBuf {
 };
 
 struct DfaBufs {
-    DevBuf<uint8_t> table, eom, cls;
+    DevBuf<uint8_t> table, eom, cls, ftable;
     DevBuf<EventPacked> events;
     DevBuf<uint32_t> wtable, eomw;
-    void release() { table.release(); eom.release(); cls.release(); events.release(); wtable.release(); eomw.release(); }
+    void release() { table.release(); eom.release(); cls.release(); ftable.release(); events.release(); wtable.release(); eomw.release(); }
 };
 
 struct QItem { int32_t prio; uint64_t ts; uint64_t handle; };
@@ -166,6 +166,7 @@ struct triage_engine {
     ScanGeometry geom{0, 0, 0};
     uint32_t pad_warps = 0;
     uint32_t row_warps = 0;        // > 0: the padded arena is scanned by the row-lane kernel (2-D TMA), arenas of >= 1 row
+    uint32_t pair_warps = 0;       // > 0: ... by its two-bytes-per-lookup variant (filter automaton, scan_pair.cuh)
     DfaBufs dm, dx;   // device copies of the scan automaton and of the exact (sequential) one
     DeviceDfa ddfa{};
     // exact (sequential, non-overlapping) automaton, only when the dictionary has self-overlapping literals
@@ -241,6 +242,15 @@ int32_t upload_dfa(const Dfa &dfa, DfaBufs *b, DeviceDfa *out) {
         CU(cudaMemcpy(b->table.p, padded.data(), padded.size(), cudaMemcpyHostToDevice));
         CU(cudaMemcpy(b->eom.p, eom.data(), 256, cudaMemcpyHostToDevice));
         d.table = b->table.p; d.eom = b->eom.p;
+        if (dfa.filter.ok) {   // filter automaton of the pair lanes, same padded row layout
+            std::vector<uint8_t> fp((size_t)dfa.filter.n_states * kRowBytes, 0);
+            for (uint32_t st = 0; st < dfa.filter.n_states; st++)
+                std::memcpy(fp.data() + (size_t)st * kRowBytes, dfa.filter.table.data() + (size_t)st * 256, 512);
+            CU(b->ftable.ensure(fp.size()));
+            CU(cudaMemcpy(b->ftable.p, fp.data(), fp.size(), cudaMemcpyHostToDevice));
+            d.has_filter = 1; d.ftable = b->ftable.p; d.f_states = dfa.filter.n_states; d.f_start = dfa.filter.start;
+            d.f_mul = dfa.filter.mul; d.f_shift = dfa.filter.shift;
+        }
     } else {
         d.start_state = dfa.start_state_w; d.neutral_state = dfa.neutral_state_w;
         d.n_classes = dfa.n_classes;
@@ -311,6 +321,7 @@ int32_t commit_dict(triage_engine *e) {
         const char *rv = getenv("TRIAGE_ROWS");   // tuning knob: 0 = keep to the mini-tile kernel
         if (!rv || atoi(rv) != 0) e->row_warps = pick_row_warps(d, (size_t)e->max_smem_optin);
     }
+    e->pair_warps = e->row_warps ? pick_pair_warps(d, (size_t)e->max_smem_optin) : 0;
     e->geom = geom;
     e->dfa = dfa;
     e->dict_dirty = false;
@@ -346,7 +357,9 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     }
     // an upload in flight is scanned chunk by chunk: the row length is chosen for the chunk, not for the arena
     const bool chunked = plan && use_rows && plan->n_chunks > 1;
-    const uint32_t row_bytes = use_rows ? scan_rows_lane_bytes(chunked ? kUploadChunk : total, e->row_warps, e->sm_count) : 0;
+    const bool use_pair = use_rows && e->pair_warps > 0;
+    const uint32_t row_warps = use_pair ? e->pair_warps : e->row_warps;
+    const uint32_t row_bytes = use_rows ? scan_rows_lane_bytes(chunked ? kUploadChunk : total, row_warps, e->sm_count) : 0;
     const uint32_t tile_bytes = !padded ? e->geom.tile
                               : use_rows ? scan_rows_super_bytes(row_bytes) : kPadMiniTile;
     const uint32_t ntiles = (uint32_t)((total + tile_bytes - 1) / tile_bytes);
@@ -366,9 +379,9 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     CU(cudaEventRecord(e->ev[0], s));
     ScanArgs sa{bytes, offsets, total, n, e->d_counters.p, e->d_tile_first.p, ntiles, tile_bytes, 0, ntiles};
     CU(launch_prepare(sa, e->d_small.p, 32 + 8 * 256, e->sm_count, s)); launches++;   // tile index + zeroed counters and scratch
-    e->tm.scan_variant = use_rows ? 3u : padded ? (e->ddfa.wide ? 4u : 2u) : 1u;
+    e->tm.scan_variant = use_pair ? 5u : use_rows ? 3u : padded ? (e->ddfa.wide ? 4u : 2u) : 1u;
     e->tm.scan_row_bytes = row_bytes;
-    e->tm.scan_warps = use_rows ? e->row_warps : padded ? e->pad_warps : e->geom.nt / 32;
+    e->tm.scan_warps = use_rows ? row_warps : padded ? e->pad_warps : e->geom.nt / 32;
     if (ntiles && chunked) {
         // scan of chunk i behind the copy of chunk i: the kernel walks the tiles of the part that has arrived
         CU(e->d_tilectr.ensure(plan->n_chunks));
@@ -380,14 +393,16 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
             sa.tile_end = std::min<uint64_t>(ntiles, (uint64_t)(c + 1) * tiles_per_chunk);
             if (sa.tile_begin >= sa.tile_end) break;
             CU(cudaStreamWaitEvent(s, plan->chunk_ev[c], 0));
-            CU(launch_scan_rows(sa, e->ddfa, e->row_warps, row_bytes, e->d_tilectr.p + c, e->sm_count, s));
+            if (use_pair) CU(launch_scan_pair(sa, e->ddfa, row_warps, row_bytes, e->d_tilectr.p + c, e->sm_count, s));
+            else CU(launch_scan_rows(sa, e->ddfa, row_warps, row_bytes, e->d_tilectr.p + c, e->sm_count, s));
             launches++;
         }
         CU(cudaStreamWaitEvent(s, plan->all_ready, 0));
     } else if (ntiles) {
         if (plan) CU(cudaStreamWaitEvent(s, plan->all_ready, 0));
         CU(cudaEventRecord(e->ev[1], s));
-        if (use_rows) CU(launch_scan_rows(sa, e->ddfa, e->row_warps, row_bytes, e->d_small.p + 20, e->sm_count, s));   // d_small[20]: spare word, zeroed by prepare
+        if (use_pair) CU(launch_scan_pair(sa, e->ddfa, row_warps, row_bytes, e->d_small.p + 20, e->sm_count, s));   // d_small[20]: spare word, zeroed by prepare
+        else if (use_rows) CU(launch_scan_rows(sa, e->ddfa, row_warps, row_bytes, e->d_small.p + 20, e->sm_count, s));
         else if (padded) CU(launch_scan_padded(sa, e->ddfa, e->pad_warps, e->sm_count, s));
         else CU(launch_scan(sa, e->ddfa, e->geom, e->sm_count, s));
         launches++;

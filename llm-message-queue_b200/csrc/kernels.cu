@@ -875,6 +875,293 @@ cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw,
 #undef TRIAGE_ROWS_CASE
 }
 
+// ---------------------------------------------------------------------------------- pair lanes --
+// Row lanes with two bytes per lookup (scan_pair.cuh): same tiles, windows, 2-D TMA feed and dynamic tile hand-out as
+// scan_rows_kernel, but the table in shared memory is the FILTER automaton over 4-bit class pairs (8 lookups per 16
+// bytes), word starts are counted by SIMD-in-register compares, and the groups the filter flags (or that hold bytes >=
+// 0x80) are queued per warp - (message, the 16 bytes before, the 16 bytes) - and walked through the exact automaton in
+// global memory by the whole warp, one queued group per lane.
+constexpr uint32_t kPairQueueCap = 24;     // flagged groups per warp (36 bytes each)
+constexpr uint32_t kPairQueueFlush = 12;
+struct PairSmem { uint32_t table, warp0, aux0, total, warp_bytes, aux_bytes, warm_off, list_off, queue_off; };
+__host__ __device__ inline PairSmem pair_layout(uint32_t f_states, uint32_t nw) {
+    PairSmem L;
+    uint32_t o = 1024;   // mbarriers
+    L.table = o; o += ((f_states * kRowBytes + 127u) / 128u) * 128u;
+    L.warm_off = 2 * 32 * kRowWin;
+    L.warp_bytes = L.warm_off + 512;
+    L.warp0 = o; o += nw * L.warp_bytes;
+    L.list_off = 0;
+    L.queue_off = 2 * 4 * kRowListCap;
+    L.aux_bytes = ((L.queue_off + 4 + 36 * kPairQueueCap + 15u) / 16u) * 16u;
+    L.aux0 = o; o += nw * L.aux_bytes;
+    L.total = o;
+    return L;
+}
+size_t scan_pair_smem_bytes(const DeviceDfa &d, uint32_t nw) { return pair_layout(d.f_states, nw).total; }
+uint32_t pick_pair_warps(const DeviceDfa &d, size_t max_smem) {
+    if (!d.has_filter || d.wide || d.warm != 16 || d.reset_pad < 0) return 0;
+    if (const char *v = getenv("TRIAGE_PAIR")) { if (atoi(v) == 0) return 0; }   // measurement knob: keep to the one-lookup-per-byte lanes
+    if (const char *w = getenv("TRIAGE_PAIR_WARPS")) {
+        uint32_t nw = (uint32_t)atoi(w);
+        if ((nw == 16 || nw == 20 || nw == 24 || nw == 28) && scan_pair_smem_bytes(d, nw) <= max_smem) return nw;
+    }
+    for (uint32_t nw : {24u, 20u, 16u})
+        if (scan_pair_smem_bytes(d, nw) <= max_smem) return nw;
+    return 0;
+}
+
+struct PairEventQueue {
+    uint32_t base_s;   // shared address: count word, then 36-byte slots (message, 4 words before, 4 words of the group)
+    __device__ __forceinline__ void push(const PairCtx &c, const Quad &warm, const Quad &q, uint32_t msg) {
+        uint32_t slot = kPairQueueCap;
+        asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(slot) : "r"(base_s) : "memory");
+        if (slot < kPairQueueCap) {
+            const uint32_t at = base_s + 4 + slot * 36;
+            const uint32_t v[9] = {msg, warm.a, warm.b, warm.c, warm.d, q.a, q.b, q.c, q.d};   // 36-byte slots: 32-bit accesses, conflict-free
+#pragma unroll
+            for (int k = 0; k < 9; k++) asm volatile("st.shared.u32 [%0], %1;" ::"r"(at + 4 * k), "r"(v[k]) : "memory");
+        } else {
+            pair_replay(c, warm, q, msg);   // queue full: walk it now
+        }
+    }
+    __device__ __forceinline__ void flush(const PairCtx &c, uint32_t lane, bool force) {
+        uint32_t n;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(n) : "r"(base_s) : "memory");
+        if (n == 0 || (!force && n < kPairQueueFlush)) return;
+        if (n > kPairQueueCap) n = kPairQueueCap;
+        if (lane < n) {
+            const uint32_t at = base_s + 4 + lane * 36;
+            uint32_t v[9];
+#pragma unroll
+            for (int k = 0; k < 9; k++) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v[k]) : "r"(at + 4 * k) : "memory");
+            Quad w, q;
+            w.a = v[1]; w.b = v[2]; w.c = v[3]; w.d = v[4];
+            q.a = v[5]; q.b = v[6]; q.c = v[7]; q.d = v[8];
+            pair_replay(c, w, q, v[0]);
+        }
+        __syncwarp();
+        if (lane == 0) asm volatile("st.shared.u32 [%0], %1;" ::"r"(base_s), "r"(0u) : "memory");
+        __syncwarp();
+    }
+};
+
+template <int NW, int LANE, bool SIMPLE>
+__global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, DeviceDfa d, const __grid_constant__ CUtensorMap tm_win,
+                                                              const __grid_constant__ CUtensorMap tm_warm, uint32_t nrows_full,
+                                                              uint32_t *__restrict__ tile_counter) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    constexpr int32_t CL = LANE, WIN = (int32_t)kRowWin, NWIN = CL / WIN;
+    constexpr uint32_t SUPER = 32 * CL;
+    const PairSmem L = pair_layout(d.f_states, NW);
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem) + warp * 2;
+    uint8_t *tbl = smem + L.table;
+    uint8_t *wbase = smem + L.warp0 + warp * L.warp_bytes;
+    uint8_t *warm_buf = wbase + L.warm_off;
+    uint8_t *aux = smem + L.aux0 + warp * L.aux_bytes;
+    int32_t *list_base = reinterpret_cast<int32_t *>(aux + L.list_off);
+
+    PairEventQueue queue;
+    queue.base_s = smem_u32(aux + L.queue_off);
+    if (lane == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(queue.base_s), "r"(0u) : "memory");
+    }
+    {
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(d.ftable);
+        uint32_t *dst = reinterpret_cast<uint32_t *>(tbl);
+        for (uint32_t i = tid; i < d.f_states * (kRowBytes / 4); i += NW * 32) dst[i] = src[i];
+    }
+    __syncthreads();   // the only CTA-wide barrier
+
+    const uint32_t nwarps = gridDim.x * NW;
+    const uint32_t t_end = a.tile_end;
+    const uint32_t t0 = a.tile_begin + blockIdx.x * NW + warp;
+    if (t0 >= t_end) return;
+    auto grab = [&]() {
+        uint32_t v = 0;
+        if (lane == 0) v = atomicAdd(tile_counter, 1u) + nwarps + a.tile_begin;
+        return __shfl_sync(0xFFFFFFFFu, v, 0);
+    };
+    auto issue = [&](uint32_t tile, uint32_t w, uint32_t buf) {
+        const int32_t row0 = (int32_t)(tile * 32u);
+        mbar_expect_tx(&bars[buf], 32 * WIN + (w == 0 ? 512u : 0u));
+        tma_load_2d(wbase + buf * (32 * WIN), &tm_win, (int32_t)(w * WIN), row0, &bars[buf]);
+        if (w == 0) tma_load_2d(warm_buf, &tm_warm, CL - 16, row0 - 1, &bars[buf]);
+    };
+
+    uint32_t t = t0, t_nxt = grab(), t_nn = grab();
+    uint32_t first_cur = a.tile_first[t0], last_cur = a.tile_first[t0 + 1];
+    if (lane == 0) issue(t0, 0, 0);
+    uint64_t ts = (uint64_t)t0 * SUPER;
+    {
+        uint32_t cnt = last_cur - first_cur + 2;
+        if (cnt <= kRowListCap) {
+            if (lane < cnt) list_base[lane] = rel_clamp(a.offsets[first_cur + lane], ts);
+            if (lane + 32 < cnt) list_base[lane + 32] = rel_clamp(a.offsets[first_cur + lane + 32], ts);
+        }
+    }
+    uint32_t first_nxt = 0, last_nxt = 0;
+    if (t_nxt < t_end) { first_nxt = a.tile_first[t_nxt]; last_nxt = a.tile_first[t_nxt + 1]; }
+    __syncwarp();
+
+    PairCtx c;
+    c.ftbl = tbl; c.ftbl_s = smem_u32(tbl); c.fstart = d.f_start; c.mul = d.f_mul; c.shift = d.f_shift;
+    c.xtbl = d.table; c.events = d.events; c.neutral_state = d.neutral_state;
+    c.pad4 = 0x01010101u * (uint32_t)(d.reset_pad & 0xFF);
+    c.list_abs = a.offsets; c.counters = a.counters;
+    Quad padq;
+    padq.a = padq.b = padq.c = padq.d = c.pad4;
+    const int32_t chunk = (int32_t)(lane * CL);
+    uint32_t g = 0;
+
+    for (uint32_t sk = 0; t < t_end; sk++) {
+        const bool has_next = t_nxt < t_end;
+        ts = (uint64_t)t * SUPER;
+        uint64_t n0 = 0, n1 = 0;
+        uint32_t cnt_nxt = 0, first_nn = 0, last_nn = 0;
+        if (has_next) {
+            cnt_nxt = last_nxt - first_nxt + 2;
+            if (cnt_nxt <= kRowListCap) {
+                if (lane < cnt_nxt) n0 = a.offsets[first_nxt + lane];
+                if (lane + 32 < cnt_nxt) n1 = a.offsets[first_nxt + lane + 32];
+            }
+            if (t_nn < t_end) { first_nn = a.tile_first[t_nn]; last_nn = a.tile_first[t_nn + 1]; }
+        }
+        const uint32_t cnt_cur = last_cur - first_cur + 2;
+        const int32_t *lst = list_base + (sk & 1) * kRowListCap;
+        c.list = cnt_cur <= kRowListCap ? lst : nullptr;
+        c.tile_start = (int64_t)ts;
+        c.list_n = cnt_cur; c.msg_lo = first_cur;
+        const uint32_t row = t * 32 + lane;
+        const bool full_row = row < nrows_full;
+        const uint64_t row_start = (uint64_t)row * CL;
+        const bool tail_row = row == nrows_full && row_start < a.total;
+
+        PairLane P;
+        uint32_t km = 0;
+        if (full_row || tail_row) {
+            if (c.list) { for (uint32_t j = 1; j + 1 < cnt_cur; j++) km += lst[j] <= chunk ? 1u : 0u; }
+            else km = find_msg(c, chunk);
+        }
+#pragma unroll 1
+        for (int32_t w = 0; w < NWIN; w++, g++) {
+            if (lane == 0) {
+                if (w + 1 < NWIN) issue(t, (uint32_t)w + 1, (g + 1) & 1);
+                else if (has_next) issue(t_nxt, 0, (g + 1) & 1);
+            }
+            mbar_wait(&bars[g & 1], (g >> 1) & 1);
+            if (full_row) {
+                if (w == 0) pair_begin<SIMPLE>(c, P, km, row == 0 ? padq : *reinterpret_cast<const Quad *>(warm_buf + lane * 16));
+                const uint8_t *wb = wbase + (g & 1) * (32 * WIN) + lane * WIN;
+                const int32_t pos = chunk + w * WIN;
+#pragma unroll 1
+                for (int32_t q = 0; q < WIN; q += 16) pair_group<SIMPLE>(c, P, *reinterpret_cast<const Quad *>(wb + q), pos + q, queue);
+            }
+            __syncwarp();
+            if ((w & 3) == 3) queue.flush(c, lane, false);
+        }
+        if (tail_row) {   // the arena's partial last row: straight from global memory, flagged groups walked on the spot
+            const uint8_t *src = a.bytes + row_start;
+            PairSinkNow now;
+            Quad wq = padq;
+            if (row != 0) { const uint4 v = __ldg(reinterpret_cast<const uint4 *>(src - 16)); wq.a = v.x; wq.b = v.y; wq.c = v.z; wq.d = v.w; }
+            pair_begin<SIMPLE>(c, P, km, wq);
+            const int32_t nb = (int32_t)(a.total - row_start);
+#pragma unroll 1
+            for (int32_t q = 0; q < nb; q += 16) pair_group<SIMPLE>(c, P, stream_quad(src + q), chunk + q, now);
+        }
+        uint32_t hm = 0xFFFFFFFFu, hw = 0;
+        if (full_row || tail_row) { pair_end(c, P); hm = P.L.head_msg; hw = P.L.head_words; }
+        {   // combine the head partials of neighbouring lanes that sit in the same message
+            const unsigned full = 0xFFFFFFFFu;
+            uint32_t prev = __shfl_up_sync(full, hm, 1);
+            bool head = lane == 0 || hm != prev;
+            uint32_t heads = __ballot_sync(full, head);
+            uint32_t v = hw;
+#pragma unroll
+            for (int dlt = 1; dlt < 32; dlt <<= 1) {
+                uint32_t tt = __shfl_up_sync(full, v, dlt);
+                if ((int)lane >= dlt) v += tt;
+            }
+            uint32_t above = heads & ~((2u << lane) - 1u);
+            uint32_t end = above ? (uint32_t)__ffs(above) - 2u : 31u;
+            uint32_t upto = __shfl_sync(full, v, end);
+            uint32_t before = __shfl_up_sync(full, v, 1);
+            if (lane == 0) before = 0;
+            if (head && hm != 0xFFFFFFFFu) {
+                uint32_t sum = upto - before;
+                if (sum) atomicAdd(a.counters + (uint64_t)hm * CNT_STRIDE + CNT_WORDS, sum);
+            }
+        }
+        if (has_next && cnt_nxt <= kRowListCap) {
+            int32_t *ln = list_base + ((sk + 1) & 1) * kRowListCap;
+            const uint64_t tsn = (uint64_t)t_nxt * SUPER;
+            if (lane < cnt_nxt) ln[lane] = rel_clamp(n0, tsn);
+            if (lane + 32 < cnt_nxt) ln[lane + 32] = rel_clamp(n1, tsn);
+        }
+        first_cur = first_nxt; last_cur = last_nxt;
+        first_nxt = first_nn; last_nxt = last_nn;
+        t = t_nxt; t_nxt = t_nn;
+        t_nn = t_nxt < t_end ? grab() : t_nxt;
+        __syncwarp();
+    }
+    queue.flush(c, lane, true);
+}
+
+template <int NW, int LANE, bool SIMPLE>
+static cudaError_t launch_scan_pair_variant(const ScanArgs &a, const DeviceDfa &d, const CUtensorMap &tw, const CUtensorMap &tm,
+                                            uint32_t nrows_full, uint32_t *tile_counter, int sm_count, cudaStream_t s) {
+    size_t smem = scan_pair_smem_bytes(d, NW);
+    static SmemConfigured configured;
+    if (cudaError_t e = ensure_dynamic_smem(scan_pair_kernel<NW, LANE, SIMPLE>, smem, configured)) return e;
+    uint32_t need = (a.tile_end - a.tile_begin + NW - 1) / NW;
+    uint32_t grid = need < (uint32_t)sm_count ? need : (uint32_t)sm_count;
+    scan_pair_kernel<NW, LANE, SIMPLE><<<grid, NW * 32, smem, s>>>(a, d, tw, tm, nrows_full, tile_counter);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_scan_pair(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, uint32_t lane_bytes, uint32_t *tile_counter, int sm_count,
+                             cudaStream_t s) {
+    if (a.tile_end <= a.tile_begin) return cudaSuccess;
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) return cudaErrorNotSupported;
+    if (lane_bytes != kRowLaneLong && lane_bytes != kRowLaneMid && lane_bytes != kRowLaneShort) return cudaErrorInvalidValue;
+    const uint64_t nrows_full = a.total / lane_bytes;
+    CUtensorMap tw, tm;
+    const cuuint64_t dims[2] = {lane_bytes, nrows_full};
+    const cuuint64_t strides[1] = {lane_bytes};
+    const cuuint32_t box_w[2] = {kRowWin, 32}, box_m[2] = {16, 32}, es[2] = {1, 1};
+    void *base = const_cast<uint8_t *>(a.bytes);
+    if (enc(&tw, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, base, dims, strides, box_w, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+            CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS ||
+        enc(&tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, base, dims, strides, box_m, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+            CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return cudaErrorInvalidValue;
+    const uint32_t nrows = (uint32_t)nrows_full;
+    const bool simple = d.f_mul == 1 && d.f_shift == 0;
+#define TRIAGE_PAIR_LANE(NW_, LANE_)                                                                                          \
+    return simple ? launch_scan_pair_variant<NW_, LANE_, true>(a, d, tw, tm, nrows, tile_counter, sm_count, s)                 \
+                  : launch_scan_pair_variant<NW_, LANE_, false>(a, d, tw, tm, nrows, tile_counter, sm_count, s);
+#define TRIAGE_PAIR_CASE(NW_)                                                     \
+    case NW_:                                                                     \
+        if (lane_bytes == kRowLaneLong) { TRIAGE_PAIR_LANE(NW_, kRowLaneLong) }   \
+        if (lane_bytes == kRowLaneMid) { TRIAGE_PAIR_LANE(NW_, kRowLaneMid) }     \
+        TRIAGE_PAIR_LANE(NW_, kRowLaneShort)
+    switch (nw) {
+        TRIAGE_PAIR_CASE(28)
+        TRIAGE_PAIR_CASE(24)
+        TRIAGE_PAIR_CASE(20)
+        TRIAGE_PAIR_CASE(16)
+        default: return cudaErrorInvalidValue;
+    }
+#undef TRIAGE_PAIR_CASE
+#undef TRIAGE_PAIR_LANE
+}
+
 // ---------------------------------------------------------------------------------- fix-up --
 // Messages in which a self-overlapping keyword ("aa", "abab") may have overlapping occurrences are re-counted by one
 // thread each, walking the whole message from its start through the exact automaton (matching such a pattern kills its

@@ -6,6 +6,7 @@
 #include "../../include/triage.h"
 #include "scan_core.cuh"
 #include "scan_wide.cuh"
+#include "scan_pair.cuh"
 #include "regex_walk.cuh"
 
 namespace triage {
@@ -30,6 +31,10 @@ struct DeviceDfa {
     const uint8_t *cls_of;       // 256
     const uint32_t *eom_w;       // n_states (fix-up kernel)
     uint32_t n_classes;
+    // filter automaton of the two-bytes-per-lookup lanes (scan_pair.cuh), padded rows like `table`
+    int32_t has_filter;
+    const uint8_t *ftable;
+    uint32_t f_states, f_start, f_mul, f_shift;
 };
 
 struct ScanArgs {
@@ -59,6 +64,12 @@ uint32_t pick_row_warps(const DeviceDfa &d, size_t max_smem);   // 0: this autom
 bool scan_rows_usable(const ScanArgs &a);
 // tile_counter: one zeroed device word (tiles beyond the first per warp are handed out through it)
 cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, uint32_t lane_bytes, uint32_t *tile_counter, int sm_count,
+                             cudaStream_t s);
+
+// pair-lane variant of the row scan (filter automaton over class pairs + SIMD word count + exact walk of flagged groups)
+size_t scan_pair_smem_bytes(const DeviceDfa &d, uint32_t nw);
+uint32_t pick_pair_warps(const DeviceDfa &d, size_t max_smem);   // 0: this dictionary / automaton cannot use it
+cudaError_t launch_scan_pair(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, uint32_t lane_bytes, uint32_t *tile_counter, int sm_count,
                              cudaStream_t s);
 
 // sequential exact recount of the messages the scan flagged (self-overlapping keywords); `exact` points at global memory

@@ -487,3 +487,83 @@ extern "C" int hostcheck_regex_count(const char *pattern, uint32_t plen, const u
     *count = triage::regex_count_host(set, 0, s, n);
     return 0;
 }
+
+// ---- two-bytes-per-lookup lane (scan_pair.cuh): rows of chunk_long bytes walked group by group, flagged groups through
+//      the exact automaton on the spot; info[0] = filter states, [1] = mul, [2] = shift, [3] = flagged groups, [4] = groups ----
+#include "../../llm-message-queue_b200/csrc/scan_pair.cuh"
+namespace {
+struct CountingSink {
+    uint64_t flagged = 0;
+    void push(const triage::PairCtx &c, const triage::Quad &warm, const triage::Quad &q, uint32_t msg) { flagged++; triage::pair_replay(c, warm, q, msg); }
+};
+}
+extern "C" int hostcheck_scan_pair(const uint8_t *prios, const uint8_t *cis, const uint32_t *lens, const uint8_t *lits, uint32_t n_pat,
+                                   const uint64_t *offsets, const uint8_t *bytes, uint32_t n_msgs, uint32_t chunk_long,
+                                   uint32_t *counters, uint64_t *info, char *err, uint32_t errcap)
+{
+    using namespace triage;
+    std::vector<DictEntry> dict;
+    size_t o = 0;
+    for (uint32_t i = 0; i < n_pat; i++) {
+        dict.push_back({prios[i], cis[i] != 0, std::string(reinterpret_cast<const char *>(lits + o), lens[i])});
+        o += lens[i];
+    }
+    Dfa dfa;
+    std::string e = build_dfa(dict, &dfa);
+    if (!e.empty() || !dfa.filter.ok) { std::strncpy(err, e.empty() ? "no pair filter for this dictionary" : e.c_str(), errcap - 1); return 4; }
+    info[0] = dfa.filter.n_states; info[1] = dfa.filter.mul; info[2] = dfa.filter.shift; info[3] = info[4] = 0;
+    if (n_msgs == 0) return 0;
+    std::vector<EventPacked> ev(dfa.events.size());
+    for (size_t i = 0; i < dfa.events.size(); i++) pack_event(dfa.events[i], &ev[i].x);
+    std::vector<uint8_t> xtbl((size_t)dfa.n_states * kRowBytes, 0), ftbl((size_t)dfa.filter.n_states * kRowBytes, 0);
+    for (uint32_t st = 0; st < dfa.n_states; st++) std::memcpy(xtbl.data() + (size_t)st * kRowBytes, dfa.table.data() + (size_t)st * 256, 512);
+    for (uint32_t st = 0; st < dfa.filter.n_states; st++) std::memcpy(ftbl.data() + (size_t)st * kRowBytes, dfa.filter.table.data() + (size_t)st * 256, 512);
+    std::vector<uint64_t> poff(n_msgs + 1, 0);
+    for (uint32_t i = 0; i < n_msgs; i++) poff[i + 1] = poff[i] + ((offsets[i + 1] - offsets[i]) / 16 + 1) * 16;
+    std::vector<uint8_t> arena_raw(poff[n_msgs] + 64, (uint8_t)dfa.reset_pad);
+    uint8_t *arena = arena_raw.data();
+    while (reinterpret_cast<uintptr_t>(arena) & 15) arena++;
+    for (uint32_t i = 0; i < n_msgs; i++) std::memcpy(arena + poff[i], bytes + offsets[i], offsets[i + 1] - offsets[i]);
+    std::memset(counters, 0, sizeof(uint32_t) * 8 * n_msgs);
+    const uint64_t total = poff[n_msgs];
+    const uint64_t st_bytes = 32ull * chunk_long;
+    CountingSink sink;
+    const bool simple = dfa.filter.mul == 1 && dfa.filter.shift == 0;
+    Quad padq;
+    padq.a = padq.b = padq.c = padq.d = 0x01010101u * (uint32_t)(dfa.reset_pad & 0xFF);
+    for (uint64_t ts = 0; ts < total; ts += st_bytes) {
+        uint64_t te = std::min(total, ts + st_bytes);
+        uint32_t lo = 0, hi = n_msgs + 1;
+        while (lo < hi) { uint32_t mid = (lo + hi) / 2; if (poff[mid] > ts) hi = mid; else lo = mid + 1; }
+        uint32_t mlo = lo - 1, mhi = mlo;
+        while (poff[mhi + 1] < te) mhi++;
+        std::vector<int32_t> list;
+        for (uint32_t m = mlo; m <= mhi + 1; m++) list.push_back((int32_t)((int64_t)poff[m] - (int64_t)ts));
+        PairCtx c;
+        c.ftbl = ftbl.data(); c.ftbl_s = 0; c.fstart = dfa.filter.start; c.mul = dfa.filter.mul; c.shift = dfa.filter.shift;
+        c.xtbl = xtbl.data(); c.events = ev.data(); c.neutral_state = dfa.neutral_state; c.pad4 = padq.a;
+        c.list = list.data(); c.list_abs = poff.data(); c.tile_start = (int64_t)ts; c.list_n = (uint32_t)list.size(); c.msg_lo = mlo;
+        c.counters = counters;
+        for (uint32_t l = 0; l < 32; l++) {
+            uint64_t cs = ts + (uint64_t)l * chunk_long;
+            if (cs >= te) break;
+            uint64_t ce = std::min<uint64_t>(cs + chunk_long, te);
+            PairLane P;
+            Quad warm = cs ? *reinterpret_cast<const Quad *>(arena + cs - 16) : padq;
+            if (simple) pair_begin<true>(c, P, find_msg(c, (int32_t)(cs - ts)), warm); else pair_begin<false>(c, P, find_msg(c, (int32_t)(cs - ts)), warm);
+            for (uint64_t g = cs; g < ce; g += 16) {
+                const Quad q = *reinterpret_cast<const Quad *>(arena + g);
+                if (simple) pair_group<true>(c, P, q, (int32_t)(g - ts), sink); else pair_group<false>(c, P, q, (int32_t)(g - ts), sink);
+                info[4]++;
+            }
+            pair_end(c, P);
+            if (P.L.head_words) counters[(uint64_t)P.L.head_msg * 8 + CNT_WORDS] += P.L.head_words;
+        }
+    }
+    info[3] = sink.flagged;
+    for (uint32_t i = 0; i < n_msgs; i++) {
+        counters[(uint64_t)i * 8 + CNT_Q] &= 1;
+        if (offsets[i + 1] > offsets[i] && bytes[offsets[i + 1] - 1] == '?') counters[(uint64_t)i * 8 + CNT_Q] |= 1;
+    }
+    return 0;
+}

@@ -12,7 +12,7 @@ SRC = [os.path.join(HERE, "csrc", "scan_host_check.cc"),
        os.path.join(ROOT, "llm-message-queue_b200", "csrc", "dfa_build.cc"),
        os.path.join(ROOT, "llm-message-queue_b200", "csrc", "regex_vm.cc")]
 DEPS = SRC + [os.path.join(ROOT, "llm-message-queue_b200", "csrc", f)
-              for f in ("dfa_build.h", "scan_core.cuh", "scan_wide.cuh", "regex_vm.h", "regex_walk.cuh")]
+              for f in ("dfa_build.h", "scan_core.cuh", "scan_wide.cuh", "scan_pair.cuh", "regex_vm.h", "regex_walk.cuh")]
 LIB = os.path.join(HERE, "csrc", "libscan_host_check.so")
 
 DEFAULT_DICT = [(1, True, b"immediate"), (1, True, b"emergency"), (1, True, b"asap"), (1, True, b"right now"),
@@ -139,3 +139,23 @@ def regex_count(pattern: bytes, content: bytes):
     if rc != 0:
         raise ValueError(err.value.decode())
     return cnt.value
+
+
+def scan_pair(dict_entries, offsets, data, chunk_long=320):
+    """counters through the two-bytes-per-lookup lane (filter automaton + SIMD word count + exact walk of flagged groups)
+    -> (counters[n,8], info dict); ValueError when the dictionary has no pair filter"""
+    n = len(offsets) - 1
+    prios = np.array([d[0] for d in dict_entries], np.uint8)
+    cis = np.array([1 if d[1] else 0 for d in dict_entries], np.uint8)
+    lens = np.array([len(d[2]) for d in dict_entries], np.uint32)
+    lits = np.frombuffer(b"".join(d[2] for d in dict_entries) or b"\0", np.uint8)
+    counters = np.zeros((max(n, 1), 8), np.uint32)
+    info = np.zeros(5, np.uint64)
+    err = C.create_string_buffer(256)
+    buf = data if len(data) else np.zeros(1, np.uint8)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    rc = lib().hostcheck_scan_pair(p(prios), p(cis), p(lens), p(lits), len(dict_entries), p(offsets), p(buf), n, chunk_long,
+                                   p(counters), p(info), err, 256)
+    if rc != 0:
+        raise ValueError(err.value.decode())
+    return counters[:n], dict(filter_states=int(info[0]), mul=int(info[1]), shift=int(info[2]), flagged=int(info[3]), groups=int(info[4]))

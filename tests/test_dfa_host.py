@@ -100,12 +100,14 @@ def test_large_dictionary_wide_format():
     assert len(bad) == 0, (bad[:5], cnt[bad[:5]], exp[bad[:5]])
 
 
-@pytest.mark.parametrize("walk", ["long-320-80", "long-48-16", "stream-512-2", "stream-512-1", "stream-64-3", "stream-1024-4"])
+@pytest.mark.parametrize("walk", ["long-320-80", "long-48-16", "stream-512-2", "stream-512-1", "stream-64-3", "stream-1024-4",
+                                  "pair-1280-0", "pair-320-0", "pair-48-0", "pair-16-0"])
 def test_long_lane_walks(golden_dir, walk):
     """padded arena, state carried along a long per-lane chunk: windowed (shared-memory staging) and streaming
     (N interleaved chains read straight from the arena) variants, on the edge cases and on generated text"""
     kind, a, b = walk.split("-")
     run = (lambda off, data: hc.scan_long(hc.DEFAULT_DICT, off, data, chunk_long=int(a), window=int(b))) if kind == "long" else \
+          (lambda off, data: hc.scan_pair(hc.DEFAULT_DICT, off, data, chunk_long=int(a))[0]) if kind == "pair" else \
           (lambda off, data: hc.scan_stream(hc.DEFAULT_DICT, off, data, chunk_long=int(a), nch=int(b)))
     cases = json.load(open(os.path.join(golden_dir, "edge_cases.json")))
     contents = [bytes.fromhex(e["content_hex"]) for e in cases]
@@ -141,10 +143,22 @@ def test_random_dictionaries_vs_oracle(seed):
         pytest.skip(str(e))
     bad = np.nonzero((cnt != exp).any(axis=1))[0]
     assert len(bad) == 0, (entries, bad[:3], [contents[i][:60] for i in bad[:3]], cnt[bad[:3]], exp[bad[:3]])
-    for walk in (lambda: hc.scan_padded(full, off, data)[0], lambda: hc.scan_stream(full, off, data, chunk_long=320, nch=1)):
+    for walk in (lambda: hc.scan_padded(full, off, data)[0], lambda: hc.scan_stream(full, off, data, chunk_long=320, nch=1),
+                 lambda: hc.scan_pair(full, off, data, chunk_long=320)[0], lambda: hc.scan_pair(full, off, data, chunk_long=48)[0]):
         try:
             cnt = walk()
         except ValueError as e:
             continue
         bad = np.nonzero((cnt != exp).any(axis=1))[0]
         assert len(bad) == 0, (entries, bad[:3], [contents[i][:60] for i in bad[:3]], cnt[bad[:3]], exp[bad[:3]])
+
+
+def test_pair_filter_facts_for_the_default_dictionary():
+    """the two-bytes-per-lookup lane: the filter automaton fits 8-bit state ids, needs no multiply for its byte classes,
+    and flags few groups of ordinary text (everything it flags is walked exactly, so this is a cost, not a correctness matter)"""
+    off, data, meta, ts = co.generate(0xC0FFEE02, 1500, 256, 4096, edge=50)
+    cnt, info = hc.scan_pair(hc.DEFAULT_DICT, off, data, 1280)
+    assert info["filter_states"] <= 160 and (info["mul"], info["shift"]) == (1, 0)
+    assert info["flagged"] < 0.02 * info["groups"]
+    contents = [bytes(data[int(off[i]):int(off[i + 1])]) for i in range(len(meta))]
+    assert np.array_equal(cnt, _expected(co.Dict(), contents))

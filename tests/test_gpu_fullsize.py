@@ -34,16 +34,19 @@ def test_default_dictionary_full_size_digests(name, monkeypatch):
     e = mq.Engine(device=0, rules_enabled=rules)
     try:
         poff, plen, pbytes = e.pack_padded(off, data)
-        variants = [("rows auto", {}), ("rows 1280", {"TRIAGE_ROW_BYTES": "1280"}), ("rows 640", {"TRIAGE_ROW_BYTES": "640"}),
-                    ("rows 320", {"TRIAGE_ROW_BYTES": "320"})]
+        # default: the pair-lane kernel (two bytes per lookup); TRIAGE_PAIR=0: the one-lookup-per-byte row kernel
+        variants = [("pair auto", {}), ("pair 1280", {"TRIAGE_ROW_BYTES": "1280"}), ("pair 640", {"TRIAGE_ROW_BYTES": "640"}),
+                    ("pair 320", {"TRIAGE_ROW_BYTES": "320"}), ("rows auto", {"TRIAGE_PAIR": "0"}),
+                    ("rows 1280", {"TRIAGE_PAIR": "0", "TRIAGE_ROW_BYTES": "1280"}), ("rows 320", {"TRIAGE_PAIR": "0", "TRIAGE_ROW_BYTES": "320"})]
         if name == "c2":
-            variants.append(("mini-tile kernel", {"TRIAGE_ROWS": "0"}))
+            variants += [("rows 640", {"TRIAGE_PAIR": "0", "TRIAGE_ROW_BYTES": "640"}), ("pair 20 warps", {"TRIAGE_PAIR_WARPS": "20"}),
+                         ("mini-tile kernel", {"TRIAGE_ROWS": "0"})]
         for ctx, env in variants:
-            for k in ("TRIAGE_ROW_BYTES", "TRIAGE_ROWS"):
+            for k in ("TRIAGE_ROW_BYTES", "TRIAGE_ROWS", "TRIAGE_PAIR", "TRIAGE_PAIR_WARPS"):
                 monkeypatch.delenv(k, raising=False)
             for k, v in env.items():
                 monkeypatch.setenv(k, v)
-            if "TRIAGE_ROWS" in env:      # read at dictionary commit
+            if any(k in env for k in ("TRIAGE_ROWS", "TRIAGE_PAIR", "TRIAGE_PAIR_WARPS")):      # read at dictionary commit
                 e2 = mq.Engine(device=0, rules_enabled=rules)
                 try:
                     res, order = _run_padded(e2, poff, plen, pbytes, meta, ts, n)
@@ -53,7 +56,7 @@ def test_default_dictionary_full_size_digests(name, monkeypatch):
                 res, order = _run_padded(e, poff, plen, pbytes, meta, ts, n)
             _compare(name, fullsize.digests(res, order), want, ctx)
         if name == "c2":                  # the packed wire format gives the same arrays
-            for k in ("TRIAGE_ROW_BYTES", "TRIAGE_ROWS"):
+            for k in ("TRIAGE_ROW_BYTES", "TRIAGE_ROWS", "TRIAGE_PAIR", "TRIAGE_PAIR_WARPS"):
                 monkeypatch.delenv(k, raising=False)
             res, base = e.submit(off, data, meta, ts)
             handles, _ = e.drain(n)

@@ -251,11 +251,14 @@ def test_padded_arena_path_vs_c_oracle(seed, n, lo, hi, edge, mix):
         e.close()
 
 
-@pytest.mark.parametrize("rows", ["1", "0", "1280", "640", "320"])
+@pytest.mark.parametrize("rows", ["1", "0", "1280", "640", "320", "p0-1", "p0-1280", "p0-320"])
 def test_padded_arena_sizes_around_row_and_tile_boundaries(rows, monkeypatch):
     """The padded arena is scanned as 320-byte rows, 32 rows per tile (2-D TMA), with the partial last row read directly;
     arenas shorter than one row go to the mini-tile kernel.  Sweep totals across those boundaries, with both kernels
     (TRIAGE_ROWS=0 keeps to the mini-tile kernel): every result must equal the oracle's."""
+    if rows.startswith("p0-"):            # the one-lookup-per-byte row kernel instead of the pair-lane kernel (the default)
+        monkeypatch.setenv("TRIAGE_PAIR", "0")
+        rows = rows[3:]
     if rows in ("1280", "640", "320"):   # force the long / short row length of the row-lane kernel whatever the arena size
         monkeypatch.setenv("TRIAGE_ROW_BYTES", rows)
     else:
@@ -279,9 +282,12 @@ def test_padded_arena_sizes_around_row_and_tile_boundaries(rows, monkeypatch):
         e.close()
 
 
-def test_event_dense_content_overflows_the_replay_queue():
-    """Row-lane scan: events are queued per warp (24 slots) and replayed in bulk; content where almost every 8-byte half
-    carries an event overflows the queue, so lanes replay on the spot as well.  Both paths must add up to the oracle."""
+@pytest.mark.parametrize("pair", ["1", "0"])
+def test_event_dense_content_overflows_the_replay_queue(pair, monkeypatch):
+    """Row-lane scans (pair lanes and one-lookup-per-byte lanes): events / flagged groups are queued per warp (24 slots) and
+    replayed in bulk; content where almost every group carries an event overflows the queue, so lanes replay on the spot
+    as well.  Both paths must add up to the oracle."""
+    monkeypatch.setenv("TRIAGE_PAIR", pair)
     rng = np.random.default_rng(17)
     words = [b"asap", b"soon", b"urgent", b"good", b"bad", b"what", b"who", b"ASAP", "a\u017fap".encode(),
              b"x", b"critical", b"happy", b"why"]
