@@ -262,6 +262,15 @@ int32_t triage_comm_init(triage_engine *e, int32_t nranks, int32_t rank, const u
  * receives the whole-job dequeue order on every rank.  rank_base[r] = first global index of rank r. */
 int32_t triage_merge_allgather(triage_engine *e, const uint64_t *rank_base, uint32_t *order_global_dev,
                                uint64_t capacity, uint64_t *n_total);
+/* The same merge started on the engine's merge stream without waiting for it: for contiguous sequence shards with
+ * engine-stamped enqueue times (enqueue_ns_dev = NULL at the submit) the exchange is ONE all-gather of [bucket counts |
+ * local order] and a concatenation that works out its geometry on the device, so the caller can submit the next batch
+ * while the previous order travels.  The next submit waits (on the device) only until its predecessor's order has been
+ * read.  triage_merge_wait blocks until the merge is complete and returns the merged count; order_global_dev may be read
+ * after it.  Explicit enqueue times need triage_merge_allgather (key exchange).  No counterpart in the reference: its
+ * queues live in one process (cmd/queue-manager/main.go:111-124 is the order being reproduced). */
+int32_t triage_merge_allgather_async(triage_engine *e, const uint64_t *rank_base, uint32_t *order_global_dev, uint64_t capacity);
+int32_t triage_merge_wait(triage_engine *e, uint64_t *n_total);
 
 #ifdef __cplusplus
 }

@@ -121,6 +121,8 @@ _SIGS = {
     "triage_comm_unique_id": (C.c_int32, [C.c_void_p]),
     "triage_comm_init": (C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     "triage_merge_allgather": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]),
+    "triage_merge_allgather_async": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]),
+    "triage_merge_wait": (C.c_int32, [C.c_void_p, C.POINTER(C.c_uint64)]),
 }
 
 
@@ -412,6 +414,16 @@ class Engine:
 
     def comm_init(self, nranks: int, rank: int, uid: bytes):
         _check(lib().triage_comm_init(self._h, nranks, rank, C.create_string_buffer(uid, 128)))
+
+    def merge_allgather_async(self, rank_base: np.ndarray, order_global_ptr: int, capacity: int) -> None:
+        """start the one-exchange merge on the merge stream (engine-stamped enqueue times only); merge_wait() completes it"""
+        self._rank_base_keep = np.ascontiguousarray(rank_base, np.uint64)
+        _check(lib().triage_merge_allgather_async(self._h, _p(self._rank_base_keep), order_global_ptr, int(capacity)))
+
+    def merge_wait(self) -> int:
+        tot = C.c_uint64()
+        _check(lib().triage_merge_wait(self._h, C.byref(tot)))
+        return tot.value
 
     def merge_allgather(self, rank_base: np.ndarray, order_global_ptr: int, capacity: int) -> int:
         tot = C.c_uint64()

@@ -208,6 +208,16 @@ struct triage_engine {
     const uint64_t *last_ts = nullptr;
     uint32_t last_n = 0, last_n_adm = 0;
     uint32_t last_counts[16]{};
+    const uint32_t *last_counts_dev = nullptr, *last_n_adm_dev = nullptr;   // the same numbers where the kernels left them
+    // one-exchange merge on its own stream (triage_merge_allgather_async)
+    cudaStream_t merge_stream = nullptr;
+    cudaEvent_t ev_packed = nullptr;       // the merge has read the last submit's order and counts
+    bool packed_pending = false;
+    DevBuf<uint32_t> d_gsrc, d_gall;
+    DevBuf<uint64_t> d_ntotal;
+    uint64_t *h_ntotal = nullptr;          // pinned
+    uint64_t merge_capacity = 0;
+    bool merge_pending = false;
     // comm
     ncclComm_t comm = nullptr;
     int nranks = 1, rank = 0;
@@ -376,6 +386,7 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     OrderScratch sc{e->d_blockhist.p, e->d_totals.p, nblocks};
 
     if (plan) CU(cudaStreamWaitEvent(s, plan->small_ready, 0));
+    if (e->packed_pending) { CU(cudaStreamWaitEvent(s, e->ev_packed, 0)); e->packed_pending = false; }   // an asynchronous merge still reads the last order
     CU(cudaEventRecord(e->ev[0], s));
     ScanArgs sa{bytes, offsets, total, n, e->d_counters.p, e->d_tile_first.p, ntiles, tile_bytes, 0, ntiles};
     CU(launch_prepare(sa, e->d_small.p, 32 + 8 * 256, e->sm_count, s)); launches++;   // tile index + zeroed counters and scratch
@@ -474,6 +485,7 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     *n_admitted = e->h_small[1];
     for (int b = 0; b < 16; b++) e->last_counts[b] = e->h_small[2 + b];
     e->last_order = order; e->last_bucket = bucket; e->last_ts = ts; e->last_n = n; e->last_n_adm = *n_admitted;
+    e->last_counts_dev = e->d_small.p + 2; e->last_n_adm_dev = e->d_totals.p + 256;
     float ms = 0;
     cudaEventElapsedTime(&ms, e->ev[1], e->ev[2]); e->tm.scan_ms = ms;
     cudaEventElapsedTime(&ms, e->ev[2], e->ev[3]); e->tm.finalize_ms = ms;
@@ -551,6 +563,10 @@ void triage_destroy(triage_engine *e) {
     e->d_all_keys.release(); e->d_header.release(); e->d_all_header.release(); e->d_run_gidx.release(); e->d_all_gidx.release();
     if (e->h_small) cudaFreeHost(e->h_small);
     if (e->h_header) cudaFreeHost(e->h_header);
+    if (e->h_ntotal) cudaFreeHost(e->h_ntotal);
+    if (e->merge_stream) { cudaStreamSynchronize(e->merge_stream); cudaStreamDestroy(e->merge_stream); }
+    if (e->ev_packed) cudaEventDestroy(e->ev_packed);
+    e->d_gsrc.release(); e->d_gall.release(); e->d_ntotal.release();
     for (auto &ev : e->ev) if (ev) cudaEventDestroy(ev);
     for (auto &ev : e->user_ev) if (ev) cudaEventDestroy(ev);
     if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
@@ -1408,10 +1424,61 @@ int32_t triage_comm_init(triage_engine *e, int32_t nranks, int32_t rank, const u
     e->nranks = nranks;
     e->rank = rank;
     CU(cudaHostAlloc(reinterpret_cast<void **>(&e->h_header), (size_t)nranks * kHeaderWords * 8, cudaHostAllocDefault));
+    CU(cudaStreamCreateWithFlags(&e->merge_stream, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&e->ev_packed, cudaEventDisableTiming));
+    CU(cudaHostAlloc(reinterpret_cast<void **>(&e->h_ntotal), 8, cudaHostAllocDefault));
+    CU(e->d_ntotal.ensure(1));
     return TRIAGE_OK;
 }
 
 }  // extern "C"
+
+// Contiguous sequence shards with engine-stamped enqueue times (the normal multi-GPU submit): inside every bucket rank q's
+// messages precede rank q+1's, so the merged order is offset arithmetic over the ranks' bucket counts.  One kernel packs
+// [counts | local order], ONE all-gather moves it, one kernel concatenates with the geometry worked out on the device -
+// all on the merge stream, no host round trip; the next submit only waits until its predecessor's order has been packed.
+static int32_t merge_one_exchange(triage_engine *e, const uint64_t *rank_base, uint32_t *order_global_dev, uint64_t capacity) {
+    cudaStream_t ms = e->merge_stream;
+    const uint32_t R = (uint32_t)e->nranks, n = e->last_n;
+    const uint32_t stride = kMergeHeaderWords + n;
+    CU(e->d_gsrc.ensure(stride));
+    CU(e->d_gall.ensure((size_t)R * stride));
+    MergeBases mb{};
+    mb.n_ranks = R; mb.stride = stride;
+    for (uint32_t q = 0; q < R; q++) mb.base[q] = (uint32_t)rank_base[q];
+    CU(launch_pack_run(e->last_order, e->last_counts_dev, e->last_n_adm_dev, n, e->d_gsrc.p, ms));
+    CU(cudaEventRecord(e->ev_packed, ms));
+    e->packed_pending = true;
+    ncclResult_t r = g_nccl.AllGather(e->d_gsrc.p, e->d_gall.p, stride, ncclUint32, e->comm, ms);
+    if (r != ncclSuccess) return fail(TRIAGE_E_CUDA, std::string("ncclAllGather(run): ") + g_nccl.GetErrorString(r));
+    CU(launch_concat_gathered(e->d_gall.p, mb, n, order_global_dev, capacity, e->d_ntotal.p, ms));
+    CU(cudaMemcpyAsync(e->h_ntotal, e->d_ntotal.p, 8, cudaMemcpyDeviceToHost, ms));
+    e->merge_capacity = capacity;
+    e->merge_pending = true;
+    return TRIAGE_OK;
+}
+
+extern "C" int32_t triage_merge_wait(triage_engine *e, uint64_t *n_total) {
+    if (!e) return fail(TRIAGE_E_ARG, "null engine");
+    if (!e->merge_pending) { if (n_total) *n_total = 0; return TRIAGE_OK; }
+    CU(cudaSetDevice(e->opts.device));
+    CU(cudaStreamSynchronize(e->merge_stream));
+    e->merge_pending = false;
+    e->packed_pending = false;
+    if (n_total) *n_total = *e->h_ntotal;
+    if (*e->h_ntotal > e->merge_capacity) return fail(TRIAGE_E_ARG, "order_global_dev is too small");
+    return TRIAGE_OK;
+}
+
+extern "C" int32_t triage_merge_allgather_async(triage_engine *e, const uint64_t *rank_base, uint32_t *order_global_dev, uint64_t capacity) {
+    if (!e || !rank_base || !order_global_dev) return fail(TRIAGE_E_ARG, "null argument");
+    if (!e->comm) return fail(TRIAGE_E_ARG, "triage_comm_init has not been called");
+    if (e->nranks > 8) return fail(TRIAGE_E_ARG, "at most 8 ranks");
+    if (e->last_ts != nullptr || !e->last_counts_dev)
+        return fail(TRIAGE_E_ARG, "the asynchronous merge needs engine-stamped enqueue times (pass no enqueue_ns to the submit); use triage_merge_allgather");
+    CU(cudaSetDevice(e->opts.device));
+    return merge_one_exchange(e, rank_base, order_global_dev, capacity);
+}
 
 extern "C" int32_t triage_merge_allgather(triage_engine *e, const uint64_t *rank_base, uint32_t *order_global_dev, uint64_t capacity,
                                           uint64_t *n_total) {
@@ -1419,6 +1486,12 @@ extern "C" int32_t triage_merge_allgather(triage_engine *e, const uint64_t *rank
     if (!e->comm) return fail(TRIAGE_E_ARG, "triage_comm_init has not been called");
     if (e->nranks > 8) return fail(TRIAGE_E_ARG, "at most 8 ranks");
     CU(cudaSetDevice(e->opts.device));
+    if (e->last_ts == nullptr && e->last_counts_dev && !getenv("TRIAGE_MERGE_TWO_STEP")) {   // contiguous shards: one exchange
+        if (e->merge_pending) { int32_t rc0 = triage_merge_wait(e, nullptr); if (rc0) return rc0; }
+        int32_t rc = merge_one_exchange(e, rank_base, order_global_dev, capacity);
+        if (rc) return rc;
+        return triage_merge_wait(e, n_total);
+    }
     cudaStream_t s = e->stream;
     const uint32_t R = (uint32_t)e->nranks;
     const uint32_t n_adm = e->last_n_adm;
@@ -1662,6 +1735,7 @@ extern "C" int32_t triage_submit_device_static(triage_engine *e, const uint64_t 
     // before the next static call on this GPU)
     for (int b = 0; b < 16; b++) e->last_counts[b] = e->h_small[2 + b];
     e->last_order = order_dev; e->last_bucket = bk; e->last_ts = enqueue_ns_dev; e->last_n = n; e->last_n_adm = *n_admitted;
+    e->last_counts_dev = small + 2; e->last_n_adm_dev = totals + 256;
     float ms_ = 0;
     cudaEventElapsedTime(&ms_, e->ev[1], e->ev[2]); e->tm.scan_ms = ms_;
     cudaEventElapsedTime(&ms_, e->ev[2], e->ev[3]); e->tm.finalize_ms = ms_;

@@ -1662,6 +1662,56 @@ __global__ void __launch_bounds__(256) merge_strided_kernel(const uint64_t *__re
     order_out[pos] = all_gidx[(uint64_t)q * t.cap + j];
 }
 
+// ---- one-exchange merge for contiguous sequence shards (engine-stamped enqueue times): every rank contributes
+// [32-word header: admitted, 16 bucket counts | its local order] at a common stride, one all-gather moves all of it, and
+// the concatenation works out its own geometry from the gathered headers - no host round trip between the two.
+__global__ void __launch_bounds__(256) pack_run_kernel(const uint32_t *__restrict__ order, const uint32_t *__restrict__ counts16,
+                                                       const uint32_t *__restrict__ n_adm, uint32_t n, uint32_t *__restrict__ gsrc) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < kMergeHeaderWords) gsrc[i] = i == 0 ? *n_adm : (i <= 16 ? counts16[i - 1] : 0u);
+    else if (i < kMergeHeaderWords + n) gsrc[i] = order[i - kMergeHeaderWords];
+}
+
+cudaError_t launch_pack_run(const uint32_t *order, const uint32_t *counts16_dev, const uint32_t *n_adm_dev, uint32_t n, uint32_t *gsrc,
+                            cudaStream_t s) {
+    const uint32_t total = kMergeHeaderWords + n;
+    pack_run_kernel<<<(total + 255) / 256, 256, 0, s>>>(order, counts16_dev, n_adm_dev, n, gsrc);
+    return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) concat_gathered_kernel(const uint32_t *__restrict__ all, MergeBases mb, uint32_t *__restrict__ order_out,
+                                                              uint64_t capacity, uint64_t *__restrict__ n_total_out) {
+    __shared__ uint32_t cnt[8], lstart[8][16], dst[8][16];
+    __shared__ uint64_t total_s;
+    if (threadIdx.x == 0) {   // geometry from the gathered headers: bucket-major, rank-minor
+        uint64_t total = 0;
+        for (uint32_t q = 0; q < mb.n_ranks; q++) { cnt[q] = all[(uint64_t)q * mb.stride]; total += cnt[q]; }
+        uint32_t d = 0;
+        for (uint32_t b = 0; b < 16; b++)
+            for (uint32_t q = 0; q < mb.n_ranks; q++) { dst[q][b] = d; d += all[(uint64_t)q * mb.stride + 1 + b]; }
+        for (uint32_t q = 0; q < mb.n_ranks; q++) {
+            uint32_t acc = 0;
+            for (uint32_t b = 0; b < 16; b++) { lstart[q][b] = acc; acc += all[(uint64_t)q * mb.stride + 1 + b]; }
+        }
+        total_s = total;
+    }
+    __syncthreads();
+    const uint32_t q = blockIdx.y, j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q == 0 && j == 0 && n_total_out) *n_total_out = total_s;
+    if (total_s > capacity || j >= cnt[q]) return;   // too small an output buffer: nothing is written, the host reports it
+    uint32_t b = 0;
+#pragma unroll
+    for (uint32_t i = 1; i < 16; i++) if (j >= lstart[q][i]) b = i;
+    order_out[dst[q][b] + (j - lstart[q][b])] = all[(uint64_t)q * mb.stride + kMergeHeaderWords + j] + mb.base[q];
+}
+
+cudaError_t launch_concat_gathered(const uint32_t *all, const MergeBases &mb, uint32_t n_per_rank, uint32_t *order_out, uint64_t capacity,
+                                   uint64_t *n_total_dev, cudaStream_t s) {
+    dim3 grid((n_per_rank + 255) / 256 ? (n_per_rank + 255) / 256 : 1, mb.n_ranks);
+    concat_gathered_kernel<<<grid, 256, 0, s>>>(all, mb, order_out, capacity, n_total_dev);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_merge_strided(const uint64_t *all_keys, const uint32_t *all_gidx, const ConcatTables &t, uint32_t *order_out, cudaStream_t s) {
     dim3 grid((t.cap + 255) / 256, t.n_ranks);
     merge_strided_kernel<<<grid, 256, 0, s>>>(all_keys, all_gidx, t, order_out);

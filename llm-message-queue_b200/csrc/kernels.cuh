@@ -143,6 +143,13 @@ struct ConcatTables {
     uint32_t dst[8][16];          // destination of the first element of (rank, bucket)
     uint32_t lstart[8][16];       // start of bucket inside the rank's run
 };
+// one-exchange merge (contiguous sequence shards): [header | order] per rank at stride kMergeHeaderWords + n
+constexpr uint32_t kMergeHeaderWords = 32;
+struct MergeBases { uint32_t base[8]; uint32_t n_ranks; uint32_t stride; };
+cudaError_t launch_pack_run(const uint32_t *order, const uint32_t *counts16_dev, const uint32_t *n_adm_dev, uint32_t n, uint32_t *gsrc,
+                            cudaStream_t s);
+cudaError_t launch_concat_gathered(const uint32_t *all, const MergeBases &mb, uint32_t n_per_rank, uint32_t *order_out, uint64_t capacity,
+                                   uint64_t *n_total_dev, cudaStream_t s);
 cudaError_t launch_header(const uint32_t *order, uint32_t n_adm, const uint32_t *counts16_host, const uint64_t *ts, uint64_t ts_base,
                           uint64_t *header_dev, cudaStream_t s);
 cudaError_t launch_concat(const uint32_t *all_order, const ConcatTables &t, uint32_t *order_out, cudaStream_t s);

@@ -50,8 +50,11 @@ def _worker(rank, world, port, q):
         d_gord = torch.zeros(n * world, dtype=torch.int32, device=dev)
         rank_base = np.arange(world, dtype=np.uint64) * np.uint64(n)
         results = {}
-        for case in ("contiguous", "interleaved"):
-            if case == "contiguous":
+        for case in ("contiguous", "contiguous-async", "contiguous-two-step", "interleaved"):
+            os.environ.pop("TRIAGE_MERGE_TWO_STEP", None)
+            if case == "contiguous-two-step":          # the header + host geometry + order exchange kept for explicit times
+                os.environ["TRIAGE_MERGE_TWO_STEP"] = "1"
+            if case.startswith("contiguous"):
                 ts_all = ts                                   # generator times: strictly increasing in global arrival order
                 ts_ptr = None                                 # engine-stamped: arrival order is time order
             else:                                             # rank r's message i gets a time between those of the other ranks
@@ -63,7 +66,15 @@ def _worker(rank, world, port, q):
             torch.cuda.synchronize()
             adm = eng.submit_device_padded(d_off.data_ptr(), d_len.data_ptr(), d_bytes.data_ptr(), int(poff[-1]), d_meta.data_ptr(), ts_ptr,
                                            n, d_res.data_ptr(), d_ord.data_ptr())
-            total = eng.merge_allgather(rank_base, d_gord.data_ptr(), n * world)
+            d_gord.fill_(-1)
+            if case == "contiguous-async":             # one exchange on the merge stream, a second submit issued under it
+                eng.merge_allgather_async(rank_base, d_gord.data_ptr(), n * world)
+                adm2 = eng.submit_device_padded(d_off.data_ptr(), d_len.data_ptr(), d_bytes.data_ptr(), int(poff[-1]), d_meta.data_ptr(), ts_ptr,
+                                                n, d_res.data_ptr(), d_ord.data_ptr())
+                assert adm2 == adm
+                total = eng.merge_wait()
+            else:
+                total = eng.merge_allgather(rank_base, d_gord.data_ptr(), n * world)
             got = d_gord.cpu().numpy()[:total].astype(np.uint32)
             # (a) the whole job through the oracle as ONE batch
             exp, order = co.pipeline(co.Dict(), off, data, meta, ts_all, nthreads=4)
