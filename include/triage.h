@@ -44,6 +44,8 @@ extern "C" {
 #define TRIAGE_UP_ABSENT        0   /* Metadata["user_priority"] absent or not a string  */
 #define TRIAGE_UP_UNRECOGNISED  5   /* a string that is none of realtime/high/normal/low */
 #define TRIAGE_META_VIP         1   /* Metadata has key "vip_user" (queue_factory.go:217) */
+#define TRIAGE_META_ANALYZE     2   /* fill words / sentiment / question even where ProcessMessage returns early
+                                       (api/handlers.go:180-190 analyses every submitted message); no Metadata is implied */
 
 #define TRIAGE_RF_ANALYZED      1   /* Metadata["analyzed"] = true (preprocessor.go:100)  */
 #define TRIAGE_RF_TIE           2   /* equal non-zero top scores: reference is random here */
@@ -203,6 +205,24 @@ int32_t triage_queue_size(triage_engine *e, int32_t level, uint64_t *size);     
 int32_t triage_stats(triage_engine *e, int32_t level, triage_qstats *st);         /* GetStats, :165 */
 int32_t triage_complete(triage_engine *e, int32_t level);                         /* CompleteMessage, :197 */
 int32_t triage_fail(triage_engine *e, int32_t level);                             /* FailMessage, :205 */
+
+/* -- the wire format on either side of the path, in batches.
+ *    triage_ingest_json = c.ShouldBindJSON(&message) (api/handlers.go:160-166) for n request bodies laid end to end
+ *    (body i = bodies[body_offsets[i] .. body_offsets[i+1])): content goes straight into the padded arena, the fields of
+ *    models.Message the path reads (pkg/models/message.go:58-74: priority, user_id -> the table of
+ *    triage_set_user_priority, metadata.user_priority / priority / vip_user) into triage_meta, with TRIAGE_META_ANALYZE set;
+ *    every other field is type-checked only.  status[i] = 1 where the handler would answer 400 (bad JSON, or a known
+ *    field of the wrong type): that message becomes an empty slot the caller skips.  arena = NULL computes offsets,
+ *    lengths, meta, status and *arena_total (the size to allocate) only.  encoding/json rules followed: csrc/ingest.cc.
+ *    triage_set_user_priority = Preprocessor.SetUserPriority (preprocessor.go:171); prio 0 removes the entry.
+ *    triage_emit_analysis_json = json.Marshal(AnalyzeMessageContent(content)) (api/handlers.go:180-190) for n results:
+ *    {"is_question":..,"sentiment":"..","word_count":..} each, message i at out[out_offsets[i] .. out_offsets[i+1]);
+ *    *needed = total bytes (call with out = NULL to size the buffer). */
+int32_t triage_set_user_priority(triage_engine *e, const char *user_id, uint32_t len, int32_t prio);
+int32_t triage_ingest_json(triage_engine *e, const uint8_t *bodies, const uint64_t *body_offsets, uint32_t n, uint8_t *arena,
+                           uint64_t arena_cap, uint64_t *offsets, uint32_t *lengths, triage_meta *meta, uint8_t *status,
+                           uint64_t *arena_total);
+int32_t triage_emit_analysis_json(const triage_result *res, uint32_t n, char *out, uint64_t cap, uint64_t *out_offsets, uint64_t *needed);
 
 /* -- batch consumer side.  triage_drain_queue = QueueManager.BatchPopMessages(queueName, count) (queue_manager.go:326-367):
  *    pops from ONE queue until it is empty or max is reached, under one lock and with one statistics update

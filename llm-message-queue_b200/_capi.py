@@ -21,6 +21,7 @@ RESULT_DTYPE = np.dtype([("label", "u1"), ("reason", "u1"), ("sentiment", "i1"),
                          ("words", "<u4"), ("score_rt", "<u2"), ("score_hi", "<u2")])
 RF_ANALYZED, RF_TIE, RF_HAS_ANALYSIS = 1, 2, 4
 META_VIP = 1
+META_ANALYZE = 2
 UP_UNRECOGNISED = 5
 
 
@@ -106,6 +107,10 @@ _SIGS = {
     "triage_stats": (C.c_int32, [C.c_void_p, C.c_int32, C.POINTER(QStats)]),
     "triage_complete": (C.c_int32, [C.c_void_p, C.c_int32]),
     "triage_fail": (C.c_int32, [C.c_void_p, C.c_int32]),
+    "triage_set_user_priority": (C.c_int32, [C.c_void_p, C.c_char_p, C.c_uint32, C.c_int32]),
+    "triage_ingest_json": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
+                                       C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]),
+    "triage_emit_analysis_json": (C.c_int32, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint64)]),
     "triage_drain_queue": (C.c_int32, [C.c_void_p, C.c_int32, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint32)]),
     "triage_complete_batch": (C.c_int32, [C.c_void_p, C.c_int32, C.c_uint32]),
     "triage_fail_batch": (C.c_int32, [C.c_void_p, C.c_int32, C.c_uint32]),
@@ -355,6 +360,40 @@ class Engine:
 
     def fail(self, q: int):
         _check(lib().triage_fail(self._h, int(q)))
+
+    # -- wire format: JSON in, analysis JSON out ------------------------------
+    def set_user_priority(self, user_id: str | bytes, prio: int):
+        b = user_id.encode("utf-8") if isinstance(user_id, str) else user_id
+        _check(lib().triage_set_user_priority(self._h, b, len(b), int(prio)))
+
+    def ingest_json(self, bodies: list[bytes]):
+        """request bodies -> (offsets, lengths, arena bytes, meta, status) in the padded layout, ready for submit_padded"""
+        n = len(bodies)
+        boff = np.zeros(n + 1, np.uint64)
+        if n:
+            np.cumsum([len(b) for b in bodies], out=boff[1:])
+        blob = np.frombuffer(b"".join(bodies) or b"\0", np.uint8)
+        off = np.zeros(n + 1, np.uint64)
+        lens = np.zeros(max(n, 1), np.uint32)
+        meta = np.zeros(max(n, 1), META_DTYPE)
+        status = np.zeros(max(n, 1), np.uint8)
+        total = C.c_uint64()
+        _check(lib().triage_ingest_json(self._h, _p(blob), _p(boff), n, None, 0, _p(off), _p(lens), _p(meta), _p(status), C.byref(total)))
+        arena = np.empty(max(total.value, 16), np.uint8)
+        _check(lib().triage_ingest_json(self._h, _p(blob), _p(boff), n, _p(arena), len(arena), _p(off), _p(lens), _p(meta), _p(status), C.byref(total)))
+        return off, lens[:n], arena[:total.value], meta[:n], status[:n]
+
+    @staticmethod
+    def emit_analysis_json(results) -> list[bytes]:
+        n = len(results)
+        res = np.ascontiguousarray(results)
+        need = C.c_uint64()
+        _check(lib().triage_emit_analysis_json(_p(res), n, None, 0, None, C.byref(need)))
+        out = np.zeros(max(need.value, 1), np.uint8)
+        offs = np.zeros(n + 1, np.uint64)
+        _check(lib().triage_emit_analysis_json(_p(res), n, _p(out), len(out), _p(offs), C.byref(need)))
+        raw = out.tobytes()
+        return [raw[int(offs[i]):int(offs[i + 1])] for i in range(n)]
 
     # -- batch consumer, retries, delayed items --------------------------------
     def drain_queue(self, q: int, max_items: int):

@@ -21,6 +21,8 @@
 #include "dfa_build.h"
 #include "kernels.cuh"
 #include "regex_vm.h"
+#include "ingest.h"
+#include <unordered_map>
 
 using namespace triage;
 
@@ -154,6 +156,7 @@ struct triage_engine {
     cudaEvent_t ev[6]{};
     cudaEvent_t user_ev[4]{};
     int32_t default_prio = TRIAGE_PRIO_NORMAL;
+    std::unordered_map<std::string, int> user_prio;   // Preprocessor.userPriorities for the JSON ingest
     std::vector<DictEntry> dict;
     RegexSet regex;                // AddKeywordPattern patterns that are not plain literals (regex_vm.h)
     DevBuf<RegexProgram> d_rx_prog;
@@ -1234,6 +1237,41 @@ int32_t push_run(triage_engine *e, int32_t queue, const uint64_t *handles, const
 }  // namespace
 
 extern "C" {
+
+int32_t triage_set_user_priority(triage_engine *e, const char *user_id, uint32_t len, int32_t prio) {
+    if (!e || (len && !user_id)) return fail(TRIAGE_E_ARG, "null argument");
+    std::lock_guard<std::mutex> lock(e->mu);
+    std::string k(user_id ? user_id : "", len);
+    if (prio == 0) e->user_prio.erase(k); else e->user_prio[k] = prio;
+    return TRIAGE_OK;
+}
+
+int32_t triage_ingest_json(triage_engine *e, const uint8_t *bodies, const uint64_t *body_offsets, uint32_t n, uint8_t *arena,
+                           uint64_t arena_cap, uint64_t *offsets, uint32_t *lengths, triage_meta *meta, uint8_t *status,
+                           uint64_t *arena_total) {
+    if (!e) return fail(TRIAGE_E_ARG, "null engine");
+    CU(cudaSetDevice(e->opts.device));
+    int32_t rc = commit_dict(e);   // the pad byte belongs to the dictionary
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lock(e->mu);
+    auto lookup = [](const void *ctx, const char *id, size_t len) -> int {
+        const auto *m = static_cast<const std::unordered_map<std::string, int> *>(ctx);
+        auto it = m->find(std::string(id, len));
+        return it == m->end() ? 0 : it->second;
+    };
+    IngestOut out{arena, arena_cap, offsets, lengths, meta, status};
+    std::string err = ingest_json(bodies, body_offsets, n, e->ddfa.reset_pad, lookup, &e->user_prio, out, arena_total);
+    if (!err.empty()) return fail(TRIAGE_E_ARG, "triage_ingest_json: " + err);
+    for (uint32_t i = 0; i < n; i++) meta[i].flags |= TRIAGE_META_ANALYZE;
+    return TRIAGE_OK;
+}
+
+int32_t triage_emit_analysis_json(const triage_result *res, uint32_t n, char *out, uint64_t cap, uint64_t *out_offsets, uint64_t *needed) {
+    if ((n && !res) || !needed) return fail(TRIAGE_E_ARG, "null argument");
+    *needed = emit_analysis_json(res, n, out, cap, out_offsets);
+    if (out && *needed > cap) return fail(TRIAGE_E_ARG, "output buffer too small");
+    return TRIAGE_OK;
+}
 
 // QueueManager.BatchPopMessages(queueName, count) (queue_manager.go:326-367): pops until the queue is empty
 int32_t triage_drain_queue(triage_engine *e, int32_t queue, uint32_t max, uint64_t *handles, uint32_t *n_out) {

@@ -1290,6 +1290,13 @@ __global__ void __launch_bounds__(256) finalize_kernel(FinalizeArgs a) {
             if (a.lengths && a.bytes[off_i + len - 1] == '?') question = 1;   // HasSuffix(content, "?") (the unpadded scan does it itself)
             rflags |= TRIAGE_RF_HAS_ANALYSIS;
         }
+    } else if ((mflags & TRIAGE_META_ANALYZE) && len > 0) {
+        // api/handlers.go:180-190 runs AnalyzeMessageContent on every message, also on those ProcessMessage leaves alone:
+        // the analysis fields are filled in for the emit, Metadata (TRIAGE_RF_HAS_ANALYSIS) stays untouched
+        words = c0.x;
+        sentiment = c1.y > c1.z ? 1 : (c1.z > c1.y ? -1 : 0);
+        question = (c1.w & 1u) ? 1 : 0;
+        if (a.lengths && a.bytes[off_i + len - 1] == '?') question = 1;
     }
     // queue level = pre-rule label (api/handlers.go:202); rules mutate msg.Priority before the push
     uint32_t level = label, bucket = 0xFF, admit = TRIAGE_E_NOT_FOUND, accepted = 0;

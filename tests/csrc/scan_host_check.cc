@@ -567,3 +567,24 @@ extern "C" int hostcheck_scan_pair(const uint8_t *prios, const uint8_t *cis, con
     }
     return 0;
 }
+
+// ---- JSON ingest / analysis emit (ingest.cc), engine-free ----
+#include "../../llm-message-queue_b200/csrc/ingest.h"
+extern "C" int hostcheck_ingest(const uint8_t *bodies, const uint64_t *body_offsets, uint32_t n, int pad, const char *vip_user, int vip_prio,
+                                uint8_t *arena, uint64_t cap, uint64_t *offsets, uint32_t *lengths, triage_meta *meta, uint8_t *status,
+                                uint64_t *total, char *err, uint32_t errcap)
+{
+    struct Ctx { std::string user; int prio; } ctx{vip_user ? vip_user : "", vip_prio};
+    auto lookup = [](const void *c, const char *id, size_t len) -> int {
+        const Ctx *x = static_cast<const Ctx *>(c);
+        return (!x->user.empty() && x->user == std::string(id, len)) ? x->prio : 0;
+    };
+    triage::IngestOut out{arena, cap, offsets, lengths, meta, status};
+    std::string e = triage::ingest_json(bodies, body_offsets, n, pad, lookup, &ctx, out, total);
+    if (!e.empty()) { snprintf(err, errcap, "%s", e.c_str()); return 5; }
+    return 0;
+}
+extern "C" uint64_t hostcheck_emit(const triage_result *res, uint32_t n, char *out, uint64_t cap, uint64_t *offsets)
+{
+    return triage::emit_analysis_json(res, n, out, cap, offsets);
+}

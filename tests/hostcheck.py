@@ -10,9 +10,10 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 SRC = [os.path.join(HERE, "csrc", "scan_host_check.cc"),
        os.path.join(ROOT, "llm-message-queue_b200", "csrc", "dfa_build.cc"),
-       os.path.join(ROOT, "llm-message-queue_b200", "csrc", "regex_vm.cc")]
+       os.path.join(ROOT, "llm-message-queue_b200", "csrc", "regex_vm.cc"),
+       os.path.join(ROOT, "llm-message-queue_b200", "csrc", "ingest.cc")]
 DEPS = SRC + [os.path.join(ROOT, "llm-message-queue_b200", "csrc", f)
-              for f in ("dfa_build.h", "scan_core.cuh", "scan_wide.cuh", "scan_pair.cuh", "regex_vm.h", "regex_walk.cuh")]
+              for f in ("dfa_build.h", "scan_core.cuh", "scan_wide.cuh", "scan_pair.cuh", "regex_vm.h", "regex_walk.cuh", "ingest.h")]
 LIB = os.path.join(HERE, "csrc", "libscan_host_check.so")
 
 DEFAULT_DICT = [(1, True, b"immediate"), (1, True, b"emergency"), (1, True, b"asap"), (1, True, b"right now"),
@@ -159,3 +160,51 @@ def scan_pair(dict_entries, offsets, data, chunk_long=320):
     if rc != 0:
         raise ValueError(err.value.decode())
     return counters[:n], dict(filter_states=int(info[0]), mul=int(info[1]), shift=int(info[2]), flagged=int(info[3]), groups=int(info[4]))
+
+
+META_DTYPE = np.dtype([("preset", "u1"), ("user_priority", "u1"), ("user_default", "u1"), ("meta_priority", "u1"), ("flags", "u1"),
+                       ("reserved", "u1", (11,))])
+RESULT_DTYPE = np.dtype([("label", "u1"), ("reason", "u1"), ("sentiment", "i1"), ("question", "u1"), ("accepted", "u1"), ("admit", "u1"),
+                         ("flags", "u1"), ("queue_level", "u1"), ("words", "<u4"), ("score_rt", "<u2"), ("score_hi", "<u2")])
+
+
+def ingest(bodies, pad=9, user=None, user_prio=0):
+    """host build of triage_ingest_json's decoder -> (contents list[bytes], meta, status)"""
+    n = len(bodies)
+    boff = np.zeros(n + 1, np.uint64)
+    if n:
+        np.cumsum([len(b) for b in bodies], out=boff[1:])
+    blob = np.frombuffer(b"".join(bodies) or b"\0", np.uint8)
+    off = np.zeros(n + 1, np.uint64)
+    lens = np.zeros(max(n, 1), np.uint32)
+    meta = np.zeros(max(n, 1), META_DTYPE)
+    status = np.zeros(max(n, 1), np.uint8)
+    total = C.c_uint64()
+    err = C.create_string_buffer(256)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    u = user.encode() if user else None
+    rc = lib().hostcheck_ingest(p(blob), p(boff), n, pad, u, user_prio, None, 0, p(off), p(lens), p(meta), p(status), C.byref(total), err, 256)
+    if rc:
+        raise ValueError(err.value.decode())
+    arena = np.zeros(max(total.value, 16), np.uint8)
+    rc = lib().hostcheck_ingest(p(blob), p(boff), n, pad, u, user_prio, p(arena), len(arena), p(off), p(lens), p(meta), p(status), C.byref(total), err, 256)
+    if rc:
+        raise ValueError(err.value.decode())
+    raw = arena.tobytes()
+    contents = [raw[int(off[i]):int(off[i]) + int(lens[i])] for i in range(n)]
+    for i in range(n):      # the layout contract of the padded arena
+        assert off[i] % 16 == 0 and 1 <= int(off[i + 1]) - int(off[i]) - int(lens[i]) <= 16
+        assert set(raw[int(off[i]) + int(lens[i]):int(off[i + 1])]) == {pad}
+    return contents, meta[:n], status[:n]
+
+
+def emit(results):
+    res = np.ascontiguousarray(results)
+    n = len(res)
+    lib().hostcheck_emit.restype = C.c_uint64
+    need = lib().hostcheck_emit(res.ctypes.data_as(C.c_void_p), n, None, 0, None)
+    out = np.zeros(max(int(need), 1), np.uint8)
+    offs = np.zeros(n + 1, np.uint64)
+    lib().hostcheck_emit(res.ctypes.data_as(C.c_void_p), n, out.ctypes.data_as(C.c_void_p), len(out), offs.ctypes.data_as(C.c_void_p))
+    raw = out.tobytes()
+    return [raw[int(offs[i]):int(offs[i + 1])] for i in range(n)]
