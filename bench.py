@@ -139,7 +139,17 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
-def workload_config(n_gpus):
+C3_GLOBAL = 1 << 24   # BASELINE configs[2]: 16 Mi mixed-length messages sharded over the GPUs
+
+
+def workload_config(n_gpus, workload="c2"):
+    if workload == "c3":
+        return {"workload": "BASELINE configs[2]: 16Mi messages in total, length mix 70% U[256,1024] / 25% U[1024,4096] / 5% U[4096,16384], "
+                            "sharded contiguously over the GPUs, NCCL all-gather merge of the sorted runs, default dictionary",
+                "messages_per_gpu": C3_GLOBAL // n_gpus, "global_messages": C3_GLOBAL,
+                "parallelism": f"shard{n_gpus}" if n_gpus > 1 else "single",
+                "l2_policy": "inputs (26.8 GB in total) larger than the 126 MB L2; no flush needed",
+                "timestamps": "engine-stamped, strictly increasing in arrival order"}
     return {"workload": "BASELINE configs[1] per GPU: 1Mi messages, content U[256,4096] bytes, 4 priority levels, default 9-keyword dictionary",
             "messages_per_gpu": N_PER_GPU, "global_messages": N_PER_GPU * n_gpus,
             "parallelism": f"shard{n_gpus}" if n_gpus > 1 else "single",
@@ -165,7 +175,7 @@ def self_check(args, mq, co, dist, rank, world, n, d_res, d_ord, d_gord, ts_host
     how = []
     labels_ok = True
     digest_path = os.path.join(ROOT, "tests", "golden", "fullsize_sha256.json")
-    if rank == 0 and n == N_PER_GPU and os.path.exists(digest_path) and not args.interleave_ts:
+    if rank == 0 and n == N_PER_GPU and args.workload == "c2" and os.path.exists(digest_path) and not args.interleave_ts:
         want = json.load(open(digest_path)).get("c2", {})
         if want.get("messages") == n:
             for f in fields + ("accepted", "admit"):
@@ -205,7 +215,7 @@ def self_check(args, mq, co, dist, rank, world, n, d_res, d_ord, d_gord, ts_host
         want_local = idx[np.argsort(bucket[idx], kind="stable")]
     got_local = d_ord.cpu().numpy().astype(np.int64)[:len(want_local)]
     out["order"] = bool(np.array_equal(got_local, want_local))
-    if rank == 0 and n == N_PER_GPU and os.path.exists(digest_path) and not args.interleave_ts:
+    if rank == 0 and n == N_PER_GPU and args.workload == "c2" and os.path.exists(digest_path) and not args.interleave_ts:
         want = json.load(open(digest_path)).get("c2", {})
         if want.get("messages") == n:
             out["order"] = out["order"] and hashlib.sha256(got_local.astype(np.uint32).tobytes()).hexdigest() == want["order"]
@@ -236,7 +246,10 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
-    ap.add_argument("--messages", type=int, default=N_PER_GPU, help="messages per GPU (default: the BASELINE config)")
+    ap.add_argument("--messages", type=int, default=0, help="messages per GPU (default: the workload's own size)")
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3"],
+                    help="c2 (default, what the driver records): configs[1], 1 Mi messages per GPU, weak scaling; "
+                         "c3: configs[2], 16 Mi mixed-length messages in total, sharded over the GPUs, strong scaling")
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--interleave-ts", action="store_true", help="(test) explicit enqueue times that interleave across ranks: exercises the general merge")
@@ -266,9 +279,15 @@ def main():
         if world > 1:
             dist.barrier()
 
-    n = args.messages
+    c3 = args.workload == "c3"
+    n = args.messages or (C3_GLOBAL // world if c3 else N_PER_GPU)
     # ---- synthetic batch of this rank (own seed => different content per rank) ----
-    off, data, meta, _ = co.generate(SEED + rank, n, LEN_LO, LEN_HI, edge=50)
+    if c3:
+        off, data, meta, _ = co.generate(0xC0FFEE03 + rank, n, 256, 16384, mix=1, edge=50)
+        if n * 1700 > (4 << 30):
+            args.skip_e2e = True      # two pinned host arenas of this size per rank are not what this line is about
+    else:
+        off, data, meta, _ = co.generate(SEED + rank, n, LEN_LO, LEN_HI, edge=50)
     total = int(off[-1])
     eng = mq.Engine(device=local)
     info = eng.dict_info()
@@ -454,8 +473,8 @@ def main():
                             "sample": f"{ns} messages of the same generator, one pass ({dt:.1f} s): C restatement of the Go path, "
                                       f"preprocess on {threads} threads, container/heap push+drain on 1 thread"}
         line = {"metric": METRIC, "value": value, "unit": "msgs/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
-                "data": "synthetic", "config": workload_config(world) | {"messages_per_gpu": n, "global_messages": n * world,
+                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if c3 else "weak", "vs_baseline": None, "dtype": "u8",
+                "data": "synthetic", "config": workload_config(world, args.workload) | {"messages_per_gpu": n, "global_messages": n * world,
                                                                           "arena_bytes_per_gpu": total, "content_bytes_per_gpu": content_bytes, "arena_layout": "padded16 (16-byte aligned starts, TAB reset pads)", "automaton_states": info["states"],
                                                                           "order_passes": passes},
                 "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,

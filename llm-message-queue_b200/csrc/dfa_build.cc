@@ -555,10 +555,11 @@ std::vector<ClassPattern> class_patterns(const std::vector<DictEntry> &dict, uin
     uint16_t ws = 0;
     for (uint32_t b : {0x09u, 0x0Au, 0x0Bu, 0x0Cu, 0x0Du, 0x20u}) ws |= static_cast<uint16_t>(1u << class4(b, mul, shift));
     for (const DictEntry &d : dict) {
+        // literals of any script: their bytes map to classes like any others (only the lead bytes C2 C4 C5 E0-E3 force an
+        // exact walk on the device, and an occurrence that holds one of those is found there)
         ClassPattern p;
-        bool ascii = true;
-        for (unsigned char ch : d.bytes) { if (ch >= 0x80) { ascii = false; break; } p.sym.push_back(letter(ch, d.ci)); }
-        if (ascii && !p.sym.empty()) out.push_back(p);   // an occurrence of a non-ASCII literal always lies in groups walked exactly
+        for (unsigned char ch : d.bytes) p.sym.push_back(letter(ch, d.ci && ch < 0x80));
+        if (!p.sym.empty()) out.push_back(p);
     }
     for (const char *q : {"what", "how", "why", "when", "where", "who"}) {
         ClassPattern p;
@@ -930,6 +931,23 @@ std::string build_dfa(const std::vector<DictEntry> &dict, Dfa *out, bool exact_n
             }
             if (ok) out->tail_pad = static_cast<int>(b);
         }
+    }
+    out->ctable.clear();
+    out->n_cmp = 0;
+    if (!wide) {   // column-merged copy of the dense table
+        std::map<std::vector<uint16_t>, uint32_t> cols;
+        std::vector<uint32_t> rep;
+        for (uint32_t b = 0; b < 256; b++) {
+            std::vector<uint16_t> col(nmin);
+            for (uint32_t st = 0; st < nmin; st++) col[st] = out->table[static_cast<size_t>(st) * 256 + b];
+            auto it = cols.find(col);
+            if (it == cols.end()) { it = cols.emplace(col, static_cast<uint32_t>(rep.size())).first; rep.push_back(b); }
+            out->ccls[b] = static_cast<uint8_t>(it->second);
+        }
+        out->n_cmp = static_cast<uint32_t>(rep.size());
+        out->ctable.resize(static_cast<size_t>(nmin) * out->n_cmp);
+        for (uint32_t st = 0; st < nmin; st++)
+            for (uint32_t c = 0; c < out->n_cmp; c++) out->ctable[static_cast<size_t>(st) * out->n_cmp + c] = out->table[static_cast<size_t>(st) * 256 + rep[c]];
     }
     if (!exact_nonoverlap) build_pair_filter(dict, *out, &out->filter);
     return "";

@@ -68,6 +68,11 @@ struct PairFilter {
 
 struct Dfa {
     PairFilter filter;
+    // D8 only: the same automaton with identical byte columns merged - entry(state, ccls[byte]), n_cmp entries per state.
+    // Small enough to sit in shared memory next to the filter table; the pair lanes walk flagged groups through it.
+    std::vector<uint16_t> ctable;
+    uint8_t ccls[256] = {0};
+    uint32_t n_cmp = 0;
     uint32_t n_states = 0;
     bool wide = false;
     std::vector<uint16_t> table;      // D8: n_states * 256

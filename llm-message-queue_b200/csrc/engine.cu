@@ -81,10 +81,11 @@ struct DevBuf {
 };
 
 struct DfaBufs {
-    DevBuf<uint8_t> table, eom, cls, ftable;
+    DevBuf<uint8_t> table, eom, cls, ftable, ccls;
+    DevBuf<uint16_t> ctable;
     DevBuf<EventPacked> events;
     DevBuf<uint32_t> wtable, eomw;
-    void release() { table.release(); eom.release(); cls.release(); ftable.release(); events.release(); wtable.release(); eomw.release(); }
+    void release() { table.release(); eom.release(); cls.release(); ftable.release(); ccls.release(); ctable.release(); events.release(); wtable.release(); eomw.release(); }
 };
 
 struct QItem { int32_t prio; uint64_t ts; uint64_t handle; };
@@ -261,8 +262,13 @@ int32_t upload_dfa(const Dfa &dfa, DfaBufs *b, DeviceDfa *out) {
                 std::memcpy(fp.data() + (size_t)st * kRowBytes, dfa.filter.table.data() + (size_t)st * 256, 512);
             CU(b->ftable.ensure(fp.size()));
             CU(cudaMemcpy(b->ftable.p, fp.data(), fp.size(), cudaMemcpyHostToDevice));
+            CU(b->ctable.ensure(dfa.ctable.size()));
+            CU(b->ccls.ensure(256));
+            CU(cudaMemcpy(b->ctable.p, dfa.ctable.data(), dfa.ctable.size() * 2, cudaMemcpyHostToDevice));
+            CU(cudaMemcpy(b->ccls.p, dfa.ccls, 256, cudaMemcpyHostToDevice));
             d.has_filter = 1; d.ftable = b->ftable.p; d.f_states = dfa.filter.n_states; d.f_start = dfa.filter.start;
             d.f_mul = dfa.filter.mul; d.f_shift = dfa.filter.shift;
+            d.ctable = b->ctable.p; d.ccls = b->ccls.p; d.n_cmp = dfa.n_cmp;
         }
     } else {
         d.start_state = dfa.start_state_w; d.neutral_state = dfa.neutral_state_w;

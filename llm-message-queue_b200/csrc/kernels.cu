@@ -881,13 +881,15 @@ cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw,
 // bytes), word starts are counted by SIMD-in-register compares, and the groups the filter flags (or that hold bytes >=
 // 0x80) are queued per warp - (message, the 16 bytes before, the 16 bytes) - and walked through the exact automaton in
 // global memory by the whole warp, one queued group per lane.
-constexpr uint32_t kPairQueueCap = 24;     // flagged groups per warp (36 bytes each)
-constexpr uint32_t kPairQueueFlush = 12;
-struct PairSmem { uint32_t table, warp0, aux0, total, warp_bytes, aux_bytes, warm_off, list_off, queue_off; };
-__host__ __device__ inline PairSmem pair_layout(uint32_t f_states, uint32_t nw) {
+constexpr uint32_t kPairQueueCap = 16;     // flagged groups per warp (36 bytes each)
+constexpr uint32_t kPairQueueFlush = 12;   // walked by the whole warp once this many wait (more can arrive in one step: those beyond the cap are walked by their own lane)
+struct PairSmem { uint32_t table, xtable, xcls, warp0, aux0, total, warp_bytes, aux_bytes, warm_off, list_off, queue_off; };
+__host__ __device__ inline PairSmem pair_layout(uint32_t f_states, uint32_t x_states, uint32_t x_cls, uint32_t nw) {
     PairSmem L;
     uint32_t o = 1024;   // mbarriers
     L.table = o; o += ((f_states * kRowBytes + 127u) / 128u) * 128u;
+    L.xtable = o; o += ((x_states * x_cls * 2u + 127u) / 128u) * 128u;   // exact automaton, column-merged: flagged groups only
+    L.xcls = o; o += 256u;
     L.warm_off = 2 * 32 * kRowWin;
     L.warp_bytes = L.warm_off + 512;
     L.warp0 = o; o += nw * L.warp_bytes;
@@ -898,7 +900,7 @@ __host__ __device__ inline PairSmem pair_layout(uint32_t f_states, uint32_t nw) 
     L.total = o;
     return L;
 }
-size_t scan_pair_smem_bytes(const DeviceDfa &d, uint32_t nw) { return pair_layout(d.f_states, nw).total; }
+size_t scan_pair_smem_bytes(const DeviceDfa &d, uint32_t nw) { return pair_layout(d.f_states, d.n_states, d.n_cmp, nw).total; }
 uint32_t pick_pair_warps(const DeviceDfa &d, size_t max_smem) {
     if (!d.has_filter || d.wide || d.warm != 16 || d.reset_pad < 0) return 0;
     if (const char *v = getenv("TRIAGE_PAIR")) { if (atoi(v) == 0) return 0; }   // measurement knob: keep to the one-lookup-per-byte lanes
@@ -953,7 +955,7 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, Devic
     extern __shared__ __align__(128) uint8_t smem[];
     constexpr int32_t CL = LANE, WIN = (int32_t)kRowWin, NWIN = CL / WIN;
     constexpr uint32_t SUPER = 32 * CL;
-    const PairSmem L = pair_layout(d.f_states, NW);
+    const PairSmem L = pair_layout(d.f_states, d.n_states, d.n_cmp, NW);
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem) + warp * 2;
     uint8_t *tbl = smem + L.table;
@@ -974,6 +976,9 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, Devic
         const uint32_t *src = reinterpret_cast<const uint32_t *>(d.ftable);
         uint32_t *dst = reinterpret_cast<uint32_t *>(tbl);
         for (uint32_t i = tid; i < d.f_states * (kRowBytes / 4); i += NW * 32) dst[i] = src[i];
+        uint16_t *xd = reinterpret_cast<uint16_t *>(smem + L.xtable);
+        for (uint32_t i = tid; i < d.n_states * d.n_cmp; i += NW * 32) xd[i] = d.ctable[i];
+        for (uint32_t i = tid; i < 256; i += NW * 32) smem[L.xcls + i] = d.ccls[i];
     }
     __syncthreads();   // the only CTA-wide barrier
 
@@ -1010,13 +1015,16 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, Devic
 
     PairCtx c;
     c.ftbl = tbl; c.ftbl_s = smem_u32(tbl); c.fstart = d.f_start; c.mul = d.f_mul; c.shift = d.f_shift;
-    c.xtbl = d.table; c.events = d.events; c.neutral_state = d.neutral_state;
+    c.xtbl = reinterpret_cast<const uint16_t *>(smem + L.xtable); c.xcls = smem + L.xcls; c.xn = d.n_cmp;
+    c.xtbl_s = smem_u32(smem + L.xtable); c.xcls_s = smem_u32(smem + L.xcls);
+    c.events = d.events; c.neutral_state = d.neutral_state;
     c.pad4 = 0x01010101u * (uint32_t)(d.reset_pad & 0xFF);
     c.list_abs = a.offsets; c.counters = a.counters;
     Quad padq;
     padq.a = padq.b = padq.c = padq.d = c.pad4;
     const int32_t chunk = (int32_t)(lane * CL);
     uint32_t g = 0;
+    uint32_t queued = 0;   // groups waiting in the warp's queue (warp-uniform, carried from tile to tile)
 
     for (uint32_t sk = 0; t < t_end; sk++) {
         const bool has_next = t_nxt < t_end;
@@ -1041,6 +1049,7 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, Devic
         const uint64_t row_start = (uint64_t)row * CL;
         const bool tail_row = row == nrows_full && row_start < a.total;
 
+        const bool all_full = (uint64_t)t * 32 + 32 <= nrows_full;   // warp-uniform: every lane of this tile owns a full row
         PairLane P;
         uint32_t km = 0;
         if (full_row || tail_row) {
@@ -1058,11 +1067,22 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, Devic
                 if (w == 0) pair_begin<SIMPLE>(c, P, km, row == 0 ? padq : *reinterpret_cast<const Quad *>(warm_buf + lane * 16));
                 const uint8_t *wb = wbase + (g & 1) * (32 * WIN) + lane * WIN;
                 const int32_t pos = chunk + w * WIN;
+                // the bytes before a group are read back from the staging buffer when a group is flagged; only the window's
+                // last group is carried in registers (the buffer of the window before is being refilled by then)
+                // The queue is emptied as soon as enough groups are waiting (a warp-uniform count kept in a register):
+                // text full of multi-byte whitespace would otherwise overflow it inside one window and fall back to
+                // one-lane walks.  All lanes of the warp own full rows here, or none does, except in the arena's last tile.
+                bool fl = pair_group<SIMPLE, false>(c, P, *reinterpret_cast<const Quad *>(wb), pos, queue);
+                if (all_full) { queued += __popc(__ballot_sync(0xFFFFFFFFu, fl)); if (queued >= kPairQueueFlush) { queue.flush(c, lane, true); queued = 0; } }
 #pragma unroll 1
-                for (int32_t q = 0; q < WIN; q += 16) pair_group<SIMPLE>(c, P, *reinterpret_cast<const Quad *>(wb + q), pos + q, queue);
+                for (int32_t q = 16; q < WIN; q += 16) {
+                    fl = pair_group<SIMPLE, false>(c, P, *reinterpret_cast<const Quad *>(wb + q), pos + q, queue, reinterpret_cast<const Quad *>(wb + q - 16));
+                    if (all_full) { queued += __popc(__ballot_sync(0xFFFFFFFFu, fl)); if (queued >= kPairQueueFlush) { queue.flush(c, lane, true); queued = 0; } }
+                }
+                P.prevq = *reinterpret_cast<const Quad *>(wb + WIN - 16);
             }
             __syncwarp();
-            if ((w & 3) == 3) queue.flush(c, lane, false);
+            if (!all_full && (w & 1)) queue.flush(c, lane, false);   // last tile: lanes diverge above, check between windows
         }
         if (tail_row) {   // the arena's partial last row: straight from global memory, flagged groups walked on the spot
             const uint8_t *src = a.bytes + row_start;

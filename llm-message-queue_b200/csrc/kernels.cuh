@@ -35,6 +35,9 @@ struct DeviceDfa {
     int32_t has_filter;
     const uint8_t *ftable;
     uint32_t f_states, f_start, f_mul, f_shift;
+    const uint16_t *ctable;      // column-merged copy of `table`: entry(state, ccls[byte]), n_cmp per state
+    const uint8_t *ccls;         // 256
+    uint32_t n_cmp;
 };
 
 struct ScanArgs {

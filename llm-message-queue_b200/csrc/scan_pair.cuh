@@ -8,14 +8,15 @@
 //     shift & 15, arithmetic only) that consumes two bytes per lookup - entry(state, class pair) = next state | "an
 //     occurrence of some pattern's class string may have ended in these two bytes".  It over-approximates: bytes that
 //     share a class are not told apart;
-//   * every group the filter flags, and every group that holds a byte >= 0x80 (multi-byte whitespace, the fold runes
-//     U+017F / U+212A / U+0130, non-ASCII literals) or follows such a group, is handed to `sink`, which walks the group
-//     through the EXACT one-byte automaton (16 warm-up bytes + the 16 bytes) and takes words and events from that walk
+//   * every group the filter flags, and every group that holds one of the lead bytes C2 C4 C5 E0-E3 (multi-byte
+//     whitespace, the fold runes U+017F / U+212A / U+0130) or follows such a group, is handed to `sink`, which walks the group
+//     through the EXACT one-byte automaton (its column-merged copy; 16 warm-up bytes + the 16 bytes) and takes words and events from that walk
 //     instead.  Flagged groups are rare on text (about 0.5 % on the benchmark set), so the exact walk is off the hot path.
 // Exactness: an event that completes in group g depends on at most 17 bytes, so every byte it depends on lies in g-1 or
-// g; if all of them are ASCII the filter's class automaton sees the occurrence and flags g, otherwise g-1 or g holds a
-// byte >= 0x80 and g is walked exactly anyway.  A group that is not walked exactly holds only ASCII and follows an
-// all-ASCII group, where the SIMD word count is Go's.
+// g; the filter's class automaton knows every way to complete an event that uses none of those lead bytes (literals of
+// any script included) and flags g when it sees one, otherwise g-1 or g holds such a lead byte and g is walked exactly
+// anyway.  A group that is not walked exactly has no multi-byte whitespace in or just before it, so its word starts are
+// what the SIMD compares count: a byte >= 0x80 outside those runes is never whitespace to Go.
 #pragma once
 #include <stdint.h>
 
@@ -28,8 +29,11 @@ struct PairCtx {
     uint32_t ftbl_s;            // device: its shared-memory address
     uint32_t fstart;            // filter root
     uint32_t mul, shift;        // byte -> class: ((b & 31) * mul >> shift) & 15
-    const uint8_t *xtbl;        // exact automaton (padded D8 rows), global memory on the device: replays only
-    const EventPacked *events;
+    const uint16_t *xtbl;       // exact automaton, column-merged: entry(state, xcls[byte]), xn per state (shared memory on the device)
+    const uint8_t *xcls;
+    uint32_t xn;
+    uint32_t xtbl_s, xcls_s;    // device: their shared-memory addresses
+    const EventPacked *events;  // global memory on the device: read when an event is applied
     uint32_t neutral_state;
     uint32_t pad4;              // reset pad byte x 4
     const int32_t *list;        // message starts of the tile (same meaning as LaneCtx)
@@ -50,21 +54,38 @@ TR_HD uint32_t pr_fnext(const PairCtx &c, uint32_t pairs, uint32_t f, uint32_t k
 #endif
 }
 TR_HD uint32_t pr_xnext(const PairCtx &c, uint32_t e, uint32_t byte) {
-    const uint16_t *p = reinterpret_cast<const uint16_t *>(c.xtbl + (e & 0xFFu) * kRowBytes + 2u * byte);
 #if defined(__CUDA_ARCH__)
-    return __ldg(p);
+    uint32_t cls;
+    uint16_t v;
+    asm("ld.shared.u8 %0, [%1];" : "=r"(cls) : "r"(c.xcls_s + byte));
+    asm("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(c.xtbl_s + 2u * ((e & 0xFFu) * c.xn + cls)));
+    return v;
 #else
-    return *p;
+    return c.xtbl[(e & 0xFFu) * c.xn + c.xcls[byte]];
 #endif
 }
 
-// bit 7 of every byte: the byte is not ASCII whitespace (bytes >= 0x80 count as non-space)
+// bit 7 of every byte: the byte is not ASCII whitespace.  Exact for words whose bytes are all < 0x80 (the per-byte sums
+// of a word with a byte >= 0x80 may carry over): groups with such bytes recompute it with pr_nonspace_any.
 TR_HD uint32_t pr_nonspace(uint32_t w) {
-    const uint32_t w7 = w & 0x7F7F7F7Fu;
-    const uint32_t ne20 = (w7 ^ 0x20202020u) + 0x7F7F7F7Fu;   // bit 7: byte != 0x20
-    const uint32_t gt13 = w7 + 0x72727272u;                   // bit 7: byte > 13
-    const uint32_t ge9 = w7 + 0x77777777u;                    // bit 7: byte >= 9
-    return ((ne20 & (gt13 | ~ge9)) | w) & 0x80808080u;
+    const uint32_t ne20 = (w ^ 0x20202020u) + 0x7F7F7F7Fu;    // bit 7: byte != 0x20
+    const uint32_t gt13 = w + 0x72727272u;                    // bit 7: byte > 13
+    const uint32_t ge9 = w + 0x77777777u;                     // bit 7: byte >= 9
+    return ne20 & (gt13 | ~ge9) & 0x80808080u;
+}
+// the same for any bytes: a byte >= 0x80 is not ASCII whitespace
+TR_HD uint32_t pr_nonspace_any(uint32_t w) { return (pr_nonspace(w & 0x7F7F7F7Fu) | w) & 0x80808080u; }
+// bit 7 of every byte that equals v (exact)
+TR_HD uint32_t pr_eq(uint32_t w, uint32_t v4) {
+    const uint32_t t = w ^ v4;
+    return ~(((t & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | t) & 0x80808080u;
+}
+// Does the word hold a byte that can start a rune the exact automaton treats specially?  Multi-byte whitespace starts
+// with C2, E1, E2 or E3; the fold runes U+017F, U+212A, U+0130 with C5, E2, C4.  (E0 is let in with E1..E3: one test.)
+// Every other byte >= 0x80 - accented Latin, Cyrillic, CJK ideographs, emoji, stray continuation bytes - is to the path
+// what an ordinary letter is: not whitespace, part of no fold.
+TR_HD uint32_t pr_special(uint32_t w) {
+    return pr_eq(w, 0xC2C2C2C2u) | pr_eq(w, 0xC4C4C4C4u) | pr_eq(w, 0xC5C5C5C5u) | pr_eq(w & 0xFCFCFCFCu, 0xE0E0E0E0u);
 }
 TR_HD uint32_t pr_funnel8(uint32_t lo, uint32_t hi) {          // (hi << 8) | (lo >> 24)
 #if defined(__CUDA_ARCH__)
@@ -101,23 +122,18 @@ struct PairLane {
 template <class Ctx>
 TR_COLD void pair_replay(const Ctx &c, Quad warm, Quad q, uint32_t msg) {   // quads by value: they stay in registers at the call
     uint32_t e = c.neutral_state, words = 0;
+    const uint32_t ww[4] = {warm.a, warm.b, warm.c, warm.d}, qw[4] = {q.a, q.b, q.c, q.d};
 #ifdef __CUDA_ARCH__
-#pragma unroll 1
+#pragma unroll
 #endif
-    for (int j = 0; j < 4; j++) {
-        const uint32_t w = j == 0 ? warm.a : j == 1 ? warm.b : j == 2 ? warm.c : warm.d;
-        for (int k = 0; k < 4; k++) e = pr_xnext(c, e, (w >> (8 * k)) & 0xFFu);
-    }
+    for (int i = 0; i < 16; i++) e = pr_xnext(c, e, (ww[i >> 2] >> (8 * (i & 3))) & 0xFFu);
 #ifdef __CUDA_ARCH__
-#pragma unroll 1
+#pragma unroll
 #endif
-    for (int j = 0; j < 4; j++) {
-        const uint32_t w = j == 0 ? q.a : j == 1 ? q.b : j == 2 ? q.c : q.d;
-        for (int k = 0; k < 4; k++) {
-            e = pr_xnext(c, e, (w >> (8 * k)) & 0xFFu);
-            words += e >> 15;
-            if (e & 0x7F00u) apply_event_raw(c.events, c.counters, (e >> 8) & 0x7Fu, msg);
-        }
+    for (int i = 0; i < 16; i++) {
+        e = pr_xnext(c, e, (qw[i >> 2] >> (8 * (i & 3))) & 0xFFu);
+        words += e >> 15;
+        if (e & 0x7F00u) apply_event_raw(c.events, c.counters, (e >> 8) & 0x7Fu, msg);
     }
     if (words) tr_add(c.counters + (uint64_t)msg * CNT_STRIDE + CNT_WORDS, words);
 }
@@ -145,18 +161,21 @@ TR_HD void pair_begin(const Ctx &c, PairLane &P, uint32_t k, const Quad &warm) {
         f = pr_fnext(c, p, f, 2);
     }
     P.f = f;
-    P.prev_ns = pr_nonspace(warm.d);
-    P.prev_rare = (warm.a | warm.b | warm.c | warm.d) & 0x80808080u;
+    P.prev_ns = pr_nonspace_any(warm.d);
+    P.prev_rare = pr_special(warm.a) | pr_special(warm.b) | pr_special(warm.c) | pr_special(warm.d);
     P.prevq = warm;
 }
 
-// one 16-byte group at tile-relative position pos
-template <bool SIMPLE, class Ctx, class Sink>
-TR_HD void pair_group(const Ctx &c, PairLane &P, const Quad &q, int32_t pos, Sink &sink) {
+// one 16-byte group at tile-relative position pos.  prevp: where the 16 bytes before the group can still be read (the
+// staging buffer, inside a window); nullptr: they are P.prevq, which the caller then keeps up to date (KEEP: this function
+// does it after every group).  Keeping them out of registers inside a window saves a reload of the group per iteration.
+template <bool SIMPLE, bool KEEP = true, class Ctx, class Sink>
+TR_HD bool pair_group(const Ctx &c, PairLane &P, const Quad &q, int32_t pos, Sink &sink, const Quad *prevp = nullptr) {
     long_boundary(c, P.L, pos);
-    const uint32_t rare = (q.a | q.b | q.c | q.d) & 0x80808080u;
+    const uint32_t high = (q.a | q.b | q.c | q.d) & 0x80808080u;
     const uint32_t qw[4] = {q.a, q.b, q.c, q.d};
-    uint32_t f = P.f, fired = 0, starts = 0, pns = P.prev_ns;
+    const uint32_t pns0 = P.prev_ns;
+    uint32_t f = P.f, fired = 0, starts = 0, pns = pns0, rare = 0;
 #ifdef __CUDA_ARCH__
 #pragma unroll
 #endif
@@ -170,12 +189,30 @@ TR_HD void pair_group(const Ctx &c, PairLane &P, const Quad &q, int32_t pos, Sin
         f = pr_fnext(c, p, f, 0); fired |= f;
         f = pr_fnext(c, p, f, 2); fired |= f;
     }
+    if (high) {   // bytes >= 0x80 in the group: is one of the few lead bytes that matter among them?
+        rare = pr_special(q.a) | pr_special(q.b) | pr_special(q.c) | pr_special(q.d);
+        if (!rare) {   // other scripts: the group is counted here after all, with space bits that are exact for any byte
+            starts = 0; pns = pns0;
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+            for (int j = 0; j < 4; j++) {
+                const uint32_t ns = pr_nonspace_any(qw[j]);
+                starts += pr_bytesum(ns & ~pr_funnel8(pns, ns));
+                pns = ns;
+            }
+        }
+        // (rare: this group and the next are walked exactly; the "byte before" bit handed on is exact whenever the group
+        // after those uses it, because that needs the last word of the next group to be free of such bytes)
+    }
     P.f = f;
     P.prev_ns = pns;
-    if (rare | P.prev_rare | (fired & 0x8000u)) sink.push(c, P.prevq, q, P.L.msg);
+    const bool flagged = (rare | P.prev_rare | (fired & 0x8000u)) != 0;
+    if (flagged) sink.push(c, prevp ? *prevp : P.prevq, q, P.L.msg);
     else P.L.words += starts >> 7;
     P.prev_rare = rare;
-    P.prevq = q;
+    if (KEEP) P.prevq = q;
+    return flagged;
 }
 
 template <class Ctx>

@@ -511,7 +511,7 @@ extern "C" int hostcheck_scan_pair(const uint8_t *prios, const uint8_t *cis, con
     Dfa dfa;
     std::string e = build_dfa(dict, &dfa);
     if (!e.empty() || !dfa.filter.ok) { std::strncpy(err, e.empty() ? "no pair filter for this dictionary" : e.c_str(), errcap - 1); return 4; }
-    info[0] = dfa.filter.n_states; info[1] = dfa.filter.mul; info[2] = dfa.filter.shift; info[3] = info[4] = 0;
+    info[0] = dfa.filter.n_states | ((uint64_t)dfa.n_cmp << 32); info[1] = dfa.filter.mul; info[2] = dfa.filter.shift; info[3] = info[4] = 0;
     if (n_msgs == 0) return 0;
     std::vector<EventPacked> ev(dfa.events.size());
     for (size_t i = 0; i < dfa.events.size(); i++) pack_event(dfa.events[i], &ev[i].x);
@@ -541,7 +541,7 @@ extern "C" int hostcheck_scan_pair(const uint8_t *prios, const uint8_t *cis, con
         for (uint32_t m = mlo; m <= mhi + 1; m++) list.push_back((int32_t)((int64_t)poff[m] - (int64_t)ts));
         PairCtx c;
         c.ftbl = ftbl.data(); c.ftbl_s = 0; c.fstart = dfa.filter.start; c.mul = dfa.filter.mul; c.shift = dfa.filter.shift;
-        c.xtbl = xtbl.data(); c.events = ev.data(); c.neutral_state = dfa.neutral_state; c.pad4 = padq.a;
+        c.xtbl = dfa.ctable.data(); c.xcls = dfa.ccls; c.xn = dfa.n_cmp; c.events = ev.data(); c.neutral_state = dfa.neutral_state; c.pad4 = padq.a;
         c.list = list.data(); c.list_abs = poff.data(); c.tile_start = (int64_t)ts; c.list_n = (uint32_t)list.size(); c.msg_lo = mlo;
         c.counters = counters;
         for (uint32_t l = 0; l < 32; l++) {

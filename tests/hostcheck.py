@@ -159,7 +159,7 @@ def scan_pair(dict_entries, offsets, data, chunk_long=320):
                                    p(counters), p(info), err, 256)
     if rc != 0:
         raise ValueError(err.value.decode())
-    return counters[:n], dict(filter_states=int(info[0]), mul=int(info[1]), shift=int(info[2]), flagged=int(info[3]), groups=int(info[4]))
+    return counters[:n], dict(filter_states=int(info[0]) & 0xFFFFFFFF, exact_classes=int(info[0]) >> 32, mul=int(info[1]), shift=int(info[2]), flagged=int(info[3]), groups=int(info[4]))
 
 
 META_DTYPE = np.dtype([("preset", "u1"), ("user_priority", "u1"), ("user_default", "u1"), ("meta_priority", "u1"), ("flags", "u1"),
