@@ -668,6 +668,45 @@ bool determinise_pairs(const std::vector<ClassPattern> &pats, PairFilter *out) {
     return true;
 }
 
+// Moore form of the minimised pair automaton: (state, the entry that led here fired), reachable part, quiet states first.
+// false: more than 256 of them
+bool moore_pairs(PairFilter *f) {
+    std::map<uint32_t, uint32_t> ids;          // state << 1 | fired -> index into `order`
+    std::vector<uint32_t> order;
+    auto intern = [&](uint32_t key) {
+        auto it = ids.find(key);
+        if (it != ids.end()) return it->second;
+        const uint32_t id = static_cast<uint32_t>(order.size());
+        ids.emplace(key, id);
+        order.push_back(key);
+        return id;
+    };
+    intern(f->start << 1);
+    std::vector<uint32_t> next;                // order-major, 256 per state
+    for (size_t k = 0; k < order.size(); k++) {
+        if (order.size() > 256) return false;
+        const uint32_t s = order[k] >> 1;
+        for (uint32_t x = 0; x < 256; x++) {
+            const uint16_t e = f->table[static_cast<size_t>(s) * 256 + x];
+            next.push_back(intern((e & 0xFFu) << 1 | (e >> 15)));
+        }
+    }
+    const uint32_t n = static_cast<uint32_t>(order.size());
+    if (n > 256) return false;
+    std::vector<uint32_t> id(n);
+    uint32_t quiet = 0;
+    for (uint32_t i = 0; i < n; i++) if (!(order[i] & 1u)) id[i] = quiet++;
+    uint32_t loud = quiet;
+    for (uint32_t i = 0; i < n; i++) if (order[i] & 1u) id[i] = loud++;
+    f->m_states = n;
+    f->m_start = id[0];
+    f->m_fired_from = quiet;
+    f->mtable.assign(static_cast<size_t>(n) * 256, 0);
+    for (uint32_t i = 0; i < n; i++)
+        for (uint32_t x = 0; x < 256; x++) f->mtable[static_cast<size_t>(id[i]) * 256 + x] = static_cast<uint8_t>(id[next[static_cast<size_t>(i) * 256 + x]]);
+    return true;
+}
+
 double pair_fire_rate(const PairFilter &f, const std::string &text) {
     uint32_t st = f.start, groups = 0, fired_groups = 0;
     for (size_t g = 0; g + 16 <= text.size(); g += 16) {
@@ -699,7 +738,7 @@ void build_pair_filter(const std::vector<DictEntry> &dict, const Dfa &exact, Pai
     for (const auto &mk : cand) {
         PairFilter f;
         f.mul = mk[0]; f.shift = mk[1];
-        if (!determinise_pairs(class_patterns(dict, f.mul, f.shift), &f)) continue;
+        if (!determinise_pairs(class_patterns(dict, f.mul, f.shift), &f) || !moore_pairs(&f)) continue;
         f.sample_fire_rate = pair_fire_rate(f, text);
         f.ok = true;
         // the first candidate needs no multiply on the device: keep it unless another one is clearly more selective

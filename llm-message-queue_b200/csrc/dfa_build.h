@@ -58,11 +58,15 @@ constexpr uint32_t kMaxEventsW = 2047;
 // complete an event (keyword literal, question word + " ", whitespace + sentiment word + whitespace) and consumes two
 // classes per table entry: entry(state, c0 | c1 << 4) = next state | fired << 15.  It over-approximates (bytes sharing
 // a class are not told apart); what it flags is re-walked through the exact automaton.
+// The device walks its Moore form - "fired" moved into the state: states >= m_fired_from are entered by a firing entry -
+// so that an entry is one byte and its address is state << 8 | class pair, a single byte permute.
 struct PairFilter {
     bool ok = false;                  // false: this dictionary keeps to the one-lookup-per-byte lanes
     uint32_t n_states = 0, start = 0;
     uint32_t mul = 1, shift = 0;
     std::vector<uint16_t> table;      // n_states * 256
+    std::vector<uint8_t> mtable;      // Moore form: m_states * 256 next states
+    uint32_t m_states = 0, m_start = 0, m_fired_from = 0;
     double sample_fire_rate = 0;      // flagged 16-byte groups on the compiler's sample text (diagnostics)
 };
 

@@ -257,16 +257,14 @@ int32_t upload_dfa(const Dfa &dfa, DfaBufs *b, DeviceDfa *out) {
         CU(cudaMemcpy(b->eom.p, eom.data(), 256, cudaMemcpyHostToDevice));
         d.table = b->table.p; d.eom = b->eom.p;
         if (dfa.filter.ok) {   // filter automaton of the pair lanes, same padded row layout
-            std::vector<uint8_t> fp((size_t)dfa.filter.n_states * kRowBytes, 0);
-            for (uint32_t st = 0; st < dfa.filter.n_states; st++)
-                std::memcpy(fp.data() + (size_t)st * kRowBytes, dfa.filter.table.data() + (size_t)st * 256, 512);
+            const std::vector<uint8_t> &fp = dfa.filter.mtable;
             CU(b->ftable.ensure(fp.size()));
             CU(cudaMemcpy(b->ftable.p, fp.data(), fp.size(), cudaMemcpyHostToDevice));
             CU(b->ctable.ensure(dfa.ctable.size()));
             CU(b->ccls.ensure(256));
             CU(cudaMemcpy(b->ctable.p, dfa.ctable.data(), dfa.ctable.size() * 2, cudaMemcpyHostToDevice));
             CU(cudaMemcpy(b->ccls.p, dfa.ccls, 256, cudaMemcpyHostToDevice));
-            d.has_filter = 1; d.ftable = b->ftable.p; d.f_states = dfa.filter.n_states; d.f_start = dfa.filter.start;
+            d.has_filter = 1; d.ftable = b->ftable.p; d.f_states = dfa.filter.m_states; d.f_start = dfa.filter.m_start; d.f_fired = dfa.filter.m_fired_from;
             d.f_mul = dfa.filter.mul; d.f_shift = dfa.filter.shift;
             d.ctable = b->ctable.p; d.ccls = b->ccls.p; d.n_cmp = dfa.n_cmp;
         }

@@ -881,29 +881,39 @@ cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw,
 // bytes), word starts are counted by SIMD-in-register compares, and the groups the filter flags (or that hold bytes >=
 // 0x80) are queued per warp - (message, the 16 bytes before, the 16 bytes) - and walked through the exact automaton in
 // global memory by the whole warp, one queued group per lane.
-constexpr uint32_t kPairQueueCap = 16;     // flagged groups per warp (36 bytes each)
-constexpr uint32_t kPairQueueFlush = 12;   // walked by the whole warp once this many wait (more can arrive in one step: those beyond the cap are walked by their own lane)
-struct PairSmem { uint32_t table, xtable, xcls, warp0, aux0, total, warp_bytes, aux_bytes, warm_off, list_off, queue_off; };
+constexpr uint32_t kPairQueueCap = 32;     // flagged groups per warp (36 bytes each)
+constexpr uint32_t kPairQueueFlush = 20;   // walked by the whole warp once this many wait (more can arrive in one window: those beyond the cap are walked by their own lane)
+// Shared-memory layout.  The filter table sits at the shared address kPairTableShared (scan_pair.cuh: its entries are
+// then addressed by a byte permute and an immediate); the kernel's dynamic shared memory starts at kPairSmemBase (the
+// first KB of the window is reserved by the system - the kernel checks), so the table is at offset 0xFC00 and the other
+// pieces are laid out around it: the small ones and the first warps' staging buffers before, the other warps' after.
+constexpr uint32_t kPairSmemBase = 0x400u;
+struct PairSmem { uint32_t table, xtable, xcls, warp_a, warp_b, n_a, aux0, total, warp_bytes, aux_bytes, warm_off, list_off, queue_off; };
 __host__ __device__ inline PairSmem pair_layout(uint32_t f_states, uint32_t x_states, uint32_t x_cls, uint32_t nw) {
     PairSmem L;
-    uint32_t o = 1024;   // mbarriers
-    L.table = o; o += ((f_states * kRowBytes + 127u) / 128u) * 128u;
-    L.xtable = o; o += ((x_states * x_cls * 2u + 127u) / 128u) * 128u;   // exact automaton, column-merged: flagged groups only
-    L.xcls = o; o += 256u;
     L.warm_off = 2 * 32 * kRowWin;
     L.warp_bytes = L.warm_off + 512;
-    L.warp0 = o; o += nw * L.warp_bytes;
     L.list_off = 0;
     L.queue_off = 2 * 4 * kRowListCap;
     L.aux_bytes = ((L.queue_off + 4 + 36 * kPairQueueCap + 15u) / 16u) * 16u;
+    uint32_t o = 1024;   // mbarriers
+    L.xtable = o; o += ((x_states * x_cls * 2u + 127u) / 128u) * 128u;   // exact automaton, column-merged: flagged groups only
+    L.xcls = o; o += 256u;
     L.aux0 = o; o += nw * L.aux_bytes;
-    L.total = o;
+    o = ((o + 127u) / 128u) * 128u;
+    L.table = kPairTableShared - kPairSmemBase;                          // filter automaton, Moore form: one byte per entry
+    L.warp_a = o;
+    L.n_a = o <= L.table ? (L.table - o) / L.warp_bytes : 0u;
+    if (L.n_a > nw) L.n_a = nw;
+    L.warp_b = L.table + f_states * 256u;
+    L.total = o <= L.table ? L.warp_b + (nw - L.n_a) * L.warp_bytes : 0xFFFFFFFFu;   // (no room before the table: no such launch)
     return L;
 }
 size_t scan_pair_smem_bytes(const DeviceDfa &d, uint32_t nw) { return pair_layout(d.f_states, d.n_states, d.n_cmp, nw).total; }
 uint32_t pick_pair_warps(const DeviceDfa &d, size_t max_smem) {
     if (!d.has_filter || d.wide || d.warm != 16 || d.reset_pad < 0) return 0;
-    if (const char *v = getenv("TRIAGE_PAIR")) { if (atoi(v) == 0) return 0; }   // measurement knob: keep to the one-lookup-per-byte lanes
+    // opt-in (TRIAGE_PAIR=1): on the benchmark set the one-lookup-per-byte row lanes are still the faster kernel
+    { const char *v = getenv("TRIAGE_PAIR"); if (!v || atoi(v) == 0) return 0; }
     if (const char *w = getenv("TRIAGE_PAIR_WARPS")) {
         uint32_t nw = (uint32_t)atoi(w);
         if ((nw == 16 || nw == 20 || nw == 24 || nw == 28) && scan_pair_smem_bytes(d, nw) <= max_smem) return nw;
@@ -927,20 +937,15 @@ struct PairEventQueue {
             pair_replay(c, warm, q, msg);   // queue full: walk it now
         }
     }
-    __device__ __forceinline__ void flush(const PairCtx &c, uint32_t lane, bool force) {
+    __device__ __noinline__ void flush(const PairCtx &c, uint32_t lane) {
         uint32_t n;
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(n) : "r"(base_s) : "memory");
-        if (n == 0 || (!force && n < kPairQueueFlush)) return;
         if (n > kPairQueueCap) n = kPairQueueCap;
         if (lane < n) {
             const uint32_t at = base_s + 4 + lane * 36;
-            uint32_t v[9];
-#pragma unroll
-            for (int k = 0; k < 9; k++) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v[k]) : "r"(at + 4 * k) : "memory");
-            Quad w, q;
-            w.a = v[1]; w.b = v[2]; w.c = v[3]; w.d = v[4];
-            q.a = v[5]; q.b = v[6]; q.c = v[7]; q.d = v[8];
-            pair_replay(c, w, q, v[0]);
+            uint32_t msg;
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(msg) : "r"(at) : "memory");
+            pair_replay_words(c, [&](int i) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(at + 4 + 4 * i) : "memory"); return v; }, msg);
         }
         __syncwarp();
         if (lane == 0) asm volatile("st.shared.u32 [%0], %1;" ::"r"(base_s), "r"(0u) : "memory");
@@ -959,10 +964,11 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, Devic
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem) + warp * 2;
     uint8_t *tbl = smem + L.table;
-    uint8_t *wbase = smem + L.warp0 + warp * L.warp_bytes;
+    uint8_t *wbase = smem + (warp < L.n_a ? L.warp_a + warp * L.warp_bytes : L.warp_b + (warp - L.n_a) * L.warp_bytes);
     uint8_t *warm_buf = wbase + L.warm_off;
     uint8_t *aux = smem + L.aux0 + warp * L.aux_bytes;
     int32_t *list_base = reinterpret_cast<int32_t *>(aux + L.list_off);
+    if (smem_u32(smem) != kPairSmemBase) __trap();   // the table's address is compiled into the lookups
 
     PairEventQueue queue;
     queue.base_s = smem_u32(aux + L.queue_off);
@@ -975,7 +981,7 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, Devic
     {
         const uint32_t *src = reinterpret_cast<const uint32_t *>(d.ftable);
         uint32_t *dst = reinterpret_cast<uint32_t *>(tbl);
-        for (uint32_t i = tid; i < d.f_states * (kRowBytes / 4); i += NW * 32) dst[i] = src[i];
+        for (uint32_t i = tid; i < d.f_states * 64u; i += NW * 32) dst[i] = src[i];
         uint16_t *xd = reinterpret_cast<uint16_t *>(smem + L.xtable);
         for (uint32_t i = tid; i < d.n_states * d.n_cmp; i += NW * 32) xd[i] = d.ctable[i];
         for (uint32_t i = tid; i < 256; i += NW * 32) smem[L.xcls + i] = d.ccls[i];
@@ -1014,7 +1020,7 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, Devic
     __syncwarp();
 
     PairCtx c;
-    c.ftbl = tbl; c.ftbl_s = smem_u32(tbl); c.fstart = d.f_start; c.mul = d.f_mul; c.shift = d.f_shift;
+    c.ftbl = tbl; c.fstart = d.f_start; c.ffired = d.f_fired; c.mul = d.f_mul; c.shift = d.f_shift;
     c.xtbl = reinterpret_cast<const uint16_t *>(smem + L.xtable); c.xcls = smem + L.xcls; c.xn = d.n_cmp;
     c.xtbl_s = smem_u32(smem + L.xtable); c.xcls_s = smem_u32(smem + L.xcls);
     c.events = d.events; c.neutral_state = d.neutral_state;
@@ -1065,24 +1071,18 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, Devic
             mbar_wait(&bars[g & 1], (g >> 1) & 1);
             if (full_row) {
                 if (w == 0) pair_begin<SIMPLE>(c, P, km, row == 0 ? padq : *reinterpret_cast<const Quad *>(warm_buf + lane * 16));
-                const uint8_t *wb = wbase + (g & 1) * (32 * WIN) + lane * WIN;
-                const int32_t pos = chunk + w * WIN;
-                // the bytes before a group are read back from the staging buffer when a group is flagged; only the window's
-                // last group is carried in registers (the buffer of the window before is being refilled by then)
-                // The queue is emptied as soon as enough groups are waiting (a warp-uniform count kept in a register):
-                // text full of multi-byte whitespace would otherwise overflow it inside one window and fall back to
-                // one-lane walks.  All lanes of the warp own full rows here, or none does, except in the arena's last tile.
-                bool fl = pair_group<SIMPLE, false>(c, P, *reinterpret_cast<const Quad *>(wb), pos, queue);
-                if (all_full) { queued += __popc(__ballot_sync(0xFFFFFFFFu, fl)); if (queued >= kPairQueueFlush) { queue.flush(c, lane, true); queued = 0; } }
-#pragma unroll 1
-                for (int32_t q = 16; q < WIN; q += 16) {
-                    fl = pair_group<SIMPLE, false>(c, P, *reinterpret_cast<const Quad *>(wb + q), pos + q, queue, reinterpret_cast<const Quad *>(wb + q - 16));
-                    if (all_full) { queued += __popc(__ballot_sync(0xFFFFFFFFu, fl)); if (queued >= kPairQueueFlush) { queue.flush(c, lane, true); queued = 0; } }
+                const Quad *win = reinterpret_cast<const Quad *>(wbase + (g & 1) * (32 * WIN) + lane * WIN);
+                // The queue is emptied as soon as enough groups are waiting (a warp-uniform count kept in a register): text
+                // full of multi-byte whitespace would otherwise overflow it and fall back to one-lane walks.  All lanes of
+                // the warp own full rows here, or none does, except in the arena's last tile.
+                const uint32_t pushed = pair_window<SIMPLE, WIN / 16>(c, P, win, chunk + w * WIN, queue);
+                if (all_full) {
+                    queued += __reduce_add_sync(0xFFFFFFFFu, pushed);
+                    if (queued >= kPairQueueFlush) { queue.flush(c, lane); queued = 0; }
                 }
-                P.prevq = *reinterpret_cast<const Quad *>(wb + WIN - 16);
             }
             __syncwarp();
-            if (!all_full && (w & 1)) queue.flush(c, lane, false);   // last tile: lanes diverge above, check between windows
+            if (!all_full) queue.flush(c, lane);   // last tile: lanes diverge above, empty it between windows
         }
         if (tail_row) {   // the arena's partial last row: straight from global memory, flagged groups walked on the spot
             const uint8_t *src = a.bytes + row_start;
@@ -1129,7 +1129,7 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, Devic
         t_nn = t_nxt < t_end ? grab() : t_nxt;
         __syncwarp();
     }
-    queue.flush(c, lane, true);
+    queue.flush(c, lane);
 }
 
 template <int NW, int LANE, bool SIMPLE>

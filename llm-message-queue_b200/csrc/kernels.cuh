@@ -34,7 +34,7 @@ struct DeviceDfa {
     // filter automaton of the two-bytes-per-lookup lanes (scan_pair.cuh), padded rows like `table`
     int32_t has_filter;
     const uint8_t *ftable;
-    uint32_t f_states, f_start, f_mul, f_shift;
+    uint32_t f_states, f_start, f_fired, f_mul, f_shift;   // ftable: Moore form, 256 one-byte entries per state; states >= f_fired were entered by a firing entry
     const uint16_t *ctable;      // column-merged copy of `table`: entry(state, ccls[byte]), n_cmp per state
     const uint8_t *ccls;         // 256
     uint32_t n_cmp;

@@ -114,12 +114,17 @@ TR_COLD void apply_event_raw(const EventPacked *events, uint32_t *counters, uint
 }
 TR_HD void apply_event(const LaneCtx &c, uint32_t id, uint32_t msg) { apply_event_raw(c.events, c.counters, id, msg); }
 
+// tiles with more message starts than the shared-memory list holds: from the arena's offsets (kept out of line, the
+// lanes meet it once in a great while)
+TR_COLD int32_t list_at_abs(const uint64_t *list_abs, uint32_t idx, int64_t tile_start) {
+    int64_t r = (int64_t)list_abs[idx] - tile_start;
+    const int64_t lim = 1 << 30;
+    return (int32_t)(r < -lim ? -lim : (r > lim ? lim : r));
+}
 template <class Ctx>
 TR_HD int32_t list_at(const Ctx &c, uint32_t k) {
     if (c.list) return c.list[k];
-    int64_t r = (int64_t)c.list_abs[c.msg_lo + k] - c.tile_start;
-    const int64_t lim = 1 << 30;
-    return (int32_t)(r < -lim ? -lim : (r > lim ? lim : r));
+    return list_at_abs(c.list_abs, c.msg_lo + k, c.tile_start);
 }
 
 // index k into list with list[k] <= pos < list[k+1]  (upper_bound - 1; empty messages repeat a value, so this lands on

@@ -2,16 +2,20 @@
 //
 // The one-lookup-per-byte lane (scan_core.cuh) is bound by the rate at which an SM accepts shared-memory loads.  This
 // lane halves the lookups and takes the word count out of the automaton:
-//   * words: strings.Fields word starts of a 16-byte group by SIMD-in-register compares (ASCII whitespace 9..13, 32),
-//     no lookups;
+//   * words: strings.Fields word starts of a 16-byte group by SIMD-in-register compares (ASCII whitespace 9..13, 32;
+//     a byte >= 0x80 counts as non-space), no lookups;
 //   * events (keywords, question words, sentiment words): a FILTER automaton over 4-bit byte classes ((b & 31) * mul >>
-//     shift & 15, arithmetic only) that consumes two bytes per lookup - entry(state, class pair) = next state | "an
-//     occurrence of some pattern's class string may have ended in these two bytes".  It over-approximates: bytes that
-//     share a class are not told apart;
+//     shift & 15, arithmetic only) that consumes two bytes per lookup.  It is walked in its Moore form: an entry is one
+//     byte, the next state, its address is state << 8 | class pair (one byte permute), and a state >= ffired says "an
+//     occurrence of some pattern's class string may have ended in the two bytes that led here".  It over-approximates:
+//     bytes that share a class are not told apart;
 //   * every group the filter flags, and every group that holds one of the lead bytes C2 C4 C5 E0-E3 (multi-byte
-//     whitespace, the fold runes U+017F / U+212A / U+0130) or follows such a group, is handed to `sink`, which walks the group
-//     through the EXACT one-byte automaton (its column-merged copy; 16 warm-up bytes + the 16 bytes) and takes words and events from that walk
-//     instead.  Flagged groups are rare on text (about 0.5 % on the benchmark set), so the exact walk is off the hot path.
+//     whitespace, the fold runes U+017F / U+212A / U+0130) or follows such a group, is handed to `sink`, which walks the
+//     group through the EXACT one-byte automaton (its column-merged copy; 16 warm-up bytes + the 16 bytes) and takes
+//     words and events from that walk instead.  Flagged groups are rare on text (under 1 % on the benchmark set).
+// A lane takes its bytes a WINDOW (NG groups) at a time: the NG groups are scanned without a branch, and one test per
+// window - nothing flagged, no byte >= 0x80, no message boundary inside - decides between adding up the window's word
+// starts and the per-group path that pushes flagged groups and steps over message boundaries.
 // Exactness: an event that completes in group g depends on at most 17 bytes, so every byte it depends on lies in g-1 or
 // g; the filter's class automaton knows every way to complete an event that uses none of those lead bytes (literals of
 // any script included) and flags g when it sees one, otherwise g-1 or g holds such a lead byte and g is walked exactly
@@ -24,10 +28,13 @@
 
 namespace triage {
 
+// The device keeps the filter table at this shared-memory address: low 16 bits zero, so state << 8 | class pair (one byte
+// permute) plus an immediate offset is the address of an entry.
+constexpr uint32_t kPairTableShared = 0x10000u;
+
 struct PairCtx {
-    const uint8_t *ftbl;        // filter table: kRowBytes per state, 256 16-bit entries: next state | fired << 15
-    uint32_t ftbl_s;            // device: its shared-memory address
-    uint32_t fstart;            // filter root
+    const uint8_t *ftbl;        // filter table, Moore form: 256 next states per state (host; the device reads kPairTableShared)
+    uint32_t fstart, ffired;    // filter root; states >= ffired were entered by a firing entry
     uint32_t mul, shift;        // byte -> class: ((b & 31) * mul >> shift) & 15
     const uint16_t *xtbl;       // exact automaton, column-merged: entry(state, xcls[byte]), xn per state (shared memory on the device)
     const uint8_t *xcls;
@@ -43,14 +50,14 @@ struct PairCtx {
     uint32_t *counters;
 };
 
+// f: a filter state (upper bytes zero); k: which byte of `pairs` holds the class pair (0 or 2)
 TR_HD uint32_t pr_fnext(const PairCtx &c, uint32_t pairs, uint32_t f, uint32_t k) {
 #if defined(__CUDA_ARCH__)
-    uint32_t addr = __dp4a(__byte_perm(pairs, f, 0x4440u | k), kDpMul, c.ftbl_s);
-    uint16_t v;
-    asm("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr));
+    uint32_t v;
+    asm("ld.shared.u8 %0, [%1+65536];" : "=r"(v) : "r"(__byte_perm(pairs, f, 0x5540u | k)));
     return v;
 #else
-    return *reinterpret_cast<const uint16_t *>(c.ftbl + (f & 0xFFu) * kRowBytes + 2u * ((pairs >> (8 * k)) & 0xFFu));
+    return c.ftbl[(f << 8) | ((pairs >> (8 * k)) & 0xFFu)];
 #endif
 }
 TR_HD uint32_t pr_xnext(const PairCtx &c, uint32_t e, uint32_t byte) {
@@ -65,27 +72,32 @@ TR_HD uint32_t pr_xnext(const PairCtx &c, uint32_t e, uint32_t byte) {
 #endif
 }
 
-// bit 7 of every byte: the byte is not ASCII whitespace.  Exact for words whose bytes are all < 0x80 (the per-byte sums
-// of a word with a byte >= 0x80 may carry over): groups with such bytes recompute it with pr_nonspace_any.
+// bit 7 of every byte: the byte is not ASCII whitespace.  The other bits are junk: users mask.  Only valid for words
+// whose bytes are all < 0x80 (the per-byte sums of a byte >= 0x80 carry over): windows with such bytes are recounted
+// with pr_nonspace_any.
 TR_HD uint32_t pr_nonspace(uint32_t w) {
     const uint32_t ne20 = (w ^ 0x20202020u) + 0x7F7F7F7Fu;    // bit 7: byte != 0x20
     const uint32_t gt13 = w + 0x72727272u;                    // bit 7: byte > 13
     const uint32_t ge9 = w + 0x77777777u;                     // bit 7: byte >= 9
-    return ne20 & (gt13 | ~ge9) & 0x80808080u;
+    return ne20 & (gt13 | ~ge9);
 }
 // the same for any bytes: a byte >= 0x80 is not ASCII whitespace
-TR_HD uint32_t pr_nonspace_any(uint32_t w) { return (pr_nonspace(w & 0x7F7F7F7Fu) | w) & 0x80808080u; }
-// bit 7 of every byte that equals v (exact)
-TR_HD uint32_t pr_eq(uint32_t w, uint32_t v4) {
-    const uint32_t t = w ^ v4;
-    return ~(((t & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | t) & 0x80808080u;
-}
+TR_HD uint32_t pr_nonspace_any(uint32_t w) { return pr_nonspace(w & 0x7F7F7F7Fu) | w; }
 // Does the word hold a byte that can start a rune the exact automaton treats specially?  Multi-byte whitespace starts
 // with C2, E1, E2 or E3; the fold runes U+017F, U+212A, U+0130 with C5, E2, C4.  (E0 is let in with E1..E3: one test.)
 // Every other byte >= 0x80 - accented Latin, Cyrillic, CJK ideographs, emoji, stray continuation bytes - is to the path
-// what an ordinary letter is: not whitespace, part of no fold.
+// what an ordinary letter is: not whitespace, part of no fold.  Bit 7 of every such byte.
 TR_HD uint32_t pr_special(uint32_t w) {
-    return pr_eq(w, 0xC2C2C2C2u) | pr_eq(w, 0xC4C4C4C4u) | pr_eq(w, 0xC5C5C5C5u) | pr_eq(w & 0xFCFCFCFCu, 0xE0E0E0E0u);
+    const uint32_t m = w & 0x7F7F7F7Fu;
+    const uint32_t n42 = (m ^ 0x42424242u) + 0x7F7F7F7Fu;     // bit 7: low seven bits != 0x42
+    const uint32_t n44 = (m ^ 0x44444444u) + 0x7F7F7F7Fu;
+    const uint32_t n45 = (m ^ 0x45454545u) + 0x7F7F7F7Fu;
+    const uint32_t n6x = ((w & 0x7C7C7C7Cu) ^ 0x60606060u) + 0x7F7F7F7Fu;   // bit 7: low seven bits not in 0x60..0x63
+    return ~(n42 & n44 & n45 & n6x) & w & 0x80808080u;
+}
+TR_HD uint32_t pr_special(const Quad &q) {
+    if (!((q.a | q.b | q.c | q.d) & 0x80808080u)) return 0;
+    return pr_special(q.a) | pr_special(q.b) | pr_special(q.c) | pr_special(q.d);
 }
 TR_HD uint32_t pr_funnel8(uint32_t lo, uint32_t hi) {          // (hi << 8) | (lo >> 24)
 #if defined(__CUDA_ARCH__)
@@ -94,13 +106,14 @@ TR_HD uint32_t pr_funnel8(uint32_t lo, uint32_t hi) {          // (hi << 8) | (l
     return (hi << 8) | (lo >> 24);
 #endif
 }
-TR_HD uint32_t pr_bytesum(uint32_t v) {                        // sum of the four bytes
+TR_HD uint32_t pr_popc(uint32_t v) {
 #if defined(__CUDA_ARCH__)
-    return __vsadu4(v, 0u);
+    return (uint32_t)__popc(v);
 #else
-    return (v & 0xFFu) + ((v >> 8) & 0xFFu) + ((v >> 16) & 0xFFu) + (v >> 24);
+    return (uint32_t)__builtin_popcount(v);
 #endif
 }
+TR_HD uint32_t pr_max(uint32_t a, uint32_t b) { return a > b ? a : b; }
 // class pairs of a word: byte 0 = c0 | c1 << 4, byte 2 = c2 | c3 << 4
 template <bool SIMPLE>
 TR_HD uint32_t pr_pairs(const PairCtx &c, uint32_t w) {
@@ -112,30 +125,48 @@ TR_HD uint32_t pr_pairs(const PairCtx &c, uint32_t w) {
 
 struct PairLane {
     LongLane L;            // message tracking and the word count of the current message (L.e is unused)
-    uint32_t f;            // filter state (entry: low byte)
-    uint32_t prev_ns;      // non-space bits of the previous word (bit 31: the byte before the group)
-    uint32_t prev_rare;    // the previous group held a byte >= 0x80
-    Quad prevq;            // the previous 16 bytes (warm-up of an exact walk)
+    uint32_t f;            // filter state
+    uint32_t prev_ns;      // pr_nonspace of the previous word (bit 31: the byte before the group)
+    uint32_t prev_rare;    // the previous group held one of the special lead bytes
+    Quad prevq;            // the 16 bytes before the window (warm-up of an exact walk of its first group)
 };
 
 // The exact walk of one flagged group: state from the 16 bytes before it, then words and events of its 16 bytes.
-template <class Ctx>
-TR_COLD void pair_replay(const Ctx &c, Quad warm, Quad q, uint32_t msg) {   // quads by value: they stay in registers at the call
+// load(i): word i of the 32 bytes (0..3 the bytes before, 4..7 the group).  Rolled by word: it runs for one group in a
+// hundred, its code should not push the scan loop out of the instruction cache.
+template <class Ctx, class Load>
+TR_HD void pair_replay_words(const Ctx &c, Load load, uint32_t msg) {
     uint32_t e = c.neutral_state, words = 0;
-    const uint32_t ww[4] = {warm.a, warm.b, warm.c, warm.d}, qw[4] = {q.a, q.b, q.c, q.d};
+#ifdef __CUDA_ARCH__
+#pragma unroll 1
+#endif
+    for (int i = 0; i < 4; i++) {
+        const uint32_t w = load(i);
+        e = pr_xnext(c, e, w & 0xFFu);
+        e = pr_xnext(c, e, (w >> 8) & 0xFFu);
+        e = pr_xnext(c, e, (w >> 16) & 0xFFu);
+        e = pr_xnext(c, e, w >> 24);
+    }
+#ifdef __CUDA_ARCH__
+#pragma unroll 1
+#endif
+    for (int i = 4; i < 8; i++) {
+        const uint32_t w = load(i);
 #ifdef __CUDA_ARCH__
 #pragma unroll
 #endif
-    for (int i = 0; i < 16; i++) e = pr_xnext(c, e, (ww[i >> 2] >> (8 * (i & 3))) & 0xFFu);
-#ifdef __CUDA_ARCH__
-#pragma unroll
-#endif
-    for (int i = 0; i < 16; i++) {
-        e = pr_xnext(c, e, (qw[i >> 2] >> (8 * (i & 3))) & 0xFFu);
-        words += e >> 15;
-        if (e & 0x7F00u) apply_event_raw(c.events, c.counters, (e >> 8) & 0x7Fu, msg);
+        for (int k = 0; k < 4; k++) {
+            e = pr_xnext(c, e, (w >> (8 * k)) & 0xFFu);
+            words += e >> 15;
+            if (e & 0x7F00u) apply_event_raw(c.events, c.counters, (e >> 8) & 0x7Fu, msg);
+        }
     }
     if (words) tr_add(c.counters + (uint64_t)msg * CNT_STRIDE + CNT_WORDS, words);
+}
+template <class Ctx>
+TR_COLD void pair_replay(const Ctx &c, Quad warm, Quad q, uint32_t msg) {
+    const uint32_t v[8] = {warm.a, warm.b, warm.c, warm.d, q.a, q.b, q.c, q.d};
+    pair_replay_words(c, [&](int i) { return v[i]; }, msg);
 }
 
 // warm: the 16 bytes before the lane's chunk (the reset pad byte x 16 when nothing precedes it: the exact walk then
@@ -162,63 +193,109 @@ TR_HD void pair_begin(const Ctx &c, PairLane &P, uint32_t k, const Quad &warm) {
     }
     P.f = f;
     P.prev_ns = pr_nonspace_any(warm.d);
-    P.prev_rare = pr_special(warm.a) | pr_special(warm.b) | pr_special(warm.c) | pr_special(warm.d);
+    P.prev_rare = pr_special(warm);
     P.prevq = warm;
 }
 
-// one 16-byte group at tile-relative position pos.  prevp: where the 16 bytes before the group can still be read (the
-// staging buffer, inside a window); nullptr: they are P.prevq, which the caller then keeps up to date (KEEP: this function
-// does it after every group).  Keeping them out of registers inside a window saves a reload of the group per iteration.
-template <bool SIMPLE, bool KEEP = true, class Ctx, class Sink>
-TR_HD bool pair_group(const Ctx &c, PairLane &P, const Quad &q, int32_t pos, Sink &sink, const Quad *prevp = nullptr) {
-    long_boundary(c, P.L, pos);
-    const uint32_t high = (q.a | q.b | q.c | q.d) & 0x80808080u;
+// Word starts of 16 bytes as a bit set: bit 7 - j of byte i <=> byte i of word j starts a word.  pns: pr_nonspace of the
+// word before (in, out).  ANY: exact for bytes >= 0x80 too.
+template <bool ANY>
+TR_HD uint32_t pair_starts16(const Quad &q, uint32_t &pns) {
     const uint32_t qw[4] = {q.a, q.b, q.c, q.d};
-    const uint32_t pns0 = P.prev_ns;
-    uint32_t f = P.f, fired = 0, starts = 0, pns = pns0, rare = 0;
+    uint32_t u = 0;
 #ifdef __CUDA_ARCH__
 #pragma unroll
 #endif
     for (int j = 0; j < 4; j++) {
-        const uint32_t w = qw[j];
-        const uint32_t ns = pr_nonspace(w);
-        const uint32_t before = pr_funnel8(pns, ns);           // non-space bit of the byte before each byte
-        starts += pr_bytesum(ns & ~before);                    // 128 per word start
+        const uint32_t ns = ANY ? pr_nonspace_any(qw[j]) : pr_nonspace(qw[j]);
+        u += ((ns & ~pr_funnel8(pns, ns)) & 0x80808080u) >> j;
         pns = ns;
-        const uint32_t p = pr_pairs<SIMPLE>(c, w);
-        f = pr_fnext(c, p, f, 0); fired |= f;
-        f = pr_fnext(c, p, f, 2); fired |= f;
     }
-    if (high) {   // bytes >= 0x80 in the group: is one of the few lead bytes that matter among them?
-        rare = pr_special(q.a) | pr_special(q.b) | pr_special(q.c) | pr_special(q.d);
-        if (!rare) {   // other scripts: the group is counted here after all, with space bits that are exact for any byte
-            starts = 0; pns = pns0;
+    return u;
+}
+
+// 16 bytes without a branch: the filter walks on (f); returns the highest filter state entered
+template <bool SIMPLE>
+TR_HD uint32_t pair_filter16(const PairCtx &c, const Quad &q, uint32_t &f) {
+    const uint32_t qw[4] = {q.a, q.b, q.c, q.d};
+    uint32_t m = 0;
 #ifdef __CUDA_ARCH__
 #pragma unroll
 #endif
-            for (int j = 0; j < 4; j++) {
-                const uint32_t ns = pr_nonspace_any(qw[j]);
-                starts += pr_bytesum(ns & ~pr_funnel8(pns, ns));
-                pns = ns;
-            }
-        }
-        // (rare: this group and the next are walked exactly; the "byte before" bit handed on is exact whenever the group
-        // after those uses it, because that needs the last word of the next group to be free of such bytes)
+    for (int j = 0; j < 4; j++) {
+        const uint32_t p = pr_pairs<SIMPLE>(c, qw[j]);
+        f = pr_fnext(c, p, f, 0); m = pr_max(m, f);
+        f = pr_fnext(c, p, f, 2); m = pr_max(m, f);
+    }
+    return m;
+}
+
+// NG 16-byte groups at tile-relative position pos.  P.prevq holds the 16 bytes before win[0] (they may no longer be
+// readable where they came from).  Returns how many groups went to the sink.
+template <bool SIMPLE, int NG, class Ctx, class Sink>
+TR_HD uint32_t pair_window(const Ctx &c, PairLane &P, const Quad *win, int32_t pos, Sink &sink) {
+    uint32_t st[NG], fm[NG], hi = 0, f = P.f, pns = P.prev_ns, top = 0;
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+    for (int g = 0; g < NG; g++) {
+        const Quad q = win[g];
+        st[g] = pair_starts16<false>(q, pns);
+        fm[g] = pair_filter16<SIMPLE>(c, q, f);
+        top = pr_max(top, fm[g]);
+        hi |= q.a | q.b | q.c | q.d;
     }
     P.f = f;
+    hi &= 0x80808080u;
+    if (top < c.ffired && !hi && !P.prev_rare && pos + 16 * (NG - 1) < P.L.mend) {
+        uint32_t n = 0;                                          // two groups' bit sets share a word: 4 + 4 bits a byte
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+        for (int g = 0; g + 1 < NG; g += 2) n += pr_popc(st[g] + (st[g + 1] >> 4));
+        if (NG & 1) n += pr_popc(st[NG - 1]);
+        P.L.words += n;
+        P.prev_ns = pns;
+        P.prevq = win[NG - 1];
+        return 0;
+    }
+    if (hi) {   // bytes >= 0x80 in the window: the word starts again, with the compares that are exact for them
+        pns = P.prev_ns;
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+        for (int g = 0; g < NG; g++) st[g] = pair_starts16<true>(win[g], pns);
+    }
     P.prev_ns = pns;
-    const bool flagged = (rare | P.prev_rare | (fired & 0x8000u)) != 0;
-    if (flagged) sink.push(c, prevp ? *prevp : P.prevq, q, P.L.msg);
-    else P.L.words += starts >> 7;
-    P.prev_rare = rare;
-    if (KEEP) P.prevq = q;
-    return flagged;
+    uint32_t pushed = 0;
+#ifdef __CUDA_ARCH__
+#pragma unroll
+#endif
+    for (int g = 0; g < NG; g++) {
+        long_boundary(c, P.L, pos + 16 * g);
+        const uint32_t rare = hi ? pr_special(win[g]) : 0u;
+        if (fm[g] >= c.ffired || rare || P.prev_rare) {
+            sink.push(c, g ? win[g - 1] : P.prevq, win[g], P.L.msg);
+            pushed++;
+        } else {
+            P.L.words += pr_popc(st[g]);
+        }
+        P.prev_rare = rare;
+    }
+    P.prevq = win[NG - 1];
+    return pushed;
+}
+
+// one group (the arena's partial last row, host checks)
+template <bool SIMPLE, class Ctx, class Sink>
+TR_HD bool pair_group(const Ctx &c, PairLane &P, const Quad &q, int32_t pos, Sink &sink) {
+    return pair_window<SIMPLE, 1>(c, P, &q, pos, sink) != 0;
 }
 
 template <class Ctx>
 TR_HD void pair_end(const Ctx &c, PairLane &P) { long_end(c, P.L); }
 
-// sink that walks a flagged group on the spot (host checks, the partial last row, message indices beyond the queue's range)
+// sink that walks a flagged group on the spot (host checks, the partial last row)
 struct PairSinkNow {
     template <class Ctx>
     TR_HD void push(const Ctx &c, const Quad &warm, const Quad &q, uint32_t msg) { pair_replay(c, warm, q, msg); }

@@ -511,13 +511,12 @@ extern "C" int hostcheck_scan_pair(const uint8_t *prios, const uint8_t *cis, con
     Dfa dfa;
     std::string e = build_dfa(dict, &dfa);
     if (!e.empty() || !dfa.filter.ok) { std::strncpy(err, e.empty() ? "no pair filter for this dictionary" : e.c_str(), errcap - 1); return 4; }
-    info[0] = dfa.filter.n_states | ((uint64_t)dfa.n_cmp << 32); info[1] = dfa.filter.mul; info[2] = dfa.filter.shift; info[3] = info[4] = 0;
+    info[0] = dfa.filter.m_states | ((uint64_t)dfa.n_cmp << 32); info[1] = dfa.filter.mul; info[2] = dfa.filter.shift; info[3] = info[4] = 0;
     if (n_msgs == 0) return 0;
     std::vector<EventPacked> ev(dfa.events.size());
     for (size_t i = 0; i < dfa.events.size(); i++) pack_event(dfa.events[i], &ev[i].x);
-    std::vector<uint8_t> xtbl((size_t)dfa.n_states * kRowBytes, 0), ftbl((size_t)dfa.filter.n_states * kRowBytes, 0);
+    std::vector<uint8_t> xtbl((size_t)dfa.n_states * kRowBytes, 0);
     for (uint32_t st = 0; st < dfa.n_states; st++) std::memcpy(xtbl.data() + (size_t)st * kRowBytes, dfa.table.data() + (size_t)st * 256, 512);
-    for (uint32_t st = 0; st < dfa.filter.n_states; st++) std::memcpy(ftbl.data() + (size_t)st * kRowBytes, dfa.filter.table.data() + (size_t)st * 256, 512);
     std::vector<uint64_t> poff(n_msgs + 1, 0);
     for (uint32_t i = 0; i < n_msgs; i++) poff[i + 1] = poff[i] + ((offsets[i + 1] - offsets[i]) / 16 + 1) * 16;
     std::vector<uint8_t> arena_raw(poff[n_msgs] + 64, (uint8_t)dfa.reset_pad);
@@ -540,7 +539,7 @@ extern "C" int hostcheck_scan_pair(const uint8_t *prios, const uint8_t *cis, con
         std::vector<int32_t> list;
         for (uint32_t m = mlo; m <= mhi + 1; m++) list.push_back((int32_t)((int64_t)poff[m] - (int64_t)ts));
         PairCtx c;
-        c.ftbl = ftbl.data(); c.ftbl_s = 0; c.fstart = dfa.filter.start; c.mul = dfa.filter.mul; c.shift = dfa.filter.shift;
+        c.ftbl = dfa.filter.mtable.data(); c.fstart = dfa.filter.m_start; c.ffired = dfa.filter.m_fired_from; c.mul = dfa.filter.mul; c.shift = dfa.filter.shift;
         c.xtbl = dfa.ctable.data(); c.xcls = dfa.ccls; c.xn = dfa.n_cmp; c.events = ev.data(); c.neutral_state = dfa.neutral_state; c.pad4 = padq.a;
         c.list = list.data(); c.list_abs = poff.data(); c.tile_start = (int64_t)ts; c.list_n = (uint32_t)list.size(); c.msg_lo = mlo;
         c.counters = counters;
@@ -551,7 +550,14 @@ extern "C" int hostcheck_scan_pair(const uint8_t *prios, const uint8_t *cis, con
             PairLane P;
             Quad warm = cs ? *reinterpret_cast<const Quad *>(arena + cs - 16) : padq;
             if (simple) pair_begin<true>(c, P, find_msg(c, (int32_t)(cs - ts)), warm); else pair_begin<false>(c, P, find_msg(c, (int32_t)(cs - ts)), warm);
-            for (uint64_t g = cs; g < ce; g += 16) {
+            // whole 80-byte windows the way the kernel takes them, the rest group by group
+            uint64_t g = cs;
+            for (; g + 80 <= ce; g += 80) {
+                const Quad *win = reinterpret_cast<const Quad *>(arena + g);
+                if (simple) pair_window<true, 5>(c, P, win, (int32_t)(g - ts), sink); else pair_window<false, 5>(c, P, win, (int32_t)(g - ts), sink);
+                info[4] += 5;
+            }
+            for (; g < ce; g += 16) {
                 const Quad q = *reinterpret_cast<const Quad *>(arena + g);
                 if (simple) pair_group<true>(c, P, q, (int32_t)(g - ts), sink); else pair_group<false>(c, P, q, (int32_t)(g - ts), sink);
                 info[4]++;

@@ -3,8 +3,8 @@ triage_submit_device_padded on each shard, then triage_merge_allgather.  Both me
 contiguous sequence shards take the offset-arithmetic merge (concat_kernel), explicit enqueue times that interleave
 across the ranks take the ranked merge (merge_strided_kernel) - and the merged whole-job dequeue order on every rank
 is compared with (a) the CPU oracle run on the whole job as one batch and (b) the reference merge of
-tests/test_multigpu_host.py over the per-rank runs.  Ranks admit different numbers of messages (the generator's
-"unknown" labels are turned away) and most of the 16 (level, priority) buckets are empty."""
+tests/test_multigpu_host.py over the per-rank runs.  Ranks admit different numbers of messages (explicit priorities
+that name no queue are turned away) and most of the 16 (level, priority) buckets are empty."""
 import os
 import socket
 
@@ -35,6 +35,9 @@ def _worker(rank, world, port, q):
         n = N_PER_RANK
         # the whole job, generated identically on every rank; rank r owns the contiguous range [r*n, (r+1)*n)
         off, data, meta, ts = co.generate(0x2D0C, n * world, 16, 900, edge=300)
+        # an explicit priority that names no queue is turned away (PushMessage: queue not found): rank r loses 37 * (r + 1)
+        for r in range(world):
+            meta["preset"][r * n + 11:r * n + 11 + 37 * (r + 1) * 3:3] = 7
         lo, hi = rank * n, (rank + 1) * n
         soff = (off[lo:hi + 1] - off[lo]).astype(np.uint64)
         sdata = data[int(off[lo]):int(off[hi])]

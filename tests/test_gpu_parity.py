@@ -256,9 +256,11 @@ def test_padded_arena_sizes_around_row_and_tile_boundaries(rows, monkeypatch):
     """The padded arena is scanned as 320-byte rows, 32 rows per tile (2-D TMA), with the partial last row read directly;
     arenas shorter than one row go to the mini-tile kernel.  Sweep totals across those boundaries, with both kernels
     (TRIAGE_ROWS=0 keeps to the mini-tile kernel): every result must equal the oracle's."""
-    if rows.startswith("p0-"):            # the one-lookup-per-byte row kernel instead of the pair-lane kernel (the default)
+    if rows.startswith("p0-"):            # the one-lookup-per-byte row kernel (the default) ...
         monkeypatch.setenv("TRIAGE_PAIR", "0")
         rows = rows[3:]
+    else:                                 # ... and the pair-lane kernel
+        monkeypatch.setenv("TRIAGE_PAIR", "1")
     if rows in ("1280", "640", "320"):   # force the long / short row length of the row-lane kernel whatever the arena size
         monkeypatch.setenv("TRIAGE_ROW_BYTES", rows)
     else:
