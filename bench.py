@@ -103,6 +103,15 @@ def cpu_reference_step(co, d, sample, threads):
     return time.perf_counter() - t0
 
 
+def oracle_dict(co, entries):
+    d = co.Dict()
+    if entries:
+        for p_, ci_, lit_ in entries:
+            d.add(p_, lit_, ci_)
+        d.set_fast()     # 10 000 keywords: the oracle's one-pass mode (checked against its per-pattern mode in tests/test_oracle.py)
+    return d
+
+
 def make_cpu_sample(co, n):
     return co.generate(SEED + 77, n, LEN_LO, LEN_HI, edge=50)
 
@@ -139,10 +148,27 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+# what bounds each scan kernel, keyed by the engine's scan_variant
+LIMITERS = {3: "shared-memory lookup rate of the SM (one table lookup per input byte), DESIGN.md 4.1",
+            5: "shared-memory lookup rate of the SM (one filter lookup per two input bytes, with bank conflicts) and instruction issue, DESIGN.md 4.1c",
+            4: "one dependent L1/L2 gather per input byte into the wide transition table, DESIGN.md 4.1b",
+            6: "one dependent L1/L2 gather per input byte into the wide transition table (L1 tag/data rate with several chains per lane), DESIGN.md 4.1b"}
+
+
 C3_GLOBAL = 1 << 24   # BASELINE configs[2]: 16 Mi mixed-length messages sharded over the GPUs
 
 
+C5_PER_GPU = 1 << 18   # BASELINE configs[4]: 256 Ki messages per GPU of skewed traffic, 10 000-keyword dictionary
+
+
 def workload_config(n_gpus, workload="c2"):
+    if workload == "c5":
+        return {"workload": "BASELINE configs[4] per GPU: 256Ki messages, content U[256,4096] bytes + injected keywords, skewed traffic "
+                            "(realtime bursts), 10 000-keyword dictionary (len 4-16) on top of the default one",
+                "messages_per_gpu": C5_PER_GPU, "global_messages": C5_PER_GPU * n_gpus,
+                "parallelism": f"shard{n_gpus}" if n_gpus > 1 else "single",
+                "l2_policy": "inputs (~0.57 GB per GPU) larger than the 126 MB L2; no flush needed",
+                "timestamps": "engine-stamped, strictly increasing in arrival order"}
     if workload == "c3":
         return {"workload": "BASELINE configs[2]: 16Mi messages in total, length mix 70% U[256,1024] / 25% U[1024,4096] / 5% U[4096,16384], "
                             "sharded contiguously over the GPUs, NCCL all-gather merge of the sorted runs, default dictionary",
@@ -157,7 +183,7 @@ def workload_config(n_gpus, workload="c2"):
             "timestamps": "engine-stamped, strictly increasing in arrival order"}
 
 
-def self_check(args, mq, co, dist, rank, world, n, d_res, d_ord, d_gord, ts_host, raw_batch, dev):
+def self_check(args, mq, co, dist, rank, world, n, d_res, d_ord, d_gord, ts_host, raw_batch, dev, entries=None):
     """Compares the results of the last timed step with the checkers.  labels: every result field of this rank's batch
     against the CPU oracle - the whole batch through the committed SHA-256 digests when the batch is the golden C2 set
     (rank 0, default size: tests/golden/fullsize_sha256.json was produced by the oracle on exactly these inputs), plus a
@@ -175,8 +201,9 @@ def self_check(args, mq, co, dist, rank, world, n, d_res, d_ord, d_gord, ts_host
     how = []
     labels_ok = True
     digest_path = os.path.join(ROOT, "tests", "golden", "fullsize_sha256.json")
-    if rank == 0 and n == N_PER_GPU and args.workload == "c2" and os.path.exists(digest_path) and not args.interleave_ts:
-        want = json.load(open(digest_path)).get("c2", {})
+    golden = {"c2": N_PER_GPU, "c5": C5_PER_GPU}.get(args.workload)
+    if rank == 0 and n == golden and os.path.exists(digest_path) and not args.interleave_ts:
+        want = json.load(open(digest_path)).get(args.workload, {})
         if want.get("messages") == n:
             for f in fields + ("accepted", "admit"):
                 if hashlib.sha256(np.ascontiguousarray(res[f]).tobytes()).hexdigest() != want[f]:
@@ -196,7 +223,7 @@ def self_check(args, mq, co, dist, rank, world, n, d_res, d_ord, d_gord, ts_host
         for j, i in enumerate(sample):
             sd[int(so[j]):int(so[j + 1])] = data[int(off[i]):int(off[i + 1])]
     threads = max(1, (os.cpu_count() or 1) // max(1, world))
-    exp = co.process_batch(co.Dict(), so, sd, meta[sample], nthreads=threads)
+    exp = co.process_batch(oracle_dict(co, entries), so, sd, meta[sample], nthreads=threads)
     for f in fields:
         if not np.array_equal(res[f][sample], exp[f]):
             labels_ok = False
@@ -215,8 +242,8 @@ def self_check(args, mq, co, dist, rank, world, n, d_res, d_ord, d_gord, ts_host
         want_local = idx[np.argsort(bucket[idx], kind="stable")]
     got_local = d_ord.cpu().numpy().astype(np.int64)[:len(want_local)]
     out["order"] = bool(np.array_equal(got_local, want_local))
-    if rank == 0 and n == N_PER_GPU and args.workload == "c2" and os.path.exists(digest_path) and not args.interleave_ts:
-        want = json.load(open(digest_path)).get("c2", {})
+    if rank == 0 and n == golden and os.path.exists(digest_path) and not args.interleave_ts:
+        want = json.load(open(digest_path)).get(args.workload, {})
         if want.get("messages") == n:
             out["order"] = out["order"] and hashlib.sha256(got_local.astype(np.uint32).tobytes()).hexdigest() == want["order"]
     # (3) merged whole-job order
@@ -247,9 +274,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--messages", type=int, default=0, help="messages per GPU (default: the workload's own size)")
-    ap.add_argument("--workload", default="c2", choices=["c2", "c3"],
+    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c5"],
                     help="c2 (default, what the driver records): configs[1], 1 Mi messages per GPU, weak scaling; "
-                         "c3: configs[2], 16 Mi mixed-length messages in total, sharded over the GPUs, strong scaling")
+                         "c3: configs[2], 16 Mi mixed-length messages in total, sharded over the GPUs, strong scaling; "
+                         "c5: configs[4], 256 Ki messages per GPU of skewed traffic against a 10 000-keyword dictionary, weak scaling")
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--interleave-ts", action="store_true", help="(test) explicit enqueue times that interleave across ranks: exercises the general merge")
@@ -279,17 +307,27 @@ def main():
         if world > 1:
             dist.barrier()
 
-    c3 = args.workload == "c3"
-    n = args.messages or (C3_GLOBAL // world if c3 else N_PER_GPU)
+    c3, c5 = args.workload == "c3", args.workload == "c5"
+    n = args.messages or (C3_GLOBAL // world if c3 else C5_PER_GPU if c5 else N_PER_GPU)
+    entries = None
     # ---- synthetic batch of this rank (own seed => different content per rank) ----
     if c3:
         off, data, meta, _ = co.generate(0xC0FFEE03 + rank, n, 256, 16384, mix=1, edge=50)
         if n * 1700 > (4 << 30):
             args.skip_e2e = True      # two pinned host arenas of this size per rank are not what this line is about
+    elif c5:      # the generator of the committed C5 digests (tests/fullsize.py), own seed per rank beyond rank 0
+        from tests import c5 as c5gen
+        off, data, meta, _ = co.generate(0xC0FFEE05 + rank, n, LEN_LO, LEN_HI, mix=2, edge=50)
+        entries = c5gen.dictionary()
+        off, data = co.pack(c5gen.inject([bytes(data[int(off[i]):int(off[i + 1])]) for i in range(n)], entries))
     else:
         off, data, meta, _ = co.generate(SEED + rank, n, LEN_LO, LEN_HI, edge=50)
     total = int(off[-1])
     eng = mq.Engine(device=local)
+    if entries:
+        for p_, ci_, lit_ in entries:
+            eng.add_literal(p_, lit_, ci_)
+        eng.commit()
     info = eng.dict_info()
 
     # the engine's preferred wire format: 16-byte aligned message starts + reset-pad fill
@@ -359,7 +397,7 @@ def main():
 
     # ---- self-check of what was just timed (outside the timed region, every run): labels / analysis / admission against
     #      the CPU oracle, this rank's dequeue order and the merged whole-job order against a numpy stable sort ----
-    checked = self_check(args, mq, co, dist, rank, world, n, d_res, d_ord, d_gord, ts_host, raw_batch, dev)
+    checked = self_check(args, mq, co, dist, rank, world, n, d_res, d_ord, d_gord, ts_host, raw_batch, dev, entries)
 
     # ---- end to end through the host-buffer C ABI call (pinned host arenas, H2D + D2H timed) ----
     e2e = None
@@ -449,13 +487,13 @@ def main():
         # charged to the scan by that definition although finalize_kernel moves them; pad bytes and lengths are not counted)
         alg = content_bytes + 8 * (n + 1) + 32 * n
         achieved = alg / (t_scan / 1000) / 1e9
-        traffic = scan_traffic_from_profile()
+        traffic = scan_traffic_from_profile() if args.workload == "c2" and last_t["scan_variant"] == 3 else None   # the capture is of that launch
         kern = f"{mq._capi.SCAN_VARIANTS.get(last_t['scan_variant'], '?')}, {last_t['scan_warps']} warps per CTA"
         if last_t["scan_row_bytes"]:
-            kern += f", {last_t['scan_row_bytes']}-byte rows per lane"
+            kern += f", {last_t['scan_row_bytes']}-byte rows"
         roofline = {"bound": "hbm", "kernel": kern, "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": achieved / peak, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg,
-                    "limiter": "shared-memory lookup rate of the SM (one table lookup per input byte), see DESIGN.md 4.1; HBM is the roofline reported",
+                    "limiter": LIMITERS.get(last_t["scan_variant"], "see DESIGN.md 4.1") + "; HBM is the roofline reported",
                     "kernel_ms": t_scan, "traffic": traffic["dram_bytes_per_launch"] if traffic else None,
                     "traffic_source": (traffic or {}).get("source", None),
                     "step_share": {"scan_ms": t_scan, "finalize_ms": sum(fin_ms) / len(fin_ms), "order_ms": sum(ord_ms) / len(ord_ms),
@@ -463,7 +501,7 @@ def main():
         cpu_baseline = None
         if world == 1 and not args.skip_cpu:
             threads = os.cpu_count() or 1
-            d = co.Dict()
+            d = oracle_dict(co, entries)
             probe = make_cpu_sample(co, 2000)
             rate = 2000 / max(cpu_reference_step(co, d, probe, threads), 1e-6)
             ns = int(min(200000, max(2000, rate * 12.0)))

@@ -44,7 +44,8 @@ SCAN_VARIANTS = {0: "none", 1: "scan_kernel (packed arena, CTA-wide tiles)", 2: 
                  3: "scan_rows_kernel (padded arena, row lanes, 2-D TMA windows of 80 B x 32 rows)",
                  4: "scan_padded_kernel<wide> (class map in shared memory, transitions in L2)",
                  5: "scan_pair_kernel (padded arena, row lanes fed by 2-D TMA, filter automaton over class pairs: 8 lookups per 16 bytes, "
-                    "SIMD word count, flagged groups walked exactly)"}
+                    "SIMD word count, flagged groups walked exactly)",
+                 6: "scan_stream_wide_kernel (wide table in L2/L1, rows streamed from global memory, several rows per lane walked interleaved)"}
 
 
 class TriageError(RuntimeError):

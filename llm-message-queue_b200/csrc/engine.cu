@@ -171,6 +171,7 @@ struct triage_engine {
     uint32_t pad_warps = 0;
     uint32_t row_warps = 0;        // > 0: the padded arena is scanned by the row-lane kernel (2-D TMA), arenas of >= 1 row
     uint32_t pair_warps = 0;       // > 0: ... by its two-bytes-per-lookup variant (filter automaton, scan_pair.cuh)
+    uint32_t wide_chains = 0, wide_warps = 0, wide_row = 0;   // > 0: wide dictionaries stream rows from global memory, several per lane
     DfaBufs dm, dx;   // device copies of the scan automaton and of the exact (sequential) one
     DeviceDfa ddfa{};
     // exact (sequential, non-overlapping) automaton, only when the dictionary has self-overlapping literals
@@ -339,6 +340,20 @@ int32_t commit_dict(triage_engine *e) {
         if (!rv || atoi(rv) != 0) e->row_warps = pick_row_warps(d, (size_t)e->max_smem_optin);
     }
     e->pair_warps = e->row_warps ? pick_pair_warps(d, (size_t)e->max_smem_optin) : 0;
+    e->wide_chains = e->wide_warps = e->wide_row = 0;
+    if (pad_warps && dfa.wide && d.warm == 16) {
+        // measurement knobs: TRIAGE_WIDE_STREAM=0 keeps to the mini-tile kernel; TRIAGE_WIDE_CHAINS=1|2|3|4 rows per lane
+        // (32, 32|24, 20, 16|12 warps: registers), TRIAGE_WIDE_ROW = row length in bytes (multiple of 16)
+        const char *sv = getenv("TRIAGE_WIDE_STREAM");
+        if (!sv || atoi(sv) != 0) {
+            uint32_t ch = 2, nw = 32, row = 160;
+            if (const char *v = getenv("TRIAGE_WIDE_CHAINS")) { uint32_t x = (uint32_t)atoi(v); if (x >= 1 && x <= 4) ch = x; }
+            nw = ch <= 2 ? 32 : ch == 3 ? 20 : 16;
+            if (const char *v = getenv("TRIAGE_WIDE_WARPS")) { uint32_t x = (uint32_t)atoi(v); if ((ch == 2 && x == 24) || (ch == 4 && x == 12)) nw = x; }
+            if (const char *v = getenv("TRIAGE_WIDE_ROW")) { uint32_t x = (uint32_t)atoi(v); if (x >= 48 && x <= 4096 && x % 16 == 0) row = x; }
+            e->wide_chains = ch; e->wide_warps = nw; e->wide_row = row;
+        }
+    }
     e->geom = geom;
     e->dfa = dfa;
     e->dict_dirty = false;
@@ -377,8 +392,10 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     const bool use_pair = use_rows && e->pair_warps > 0;
     const uint32_t row_warps = use_pair ? e->pair_warps : e->row_warps;
     const uint32_t row_bytes = use_rows ? scan_rows_lane_bytes(chunked ? kUploadChunk : total, row_warps, e->sm_count) : 0;
+    const uint32_t stream_tile = 32u * e->wide_chains * e->wide_row;
+    const bool use_stream = padded && e->wide_chains > 0 && total >= 4ull * stream_tile;   // wide dictionaries: rows streamed from global memory
     const uint32_t tile_bytes = !padded ? e->geom.tile
-                              : use_rows ? scan_rows_super_bytes(row_bytes) : kPadMiniTile;
+                              : use_rows ? scan_rows_super_bytes(row_bytes) : use_stream ? stream_tile : kPadMiniTile;
     const uint32_t ntiles = (uint32_t)((total + tile_bytes - 1) / tile_bytes);
     const uint32_t nblocks = (n + kOrderBlock - 1) / kOrderBlock;
     CU(e->d_counters.ensure((size_t)n * CNT_STRIDE));
@@ -397,9 +414,9 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     CU(cudaEventRecord(e->ev[0], s));
     ScanArgs sa{bytes, offsets, total, n, e->d_counters.p, e->d_tile_first.p, ntiles, tile_bytes, 0, ntiles};
     CU(launch_prepare(sa, e->d_small.p, 32 + 8 * 256, e->sm_count, s)); launches++;   // tile index + zeroed counters and scratch
-    e->tm.scan_variant = use_pair ? 5u : use_rows ? 3u : padded ? (e->ddfa.wide ? 4u : 2u) : 1u;
-    e->tm.scan_row_bytes = row_bytes;
-    e->tm.scan_warps = use_rows ? row_warps : padded ? e->pad_warps : e->geom.nt / 32;
+    e->tm.scan_variant = use_pair ? 5u : use_rows ? 3u : use_stream ? 6u : padded ? (e->ddfa.wide ? 4u : 2u) : 1u;
+    e->tm.scan_row_bytes = use_stream ? e->wide_row : row_bytes;
+    e->tm.scan_warps = use_rows ? row_warps : use_stream ? e->wide_warps : padded ? e->pad_warps : e->geom.nt / 32;
     if (ntiles && chunked) {
         // scan of chunk i behind the copy of chunk i: the kernel walks the tiles of the part that has arrived
         CU(e->d_tilectr.ensure(plan->n_chunks));
@@ -421,6 +438,7 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
         CU(cudaEventRecord(e->ev[1], s));
         if (use_pair) CU(launch_scan_pair(sa, e->ddfa, row_warps, row_bytes, e->d_small.p + 20, e->sm_count, s));   // d_small[20]: spare word, zeroed by prepare
         else if (use_rows) CU(launch_scan_rows(sa, e->ddfa, row_warps, row_bytes, e->d_small.p + 20, e->sm_count, s));
+        else if (use_stream) CU(launch_scan_stream_wide(sa, e->ddfa, e->wide_warps, e->wide_chains, e->wide_row, e->d_small.p + 20, e->sm_count, s));
         else if (padded) CU(launch_scan_padded(sa, e->ddfa, e->pad_warps, e->sm_count, s));
         else CU(launch_scan(sa, e->ddfa, e->geom, e->sm_count, s));
         launches++;

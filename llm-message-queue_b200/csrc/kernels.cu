@@ -529,6 +529,111 @@ cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, uint32_t n
     }
 }
 
+// ---------------------------------------------------------------- wide format, streamed rows --
+// The wide format's walk is one dependent gather per input byte into a table that lives in L2/L1, so what it needs is
+// gathers in flight and L1 capacity, not staging: here every lane walks N rows of `cl` bytes at once (chains
+// interleaved transition by transition, scan_core.cuh long_stream_n) and reads its bytes straight from global memory,
+// 16 bytes a row at a time.  Shared memory holds the 256-byte class map and one message list per warp, the rest of
+// the SM's 256 KB stays L1 for the table.  Rows cost one 16-byte warm-up per `cl` bytes instead of one per 80.
+// Tiles of 32 * N rows are handed out dynamically.
+constexpr uint32_t kStreamListCap = 98;   // message starts of a tile kept in shared memory (lane, lane + 32, lane + 64)
+template <int NW, int N>
+__global__ void __launch_bounds__(NW * 32, 1) scan_stream_wide_kernel(ScanArgs a, DeviceDfa d, uint32_t cl, uint32_t *__restrict__ tile_counter) {
+    __shared__ uint8_t cls[256];
+    __shared__ int32_t lists[NW][kStreamListCap + 2];
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (uint32_t i = tid; i < 256; i += NW * 32) cls[i] = d.cls_of[i];
+    __syncthreads();   // the only CTA-wide barrier
+
+    const uint32_t nwarps = gridDim.x * NW, t_end = a.tile_end;
+    uint32_t t = a.tile_begin + blockIdx.x * NW + warp;
+    WideCtx c;
+    c.wtbl = d.wtable; c.cls = cls; c.ncls = d.n_classes; c.events = d.events; c.stage = nullptr;
+    c.list_abs = a.offsets; c.counters = a.counters; c.warm = (int32_t)d.warm;
+    c.start_state = d.start_state; c.neutral_state = d.neutral_state;
+    const uint32_t super = 32u * N * cl;
+    int32_t *lst = lists[warp];
+    const uint8_t *limit = a.bytes + a.total;
+
+    while (t < t_end) {
+        const uint64_t ts = (uint64_t)t * super;
+        const uint32_t first = a.tile_first[t], last = a.tile_first[t + 1];
+        const uint32_t cnt = last - first + 2;
+        if (cnt <= kStreamListCap) {
+            for (uint32_t j = lane; j < cnt; j += 32) lst[j] = rel_clamp(a.offsets[first + j], ts);
+        }
+        __syncwarp();
+        c.list = cnt <= kStreamListCap ? lst : nullptr;
+        c.tile_start = (int64_t)ts;
+        c.list_n = cnt; c.msg_lo = first;
+
+        LongLane L[N];
+        const uint8_t *src[N];
+        int32_t pos[N], nb[N];
+        bool all_full = true;
+#pragma unroll
+        for (int ch = 0; ch < N; ch++) {
+            const uint64_t cs = ts + (uint64_t)(ch * 32 + lane) * cl;
+            nb[ch] = cs >= a.total ? 0 : (int32_t)(a.total - cs < cl ? a.total - cs : cl);
+            all_full = all_full && nb[ch] == (int32_t)cl;
+            src[ch] = a.bytes + cs;
+            pos[ch] = (int32_t)(cs - ts);
+            if (nb[ch]) long_begin(c, L[ch], find_msg(c, pos[ch]), cs == 0, cs ? a.bytes + cs - c.warm : a.bytes);
+        }
+        if (all_full) {
+            long_stream_n<N>(c, L, src, pos, (int32_t)cl, limit);
+        } else {   // the arena's last tile: rows cut short (or absent) are walked one at a time
+#pragma unroll
+            for (int ch = 0; ch < N; ch++) {
+                if (!nb[ch]) continue;
+                LongLane L1[1] = {L[ch]};
+                const uint8_t *const s1[1] = {src[ch]};
+                const int32_t p1[1] = {pos[ch]};
+                long_stream_n<1>(c, L1, s1, p1, nb[ch], limit);
+                L[ch] = L1[0];
+            }
+        }
+#pragma unroll
+        for (int ch = 0; ch < N; ch++) {
+            if (!nb[ch]) continue;
+            long_end(c, L[ch]);
+            if (L[ch].head_words) atomicAdd(a.counters + (uint64_t)L[ch].head_msg * CNT_STRIDE + CNT_WORDS, L[ch].head_words);
+        }
+        __syncwarp();   // the list is rewritten for the next tile
+        uint32_t v = 0;
+        if (lane == 0) v = atomicAdd(tile_counter, 1u) + nwarps + a.tile_begin;
+        t = __shfl_sync(0xFFFFFFFFu, v, 0);
+    }
+}
+
+template <int NW, int N>
+static cudaError_t launch_scan_stream_wide_variant(const ScanArgs &a, const DeviceDfa &d, uint32_t cl, uint32_t *tile_counter, int sm_count,
+                                                   cudaStream_t s) {
+    uint32_t need = (a.tile_end - a.tile_begin + NW - 1) / NW;
+    uint32_t grid = need < (uint32_t)sm_count ? need : (uint32_t)sm_count;
+    static bool carveout_set = false;
+    if (!carveout_set) {   // as much L1 as the SM can give: the kernel's shared memory is a few KB
+        cudaFuncSetAttribute(scan_stream_wide_kernel<NW, N>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxL1);
+        carveout_set = true;
+    }
+    scan_stream_wide_kernel<NW, N><<<grid, NW * 32, 0, s>>>(a, d, cl, tile_counter);
+    return cudaGetLastError();
+}
+
+// a.tile_bytes must be 32 * chains * row_bytes (scan_stream_wide_super_bytes)
+cudaError_t launch_scan_stream_wide(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, uint32_t chains, uint32_t row_bytes, uint32_t *tile_counter,
+                                    int sm_count, cudaStream_t s) {
+    if (a.tile_end <= a.tile_begin) return cudaSuccess;
+    if (!d.wide || row_bytes == 0 || (row_bytes & 15u) || a.tile_bytes != 32u * chains * row_bytes) return cudaErrorInvalidValue;
+    if (chains == 1 && nw == 32) return launch_scan_stream_wide_variant<32, 1>(a, d, row_bytes, tile_counter, sm_count, s);
+    if (chains == 2 && nw == 32) return launch_scan_stream_wide_variant<32, 2>(a, d, row_bytes, tile_counter, sm_count, s);
+    if (chains == 2 && nw == 24) return launch_scan_stream_wide_variant<24, 2>(a, d, row_bytes, tile_counter, sm_count, s);
+    if (chains == 3 && nw == 20) return launch_scan_stream_wide_variant<20, 3>(a, d, row_bytes, tile_counter, sm_count, s);
+    if (chains == 4 && nw == 16) return launch_scan_stream_wide_variant<16, 4>(a, d, row_bytes, tile_counter, sm_count, s);
+    if (chains == 4 && nw == 12) return launch_scan_stream_wide_variant<12, 4>(a, d, row_bytes, tile_counter, sm_count, s);
+    return cudaErrorInvalidValue;
+}
+
 // ---------------------------------------------------------------------------------- row lanes --
 // Padded arena, dense table, long lanes fed by the TMA: the arena is viewed as a matrix of LANE-byte rows, lane l
 // of a warp owns row 32 * tile + l, and ONE tensor copy per warp and window brings the next 80-byte window of all 32
@@ -664,7 +769,7 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
     __syncthreads();   // the only CTA-wide barrier
 
     // Tiles are handed out dynamically: the first one per warp by position, every further one from a global counter
-    // (zeroed by prepare_kernel), fetched two tiles ahead so that the next tile's message list and first window can be
+    // (zeroed by prepare_kernel), fetched one tile ahead so that the next tile's message list and first window can be
     // prefetched while the current one is walked.
     // One launch walks the tiles [a.tile_begin, t_end): the whole arena, or the part of it that has already arrived when
     // the upload is pipelined chunk by chunk (engine.cu, submit from host buffers).
@@ -686,7 +791,7 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
         if (w == 0) tma_load_2d(warm_buf, &tm_warm, CL - 16, row0 - 1, &bars[buf]);
     };
 
-    uint32_t t = t0, t_nxt = grab(), t_nn = grab();
+    uint32_t t = t0, t_nxt = grab();
     uint32_t first_cur = a.tile_first[t0], last_cur = a.tile_first[t0 + 1];
     if (lane == 0) issue(t0, 0, 0);
     uint64_t ts = (uint64_t)t0 * SUPER;
@@ -698,7 +803,6 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
         }
     }
     uint32_t first_nxt = 0, last_nxt = 0;
-    if (t_nxt < t_end) { first_nxt = a.tile_first[t_nxt]; last_nxt = a.tile_first[t_nxt + 1]; }
     __syncwarp();
 
     LaneCtx c;
@@ -714,14 +818,14 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
         const bool has_next = t_nxt < t_end;
         ts = (uint64_t)t * SUPER;
         uint64_t n0 = 0, n1 = 0;
-        uint32_t cnt_nxt = 0, first_nn = 0, last_nn = 0;
+        uint32_t cnt_nxt = 0;
         if (has_next) {
+            first_nxt = a.tile_first[t_nxt]; last_nxt = a.tile_first[t_nxt + 1];
             cnt_nxt = last_nxt - first_nxt + 2;
             if (cnt_nxt <= kRowListCap) {
                 if (lane < cnt_nxt) n0 = a.offsets[first_nxt + lane];
                 if (lane + 32 < cnt_nxt) n1 = a.offsets[first_nxt + lane + 32];
             }
-            if (t_nn < t_end) { first_nn = a.tile_first[t_nn]; last_nn = a.tile_first[t_nn + 1]; }
         }
         const uint32_t cnt_cur = last_cur - first_cur + 2;
         const int32_t *lst = list_base + (sk & 1) * kRowListCap;
@@ -803,9 +907,8 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_rows_kernel(ScanArgs a, Devic
             if (lane + 32 < cnt_nxt) ln[lane + 32] = rel_clamp(n1, tsn);
         }
         first_cur = first_nxt; last_cur = last_nxt;
-        first_nxt = first_nn; last_nxt = last_nn;
-        t = t_nxt; t_nxt = t_nn;
-        t_nn = t_nxt < t_end ? grab() : t_nxt;   // warp-uniform: no more fetches once the counter has run past the end
+        t = t_nxt;
+        t_nxt = t < t_end ? grab() : t;   // one tile ahead only: a tile a warp has claimed cannot be taken over by an idle one (warp-uniform: no more fetches past the end)
         __syncwarp();
     }
     queue.flush(c, lane, true);
@@ -905,7 +1008,7 @@ __host__ __device__ inline PairSmem pair_layout(uint32_t f_states, uint32_t x_st
     L.warp_a = o;
     L.n_a = o <= L.table ? (L.table - o) / L.warp_bytes : 0u;
     if (L.n_a > nw) L.n_a = nw;
-    L.warp_b = L.table + f_states * 256u;
+    L.warp_b = L.table + ((f_states * kPairRowBytes + 127u) / 128u) * 128u;
     L.total = o <= L.table ? L.warp_b + (nw - L.n_a) * L.warp_bytes : 0xFFFFFFFFu;   // (no room before the table: no such launch)
     return L;
 }
@@ -981,7 +1084,7 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, Devic
     {
         const uint32_t *src = reinterpret_cast<const uint32_t *>(d.ftable);
         uint32_t *dst = reinterpret_cast<uint32_t *>(tbl);
-        for (uint32_t i = tid; i < d.f_states * 64u; i += NW * 32) dst[i] = src[i];
+        for (uint32_t i = tid; i < d.f_states * 64u; i += NW * 32) dst[(i >> 6) * (kPairRowBytes / 4) + (i & 63u)] = src[i];   // rows of 260 bytes: row r starts at bank r mod 32
         uint16_t *xd = reinterpret_cast<uint16_t *>(smem + L.xtable);
         for (uint32_t i = tid; i < d.n_states * d.n_cmp; i += NW * 32) xd[i] = d.ctable[i];
         for (uint32_t i = tid; i < 256; i += NW * 32) smem[L.xcls + i] = d.ccls[i];
@@ -1004,7 +1107,7 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, Devic
         if (w == 0) tma_load_2d(warm_buf, &tm_warm, CL - 16, row0 - 1, &bars[buf]);
     };
 
-    uint32_t t = t0, t_nxt = grab(), t_nn = grab();
+    uint32_t t = t0, t_nxt = grab();
     uint32_t first_cur = a.tile_first[t0], last_cur = a.tile_first[t0 + 1];
     if (lane == 0) issue(t0, 0, 0);
     uint64_t ts = (uint64_t)t0 * SUPER;
@@ -1016,7 +1119,6 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, Devic
         }
     }
     uint32_t first_nxt = 0, last_nxt = 0;
-    if (t_nxt < t_end) { first_nxt = a.tile_first[t_nxt]; last_nxt = a.tile_first[t_nxt + 1]; }
     __syncwarp();
 
     PairCtx c;
@@ -1036,14 +1138,14 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, Devic
         const bool has_next = t_nxt < t_end;
         ts = (uint64_t)t * SUPER;
         uint64_t n0 = 0, n1 = 0;
-        uint32_t cnt_nxt = 0, first_nn = 0, last_nn = 0;
+        uint32_t cnt_nxt = 0;
         if (has_next) {
+            first_nxt = a.tile_first[t_nxt]; last_nxt = a.tile_first[t_nxt + 1];
             cnt_nxt = last_nxt - first_nxt + 2;
             if (cnt_nxt <= kRowListCap) {
                 if (lane < cnt_nxt) n0 = a.offsets[first_nxt + lane];
                 if (lane + 32 < cnt_nxt) n1 = a.offsets[first_nxt + lane + 32];
             }
-            if (t_nn < t_end) { first_nn = a.tile_first[t_nn]; last_nn = a.tile_first[t_nn + 1]; }
         }
         const uint32_t cnt_cur = last_cur - first_cur + 2;
         const int32_t *lst = list_base + (sk & 1) * kRowListCap;
@@ -1055,7 +1157,8 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, Devic
         const uint64_t row_start = (uint64_t)row * CL;
         const bool tail_row = row == nrows_full && row_start < a.total;
 
-        const bool all_full = (uint64_t)t * 32 + 32 <= nrows_full;   // warp-uniform: every lane of this tile owns a full row
+        uint32_t all_full = (uint64_t)t * 32 + 32 <= nrows_full ? 1u : 0u;   // warp-uniform: every lane of this tile owns a full row
+        asm volatile("" : "+r"(all_full));                                    // (kept in a register: not recomputed every window)
         PairLane P;
         uint32_t km = 0;
         if (full_row || tail_row) {
@@ -1124,9 +1227,8 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, Devic
             if (lane + 32 < cnt_nxt) ln[lane + 32] = rel_clamp(n1, tsn);
         }
         first_cur = first_nxt; last_cur = last_nxt;
-        first_nxt = first_nn; last_nxt = last_nn;
-        t = t_nxt; t_nxt = t_nn;
-        t_nn = t_nxt < t_end ? grab() : t_nxt;
+        t = t_nxt;
+        t_nxt = t < t_end ? grab() : t;   // one tile ahead only: a tile a warp has claimed cannot be taken over by an idle one (warp-uniform: no more fetches past the end)
         __syncwarp();
     }
     queue.flush(c, lane);

@@ -71,6 +71,9 @@ cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw,
 
 // pair-lane variant of the row scan (filter automaton over class pairs + SIMD word count + exact walk of flagged groups)
 size_t scan_pair_smem_bytes(const DeviceDfa &d, uint32_t nw);
+// wide format, rows streamed from global memory, `chains` rows per lane (tile = 32 * chains * row_bytes bytes)
+cudaError_t launch_scan_stream_wide(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, uint32_t chains, uint32_t row_bytes, uint32_t *tile_counter,
+                                    int sm_count, cudaStream_t s);
 uint32_t pick_pair_warps(const DeviceDfa &d, size_t max_smem);   // 0: this dictionary / automaton cannot use it
 cudaError_t launch_scan_pair(const ScanArgs &a, const DeviceDfa &d, uint32_t nw, uint32_t lane_bytes, uint32_t *tile_counter, int sm_count,
                              cudaStream_t s);

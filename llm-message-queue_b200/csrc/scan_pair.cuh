@@ -28,9 +28,11 @@
 
 namespace triage {
 
-// The device keeps the filter table at this shared-memory address: low 16 bits zero, so state << 8 | class pair (one byte
-// permute) plus an immediate offset is the address of an entry.
+// The device keeps the filter table at this shared-memory address, so that the address of an entry is one multiply-add
+// plus an immediate: state * kPairRowBytes + class pair.  Rows are 260 bytes apart: row r starts at bank r mod 32, lanes in
+// different states that read the same class pair do not collide.
 constexpr uint32_t kPairTableShared = 0x10000u;
+constexpr uint32_t kPairRowBytes = 260u;
 
 struct PairCtx {
     const uint8_t *ftbl;        // filter table, Moore form: 256 next states per state (host; the device reads kPairTableShared)
@@ -54,7 +56,7 @@ struct PairCtx {
 TR_HD uint32_t pr_fnext(const PairCtx &c, uint32_t pairs, uint32_t f, uint32_t k) {
 #if defined(__CUDA_ARCH__)
     uint32_t v;
-    asm("ld.shared.u8 %0, [%1+65536];" : "=r"(v) : "r"(__byte_perm(pairs, f, 0x5540u | k)));
+    asm("ld.shared.u8 %0, [%1+65536];" : "=r"(v) : "r"(f * kPairRowBytes + __byte_perm(pairs, 0u, 0x4440u | k)));
     return v;
 #else
     return c.ftbl[(f << 8) | ((pairs >> (8 * k)) & 0xFFu)];
@@ -230,59 +232,95 @@ TR_HD uint32_t pair_filter16(const PairCtx &c, const Quad &q, uint32_t &f) {
     return m;
 }
 
-// NG 16-byte groups at tile-relative position pos.  P.prevq holds the 16 bytes before win[0] (they may no longer be
-// readable where they came from).  Returns how many groups went to the sink.
+// byte k of v
+TR_HD uint32_t pr_byte(uint32_t v, uint32_t k) {
+#if defined(__CUDA_ARCH__)
+    return __byte_perm(v, 0u, 0x4440u | k);
+#else
+    return (v >> (8 * k)) & 0xFFu;
+#endif
+}
+
+// NG (<= 5) 16-byte groups at tile-relative position pos.  P.prevq holds the 16 bytes before win[0] (they may no longer
+// be readable where they came from).  Returns how many groups went to the sink.
+// The groups are scanned without a branch; what the window leaves behind is small: `flags` (bit g: the filter fired in
+// group g), the running count of word starts after each group (four of them packed into `cum`, the last one `total`) and
+// `hi`.  Windows where nothing fired, no byte is >= 0x80 and no message ends add `total` and are done; the others visit
+// only the groups that need a look (message boundary, flagged), unless bytes >= 0x80 make every group one.
 template <bool SIMPLE, int NG, class Ctx, class Sink>
 TR_HD uint32_t pair_window(const Ctx &c, PairLane &P, const Quad *win, int32_t pos, Sink &sink) {
-    uint32_t st[NG], fm[NG], hi = 0, f = P.f, pns = P.prev_ns, top = 0;
+    static_assert(NG >= 1 && NG <= 5, "the running counts of the first NG - 1 groups share one register");
+    uint32_t hi = 0, f = P.f, pns = P.prev_ns, flags = 0, cum = 0, total = 0;
 #ifdef __CUDA_ARCH__
 #pragma unroll
 #endif
     for (int g = 0; g < NG; g++) {
         const Quad q = win[g];
-        st[g] = pair_starts16<false>(q, pns);
-        fm[g] = pair_filter16<SIMPLE>(c, q, f);
-        top = pr_max(top, fm[g]);
+        total += pr_popc(pair_starts16<false>(q, pns));
+        if (g < NG - 1) cum |= total << (8 * g);
+        if (pair_filter16<SIMPLE>(c, q, f) >= c.ffired) flags |= 1u << g;
         hi |= q.a | q.b | q.c | q.d;
     }
     P.f = f;
     hi &= 0x80808080u;
-    if (top < c.ffired && !hi && !P.prev_rare && pos + 16 * (NG - 1) < P.L.mend) {
-        uint32_t n = 0;                                          // two groups' bit sets share a word: 4 + 4 bits a byte
-#ifdef __CUDA_ARCH__
-#pragma unroll
-#endif
-        for (int g = 0; g + 1 < NG; g += 2) n += pr_popc(st[g] + (st[g + 1] >> 4));
-        if (NG & 1) n += pr_popc(st[NG - 1]);
-        P.L.words += n;
+    const Quad last = win[NG - 1];
+    if (!flags && !hi && !P.prev_rare && pos + 16 * (NG - 1) < P.L.mend) {
+        P.L.words += total;
         P.prev_ns = pns;
-        P.prevq = win[NG - 1];
+        P.prevq = last;
         return 0;
     }
-    if (hi) {   // bytes >= 0x80 in the window: the word starts again, with the compares that are exact for them
+    uint32_t pushed = 0;
+    if (hi) {   // bytes >= 0x80 in the window: every group is looked at, word starts with the compares that are exact for them
         pns = P.prev_ns;
 #ifdef __CUDA_ARCH__
-#pragma unroll
+#pragma unroll 1
 #endif
-        for (int g = 0; g < NG; g++) st[g] = pair_starts16<true>(win[g], pns);
+        for (int g = 0; g < NG; g++) {
+            long_boundary(c, P.L, pos + 16 * g);
+            const Quad q = win[g];
+            const uint32_t n = pr_popc(pair_starts16<true>(q, pns));
+            const uint32_t rare = pr_special(q);
+            if (((flags >> g) & 1u) || rare || P.prev_rare) {
+                sink.push(c, g ? win[g - 1] : P.prevq, q, P.L.msg);
+                pushed++;
+            } else {
+                P.L.words += n;
+            }
+            P.prev_rare = rare;
+        }
+    } else {
+        uint32_t need = flags | (P.prev_rare ? 1u : 0u), done = 0;
+        {
+            const int32_t gb = (P.L.mend - pos) >> 4;              // first group of the next message, if it is in this window
+            if (gb < NG) need |= 1u << (gb < 0 ? 0 : gb);
+        }
+        while (need) {
+#if defined(__CUDA_ARCH__)
+            const uint32_t g = (uint32_t)__ffs((int)need) - 1u;
+#else
+            const uint32_t g = (uint32_t)__builtin_ctz(need);
+#endif
+            need &= need - 1u;
+            const uint32_t before = g ? pr_byte(cum, g - 1) : 0u;   // word starts of the groups before g
+            P.L.words += before - done;
+            done = before;
+            if (pos + 16 * (int32_t)g >= P.L.mend) {
+                long_boundary(c, P.L, pos + 16 * (int32_t)g);
+                const int32_t gb = (P.L.mend - pos) >> 4;          // short messages: the next one may end in this window too
+                if (gb < NG) need |= 1u << gb;
+            }
+            if (((flags >> g) & 1u) || (g == 0 && P.prev_rare)) {
+                sink.push(c, g ? win[g - 1] : P.prevq, win[g], P.L.msg);
+                pushed++;
+                done = g + 1u < (uint32_t)NG ? pr_byte(cum, g) : total;   // its word starts come from the exact walk
+            }
+        }
+        P.L.words += total - done;
+        P.prev_rare = 0;
     }
     P.prev_ns = pns;
-    uint32_t pushed = 0;
-#ifdef __CUDA_ARCH__
-#pragma unroll
-#endif
-    for (int g = 0; g < NG; g++) {
-        long_boundary(c, P.L, pos + 16 * g);
-        const uint32_t rare = hi ? pr_special(win[g]) : 0u;
-        if (fm[g] >= c.ffired || rare || P.prev_rare) {
-            sink.push(c, g ? win[g - 1] : P.prevq, win[g], P.L.msg);
-            pushed++;
-        } else {
-            P.L.words += pr_popc(st[g]);
-        }
-        P.prev_rare = rare;
-    }
-    P.prevq = win[NG - 1];
+    P.prevq = last;
     return pushed;
 }
 
