@@ -346,7 +346,7 @@ int32_t commit_dict(triage_engine *e) {
         // (32, 32|24, 20, 16|12 warps: registers), TRIAGE_WIDE_ROW = row length in bytes (multiple of 16)
         const char *sv = getenv("TRIAGE_WIDE_STREAM");
         if (!sv || atoi(sv) != 0) {
-            uint32_t ch = 2, nw = 32, row = 160;
+            uint32_t ch = 1, nw = 32, row = 320;   // measured best on the 10 000-keyword set (more chains per lane thrash L1: DESIGN.md 4.1b)
             if (const char *v = getenv("TRIAGE_WIDE_CHAINS")) { uint32_t x = (uint32_t)atoi(v); if (x >= 1 && x <= 4) ch = x; }
             nw = ch <= 2 ? 32 : ch == 3 ? 20 : 16;
             if (const char *v = getenv("TRIAGE_WIDE_WARPS")) { uint32_t x = (uint32_t)atoi(v); if ((ch == 2 && x == 24) || (ch == 4 && x == 12)) nw = x; }

@@ -145,6 +145,11 @@ TR_HD uint32_t find_msg_from(const LaneCtx &c, int32_t pos, uint32_t k) {
 }
 
 // ------------------------------------------------------------------------------------------- group code ---
+// Formats whose walk is bound by the latency of the table reads and whose traffic is event-dense (the wide format:
+// thousands of keywords) apply an event where it is met instead of re-walking the half group afterwards: one test per
+// transition costs less there than eight more dependent reads per event.  Specialised next to the format's context.
+template <class Ctx> struct InlineEvents { static constexpr bool value = false; };
+
 #define TR_STEP(wd, k)                                                                      \
     e = tr_next(c, wd, e, k); words += tr_ws(c, e); ev |= e;
 #define TR_STEP4(wd) TR_STEP(wd, 0) TR_STEP(wd, 1) TR_STEP(wd, 2) TR_STEP(wd, 3)
@@ -175,6 +180,7 @@ TR_HD void half8_events(const Ctx &c, uint32_t wa, uint32_t wb, uint32_t &e, uin
 // counts of the fast pass stand, the replay only applies the events)
 template <class Ctx>
 TR_HD void group16_counted(const Ctx &c, const Quad &q, uint32_t &e, uint32_t &words, uint32_t msg) {
+    if (InlineEvents<Ctx>::value) { group16_events(c, q, e, words, msg); return; }
     const uint32_t e0 = e;
     uint32_t ev = 0, ev2 = 0;
     TR_STEP4(q.a) TR_STEP4(q.b)
@@ -401,8 +407,18 @@ TR_COLD void replay_half(const Ctx &c, uint32_t wa, uint32_t wb, uint32_t e, uin
         L[ch].e = tr_next(c, q[ch].fld, L[ch].e, k); L[ch].words += tr_ws(c, L[ch].e); EV[ch] |= L[ch].e; }
 #define TR_STEPN4(fld, EV) TR_STEPN(fld, 0, EV) TR_STEPN(fld, 1, EV) TR_STEPN(fld, 2, EV) TR_STEPN(fld, 3, EV)
 
+#define TR_STEPNF(fld, k)                                                                      \
+    _Pragma("unroll") for (int ch = 0; ch < N; ch++) {                                         \
+        L[ch].e = tr_next(c, q[ch].fld, L[ch].e, k); L[ch].words += tr_ws(c, L[ch].e);         \
+        if (L[ch].e & tr_evmask(c)) apply_event(c, tr_evid(c, L[ch].e), L[ch].msg); }
+#define TR_STEPNF4(fld) TR_STEPNF(fld, 0) TR_STEPNF(fld, 1) TR_STEPNF(fld, 2) TR_STEPNF(fld, 3)
+
 template <int N, class Ctx>
 TR_HD void group16_counted_n(const Ctx &c, const Quad (&q)[N], LongLane (&L)[N]) {
+    if (InlineEvents<Ctx>::value) {
+        TR_STEPNF4(a) TR_STEPNF4(b) TR_STEPNF4(c) TR_STEPNF4(d)
+        return;
+    }
     uint32_t e0[N], e8[N], eva[N], evb[N], any = 0;
 #pragma unroll
     for (int ch = 0; ch < N; ch++) { e0[ch] = L[ch].e; eva[ch] = 0; evb[ch] = 0; }

@@ -36,5 +36,6 @@ TR_HD uint32_t tr_ws(const WideCtx &, uint32_t e) { return e >> 31; }
 TR_HD uint32_t tr_evmask(const WideCtx &) { return 0x7FF00000u; }
 TR_HD uint32_t tr_evid(const WideCtx &, uint32_t e) { return (e >> 20) & 0x7FFu; }
 TR_HD void apply_event(const WideCtx &c, uint32_t id, uint32_t msg) { apply_event_raw(c.events, c.counters, id, msg); }
+template <> struct InlineEvents<WideCtx> { static constexpr bool value = true; };
 
 }  // namespace triage
