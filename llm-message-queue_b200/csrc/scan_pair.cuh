@@ -271,7 +271,10 @@ TR_HD uint32_t pair_window(const Ctx &c, PairLane &P, const Quad *win, int32_t p
         return 0;
     }
     uint32_t pushed = 0;
-    if (hi) {   // bytes >= 0x80 in the window: every group is looked at, word starts with the compares that are exact for them
+    if (hi) {   // bytes >= 0x80 in the window: every group is looked at; those that hold such bytes, or follow one that
+                // does, get their word starts from the compares that are exact for them
+        uint32_t done = 0;
+        bool prev_high = false;   // (P.prev_ns, the word before the window, is always exact)
         pns = P.prev_ns;
 #ifdef __CUDA_ARCH__
 #pragma unroll 1
@@ -279,8 +282,16 @@ TR_HD uint32_t pair_window(const Ctx &c, PairLane &P, const Quad *win, int32_t p
         for (int g = 0; g < NG; g++) {
             long_boundary(c, P.L, pos + 16 * g);
             const Quad q = win[g];
-            const uint32_t n = pr_popc(pair_starts16<true>(q, pns));
-            const uint32_t rare = pr_special(q);
+            const uint32_t upto = g + 1 < NG ? pr_byte(cum, (uint32_t)g) : total;
+            const bool high = ((q.a | q.b | q.c | q.d) & 0x80808080u) != 0;
+            uint32_t n = upto - done, rare = 0;
+            done = upto;
+            if (high || prev_high) {
+                if (g) pns = pr_nonspace_any(win[g - 1].d);
+                n = pr_popc(pair_starts16<true>(q, pns));
+                if (high) rare = pr_special(q);
+            }
+            prev_high = high;
             if (((flags >> g) & 1u) || rare || P.prev_rare) {
                 sink.push(c, g ? win[g - 1] : P.prevq, q, P.L.msg);
                 pushed++;
@@ -289,6 +300,7 @@ TR_HD uint32_t pair_window(const Ctx &c, PairLane &P, const Quad *win, int32_t p
             }
             P.prev_rare = rare;
         }
+        pns = pr_nonspace_any(last.d);
     } else {
         uint32_t need = flags | (P.prev_rare ? 1u : 0u), done = 0;
         {
