@@ -487,7 +487,9 @@ def main():
         # charged to the scan by that definition although finalize_kernel moves them; pad bytes and lengths are not counted)
         alg = content_bytes + 8 * (n + 1) + 32 * n
         achieved = alg / (t_scan / 1000) / 1e9
-        traffic = scan_traffic_from_profile() if args.workload == "c2" and last_t["scan_variant"] == 3 else None   # the capture is of that launch
+        traffic = scan_traffic_from_profile()
+        if traffic and not (args.workload == "c2" and traffic.get("scan_variant") == last_t["scan_variant"]):
+            traffic = None      # the capture is of another kernel / workload
         kern = f"{mq._capi.SCAN_VARIANTS.get(last_t['scan_variant'], '?')}, {last_t['scan_warps']} warps per CTA"
         if last_t["scan_row_bytes"]:
             kern += f", {last_t['scan_row_bytes']}-byte rows"

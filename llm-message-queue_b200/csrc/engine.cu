@@ -43,6 +43,7 @@ struct NcclApi {
     void *h = nullptr;
     ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
     ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommInitRankConfig)(ncclComm_t *, int, ncclUniqueId, int, ncclConfig_t *) = nullptr;   // optional (NCCL >= 2.14)
     ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     const char *(*GetErrorString)(ncclResult_t) = nullptr;
@@ -53,6 +54,7 @@ struct NcclApi {
         if (!h) { *err = std::string("dlopen libnccl.so.2: ") + dlerror(); return false; }
         GetUniqueId = reinterpret_cast<decltype(GetUniqueId)>(dlsym(h, "ncclGetUniqueId"));
         CommInitRank = reinterpret_cast<decltype(CommInitRank)>(dlsym(h, "ncclCommInitRank"));
+        CommInitRankConfig = reinterpret_cast<decltype(CommInitRankConfig)>(dlsym(h, "ncclCommInitRankConfig"));
         AllGather = reinterpret_cast<decltype(AllGather)>(dlsym(h, "ncclAllGather"));
         CommDestroy = reinterpret_cast<decltype(CommDestroy)>(dlsym(h, "ncclCommDestroy"));
         GetErrorString = reinterpret_cast<decltype(GetErrorString)>(dlsym(h, "ncclGetErrorString"));
@@ -225,6 +227,7 @@ struct triage_engine {
     bool merge_pending = false;
     // comm
     ncclComm_t comm = nullptr;
+    int comm_sms = 0;              // SMs the persistent scan leaves to the exchange's kernels
     int nranks = 1, rank = 0;
     DevBuf<uint64_t> d_run_keys, d_all_keys, d_header, d_all_header;
     DevBuf<uint32_t> d_run_gidx, d_all_gidx;
@@ -391,7 +394,11 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     const bool chunked = plan && use_rows && plan->n_chunks > 1;
     const bool use_pair = use_rows && e->pair_warps > 0;
     const uint32_t row_warps = use_pair ? e->pair_warps : e->row_warps;
-    const uint32_t row_bytes = use_rows ? scan_rows_lane_bytes(chunked ? kUploadChunk : total, row_warps, e->sm_count) : 0;
+    const uint32_t row_bytes = use_rows ? scan_rows_lane_bytes(chunked ? kUploadChunk : total, row_warps, e->sm_count, use_pair) : 0;
+    // With a communicator the exchange of step k runs on a second stream under the scan of step k+1, and the scan is one
+    // persistent CTA per SM that fills the SM: the exchange's kernels would only get an SM when a scan ends.  A few SMs are
+    // left to them (triage_comm_init: TRIAGE_COMM_SMS, default 4).
+    const int scan_sms = e->sm_count - (e->comm ? e->comm_sms : 0);
     const uint32_t stream_tile = 32u * e->wide_chains * e->wide_row;
     const bool use_stream = padded && e->wide_chains > 0 && total >= 4ull * stream_tile;   // wide dictionaries: rows streamed from global memory
     const uint32_t tile_bytes = !padded ? e->geom.tile
@@ -428,18 +435,18 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
             sa.tile_end = std::min<uint64_t>(ntiles, (uint64_t)(c + 1) * tiles_per_chunk);
             if (sa.tile_begin >= sa.tile_end) break;
             CU(cudaStreamWaitEvent(s, plan->chunk_ev[c], 0));
-            if (use_pair) CU(launch_scan_pair(sa, e->ddfa, row_warps, row_bytes, e->d_tilectr.p + c, e->sm_count, s));
-            else CU(launch_scan_rows(sa, e->ddfa, row_warps, row_bytes, e->d_tilectr.p + c, e->sm_count, s));
+            if (use_pair) CU(launch_scan_pair(sa, e->ddfa, row_warps, row_bytes, e->d_tilectr.p + c, scan_sms, s));
+            else CU(launch_scan_rows(sa, e->ddfa, row_warps, row_bytes, e->d_tilectr.p + c, scan_sms, s));
             launches++;
         }
         CU(cudaStreamWaitEvent(s, plan->all_ready, 0));
     } else if (ntiles) {
         if (plan) CU(cudaStreamWaitEvent(s, plan->all_ready, 0));
         CU(cudaEventRecord(e->ev[1], s));
-        if (use_pair) CU(launch_scan_pair(sa, e->ddfa, row_warps, row_bytes, e->d_small.p + 20, e->sm_count, s));   // d_small[20]: spare word, zeroed by prepare
-        else if (use_rows) CU(launch_scan_rows(sa, e->ddfa, row_warps, row_bytes, e->d_small.p + 20, e->sm_count, s));
-        else if (use_stream) CU(launch_scan_stream_wide(sa, e->ddfa, e->wide_warps, e->wide_chains, e->wide_row, e->d_small.p + 20, e->sm_count, s));
-        else if (padded) CU(launch_scan_padded(sa, e->ddfa, e->pad_warps, e->sm_count, s));
+        if (use_pair) CU(launch_scan_pair(sa, e->ddfa, row_warps, row_bytes, e->d_small.p + 20, scan_sms, s));   // d_small[20]: spare word, zeroed by prepare
+        else if (use_rows) CU(launch_scan_rows(sa, e->ddfa, row_warps, row_bytes, e->d_small.p + 20, scan_sms, s));
+        else if (use_stream) CU(launch_scan_stream_wide(sa, e->ddfa, e->wide_warps, e->wide_chains, e->wide_row, e->d_small.p + 20, scan_sms, s));
+        else if (padded) CU(launch_scan_padded(sa, e->ddfa, e->pad_warps, scan_sms, s));
         else CU(launch_scan(sa, e->ddfa, e->geom, e->sm_count, s));
         launches++;
     } else {
@@ -1479,7 +1486,22 @@ int32_t triage_comm_init(triage_engine *e, int32_t nranks, int32_t rank, const u
     CU(cudaSetDevice(e->opts.device));
     ncclUniqueId u;
     std::memcpy(&u, id, 128);
-    ncclResult_t r = g_nccl.CommInitRank(&e->comm, nranks, u, rank);
+    // The exchange runs on a second stream under the next step's scan, and the scan is one persistent CTA per SM: every SM
+    // a collective's CTAs hold is an SM whose scan CTA starts late.  The order all-gather is small (4 bytes a message),
+    // so the communicator is capped at a few CTAs (TRIAGE_NCCL_CTAS, 0 = NCCL's own choice).
+    int ctas = 4;
+    if (const char *v = getenv("TRIAGE_NCCL_CTAS")) ctas = atoi(v);
+    e->comm_sms = 4;
+    if (const char *v = getenv("TRIAGE_COMM_SMS")) { int x = atoi(v); if (x >= 0 && x <= 32) e->comm_sms = x; }
+    ncclResult_t r;
+    if (g_nccl.CommInitRankConfig && ctas > 0) {
+        ncclConfig_t cfg = NCCL_CONFIG_INITIALIZER;
+        cfg.minCTAs = 1;
+        cfg.maxCTAs = ctas;
+        r = g_nccl.CommInitRankConfig(&e->comm, nranks, u, rank, &cfg);
+    } else {
+        r = g_nccl.CommInitRank(&e->comm, nranks, u, rank);
+    }
     if (r != ncclSuccess) return fail(TRIAGE_E_CUDA, std::string("ncclCommInitRank: ") + g_nccl.GetErrorString(r));
     e->nranks = nranks;
     e->rank = rank;

@@ -650,7 +650,9 @@ constexpr uint32_t kRowWin = 80, kRowLaneLong = 1280, kRowLaneMid = 640, kRowLan
 __host__ __device__ constexpr uint32_t row_win(uint32_t) { return kRowWin; }
 // Longest row that still leaves every warp several tiles: tiles are handed out dynamically, so the kernel's tail is
 // half a tile per warp on average (1280-byte rows: 40 KB tiles, 0.955 ms on the 2.3 GB bench arena; 640: 0.98; 320: 1.03).
-uint32_t scan_rows_lane_bytes(uint64_t total, uint32_t nw, int sm_count) {
+// pair: the two-bytes-per-lookup lanes, whose tiles vary more in duration (flagged groups): 640-byte rows at most
+// (2.29 GB: 1280 -> 0.923 ms, 640 -> 0.880).
+uint32_t scan_rows_lane_bytes(uint64_t total, uint32_t nw, int sm_count, bool pair) {
     if (const char *v = getenv("TRIAGE_ROW_BYTES")) {   // test / tuning knob: force a row length
         const uint32_t want = (uint32_t)atoi(v);
         if ((want == kRowLaneLong || want == kRowLaneMid || want == kRowLaneShort) && total >= want) return want;
@@ -658,7 +660,7 @@ uint32_t scan_rows_lane_bytes(uint64_t total, uint32_t nw, int sm_count) {
     const uint64_t warp_rows = (uint64_t)nw * (uint32_t)sm_count * 32;   // rows one round of tiles covers
     // measured on one box: 2.29 GB (16 tiles of 40 KB per warp) 1280 -> 0.955 ms, 640 -> 0.98, 320 -> 1.03; 1.69 GB mixed
     // lengths 0.783 / 0.778 / 0.810; 1.34 GB of 32-128 KB payloads 0.680 / 0.608 / 0.601; 575 MB 2.39 / 2.43 / 2.31 TB/s
-    if (total >= 12 * warp_rows * kRowLaneLong) return kRowLaneLong;
+    if (!pair && total >= 12 * warp_rows * kRowLaneLong) return kRowLaneLong;
     if (total >= 3 * warp_rows * kRowLaneMid) return kRowLaneMid;
     return kRowLaneShort;
 }
@@ -984,8 +986,8 @@ cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw,
 // bytes), word starts are counted by SIMD-in-register compares, and the groups the filter flags (or that hold bytes >=
 // 0x80) are queued per warp - (message, the 16 bytes before, the 16 bytes) - and walked through the exact automaton in
 // global memory by the whole warp, one queued group per lane.
-constexpr uint32_t kPairQueueCap = 32;     // flagged groups per warp (36 bytes each)
-constexpr uint32_t kPairQueueFlush = 20;   // walked by the whole warp once this many wait (more can arrive in one window: those beyond the cap are walked by their own lane)
+constexpr uint32_t kPairQueueCap = 64;     // flagged groups per warp: (message, arena position / 16 | "words too" << 31), 8 bytes each
+constexpr uint32_t kPairQueueFlush = 32;   // walked by the whole warp, one group per lane, once this many wait (more can arrive in one window: those beyond the cap are walked by their own lane)
 // Shared-memory layout.  The filter table sits at the shared address kPairTableShared (scan_pair.cuh: its entries are
 // then addressed by a byte permute and an immediate); the kernel's dynamic shared memory starts at kPairSmemBase (the
 // first KB of the window is reserved by the system - the kernel checks), so the table is at offset 0xFC00 and the other
@@ -998,7 +1000,7 @@ __host__ __device__ inline PairSmem pair_layout(uint32_t f_states, uint32_t x_st
     L.warp_bytes = L.warm_off + 512;
     L.list_off = 0;
     L.queue_off = 2 * 4 * kRowListCap;
-    L.aux_bytes = ((L.queue_off + 4 + 36 * kPairQueueCap + 15u) / 16u) * 16u;
+    L.aux_bytes = ((L.queue_off + 8 + 8 * kPairQueueCap + 15u) / 16u) * 16u;
     uint32_t o = 1024;   // mbarriers
     L.xtable = o; o += ((x_states * x_cls * 2u + 127u) / 128u) * 128u;   // exact automaton, column-merged: flagged groups only
     L.xcls = o; o += 256u;
@@ -1015,8 +1017,7 @@ __host__ __device__ inline PairSmem pair_layout(uint32_t f_states, uint32_t x_st
 size_t scan_pair_smem_bytes(const DeviceDfa &d, uint32_t nw) { return pair_layout(d.f_states, d.n_states, d.n_cmp, nw).total; }
 uint32_t pick_pair_warps(const DeviceDfa &d, size_t max_smem) {
     if (!d.has_filter || d.wide || d.warm != 16 || d.reset_pad < 0) return 0;
-    // opt-in (TRIAGE_PAIR=1): on the benchmark set the one-lookup-per-byte row lanes are still the faster kernel
-    { const char *v = getenv("TRIAGE_PAIR"); if (!v || atoi(v) == 0) return 0; }
+    if (const char *v = getenv("TRIAGE_PAIR")) { if (atoi(v) == 0) return 0; }   // measurement knob: keep to the one-lookup-per-byte lanes
     if (const char *w = getenv("TRIAGE_PAIR_WARPS")) {
         uint32_t nw = (uint32_t)atoi(w);
         if ((nw == 16 || nw == 20 || nw == 24 || nw == 28) && scan_pair_smem_bytes(d, nw) <= max_smem) return nw;
@@ -1027,28 +1028,32 @@ uint32_t pick_pair_warps(const DeviceDfa &d, size_t max_smem) {
 }
 
 struct PairEventQueue {
-    uint32_t base_s;   // shared address: count word, then 36-byte slots (message, 4 words before, 4 words of the group)
-    __device__ __forceinline__ void push(const PairCtx &c, const Quad &warm, const Quad &q, uint32_t msg) {
-        uint32_t slot = kPairQueueCap;
+    uint32_t base_s;   // shared address: count word (+ 4 bytes of padding), then 8-byte slots
+    int64_t tile_start;
+    // the bytes are not copied: the flush reads the group and the 16 bytes before it back from the arena (L2)
+    __device__ __forceinline__ void push(const PairCtx &c, const Quad &, const Quad &, uint32_t msg, int32_t pos, bool count_words) {
+        const uint32_t where = (uint32_t)((uint64_t)(tile_start + pos) >> 4) | (count_words ? 0x80000000u : 0u);
+        uint32_t slot;
         asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(slot) : "r"(base_s) : "memory");
-        if (slot < kPairQueueCap) {
-            const uint32_t at = base_s + 4 + slot * 36;
-            const uint32_t v[9] = {msg, warm.a, warm.b, warm.c, warm.d, q.a, q.b, q.c, q.d};   // 36-byte slots: 32-bit accesses, conflict-free
-#pragma unroll
-            for (int k = 0; k < 9; k++) asm volatile("st.shared.u32 [%0], %1;" ::"r"(at + 4 * k), "r"(v[k]) : "memory");
-        } else {
-            pair_replay(c, warm, q, msg);   // queue full: walk it now
-        }
+        if (slot < kPairQueueCap) asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(base_s + 8 + slot * 8), "r"(msg), "r"(where) : "memory");
+        else walk(c, msg, where);   // queue full: walk it now
+    }
+    static __device__ __noinline__ void walk(const PairCtx &c, uint32_t msg, uint32_t where) {
+        const uint64_t at = (uint64_t)(where & 0x7FFFFFFFu) << 4;
+        uint4 w = make_uint4(c.pad4, c.pad4, c.pad4, c.pad4);
+        if (at) w = __ldg(reinterpret_cast<const uint4 *>(c.arena + at - 16));
+        const uint4 q = __ldg(reinterpret_cast<const uint4 *>(c.arena + at));
+        const uint32_t v[8] = {w.x, w.y, w.z, w.w, q.x, q.y, q.z, q.w};
+        pair_replay_words(c, [&](int i) { return v[i]; }, msg, (where >> 31) != 0);
     }
     __device__ __noinline__ void flush(const PairCtx &c, uint32_t lane) {
         uint32_t n;
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(n) : "r"(base_s) : "memory");
         if (n > kPairQueueCap) n = kPairQueueCap;
-        if (lane < n) {
-            const uint32_t at = base_s + 4 + lane * 36;
-            uint32_t msg;
-            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(msg) : "r"(at) : "memory");
-            pair_replay_words(c, [&](int i) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(at + 4 + 4 * i) : "memory"); return v; }, msg);
+        for (uint32_t k = lane; k < n; k += 32) {
+            uint32_t msg, where;
+            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(msg), "=r"(where) : "r"(base_s + 8 + k * 8) : "memory");
+            walk(c, msg, where);
         }
         __syncwarp();
         if (lane == 0) asm volatile("st.shared.u32 [%0], %1;" ::"r"(base_s), "r"(0u) : "memory");
@@ -1127,7 +1132,7 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, Devic
     c.xtbl_s = smem_u32(smem + L.xtable); c.xcls_s = smem_u32(smem + L.xcls);
     c.events = d.events; c.neutral_state = d.neutral_state;
     c.pad4 = 0x01010101u * (uint32_t)(d.reset_pad & 0xFF);
-    c.list_abs = a.offsets; c.counters = a.counters;
+    c.list_abs = a.offsets; c.counters = a.counters; c.arena = a.bytes;
     Quad padq;
     padq.a = padq.b = padq.c = padq.d = c.pad4;
     const int32_t chunk = (int32_t)(lane * CL);
@@ -1151,6 +1156,7 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, Devic
         const int32_t *lst = list_base + (sk & 1) * kRowListCap;
         c.list = cnt_cur <= kRowListCap ? lst : nullptr;
         c.tile_start = (int64_t)ts;
+        queue.tile_start = (int64_t)ts;
         c.list_n = cnt_cur; c.msg_lo = first_cur;
         const uint32_t row = t * 32 + lane;
         const bool full_row = row < nrows_full;

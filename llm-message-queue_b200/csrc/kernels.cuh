@@ -61,7 +61,7 @@ cudaError_t launch_scan_padded(const ScanArgs &a, const DeviceDfa &d, uint32_t n
 
 // row-lane variant of the padded scan (dense table, 16-byte warm-up): rows of 1280 / 640 / 320 bytes fed by 2-D TMA tile copies
 size_t scan_rows_smem_bytes(const DeviceDfa &d, uint32_t nw);
-uint32_t scan_rows_lane_bytes(uint64_t total, uint32_t nw, int sm_count);   // row length for an arena of that size (1280, 640 or 320)
+uint32_t scan_rows_lane_bytes(uint64_t total, uint32_t nw, int sm_count, bool pair = false);   // row length for an arena of that size (1280, 640 or 320)
 uint32_t scan_rows_super_bytes(uint32_t lane_bytes);
 uint32_t pick_row_warps(const DeviceDfa &d, size_t max_smem);   // 0: this automaton cannot use it
 bool scan_rows_usable(const ScanArgs &a);

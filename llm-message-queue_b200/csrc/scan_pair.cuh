@@ -50,6 +50,7 @@ struct PairCtx {
     int64_t tile_start;
     uint32_t list_n, msg_lo;
     uint32_t *counters;
+    const uint8_t *arena;       // device: the arena (a queued group is read back from it when it is walked)
 };
 
 // f: a filter state (upper bytes zero); k: which byte of `pairs` holds the class pair (0 or 2)
@@ -136,8 +137,10 @@ struct PairLane {
 // The exact walk of one flagged group: state from the 16 bytes before it, then words and events of its 16 bytes.
 // load(i): word i of the 32 bytes (0..3 the bytes before, 4..7 the group).  Rolled by word: it runs for one group in a
 // hundred, its code should not push the scan loop out of the instruction cache.
+// count_words: the group's word starts come from this walk too (groups with, or right after, the special lead bytes);
+// otherwise the SIMD count of the group stands and only the events are taken.
 template <class Ctx, class Load>
-TR_HD void pair_replay_words(const Ctx &c, Load load, uint32_t msg) {
+TR_HD void pair_replay_words(const Ctx &c, Load load, uint32_t msg, bool count_words) {
     uint32_t e = c.neutral_state, words = 0;
 #ifdef __CUDA_ARCH__
 #pragma unroll 1
@@ -163,12 +166,12 @@ TR_HD void pair_replay_words(const Ctx &c, Load load, uint32_t msg) {
             if (e & 0x7F00u) apply_event_raw(c.events, c.counters, (e >> 8) & 0x7Fu, msg);
         }
     }
-    if (words) tr_add(c.counters + (uint64_t)msg * CNT_STRIDE + CNT_WORDS, words);
+    if (count_words && words) tr_add(c.counters + (uint64_t)msg * CNT_STRIDE + CNT_WORDS, words);
 }
 template <class Ctx>
-TR_COLD void pair_replay(const Ctx &c, Quad warm, Quad q, uint32_t msg) {
+TR_COLD void pair_replay(const Ctx &c, Quad warm, Quad q, uint32_t msg, bool count_words) {
     const uint32_t v[8] = {warm.a, warm.b, warm.c, warm.d, q.a, q.b, q.c, q.d};
-    pair_replay_words(c, [&](int i) { return v[i]; }, msg);
+    pair_replay_words(c, [&](int i) { return v[i]; }, msg, count_words);
 }
 
 // warm: the 16 bytes before the lane's chunk (the reset pad byte x 16 when nothing precedes it: the exact walk then
@@ -264,13 +267,25 @@ TR_HD uint32_t pair_window(const Ctx &c, PairLane &P, const Quad *win, int32_t p
     P.f = f;
     hi &= 0x80808080u;
     const Quad last = win[NG - 1];
-    if (!flags && !hi && !P.prev_rare && pos + 16 * (NG - 1) < P.L.mend) {
+    uint32_t pushed = 0;
+    if (!hi && !P.prev_rare && pos + 16 * (NG - 1) < P.L.mend) {
+        // one message, no byte >= 0x80 in or right before the window: the SIMD counts stand; what the filter flagged is
+        // queued for its events only
         P.L.words += total;
         P.prev_ns = pns;
+        while (flags) {
+#if defined(__CUDA_ARCH__)
+            const uint32_t g = (uint32_t)__ffs((int)flags) - 1u;
+#else
+            const uint32_t g = (uint32_t)__builtin_ctz(flags);
+#endif
+            flags &= flags - 1u;
+            sink.push(c, g ? win[g - 1] : P.prevq, win[g], P.L.msg, pos + 16 * (int32_t)g, false);
+            pushed++;
+        }
         P.prevq = last;
-        return 0;
+        return pushed;
     }
-    uint32_t pushed = 0;
     if (hi) {   // bytes >= 0x80 in the window: every group is looked at; those that hold such bytes, or follow one that
                 // does, get their word starts from the compares that are exact for them
         uint32_t done = 0;
@@ -292,12 +307,12 @@ TR_HD uint32_t pair_window(const Ctx &c, PairLane &P, const Quad *win, int32_t p
                 if (high) rare = pr_special(q);
             }
             prev_high = high;
-            if (((flags >> g) & 1u) || rare || P.prev_rare) {
-                sink.push(c, g ? win[g - 1] : P.prevq, q, P.L.msg);
+            const bool exact_words = rare || P.prev_rare;        // multi-byte whitespace may be in play: words from the walk
+            if (exact_words || ((flags >> g) & 1u)) {
+                sink.push(c, g ? win[g - 1] : P.prevq, q, P.L.msg, pos + 16 * g, exact_words);
                 pushed++;
-            } else {
-                P.L.words += n;
             }
+            if (!exact_words) P.L.words += n;
             P.prev_rare = rare;
         }
         pns = pr_nonspace_any(last.d);
@@ -322,10 +337,11 @@ TR_HD uint32_t pair_window(const Ctx &c, PairLane &P, const Quad *win, int32_t p
                 const int32_t gb = (P.L.mend - pos) >> 4;          // short messages: the next one may end in this window too
                 if (gb < NG) need |= 1u << gb;
             }
-            if (((flags >> g) & 1u) || (g == 0 && P.prev_rare)) {
-                sink.push(c, g ? win[g - 1] : P.prevq, win[g], P.L.msg);
+            const bool exact_words = g == 0 && P.prev_rare;
+            if (exact_words || ((flags >> g) & 1u)) {
+                sink.push(c, g ? win[g - 1] : P.prevq, win[g], P.L.msg, pos + 16 * (int32_t)g, exact_words);
                 pushed++;
-                done = g + 1u < (uint32_t)NG ? pr_byte(cum, g) : total;   // its word starts come from the exact walk
+                if (exact_words) done = g + 1u < (uint32_t)NG ? pr_byte(cum, g) : total;   // its word starts come from the exact walk
             }
         }
         P.L.words += total - done;
@@ -348,7 +364,7 @@ TR_HD void pair_end(const Ctx &c, PairLane &P) { long_end(c, P.L); }
 // sink that walks a flagged group on the spot (host checks, the partial last row)
 struct PairSinkNow {
     template <class Ctx>
-    TR_HD void push(const Ctx &c, const Quad &warm, const Quad &q, uint32_t msg) { pair_replay(c, warm, q, msg); }
+    TR_HD void push(const Ctx &c, const Quad &warm, const Quad &q, uint32_t msg, int32_t, bool count_words) { pair_replay(c, warm, q, msg, count_words); }
 };
 
 }  // namespace triage

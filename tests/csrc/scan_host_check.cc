@@ -494,7 +494,7 @@ extern "C" int hostcheck_regex_count(const char *pattern, uint32_t plen, const u
 namespace {
 struct CountingSink {
     uint64_t flagged = 0;
-    void push(const triage::PairCtx &c, const triage::Quad &warm, const triage::Quad &q, uint32_t msg) { flagged++; triage::pair_replay(c, warm, q, msg); }
+    void push(const triage::PairCtx &c, const triage::Quad &warm, const triage::Quad &q, uint32_t msg, int32_t, bool count_words) { flagged++; triage::pair_replay(c, warm, q, msg, count_words); }
 };
 }
 extern "C" int hostcheck_scan_pair(const uint8_t *prios, const uint8_t *cis, const uint32_t *lens, const uint8_t *lits, uint32_t n_pat,
@@ -542,7 +542,7 @@ extern "C" int hostcheck_scan_pair(const uint8_t *prios, const uint8_t *cis, con
         c.ftbl = dfa.filter.mtable.data(); c.fstart = dfa.filter.m_start; c.ffired = dfa.filter.m_fired_from; c.mul = dfa.filter.mul; c.shift = dfa.filter.shift;
         c.xtbl = dfa.ctable.data(); c.xcls = dfa.ccls; c.xn = dfa.n_cmp; c.events = ev.data(); c.neutral_state = dfa.neutral_state; c.pad4 = padq.a;
         c.list = list.data(); c.list_abs = poff.data(); c.tile_start = (int64_t)ts; c.list_n = (uint32_t)list.size(); c.msg_lo = mlo;
-        c.counters = counters;
+        c.counters = counters; c.arena = nullptr;
         for (uint32_t l = 0; l < 32; l++) {
             uint64_t cs = ts + (uint64_t)l * chunk_long;
             if (cs >= te) break;

@@ -34,10 +34,10 @@ def test_default_dictionary_full_size_digests(name, monkeypatch):
     e = mq.Engine(device=0, rules_enabled=rules)
     try:
         poff, plen, pbytes = e.pack_padded(off, data)
-        # default: the one-lookup-per-byte row kernel; TRIAGE_PAIR=1: the pair-lane kernel (two bytes per lookup)
+        # default: the pair-lane kernel (two bytes per lookup); TRIAGE_PAIR=0: the one-lookup-per-byte row kernel
         variants = [("pair auto", {"TRIAGE_PAIR": "1"}), ("pair 1280", {"TRIAGE_PAIR": "1", "TRIAGE_ROW_BYTES": "1280"}),
                     ("pair 640", {"TRIAGE_PAIR": "1", "TRIAGE_ROW_BYTES": "640"}),
-                    ("pair 320", {"TRIAGE_PAIR": "1", "TRIAGE_ROW_BYTES": "320"}), ("rows auto", {}),
+                    ("pair 320", {"TRIAGE_PAIR": "1", "TRIAGE_ROW_BYTES": "320"}), ("rows auto", {"TRIAGE_PAIR": "0"}), ("default", {}),
                     ("rows 1280", {"TRIAGE_PAIR": "0", "TRIAGE_ROW_BYTES": "1280"}), ("rows 320", {"TRIAGE_PAIR": "0", "TRIAGE_ROW_BYTES": "320"})]
         if name == "c2":
             variants += [("rows 640", {"TRIAGE_PAIR": "0", "TRIAGE_ROW_BYTES": "640"}), ("pair 20 warps", {"TRIAGE_PAIR": "1", "TRIAGE_PAIR_WARPS": "20"}),
