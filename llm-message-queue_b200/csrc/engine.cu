@@ -164,6 +164,7 @@ struct triage_engine {
     RegexSet regex;                // AddKeywordPattern patterns that are not plain literals (regex_vm.h)
     DevBuf<RegexProgram> d_rx_prog;
     DevBuf<RegexInst> d_rx_inst;
+    DevBuf<uint64_t> d_trace;
     DevBuf<RegexClass> d_rx_cls;
     DevBuf<uint32_t> d_rx_rng;
     RegexView rxview{};            // device view, n_programs == 0: none
@@ -443,12 +444,31 @@ int32_t run_device(triage_engine *e, RunMode mode, const uint64_t *offsets, cons
     } else if (ntiles) {
         if (plan) CU(cudaStreamWaitEvent(s, plan->all_ready, 0));
         CU(cudaEventRecord(e->ev[1], s));
+#ifdef TRIAGE_SCAN_TRACE_BUILD
+        const char *trace_path = use_pair ? getenv("TRIAGE_SCAN_TRACE") : nullptr;   // measurement aid: when each warp of the scan ended
+#else
+        const char *trace_path = nullptr;
+#endif
+        const size_t trace_words = 4ull * (size_t)e->sm_count * 32;
+        if (trace_path) { CU(e->d_trace.ensure(trace_words)); CU(cudaMemsetAsync(e->d_trace.p, 0, trace_words * 8, s)); sa.trace = e->d_trace.p; }
         if (use_pair) CU(launch_scan_pair(sa, e->ddfa, row_warps, row_bytes, e->d_small.p + 20, scan_sms, s));   // d_small[20]: spare word, zeroed by prepare
         else if (use_rows) CU(launch_scan_rows(sa, e->ddfa, row_warps, row_bytes, e->d_small.p + 20, scan_sms, s));
         else if (use_stream) CU(launch_scan_stream_wide(sa, e->ddfa, e->wide_warps, e->wide_chains, e->wide_row, e->d_small.p + 20, scan_sms, s));
         else if (padded) CU(launch_scan_padded(sa, e->ddfa, e->pad_warps, scan_sms, s));
         else CU(launch_scan(sa, e->ddfa, e->geom, e->sm_count, s));
         launches++;
+        if (trace_path) {
+            std::vector<uint64_t> h(trace_words);
+            CU(cudaMemcpyAsync(h.data(), e->d_trace.p, trace_words * 8, cudaMemcpyDeviceToHost, s));
+            CU(cudaStreamSynchronize(s));
+            if (FILE *f = fopen(trace_path, "w")) {
+                for (size_t w = 0; w < trace_words / 4; w++)
+                    if (h[4 * w + 1]) fprintf(f, "%zu %llu %llu %llu %llu\n", w, (unsigned long long)h[4 * w], (unsigned long long)h[4 * w + 1],
+                                              (unsigned long long)h[4 * w + 2], (unsigned long long)h[4 * w + 3]);
+                fclose(f);
+            }
+            sa.trace = nullptr;
+        }
     } else {
         if (plan) CU(cudaStreamWaitEvent(s, plan->all_ready, 0));
         CU(cudaEventRecord(e->ev[1], s));
@@ -584,7 +604,7 @@ void triage_destroy(triage_engine *e) {
         for (cudaEvent_t ev : ps->chunk_ev) cudaEventDestroy(ev);
         for (cudaEvent_t ev : {ps->ready, ps->small_ready, ps->t_begin, ps->t_end}) if (ev) cudaEventDestroy(ev);
     }
-    e->d_tilectr.release();
+    e->d_tilectr.release(); e->d_trace.release();
     if (e->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(e->comm);
     e->d_rx_prog.release(); e->d_rx_inst.release(); e->d_rx_cls.release(); e->d_rx_rng.release();
     e->d_keys.release(); e->d_kprio.release(); e->d_korder.release();
@@ -1489,9 +1509,10 @@ int32_t triage_comm_init(triage_engine *e, int32_t nranks, int32_t rank, const u
     // The exchange runs on a second stream under the next step's scan, and the scan is one persistent CTA per SM: every SM
     // a collective's CTAs hold is an SM whose scan CTA starts late.  The order all-gather is small (4 bytes a message),
     // so the communicator is capped at a few CTAs (TRIAGE_NCCL_CTAS, 0 = NCCL's own choice).
-    int ctas = 4;
+    // (measured on 8 B200s, 1 Mi messages per rank: 0 / 4 / 8 SMs left free -> 1.46 / 1.31 / 1.22 ms per step)
+    int ctas = nranks >= 8 ? 8 : 4;
     if (const char *v = getenv("TRIAGE_NCCL_CTAS")) ctas = atoi(v);
-    e->comm_sms = 4;
+    e->comm_sms = nranks >= 8 ? 8 : 4;
     if (const char *v = getenv("TRIAGE_COMM_SMS")) { int x = atoi(v); if (x >= 0 && x <= 32) e->comm_sms = x; }
     ncclResult_t r;
     if (g_nccl.CommInitRankConfig && ctas > 0) {

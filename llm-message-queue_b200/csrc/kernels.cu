@@ -1100,6 +1100,11 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, Devic
     const uint32_t t_end = a.tile_end;
     const uint32_t t0 = a.tile_begin + blockIdx.x * NW + warp;
     if (t0 >= t_end) return;
+#ifdef TRIAGE_SCAN_TRACE_BUILD
+    uint64_t trace_t0 = 0, trace_last = 0, trace_worst = 0;
+    uint32_t trace_tiles = 0, trace_worst_tile = 0;
+    if (a.trace) { asm volatile("mov.u64 %0, %globaltimer;" : "=l"(trace_t0)); trace_last = trace_t0; }
+#endif
     auto grab = [&]() {
         uint32_t v = 0;
         if (lane == 0) v = atomicAdd(tile_counter, 1u) + nwarps + a.tile_begin;
@@ -1234,10 +1239,32 @@ __global__ void __launch_bounds__(NW * 32, 1) scan_pair_kernel(ScanArgs a, Devic
         }
         first_cur = first_nxt; last_cur = last_nxt;
         t = t_nxt;
-        t_nxt = t < t_end ? grab() : t;   // one tile ahead only: a tile a warp has claimed cannot be taken over by an idle one (warp-uniform: no more fetches past the end)
+#ifdef TRIAGE_SCAN_TRACE_BUILD
+        trace_tiles++;
+        if (a.trace) {
+            uint64_t now;
+            asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+            if (now - trace_last > trace_worst) { trace_worst = now - trace_last; trace_worst_tile = (uint32_t)(ts / SUPER); }
+            trace_last = now;
+        }
+#endif
+        // one tile ahead only: a tile a warp has claimed cannot be taken over by an idle one (warp-uniform: no more fetches
+        // past the end).  Claiming the last rounds' tiles only when the current one is done was measured: slower (0.91 ms
+        // against 0.88), the cold starts cost more than the shorter tail brings.
+        t_nxt = t < t_end ? grab() : t;
         __syncwarp();
     }
     queue.flush(c, lane);
+#ifdef TRIAGE_SCAN_TRACE_BUILD
+    if (a.trace && lane == 0) {
+        uint64_t t1;
+        uint32_t smid;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+        asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+        uint64_t *o = a.trace + 4ull * (blockIdx.x * NW + warp);
+        o[0] = trace_t0; o[1] = t1; o[2] = trace_tiles | (trace_worst << 32); o[3] = smid | ((uint64_t)trace_worst_tile << 32);
+    }
+#endif
 }
 
 template <int NW, int LANE, bool SIMPLE>
@@ -1800,49 +1827,63 @@ __global__ void __launch_bounds__(256) merge_strided_kernel(const uint64_t *__re
 // ---- one-exchange merge for contiguous sequence shards (engine-stamped enqueue times): every rank contributes
 // [32-word header: admitted, 16 bucket counts | its local order] at a common stride, one all-gather moves all of it, and
 // the concatenation works out its own geometry from the gathered headers - no host round trip between the two.
-__global__ void __launch_bounds__(256) pack_run_kernel(const uint32_t *__restrict__ order, const uint32_t *__restrict__ counts16,
-                                                       const uint32_t *__restrict__ n_adm, uint32_t n, uint32_t *__restrict__ gsrc) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(32) pack_header_kernel(const uint32_t *__restrict__ counts16, const uint32_t *__restrict__ n_adm,
+                                                         uint32_t *__restrict__ gsrc) {
+    const uint32_t i = threadIdx.x;
     if (i < kMergeHeaderWords) gsrc[i] = i == 0 ? *n_adm : (i <= 16 ? counts16[i - 1] : 0u);
-    else if (i < kMergeHeaderWords + n) gsrc[i] = order[i - kMergeHeaderWords];
 }
 
+// header by one warp, the order by the copy engine: no SM is taken from the scan that runs next to it
 cudaError_t launch_pack_run(const uint32_t *order, const uint32_t *counts16_dev, const uint32_t *n_adm_dev, uint32_t n, uint32_t *gsrc,
                             cudaStream_t s) {
-    const uint32_t total = kMergeHeaderWords + n;
-    pack_run_kernel<<<(total + 255) / 256, 256, 0, s>>>(order, counts16_dev, n_adm_dev, n, gsrc);
-    return cudaGetLastError();
+    static_assert(kMergeHeaderWords <= 32, "one warp writes the header");
+    pack_header_kernel<<<1, 32, 0, s>>>(counts16_dev, n_adm_dev, gsrc);
+    if (cudaError_t e = cudaGetLastError()) return e;
+    if (n == 0) return cudaSuccess;
+    return cudaMemcpyAsync(gsrc + kMergeHeaderWords, order, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToDevice, s);
 }
 
+// The kernel runs on the few SMs the persistent scan of the next step leaves free (engine.cu: comm_sms), so it is a small
+// grid of grid-stride copies, and the geometry is worked out once per CTA from a parallel read of the gathered headers.
 __global__ void __launch_bounds__(256) concat_gathered_kernel(const uint32_t *__restrict__ all, MergeBases mb, uint32_t *__restrict__ order_out,
                                                               uint64_t capacity, uint64_t *__restrict__ n_total_out) {
-    __shared__ uint32_t cnt[8], lstart[8][16], dst[8][16];
+    __shared__ uint32_t hdr[8][17], lstart[8][16], dst[8][16];
     __shared__ uint64_t total_s;
+    for (uint32_t i = threadIdx.x; i < mb.n_ranks * 17u; i += blockDim.x) hdr[i / 17u][i % 17u] = all[(uint64_t)(i / 17u) * mb.stride + (i % 17u)];
+    __syncthreads();
     if (threadIdx.x == 0) {   // geometry from the gathered headers: bucket-major, rank-minor
         uint64_t total = 0;
-        for (uint32_t q = 0; q < mb.n_ranks; q++) { cnt[q] = all[(uint64_t)q * mb.stride]; total += cnt[q]; }
+        for (uint32_t q = 0; q < mb.n_ranks; q++) total += hdr[q][0];
         uint32_t d = 0;
         for (uint32_t b = 0; b < 16; b++)
-            for (uint32_t q = 0; q < mb.n_ranks; q++) { dst[q][b] = d; d += all[(uint64_t)q * mb.stride + 1 + b]; }
+            for (uint32_t q = 0; q < mb.n_ranks; q++) { dst[q][b] = d; d += hdr[q][1 + b]; }
         for (uint32_t q = 0; q < mb.n_ranks; q++) {
             uint32_t acc = 0;
-            for (uint32_t b = 0; b < 16; b++) { lstart[q][b] = acc; acc += all[(uint64_t)q * mb.stride + 1 + b]; }
+            for (uint32_t b = 0; b < 16; b++) { lstart[q][b] = acc; acc += hdr[q][1 + b]; }
         }
         total_s = total;
     }
     __syncthreads();
-    const uint32_t q = blockIdx.y, j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (q == 0 && j == 0 && n_total_out) *n_total_out = total_s;
-    if (total_s > capacity || j >= cnt[q]) return;   // too small an output buffer: nothing is written, the host reports it
-    uint32_t b = 0;
+    const uint32_t q = blockIdx.y;
+    if (q == 0 && blockIdx.x == 0 && threadIdx.x == 0 && n_total_out) *n_total_out = total_s;
+    if (total_s > capacity) return;   // too small an output buffer: nothing is written, the host reports it
+    const uint32_t cnt = hdr[q][0];
+    const uint32_t *src = all + (uint64_t)q * mb.stride + kMergeHeaderWords;
+    const uint32_t base = mb.base[q];
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < cnt; j += gridDim.x * blockDim.x) {
+        uint32_t b = 0;
 #pragma unroll
-    for (uint32_t i = 1; i < 16; i++) if (j >= lstart[q][i]) b = i;
-    order_out[dst[q][b] + (j - lstart[q][b])] = all[(uint64_t)q * mb.stride + kMergeHeaderWords + j] + mb.base[q];
+        for (uint32_t i = 1; i < 16; i++) if (j >= lstart[q][i]) b = i;
+        order_out[dst[q][b] + (j - lstart[q][b])] = src[j] + base;
+    }
 }
 
 cudaError_t launch_concat_gathered(const uint32_t *all, const MergeBases &mb, uint32_t n_per_rank, uint32_t *order_out, uint64_t capacity,
                                    uint64_t *n_total_dev, cudaStream_t s) {
-    dim3 grid((n_per_rank + 255) / 256 ? (n_per_rank + 255) / 256 : 1, mb.n_ranks);
+    uint32_t gx = (n_per_rank + 4095) / 4096;   // 16 elements a thread at least
+    if (gx > 48) gx = 48;
+    if (gx == 0) gx = 1;
+    dim3 grid(gx, mb.n_ranks);
     concat_gathered_kernel<<<grid, 256, 0, s>>>(all, mb, order_out, capacity, n_total_dev);
     return cudaGetLastError();
 }

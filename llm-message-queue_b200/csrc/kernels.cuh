@@ -50,6 +50,7 @@ struct ScanArgs {
     uint32_t ntiles;
     uint32_t tile_bytes;         // = geometry.tile
     uint32_t tile_begin, tile_end;   // row-lane scan only: the tiles this launch walks (the whole arena: 0, ntiles)
+    uint64_t *trace = nullptr;       // measurement aid (TRIAGE_SCAN_TRACE): per warp {start ns, end ns, tiles walked, SM id}
 };
 
 // padded-arena scan: warps are autonomous (own staging buffers, own mbarriers, no CTA barrier in the loop)

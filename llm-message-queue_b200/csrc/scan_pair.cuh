@@ -6,13 +6,15 @@
 //     a byte >= 0x80 counts as non-space), no lookups;
 //   * events (keywords, question words, sentiment words): a FILTER automaton over 4-bit byte classes ((b & 31) * mul >>
 //     shift & 15, arithmetic only) that consumes two bytes per lookup.  It is walked in its Moore form: an entry is one
-//     byte, the next state, its address is state << 8 | class pair (one byte permute), and a state >= ffired says "an
-//     occurrence of some pattern's class string may have ended in the two bytes that led here".  It over-approximates:
-//     bytes that share a class are not told apart;
+//     byte, the next state, at state * 260 + class pair of a table at a fixed shared-memory address (one multiply-add,
+//     the base is an immediate of the load), and a state >= ffired says "an occurrence of some pattern's class string
+//     may have ended in the two bytes that led here".  It over-approximates: bytes that share a class are not told apart;
 //   * every group the filter flags, and every group that holds one of the lead bytes C2 C4 C5 E0-E3 (multi-byte
 //     whitespace, the fold runes U+017F / U+212A / U+0130) or follows such a group, is handed to `sink`, which walks the
-//     group through the EXACT one-byte automaton (its column-merged copy; 16 warm-up bytes + the 16 bytes) and takes
-//     words and events from that walk instead.  Flagged groups are rare on text (under 1 % on the benchmark set).
+//     group through the EXACT one-byte automaton (its column-merged copy; 16 warm-up bytes + the 16 bytes).  A group the
+//     filter alone flagged is walked for its events, its word starts stay the SIMD count; a group with, or right after,
+//     one of those lead bytes takes its word starts from the walk too.  Flagged groups are rare on text (under 1 % on the
+//     benchmark set).
 // A lane takes its bytes a WINDOW (NG groups) at a time: the NG groups are scanned without a branch, and one test per
 // window - nothing flagged, no byte >= 0x80, no message boundary inside - decides between adding up the window's word
 // starts and the per-group path that pushes flagged groups and steps over message boundaries.

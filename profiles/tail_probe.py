@@ -9,6 +9,8 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import llm_message_queue_b200 as mq
+if os.environ.get("TRIAGE_LIB"):          # A/B of two builds on one box
+    mq._capi.LIB_PATH = os.environ["TRIAGE_LIB"]
 from oracle import c_oracle as co
 
 n = 1 << 20
