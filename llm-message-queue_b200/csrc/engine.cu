@@ -1509,10 +1509,11 @@ int32_t triage_comm_init(triage_engine *e, int32_t nranks, int32_t rank, const u
     // The exchange runs on a second stream under the next step's scan, and the scan is one persistent CTA per SM: every SM
     // a collective's CTAs hold is an SM whose scan CTA starts late.  The order all-gather is small (4 bytes a message),
     // so the communicator is capped at a few CTAs (TRIAGE_NCCL_CTAS, 0 = NCCL's own choice).
-    // (measured on 8 B200s, 1 Mi messages per rank: 0 / 4 / 8 SMs left free -> 1.46 / 1.31 / 1.22 ms per step)
+    // (measured on 8 B200s, 1 Mi messages per rank: 0 / 4 / 8 / 12 SMs left free -> 1.46 / 1.31 / 1.30 / 1.20 ms per step:
+    // at 8 ranks the exchange chain - 32 MB gathered and re-ordered on every rank - is what a step waits for)
     int ctas = nranks >= 8 ? 8 : 4;
     if (const char *v = getenv("TRIAGE_NCCL_CTAS")) ctas = atoi(v);
-    e->comm_sms = nranks >= 8 ? 8 : 4;
+    e->comm_sms = nranks >= 8 ? 12 : 4;
     if (const char *v = getenv("TRIAGE_COMM_SMS")) { int x = atoi(v); if (x >= 0 && x <= 32) e->comm_sms = x; }
     ncclResult_t r;
     if (g_nccl.CommInitRankConfig && ctas > 0) {
