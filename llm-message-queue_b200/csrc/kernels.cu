@@ -983,13 +983,14 @@ cudaError_t launch_scan_rows(const ScanArgs &a, const DeviceDfa &d, uint32_t nw,
 // ---------------------------------------------------------------------------------- pair lanes --
 // Row lanes with two bytes per lookup (scan_pair.cuh): same tiles, windows, 2-D TMA feed and dynamic tile hand-out as
 // scan_rows_kernel, but the table in shared memory is the FILTER automaton over 4-bit class pairs (8 lookups per 16
-// bytes), word starts are counted by SIMD-in-register compares, and the groups the filter flags (or that hold bytes >=
-// 0x80) are queued per warp - (message, the 16 bytes before, the 16 bytes) - and walked through the exact automaton in
-// global memory by the whole warp, one queued group per lane.
+// bytes), word starts are counted by SIMD-in-register compares, and the groups the filter flags (or that hold one of the
+// special lead bytes, or follow such a group) are queued per warp - (message, position) - and walked through the exact
+// automaton (its column-merged copy in shared memory) by the whole warp, one queued group per lane, which reads the
+// group's bytes back from the arena.  The default scan of dictionaries that have a pair filter.
 constexpr uint32_t kPairQueueCap = 64;     // flagged groups per warp: (message, arena position / 16 | "words too" << 31), 8 bytes each
 constexpr uint32_t kPairQueueFlush = 32;   // walked by the whole warp, one group per lane, once this many wait (more can arrive in one window: those beyond the cap are walked by their own lane)
 // Shared-memory layout.  The filter table sits at the shared address kPairTableShared (scan_pair.cuh: its entries are
-// then addressed by a byte permute and an immediate); the kernel's dynamic shared memory starts at kPairSmemBase (the
+// then addressed by a multiply-add and an immediate); the kernel's dynamic shared memory starts at kPairSmemBase (the
 // first KB of the window is reserved by the system - the kernel checks), so the table is at offset 0xFC00 and the other
 // pieces are laid out around it: the small ones and the first warps' staging buffers before, the other warps' after.
 constexpr uint32_t kPairSmemBase = 0x400u;

@@ -233,6 +233,35 @@ extern "C" int hostcheck_exact(const uint8_t *prios, const uint8_t *cis, const u
 // wide-format check: padded arena + lane_scan_padded<WideCtx> over warp mini-tiles (what scan_wide_kernel runs), and,
 // when the dictionary has self-overlapping literals, the sequential exact recount of flagged messages
 #include "../../llm-message-queue_b200/csrc/scan_wide.cuh"
+// exact recount of flagged messages (self-overlapping literals), what fixup_kernel does with the wide format
+static int wide_exact_recount(const std::vector<DictEntry> &dict, const uint64_t *offsets, const uint8_t *bytes, uint32_t n_msgs,
+                              uint32_t *counters, char *err, uint32_t errcap)
+{
+    if (!dict_has_bordered(dict)) return 0;
+    Dfa x;
+    std::string e2 = build_dfa(dict, &x, true);
+    if (!e2.empty() || !x.wide) { std::strncpy(err, "exact automaton", errcap - 1); return 7; }
+    for (uint32_t i = 0; i < n_msgs; i++) {
+        uint32_t *acc = counters + (size_t)i * 8;
+        if (!(acc[CNT_Q] & 2)) continue;
+        std::memset(acc, 0, 32);
+        uint32_t st = x.start_state_w;
+        auto event = [&](uint32_t id) {
+            const EventVec &v = x.events[id];
+            for (int k = 0; k < 4; k++) acc[CNT_KW + k] += v.kw[k];
+            acc[CNT_POS] += v.pos; acc[CNT_NEG] += v.neg; if (v.question) acc[CNT_Q] |= 1;
+        };
+        for (uint64_t p = offsets[i]; p < offsets[i + 1]; p++) {
+            uint32_t t = x.wtable[(size_t)st * x.n_classes + x.cls_of[bytes[p]]];
+            st = t & 0xFFFFF; acc[CNT_WORDS] += t >> 31;
+            if (t & 0x7FF00000u) event((t >> 20) & 0x7FF);
+        }
+        uint32_t eo = x.eom_w[st];
+        acc[CNT_WORDS] += eo >> 31;
+        if (eo & 0x7FFFFFFF) event(eo & 0x7FFFFFFF);
+    }
+    return 0;
+}
 extern "C" int hostcheck_scan_wide(const uint8_t *prios, const uint8_t *cis, const uint32_t *lens, const uint8_t *lits, uint32_t n_pat,
                                    const uint64_t *offsets, const uint8_t *bytes, uint32_t n_msgs, uint32_t chunk,
                                    uint32_t *counters, uint32_t *info, char *err, uint32_t errcap)
@@ -287,31 +316,7 @@ extern "C" int hostcheck_scan_wide(const uint8_t *prios, const uint8_t *cis, con
             if (hw) counters[(uint64_t)hm * 8 + CNT_WORDS] += hw;
         }
     }
-    // exact recount of flagged messages (self-overlapping literals)
-    if (dict_has_bordered(dict)) {
-        Dfa x;
-        std::string e2 = build_dfa(dict, &x, true);
-        if (!e2.empty() || !x.wide) { std::strncpy(err, "exact automaton", errcap - 1); return 7; }
-        for (uint32_t i = 0; i < n_msgs; i++) {
-            uint32_t *acc = counters + (size_t)i * 8;
-            if (!(acc[CNT_Q] & 2)) continue;
-            std::memset(acc, 0, 32);
-            uint32_t st = x.start_state_w;
-            auto event = [&](uint32_t id) {
-                const EventVec &v = x.events[id];
-                for (int k = 0; k < 4; k++) acc[CNT_KW + k] += v.kw[k];
-                acc[CNT_POS] += v.pos; acc[CNT_NEG] += v.neg; if (v.question) acc[CNT_Q] |= 1;
-            };
-            for (uint64_t p = offsets[i]; p < offsets[i + 1]; p++) {
-                uint32_t t = x.wtable[(size_t)st * x.n_classes + x.cls_of[bytes[p]]];
-                st = t & 0xFFFFF; acc[CNT_WORDS] += t >> 31;
-                if (t & 0x7FF00000u) event((t >> 20) & 0x7FF);
-            }
-            uint32_t eo = x.eom_w[st];
-            acc[CNT_WORDS] += eo >> 31;
-            if (eo & 0x7FFFFFFF) event(eo & 0x7FFFFFFF);
-        }
-    }
+    if (int rc = wide_exact_recount(dict, offsets, bytes, n_msgs, counters, err, errcap)) return rc;
     for (uint32_t i = 0; i < n_msgs; i++) {
         counters[(uint64_t)i * 8 + CNT_Q] &= 1;
         if (offsets[i + 1] > offsets[i] && bytes[offsets[i + 1] - 1] == '?') counters[(uint64_t)i * 8 + CNT_Q] |= 1;
@@ -383,8 +388,8 @@ extern "C" int hostcheck_scan_long(const uint8_t *prios, const uint8_t *cis, con
 
 // streaming variant: a lane owns `nch` chunks of chunk_long bytes (chunk v = ch * 32 + lane of the super-tile) and walks
 // them interleaved with long_stream_n; a chunk cut short by the end of the arena is walked alone
-template <int N>
-static void stream_lane(const LaneCtx &c, const uint8_t *arena, uint64_t ts, uint64_t te, uint32_t l, uint32_t chunk_long, int32_t warm,
+template <int N, class Ctx>
+static void stream_lane(const Ctx &c, const uint8_t *arena, uint64_t ts, uint64_t te, uint32_t l, uint32_t chunk_long, int32_t warm,
                         uint32_t *counters)
 {
     LongLane L[N];
@@ -469,6 +474,64 @@ extern "C" int hostcheck_scan_stream(const uint8_t *prios, const uint8_t *cis, c
             }
         }
     }
+    for (uint32_t i = 0; i < n_msgs; i++) {
+        counters[(uint64_t)i * 8 + CNT_Q] &= 1;
+        if (offsets[i + 1] > offsets[i] && bytes[offsets[i + 1] - 1] == '?') counters[(uint64_t)i * 8 + CNT_Q] |= 1;
+    }
+    return 0;
+}
+
+
+// wide format, rows streamed from global memory (scan_stream_wide_kernel): lanes own `nch` rows of chunk_long bytes of a
+// super-tile and walk them interleaved, events applied where they are met (InlineEvents<WideCtx>)
+extern "C" int hostcheck_scan_stream_wide(const uint8_t *prios, const uint8_t *cis, const uint32_t *lens, const uint8_t *lits, uint32_t n_pat,
+                                          const uint64_t *offsets, const uint8_t *bytes, uint32_t n_msgs, uint32_t chunk_long, uint32_t nch,
+                                          uint32_t *counters, char *err, uint32_t errcap)
+{
+    std::vector<DictEntry> dict;
+    size_t o = 0;
+    for (uint32_t i = 0; i < n_pat; i++) {
+        dict.push_back({prios[i], cis[i] != 0, std::string(reinterpret_cast<const char *>(lits + o), lens[i])});
+        o += lens[i];
+    }
+    Dfa dfa;
+    std::string e = build_dfa(dict, &dfa);
+    if (!e.empty() || !dfa.wide || dfa.reset_pad < 0 || nch < 1 || nch > 4 || (chunk_long & 15)) { std::strncpy(err, "unsupported", errcap - 1); return 4; }
+    if (n_msgs == 0) return 0;
+    std::vector<EventPacked> ev(dfa.events.size());
+    for (size_t i = 0; i < dfa.events.size(); i++) pack_event(dfa.events[i], &ev[i].x);
+    std::vector<uint64_t> poff(n_msgs + 1, 0);
+    for (uint32_t i = 0; i < n_msgs; i++) poff[i + 1] = poff[i] + ((offsets[i + 1] - offsets[i]) / 16 + 1) * 16;
+    std::vector<uint8_t> arena_raw(poff[n_msgs] + 64, (uint8_t)dfa.reset_pad);
+    uint8_t *arena = arena_raw.data();
+    while (reinterpret_cast<uintptr_t>(arena) & 15) arena++;
+    for (uint32_t i = 0; i < n_msgs; i++) std::memcpy(arena + poff[i], bytes + offsets[i], offsets[i + 1] - offsets[i]);
+    std::memset(counters, 0, sizeof(uint32_t) * 8 * n_msgs);
+    const uint64_t total = poff[n_msgs];
+    const uint64_t st_bytes = 32ull * chunk_long * nch;
+    const int32_t warm = (int32_t)dfa.warm_bytes;
+    for (uint64_t ts = 0; ts < total; ts += st_bytes) {
+        uint64_t te = std::min(total, ts + st_bytes);
+        uint32_t lo = 0, hi = n_msgs + 1;
+        while (lo < hi) { uint32_t mid = (lo + hi) / 2; if (poff[mid] > ts) hi = mid; else lo = mid + 1; }
+        uint32_t mlo = lo - 1, mhi = mlo;
+        while (poff[mhi + 1] < te) mhi++;
+        std::vector<int32_t> list;
+        for (uint32_t m = mlo; m <= mhi + 1; m++) list.push_back((int32_t)((int64_t)poff[m] - (int64_t)ts));
+        WideCtx c;
+        c.wtbl = dfa.wtable.data(); c.cls = dfa.cls_of; c.ncls = dfa.n_classes; c.events = ev.data(); c.stage = nullptr;
+        c.list = list.data(); c.list_abs = poff.data(); c.tile_start = (int64_t)ts; c.list_n = (uint32_t)list.size(); c.msg_lo = mlo;
+        c.counters = counters; c.warm = warm; c.start_state = dfa.start_state_w; c.neutral_state = dfa.neutral_state_w;
+        for (uint32_t l = 0; l < 32; l++) {
+            switch (nch) {
+                case 1: stream_lane<1>(c, arena, ts, te, l, chunk_long, warm, counters); break;
+                case 2: stream_lane<2>(c, arena, ts, te, l, chunk_long, warm, counters); break;
+                case 3: stream_lane<3>(c, arena, ts, te, l, chunk_long, warm, counters); break;
+                default: stream_lane<4>(c, arena, ts, te, l, chunk_long, warm, counters); break;
+            }
+        }
+    }
+    if (int rc = wide_exact_recount(dict, offsets, bytes, n_msgs, counters, err, errcap)) return rc;
     for (uint32_t i = 0; i < n_msgs; i++) {
         counters[(uint64_t)i * 8 + CNT_Q] &= 1;
         if (offsets[i + 1] > offsets[i] && bytes[offsets[i + 1] - 1] == '?') counters[(uint64_t)i * 8 + CNT_Q] |= 1;

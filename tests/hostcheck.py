@@ -113,8 +113,9 @@ def scan_long(dict_entries, offsets, data, chunk_long=320, window=80):
     return counters[:n]
 
 
-def scan_stream(dict_entries, offsets, data, chunk_long=512, nch=2):
-    """counters through the streaming walk (nch interleaved chains of chunk_long bytes per lane)"""
+def scan_stream(dict_entries, offsets, data, chunk_long=512, nch=2, wide=False):
+    """counters through the streaming walk (nch interleaved chains of chunk_long bytes per lane); wide: the wide table
+    format with events applied where they are met (scan_stream_wide_kernel) + the exact recount of flagged messages"""
     n = len(offsets) - 1
     prios = np.array([d[0] for d in dict_entries], np.uint8)
     cis = np.array([1 if d[1] else 0 for d in dict_entries], np.uint8)
@@ -124,8 +125,8 @@ def scan_stream(dict_entries, offsets, data, chunk_long=512, nch=2):
     err = C.create_string_buffer(256)
     buf = data if len(data) else np.zeros(1, np.uint8)
     p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
-    rc = lib().hostcheck_scan_stream(p(prios), p(cis), p(lens), p(lits), len(dict_entries), p(offsets), p(buf), n, chunk_long, nch,
-                                     p(counters), err, 256)
+    fn = lib().hostcheck_scan_stream_wide if wide else lib().hostcheck_scan_stream
+    rc = fn(p(prios), p(cis), p(lens), p(lits), len(dict_entries), p(offsets), p(buf), n, chunk_long, nch, p(counters), err, 256)
     if rc != 0:
         raise ValueError(err.value.decode())
     return counters[:n]
