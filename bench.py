@@ -516,7 +516,8 @@ def main():
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if c3 else "weak", "vs_baseline": None, "dtype": "u8",
                 "data": "synthetic", "config": workload_config(world, args.workload) | {"messages_per_gpu": n, "global_messages": n * world,
                                                                           "arena_bytes_per_gpu": total, "content_bytes_per_gpu": content_bytes, "arena_layout": "padded16 (16-byte aligned starts, TAB reset pads)", "automaton_states": info["states"],
-                                                                          "order_passes": passes},
+                                                                          "order_passes": passes}
+                          | ({"timestamps": "explicit enqueue times, increasing within a rank and interleaved across the ranks (general merge: every key ranked in the other ranks' runs)"} if args.interleave_ts else {}),
                 "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
                 "checked": checked,
                 "timing": {"device_ms_total": dev_ms_max, "wall_ms_total": wall_ms_max, "admitted": adm}}
