@@ -12,8 +12,11 @@
 // are unquoted with invalid UTF-8 bytes and lone surrogate escapes replaced by U+FFFD; integers must be written without
 // fraction or exponent and fit int64; time.Time fields take RFC 3339 strings; Decoder.Decode reads ONE value and ignores
 // what follows it.  Metadata is a map[string]interface{}: its keys are case-sensitive.
+#include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/triage.h"
@@ -67,6 +70,21 @@ bool parse_string(Cur &c, std::string *out) {
     if (!c.eat('"')) return c.ok = false;
     if (out) out->clear();
     while (c.p < c.end) {
+        {   // a run of plain bytes (printable ASCII other than '"' and '\\'), eight at a time: copied as it is
+            const uint8_t *s = c.p;
+            while (c.p + 8 <= c.end) {
+                uint64_t w;
+                std::memcpy(&w, c.p, 8);
+                const uint64_t k01 = 0x0101010101010101ull, k80 = 0x8080808080808080ull;
+                const uint64_t q = w ^ (k01 * 0x22), bs = w ^ (k01 * 0x5C);
+                const uint64_t stop = (w | ((w - k01 * 0x20) & ~w) | ((q - k01) & ~q) | ((bs - k01) & ~bs)) & k80;
+                if (stop) break;
+                c.p += 8;
+            }
+            while (c.p < c.end && *c.p >= 0x20 && *c.p < 0x80 && *c.p != '"' && *c.p != '\\') c.p++;
+            if (out && c.p != s) out->append(reinterpret_cast<const char *>(s), (size_t)(c.p - s));
+            if (c.p >= c.end) break;
+        }
         const uint8_t b = *c.p;
         if (b == '"') { c.p++; return true; }
         if (b < 0x20) return c.ok = false;                       // raw control character: syntax error
@@ -248,6 +266,10 @@ struct Decoded {
     bool has_meta = false;            // Metadata != nil
     uint8_t user_priority = TRIAGE_UP_ABSENT, meta_priority = 0;
     bool vip = false;
+    void reset() {                    // (keeps the strings' capacity from message to message)
+        content.clear(); user_id.clear();
+        priority = 0; has_meta = false; user_priority = TRIAGE_UP_ABSENT; meta_priority = 0; vip = false;
+    }
 };
 
 // Metadata map[string]interface{}: only three keys matter; a later duplicate overrides (the map entry is replaced)
@@ -306,9 +328,7 @@ bool decode_message(const uint8_t *p, const uint8_t *end, Decoded *d) {
         else if (want == STR) {
             if (vk != '"') { char k; if (!skip_value(c, &k)) return false; type_error = true; }
             else {
-                if (!parse_string(c, &sval)) return false;
-                if (field == 3) d->content = sval;
-                if (field == 2) d->user_id = sval;
+                if (!parse_string(c, field == 3 ? &d->content : field == 2 ? &d->user_id : nullptr)) return false;   // (a later duplicate overrides)
             }
         } else if (want == INT) {
             if (vk == '-' || (vk >= '0' && vk <= '9')) {
@@ -337,35 +357,70 @@ std::string ingest_json(const uint8_t *bodies, const uint64_t *body_offsets, uin
                         const IngestOut &out, uint64_t *total) {
     if ((n && (!bodies || !body_offsets)) || !out.offsets || !out.lengths || !out.meta || !out.status || !total) return "null argument";
     if (pad < 0 || pad > 255) return "this dictionary has no pad byte for the padded arena";
+    // Messages are independent until their place in the arena is fixed, so the bodies are decoded a block at a time on a
+    // few threads (TRIAGE_INGEST_THREADS, default: up to 16), then laid out in order and copied into the arena by the same
+    // threads.  The lookup callback is called from those threads: it only reads the engine's table.
+    unsigned nthr = 1;
+    if (n >= 2048) {
+        nthr = std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
+        if (const char *v = getenv("TRIAGE_INGEST_THREADS")) { const int x = atoi(v); if (x >= 1 && x <= 64) nthr = (unsigned)x; }
+    }
+    constexpr uint32_t kBlock = 8192;
+    std::vector<Decoded> dec(std::min<uint32_t>(n, kBlock));
+    std::string err;
     uint64_t o = 0;
-    Decoded d;
-    for (uint32_t i = 0; i < n; i++) {
-        d = Decoded();
-        const bool ok = decode_message(bodies + body_offsets[i], bodies + body_offsets[i + 1], &d);
-        if (!ok) d = Decoded();                                  // rejected: an empty slot keeps the indices aligned
-        out.status[i] = ok ? 0 : 1;
-        triage_meta m;
-        std::memset(&m, 0, sizeof(m));
-        m.preset = (uint8_t)((d.priority < 0 || d.priority > 254) ? 255 : d.priority);   // any other explicit priority: left untouched (:63-65)
-        m.user_priority = d.user_priority;
-        m.meta_priority = d.meta_priority;
-        m.flags = d.vip ? TRIAGE_META_VIP : 0;
-        if (ok && lookup) { const int up = lookup(ctx, d.user_id.data(), d.user_id.size()); m.user_default = (uint8_t)((up < 0 || up > 254) ? 0 : up); }
-        out.meta[i] = m;
-        if (d.content.size() > 0xFFFFFFFFull) return "message longer than 4 GiB";
-        const uint64_t len = d.content.size(), slot = (len / 16 + 1) * 16;   // 1..16 pad bytes after every message
-        out.offsets[i] = o;
-        out.lengths[i] = (uint32_t)len;
-        if (out.arena) {
-            if (o + slot > out.cap) return "arena too small";
-            if (len) std::memcpy(out.arena + o, d.content.data(), len);
-            std::memset(out.arena + o + len, pad, slot - len);
+    auto parallel = [&](uint32_t count, auto &&fn) {
+        if (nthr <= 1 || count < 512) { fn(0u, count); return; }
+        std::vector<std::thread> th;
+        const uint32_t per = (count + nthr - 1) / nthr;
+        for (unsigned t = 0; t < nthr; t++) {
+            const uint32_t lo = std::min(count, t * per), hi = std::min(count, lo + per);
+            if (lo < hi) th.emplace_back([&fn, lo, hi] { fn(lo, hi); });
         }
-        o += slot;
+        for (auto &x : th) x.join();
+    };
+    for (uint32_t base = 0; base < n; base += kBlock) {
+        const uint32_t cnt = std::min<uint32_t>(kBlock, n - base);
+        parallel(cnt, [&](uint32_t lo, uint32_t hi) {
+            for (uint32_t j = lo; j < hi; j++) {
+                const uint32_t i = base + j;
+                Decoded &d = dec[j];
+                d.reset();
+                const bool ok = decode_message(bodies + body_offsets[i], bodies + body_offsets[i + 1], &d);
+                if (!ok) d.reset();                              // rejected: an empty slot keeps the indices aligned
+                out.status[i] = ok ? 0 : 1;
+                triage_meta m;
+                std::memset(&m, 0, sizeof(m));
+                m.preset = (uint8_t)((d.priority < 0 || d.priority > 254) ? 255 : d.priority);   // any other explicit priority: left untouched (:63-65)
+                m.user_priority = d.user_priority;
+                m.meta_priority = d.meta_priority;
+                m.flags = d.vip ? TRIAGE_META_VIP : 0;
+                if (ok && lookup) { const int up = lookup(ctx, d.user_id.data(), d.user_id.size()); m.user_default = (uint8_t)((up < 0 || up > 254) ? 0 : up); }
+                out.meta[i] = m;
+            }
+        });
+        for (uint32_t j = 0; j < cnt; j++) {                     // layout: 1..16 pad bytes after every message
+            const uint64_t len = dec[j].content.size();
+            if (len > 0xFFFFFFFFull) return "message longer than 4 GiB";
+            out.offsets[base + j] = o;
+            out.lengths[base + j] = (uint32_t)len;
+            o += (len / 16 + 1) * 16;
+        }
+        if (out.arena) {
+            if (o > out.cap) return "arena too small";
+            out.offsets[base + cnt] = o;
+            parallel(cnt, [&](uint32_t lo, uint32_t hi) {
+                for (uint32_t j = lo; j < hi; j++) {
+                    const uint64_t at = out.offsets[base + j], len = dec[j].content.size(), slot = out.offsets[base + j + 1] - at;
+                    if (len) std::memcpy(out.arena + at, dec[j].content.data(), len);
+                    std::memset(out.arena + at + len, pad, slot - len);
+                }
+            });
+        }
     }
     out.offsets[n] = o;
     *total = o;
-    return "";
+    return err;
 }
 
 uint64_t emit_analysis_json(const triage_result *res, uint32_t n, char *out, uint64_t cap, uint64_t *offsets) {
