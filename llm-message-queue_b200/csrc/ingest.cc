@@ -424,18 +424,51 @@ std::string ingest_json(const uint8_t *bodies, const uint64_t *body_offsets, uin
 }
 
 uint64_t emit_analysis_json(const triage_result *res, uint32_t n, char *out, uint64_t cap, uint64_t *offsets) {
-    // json.Marshal of map[string]interface{}{"word_count": int, "sentiment": string, "is_question": bool}: keys sorted
+    // json.Marshal of map[string]interface{}{"word_count": int, "sentiment": string, "is_question": bool}: keys sorted.
+    // Written by hand (no printf): the lengths first, then the bytes, on a few threads for large batches.
+    static const char *const kHead[2] = {"{\"is_question\":false,\"sentiment\":\"", "{\"is_question\":true,\"sentiment\":\""};
+    static const char *const kSent[3] = {"negative", "neutral", "positive"};
+    static const char kMid[] = "\",\"word_count\":";
+    static const uint32_t kHeadLen[2] = {(uint32_t)std::strlen(kHead[0]), (uint32_t)std::strlen(kHead[1])};
+    static const uint32_t kSentLen[3] = {8, 7, 8};
+    const uint32_t kMidLen = (uint32_t)sizeof(kMid) - 1;
+    auto digits = [](uint32_t v) { uint32_t d = 1; while (v >= 10) { v /= 10; d++; } return d; };
+    auto sent_of = [](const triage_result &r) { return r.sentiment > 0 ? 2 : (r.sentiment < 0 ? 0 : 1); };
+    std::vector<uint64_t> own;
+    uint64_t *offs = offsets;
+    if (!offs && out) { own.resize((size_t)n + 1); offs = own.data(); }
     uint64_t o = 0;
-    char buf[96];
     for (uint32_t i = 0; i < n; i++) {
-        const char *sent = res[i].sentiment > 0 ? "positive" : (res[i].sentiment < 0 ? "negative" : "neutral");
-        const int len = snprintf(buf, sizeof(buf), "{\"is_question\":%s,\"sentiment\":\"%s\",\"word_count\":%u}", res[i].question ? "true" : "false", sent,
-                                 (unsigned)res[i].words);
-        if (offsets) offsets[i] = o;
-        if (out && o + (uint64_t)len <= cap) std::memcpy(out + o, buf, (size_t)len);
-        o += (uint64_t)len;
+        if (offs) offs[i] = o;
+        o += kHeadLen[res[i].question ? 1 : 0] + kSentLen[sent_of(res[i])] + kMidLen + digits(res[i].words) + 1;
     }
-    if (offsets) offsets[n] = o;
+    if (offs) offs[n] = o;
+    if (!out) return o;
+    auto fill = [&](uint32_t lo, uint32_t hi) {
+        for (uint32_t i = lo; i < hi; i++) {
+            if (offs[i + 1] > cap) break;                       // nothing is written beyond cap
+            char *p = out + offs[i];
+            const int q = res[i].question ? 1 : 0, sn = sent_of(res[i]);
+            std::memcpy(p, kHead[q], kHeadLen[q]); p += kHeadLen[q];
+            std::memcpy(p, kSent[sn], kSentLen[sn]); p += kSentLen[sn];
+            std::memcpy(p, kMid, kMidLen); p += kMidLen;
+            uint32_t v = res[i].words;
+            const uint32_t d = digits(v);
+            for (uint32_t k = d; k-- > 0;) { p[k] = (char)('0' + v % 10); v /= 10; }
+            p[d] = '}';
+        }
+    };
+    unsigned nthr = n >= 65536 ? std::min(8u, std::max(1u, std::thread::hardware_concurrency())) : 1;
+    if (nthr <= 1) fill(0, n);
+    else {
+        std::vector<std::thread> th;
+        const uint32_t per = (n + nthr - 1) / nthr;
+        for (unsigned t = 0; t < nthr; t++) {
+            const uint32_t lo = std::min(n, t * per), hi = std::min(n, lo + per);
+            if (lo < hi) th.emplace_back([&fill, lo, hi] { fill(lo, hi); });
+        }
+        for (auto &x : th) x.join();
+    }
     return o;
 }
 
