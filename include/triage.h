@@ -217,7 +217,8 @@ int32_t triage_fail(triage_engine *e, int32_t level);                           
  *    triage_set_user_priority = Preprocessor.SetUserPriority (preprocessor.go:171); prio 0 removes the entry.
  *    triage_emit_analysis_json = json.Marshal(AnalyzeMessageContent(content)) (api/handlers.go:180-190) for n results:
  *    {"is_question":..,"sentiment":"..","word_count":..} each, message i at out[out_offsets[i] .. out_offsets[i+1]);
- *    *needed = total bytes (call with out = NULL to size the buffer). */
+ *    *needed = total bytes (call with out = NULL to size the buffer).
+ *    Both run on the host; large batches are decoded / written on several threads (TRIAGE_INGEST_THREADS, default up to 16). */
 int32_t triage_set_user_priority(triage_engine *e, const char *user_id, uint32_t len, int32_t prio);
 int32_t triage_ingest_json(triage_engine *e, const uint8_t *bodies, const uint64_t *body_offsets, uint32_t n, uint8_t *arena,
                            uint64_t arena_cap, uint64_t *offsets, uint32_t *lengths, triage_meta *meta, uint8_t *status,
@@ -274,7 +275,9 @@ int32_t triage_last_timings(triage_engine *e, triage_timings *t);
 int32_t triage_event_record(triage_engine *e, int32_t slot);
 int32_t triage_event_elapsed_ms(triage_engine *e, int32_t from_slot, int32_t to_slot, float *ms);
 
-/* -- multi-GPU: one engine per rank/GPU; the caller broadcasts the 128-byte id (rank 0 makes it). */
+/* -- multi-GPU: one engine per rank/GPU; the caller broadcasts the 128-byte id (rank 0 makes it).  With a communicator the
+ *    scan leaves a few SMs to the exchange, which runs next to it (TRIAGE_COMM_SMS: 4, 12 from 8 ranks on), and the NCCL
+ *    communicator is created with as few CTAs (TRIAGE_NCCL_CTAS: 4 / 8; 0 = NCCL's own choice). */
 int32_t triage_comm_unique_id(uint8_t id[128]);
 int32_t triage_comm_init(triage_engine *e, int32_t nranks, int32_t rank, const uint8_t id[128]);
 /* all-gather every rank's sorted (key, global index) run of the last triage_submit_device and
