@@ -13,6 +13,9 @@
 // fraction or exponent and fit int64; time.Time fields take RFC 3339 strings; Decoder.Decode reads ONE value and ignores
 // what follows it.  Metadata is a map[string]interface{}: its keys are case-sensitive.
 #include <algorithm>
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
 #include <cstdlib>
 #include <cstring>
 #include <string>
@@ -72,6 +75,16 @@ bool parse_string(Cur &c, std::string *out) {
     while (c.p < c.end) {
         {   // a run of plain bytes (printable ASCII other than '"' and '\\'), eight at a time: copied as it is
             const uint8_t *s = c.p;
+#if defined(__SSE2__)
+            while (c.p + 16 <= c.end) {   // 16 at a time where the host has SSE2 (signed compares: bytes >= 0x80 are negative)
+                const __m128i v = _mm_loadu_si128(reinterpret_cast<const __m128i *>(c.p));
+                const __m128i stop = _mm_or_si128(_mm_or_si128(_mm_cmpeq_epi8(v, _mm_set1_epi8('"')), _mm_cmpeq_epi8(v, _mm_set1_epi8('\\'))),
+                                                  _mm_cmplt_epi8(v, _mm_set1_epi8(0x20)));
+                const int mask = _mm_movemask_epi8(stop);
+                if (mask) { c.p += __builtin_ctz((unsigned)mask); break; }
+                c.p += 16;
+            }
+#endif
             while (c.p + 8 <= c.end) {
                 uint64_t w;
                 std::memcpy(&w, c.p, 8);
